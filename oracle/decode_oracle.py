@@ -1,0 +1,374 @@
+"""CPU oracle for the decode hot path (TEST INFRASTRUCTURE — never the product path).
+
+PARITY UNPINNED.  The reference (psurabh/Enterprise-Inference v1.3.0) holds no source
+for this path: its chart only names the third-party image
+``public.ecr.aws/q9t5s3a7/vllm-cpu-release-repo:v0.10.2``
+(/root/reference/core/helm-charts/vllm/values.yaml:23-28,
+ /root/reference/core/helm-charts/vllm/xeon-values.yaml:29-32) and its tests/docs pin
+no outputs (only ``temperature: 0`` smoke prompts whose completions are not recorded,
+/root/reference/docs/single-node-deployment.md:80-87).  The algorithm restated here is
+the published vLLM "native" forward for Llama / Qwen2 (vLLM v0.10.2 CPU build is the
+pinned dependency; the readable copy consulted is the vLLM 0.22 wheel in this image,
+cited as [V22]).  Because no golden vector exists in the reference, this oracle is
+cross-checked against HuggingFace ``transformers`` 5.5.0 ``LlamaForCausalLM`` /
+``Qwen2ForCausalLM`` (CPU, bf16) by ``oracle/make_golden.py`` — a stand-in, not the
+reference — and its outputs are frozen under ``tests/golden/``.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline /
+``--impl reference`` legs may import this module.
+
+Rounding points (each is a decision; the CUDA path makes the same ones):
+  R1  residual stream is bf16.  add+RMSNorm: s = fp32(x)+fp32(res); res' = bf16(s);
+      var from the UNROUNDED s; n = bf16(s*rsqrt(var+eps)); y = bf16(fp32(n)*fp32(w))
+      [V22] vllm/ir/ops/layernorm.py:10-21,40-58
+  R2  linear: exact bf16*bf16 products, fp32 accumulation, (+fp32 bias), ONE rounding
+      to bf16.  [V22] vllm/model_executor/layers/utils.py:277-299 (CPU linear dispatch)
+  R3  RoPE: NeoX halves, cos/sin cache STORED bf16, arithmetic in bf16 — every
+      elementwise op rounds: o1 = bf16(bf16(x1*c) - bf16(x2*s)), o2 = bf16(bf16(x2*c)
+      + bf16(x1*s)).  [V22] rotary_embedding/base.py:58-63,69-92; common.py:160-183;
+      llama3 frequency scaling: llama3_rope.py:33-54
+  R4  attention (q_len 1 per query row, causal over the paged cache): scores fp32 =
+      (q . k) * head_dim**-0.5, softmax fp32, P kept fp32, out = bf16(sum P*v).
+      [V22] vllm/v1/attention/backends/cpu_attn.py:377-396; scale llama.py:160-161
+  R5  SiLU*mul in bf16: a = bf16(fp32(bf16(silu(fp32 g))) * fp32(u)).
+      [V22] vllm/model_executor/layers/activation.py:137-141
+  R6  logits are bf16; sampler casts to fp32 and takes argmax, ties -> lowest index.
+      [V22] vllm/v1/sample/sampler.py:90-91,235-236
+"""
+from __future__ import annotations
+
+import hashlib
+import math
+from dataclasses import dataclass, field, asdict
+from typing import Dict, List, Optional
+
+import torch
+
+BF16 = torch.bfloat16
+
+
+@dataclass
+class ModelConfig:
+    """Shape of one decoder-only Llama/Qwen2 model (SURVEY.md §8 shape table)."""
+    name: str = "tiny"
+    hidden: int = 512
+    n_layers: int = 2
+    n_q_heads: int = 4
+    n_kv_heads: int = 1
+    head_dim: int = 128
+    intermediate: int = 1024
+    vocab: int = 1024
+    qkv_bias: bool = False
+    rope_theta: float = 500000.0
+    rope_llama3: bool = True          # llama3 scaling: factor 8, low 1, high 4, orig 8192
+    rms_eps: float = 1e-5
+    max_pos: int = 32768
+
+    def to_dict(self):
+        return asdict(self)
+
+    @property
+    def q_size(self):
+        return self.n_q_heads * self.head_dim
+
+    @property
+    def kv_size(self):
+        return self.n_kv_heads * self.head_dim
+
+    def decode_params(self) -> int:
+        """P_dec of SURVEY.md §8: parameters streamed once per decode step."""
+        h, L, I, V = self.hidden, self.n_layers, self.intermediate, self.vocab
+        return L * (h * (self.q_size + 2 * self.kv_size) + self.q_size * h + 3 * h * I) + V * h
+
+    def kv_bytes_per_token(self) -> int:
+        return 2 * self.n_kv_heads * self.head_dim * 2 * self.n_layers
+
+
+CONFIGS: Dict[str, ModelConfig] = {
+    "tiny": ModelConfig(),
+    # G=5 and bias: the Qwen2-32B head ratio on a small body
+    "tiny-qwen": ModelConfig(name="tiny-qwen", hidden=640, n_layers=2, n_q_heads=5, n_kv_heads=1,
+                             intermediate=1536, vocab=2048, qkv_bias=True, rope_theta=1e6,
+                             rope_llama3=False),
+    # G=8 (70B head ratio), 2 kv heads so TP=2 can shard it
+    "tiny-g8": ModelConfig(name="tiny-g8", hidden=1024, n_layers=2, n_q_heads=16, n_kv_heads=2,
+                           intermediate=2048, vocab=4096),
+    "llama-3.1-8b": ModelConfig(name="llama-3.1-8b", hidden=4096, n_layers=32, n_q_heads=32,
+                                n_kv_heads=8, intermediate=14336, vocab=128256, max_pos=131072),
+    "qwen2-32b": ModelConfig(name="qwen2-32b", hidden=5120, n_layers=64, n_q_heads=40, n_kv_heads=8,
+                             intermediate=27648, vocab=152064, qkv_bias=True, rope_theta=1e6,
+                             rope_llama3=False, max_pos=131072),
+    "llama-3.1-70b": ModelConfig(name="llama-3.1-70b", hidden=8192, n_layers=80, n_q_heads=64,
+                                 n_kv_heads=8, intermediate=28672, vocab=128256, max_pos=131072),
+}
+
+
+def truncated(cfg: ModelConfig, n_layers: int, vocab: Optional[int] = None) -> ModelConfig:
+    """Shape-faithful, layer-truncated copy (full h/I/heads) for full-width parity."""
+    d = cfg.to_dict()
+    d["n_layers"] = n_layers
+    d["name"] = f"{cfg.name}-L{n_layers}"
+    if vocab:
+        d["vocab"] = vocab
+    return ModelConfig(**d)
+
+
+# --------------------------------------------------------------------------------------
+# weights: HF names ([V22] vllm/model_executor/models/llama.py:437-444 packing map)
+# --------------------------------------------------------------------------------------
+def weight_names(cfg: ModelConfig) -> List[str]:
+    names = ["model.embed_tokens.weight"]
+    for i in range(cfg.n_layers):
+        p = f"model.layers.{i}."
+        names += [p + "input_layernorm.weight",
+                  p + "self_attn.q_proj.weight", p + "self_attn.k_proj.weight",
+                  p + "self_attn.v_proj.weight"]
+        if cfg.qkv_bias:
+            names += [p + "self_attn.q_proj.bias", p + "self_attn.k_proj.bias",
+                      p + "self_attn.v_proj.bias"]
+        names += [p + "self_attn.o_proj.weight", p + "post_attention_layernorm.weight",
+                  p + "mlp.gate_proj.weight", p + "mlp.up_proj.weight", p + "mlp.down_proj.weight"]
+    names += ["model.norm.weight", "lm_head.weight"]
+    return names
+
+
+def weight_shape(cfg: ModelConfig, name: str):
+    h, I = cfg.hidden, cfg.intermediate
+    if name.endswith("embed_tokens.weight") or name == "lm_head.weight":
+        return (cfg.vocab, h)
+    if name.endswith("layernorm.weight") or name == "model.norm.weight":
+        return (h,)
+    if "q_proj" in name:
+        return (cfg.q_size, h) if name.endswith("weight") else (cfg.q_size,)
+    if "k_proj" in name or "v_proj" in name:
+        return (cfg.kv_size, h) if name.endswith("weight") else (cfg.kv_size,)
+    if "o_proj" in name:
+        return (h, cfg.q_size)
+    if "gate_proj" in name or "up_proj" in name:
+        return (I, h)
+    if "down_proj" in name:
+        return (h, I)
+    raise KeyError(name)
+
+
+def make_weights(cfg: ModelConfig, seed: int = 1234, norm_jitter: float = 0.0,
+                 std: float = 0.02) -> Dict[str, torch.Tensor]:
+    """Seeded N(0, std^2) bf16 weights, one torch.Generator stream in name order
+    (SURVEY.md §8d).  Norm weights are 1 (+ N(0,norm_jitter^2) when asked, so that the
+    bf16 weight multiply of R1 is exercised)."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    out = {}
+    for n in weight_names(cfg):
+        shp = weight_shape(cfg, n)
+        if len(shp) == 1 and not n.endswith("bias"):
+            w = torch.ones(shp, dtype=torch.float32)
+            if norm_jitter:
+                w = w + norm_jitter * torch.randn(shp, generator=g, dtype=torch.float32)
+        elif n.endswith("bias"):
+            w = 0.1 * torch.randn(shp, generator=g, dtype=torch.float32)
+        else:
+            w = std * torch.randn(shp, generator=g, dtype=torch.float32)
+        out[n] = w.to(BF16)
+    return out
+
+
+def weights_digest(w: Dict[str, torch.Tensor]) -> str:
+    """sha256 over the raw bf16 bytes in name order — detects RNG drift between boxes."""
+    hsh = hashlib.sha256()
+    for n in sorted(w):
+        hsh.update(n.encode())
+        hsh.update(w[n].contiguous().view(torch.int16).numpy().tobytes())
+    return hsh.hexdigest()
+
+
+def make_prompt(cfg: ModelConfig, request_index: int, length: int) -> List[int]:
+    """Uniform token ids, seed = 1000 + request index."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(1000 + request_index)
+    return torch.randint(0, cfg.vocab, (length,), generator=g).tolist()
+
+
+# --------------------------------------------------------------------------------------
+# the ops (R1..R6)
+# --------------------------------------------------------------------------------------
+def rope_inv_freq(cfg: ModelConfig) -> torch.Tensor:
+    d = cfg.head_dim
+    inv = 1.0 / (cfg.rope_theta ** (torch.arange(0, d, 2, dtype=torch.float32) / d))
+    if cfg.rope_llama3:
+        # [V22] rotary_embedding/llama3_rope.py:33-54
+        factor, low, high, orig = 8.0, 1.0, 4.0, 8192
+        low_wl, high_wl = orig / low, orig / high
+        wl = 2 * math.pi / inv
+        smooth = (orig / wl - low) / (high - low)
+        inv = torch.where(wl < high_wl, inv,
+                          torch.where(wl > low_wl, inv / factor,
+                                      (1 - smooth) * inv / factor + smooth * inv))
+    return inv
+
+
+def cos_sin_cache(cfg: ModelConfig, max_pos: Optional[int] = None) -> torch.Tensor:
+    """[max_pos, head_dim] bf16 = cos(0..d/2) | sin(0..d/2).  R3: stored in bf16."""
+    t = torch.arange(max_pos or cfg.max_pos, dtype=torch.float32)
+    fr = torch.einsum("i,j->ij", t, rope_inv_freq(cfg))
+    return torch.cat((fr.cos(), fr.sin()), dim=-1).to(BF16)
+
+
+def rms_norm(x: torch.Tensor, w: torch.Tensor, eps: float) -> torch.Tensor:
+    xf = x.float()
+    var = xf.pow(2).mean(dim=-1, keepdim=True)
+    n = (xf * torch.rsqrt(var + eps)).to(BF16)
+    return (n.float() * w.float()).to(BF16)
+
+
+def add_rms_norm(x: torch.Tensor, res: torch.Tensor, w: torch.Tensor, eps: float):
+    s = x.float() + res.float()
+    new_res = s.to(BF16)
+    var = s.pow(2).mean(dim=-1, keepdim=True)
+    n = (s * torch.rsqrt(var + eps)).to(BF16)
+    return (n.float() * w.float()).to(BF16), new_res
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
+    y = x.float() @ w.float().t()
+    if b is not None:
+        y = y + b.float()
+    return y.to(BF16)
+
+
+def rope_apply(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
+    """x [T, heads, d] bf16; cos/sin [T, d/2] bf16.  All arithmetic in bf16 (R3)."""
+    c, s = cos.unsqueeze(1), sin.unsqueeze(1)
+    x1, x2 = x[..., : x.shape[-1] // 2], x[..., x.shape[-1] // 2:]
+    o1 = x1 * c - x2 * s          # torch bf16 ops: each rounds to bf16
+    o2 = x2 * c + x1 * s
+    return torch.cat((o1, o2), dim=-1)
+
+
+def attend(q: torch.Tensor, K: torch.Tensor, V: torch.Tensor, n_ctx: int, scale: float) -> torch.Tensor:
+    """q [Hq, d] bf16; K,V [>=n_ctx, Hkv, d] bf16 -> [Hq, d] bf16 (R4)."""
+    Hq, d = q.shape
+    Hkv = K.shape[1]
+    G = Hq // Hkv
+    k = K[:n_ctx].float().permute(1, 0, 2)                 # [Hkv, n, d]
+    v = V[:n_ctx].float().permute(1, 0, 2)
+    qf = q.float().view(Hkv, G, d)
+    s = torch.einsum("hgd,hnd->hgn", qf, k) * scale
+    p = torch.softmax(s, dim=-1)
+    o = torch.einsum("hgn,hnd->hgd", p, v)
+    return o.reshape(Hq, d).to(BF16)
+
+
+def silu_mul(gu: torch.Tensor) -> torch.Tensor:
+    d = gu.shape[-1] // 2
+    g, u = gu[..., :d], gu[..., d:]
+    sg = torch.nn.functional.silu(g.float()).to(BF16)
+    return (sg.float() * u.float()).to(BF16)
+
+
+def greedy(logits_bf16: torch.Tensor) -> torch.Tensor:
+    return logits_bf16.float().argmax(dim=-1)
+
+
+# --------------------------------------------------------------------------------------
+# the model
+# --------------------------------------------------------------------------------------
+@dataclass
+class SeqState:
+    """Contiguous (un-paged) KV of one sequence: K[l], V[l] are [capacity, Hkv, d]."""
+    K: List[torch.Tensor] = field(default_factory=list)
+    V: List[torch.Tensor] = field(default_factory=list)
+    n: int = 0
+
+
+class OracleModel:
+    """Token-at-a-time restatement of [V22] vllm/model_executor/models/llama.py:223-233
+    (attention), :316-333 (decoder layer), :395-434 (model), :577-582 (logits) and
+    models/qwen2.py:156-171 (qkv bias)."""
+
+    def __init__(self, cfg: ModelConfig, weights: Dict[str, torch.Tensor], capacity: int = 1024):
+        self.cfg = cfg
+        self.w = weights
+        self.capacity = capacity
+        self.cs = cos_sin_cache(cfg, max(capacity, 16))
+        self.scale = cfg.head_dim ** -0.5
+        self.layers = []
+        for i in range(cfg.n_layers):
+            p = f"model.layers.{i}."
+            qkv_w = torch.cat([weights[p + f"self_attn.{x}_proj.weight"] for x in "qkv"], 0)
+            qkv_b = (torch.cat([weights[p + f"self_attn.{x}_proj.bias"] for x in "qkv"], 0)
+                     if cfg.qkv_bias else None)
+            gu_w = torch.cat([weights[p + "mlp.gate_proj.weight"], weights[p + "mlp.up_proj.weight"]], 0)
+            self.layers.append(dict(
+                ln1=weights[p + "input_layernorm.weight"], qkv_w=qkv_w, qkv_b=qkv_b,
+                o_w=weights[p + "self_attn.o_proj.weight"],
+                ln2=weights[p + "post_attention_layernorm.weight"], gu_w=gu_w,
+                d_w=weights[p + "mlp.down_proj.weight"]))
+
+    def new_seq(self) -> SeqState:
+        c = self.cfg
+        st = SeqState()
+        for _ in range(c.n_layers):
+            st.K.append(torch.zeros(self.capacity, c.n_kv_heads, c.head_dim, dtype=BF16))
+            st.V.append(torch.zeros(self.capacity, c.n_kv_heads, c.head_dim, dtype=BF16))
+        return st
+
+    def forward(self, st: SeqState, token_ids: List[int], return_hidden: bool = False):
+        """Append T tokens to the sequence (causal) and return bf16 logits [T, V].
+        T>1 is a (chunked) prefill, T==1 a decode step: the arithmetic per token is the same."""
+        c = self.cfg
+        T = len(token_ids)
+        pos = torch.arange(st.n, st.n + T)
+        assert st.n + T <= self.capacity
+        cos = self.cs[pos, : c.head_dim // 2]
+        sin = self.cs[pos, c.head_dim // 2:]
+        x = self.w["model.embed_tokens.weight"][torch.tensor(token_ids)]
+        res = None
+        hidden = []
+        for l, L in enumerate(self.layers):
+            if res is None:
+                res = x
+                y = rms_norm(x, L["ln1"], c.rms_eps)
+            else:
+                y, res = add_rms_norm(x, res, L["ln1"], c.rms_eps)
+            qkv = linear(y, L["qkv_w"], L["qkv_b"])
+            q = qkv[:, : c.q_size].view(T, c.n_q_heads, c.head_dim)
+            k = qkv[:, c.q_size: c.q_size + c.kv_size].view(T, c.n_kv_heads, c.head_dim)
+            v = qkv[:, c.q_size + c.kv_size:].view(T, c.n_kv_heads, c.head_dim)
+            q = rope_apply(q, cos, sin)
+            k = rope_apply(k, cos, sin)
+            st.K[l][st.n: st.n + T] = k
+            st.V[l][st.n: st.n + T] = v
+            a = torch.stack([attend(q[t], st.K[l], st.V[l], st.n + t + 1, self.scale)
+                             for t in range(T)]).view(T, c.q_size)
+            x = linear(a, L["o_w"])
+            y, res = add_rms_norm(x, res, L["ln2"], c.rms_eps)
+            gu = linear(y, L["gu_w"])
+            x = linear(silu_mul(gu), L["d_w"])
+            if return_hidden:
+                hidden.append((x.clone(), res.clone()))
+        y, _ = add_rms_norm(x, res, self.w["model.norm.weight"], c.rms_eps)
+        logits = linear(y, self.w["lm_head.weight"])
+        st.n += T
+        return (logits, hidden) if return_hidden else logits
+
+    def generate(self, prompt: List[int], n_new: int, keep_logits: bool = False):
+        """Greedy, ignore_eos: exactly n_new tokens."""
+        st = self.new_seq()
+        logits = self.forward(st, prompt)[-1:]
+        toks, all_logits = [], []
+        for _ in range(n_new):
+            t = int(greedy(logits)[0])
+            toks.append(t)
+            if keep_logits:
+                all_logits.append(logits[0].float().clone())
+            if len(toks) == n_new:
+                break
+            logits = self.forward(st, [t])
+        return (toks, torch.stack(all_logits)) if keep_logits else toks
+
+
+def top2_margin(logits_f32: torch.Tensor) -> torch.Tensor:
+    """Oracle top-1/top-2 logit margin per row — used by the margin-aware greedy check."""
+    v, _ = torch.topk(logits_f32, 2, dim=-1)
+    return v[..., 0] - v[..., 1]
