@@ -1,0 +1,637 @@
+// The C-ABI of include/b200_decode.h: error plumbing, the per-rank context (weights, caller-owned
+// KV cache, private activations/scratch, CUDA graphs, NCCL communicator) and the decode step that
+// strings the kernels together.  No torch types anywhere: plain pointers and sizes.
+#include <dlfcn.h>
+#include <nccl.h>  // types only; the library is resolved at run time from the process (torch's copy)
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+
+namespace b200 {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+  return B200_ERR_CUDA;
+}
+
+LaunchOpts& launch_opts() {
+  static thread_local LaunchOpts o;
+  return o;
+}
+int& launch_counter() {
+  static thread_local int c = 0;
+  return c;
+}
+
+// ---- NCCL, resolved from the already-loaded library -------------------------------------------
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  bool ok = false;
+};
+
+static NcclApi& nccl() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api;
+  tried = true;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return api;
+  api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+  api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
+  api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
+  api.AllReduce = (decltype(api.AllReduce))dlsym(h, "ncclAllReduce");
+  api.AllGather = (decltype(api.AllGather))dlsym(h, "ncclAllGather");
+  api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
+  api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce && api.AllGather;
+  return api;
+}
+
+#define B200_NCCL(expr)                                                                      \
+  do {                                                                                       \
+    ncclResult_t _r = (expr);                                                                \
+    if (_r != ncclSuccess) {                                                                 \
+      set_error("NCCL error %d (%s): %s", (int)_r,                                           \
+                nccl().GetErrorString ? nccl().GetErrorString(_r) : "?", #expr);             \
+      return B200_ERR_NCCL;                                                                  \
+    }                                                                                        \
+  } while (0)
+
+// Pick the winner among the ranks' (max, index) pairs: highest value, lowest index on ties.
+__global__ void tp_pick_kernel(const float* __restrict__ gathered, int world, int rows, int32_t* __restrict__ out) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  float bv = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int w = 0; w < world; ++w) {
+    const float v = gathered[((int64_t)w * rows + r) * 2];
+    const int i = __float_as_int(gathered[((int64_t)w * rows + r) * 2 + 1]);
+    if (v > bv || (v == bv && i < bi)) {
+      bv = v;
+      bi = i;
+    }
+  }
+  out[r] = bi;
+}
+__global__ void tp_pack_kernel(const float* __restrict__ mx, const int32_t* __restrict__ idx, int rows,
+                               float* __restrict__ packed) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  packed[r * 2] = mx[r];
+  packed[r * 2 + 1] = __int_as_float(idx[r]);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// ------------------------------------------------------------------------------------------------
+struct LayerW {
+  const __nv_bfloat16 *ln1 = nullptr, *qkv = nullptr, *qkv_b = nullptr, *o = nullptr, *ln2 = nullptr, *gu = nullptr,
+                      *down = nullptr;
+};
+
+struct GraphKey {
+  uint64_t h;
+  bool operator==(const GraphKey& o) const { return h == o.h; }
+};
+struct GraphKeyHash {
+  size_t operator()(const GraphKey& k) const { return (size_t)k.h; }
+};
+
+struct b200_ctx {
+  b200_model_cfg cfg;
+  int hq, hkv, inter, vocab_local, qkv_w;  // local (per TP rank) sizes
+  int max_logit_rows;
+  std::vector<LayerW> layers;
+  const __nv_bfloat16 *embed = nullptr, *final_norm = nullptr, *lm_head = nullptr, *cos_sin = nullptr;
+  int64_t max_pos = 0;
+  __nv_bfloat16 *kc = nullptr, *vc = nullptr;
+  int64_t n_blocks = 0;
+  // private device buffers
+  void* pool = nullptr;
+  int64_t pool_bytes = 0;
+  __nv_bfloat16 *x, *res, *normed, *qkv_buf, *attn_out, *gu_buf, *act, *lm_in, *logits;
+  void* attn_ws;
+  int64_t attn_ws_bytes;
+  void* lin_ws;
+  int64_t lin_ws_bytes;
+  int32_t* d_meta;
+  int64_t meta_ints;
+  int32_t* d_tokens;
+  float* d_max;
+  float* d_pairs;     // [rows][2] local (max, idx)
+  float* d_gathered;  // [world][rows][2]
+  // graphs
+  bool graphs = true;
+  std::unordered_map<GraphKey, cudaGraphExec_t, GraphKeyHash> graph_cache;
+  int last_launches = 0;
+  // taps
+  int tap_layer = -1;
+  void *tap_hidden = nullptr, *tap_res = nullptr;
+  // TP
+  ncclComm_t comm = nullptr;
+  int gemv_max_t = 4;
+};
+
+static int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+extern "C" const char* b200_last_error(void) { return g_err; }
+extern "C" int b200_abi_version(void) { return 1; }
+
+extern "C" int b200_device_ok(void) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  cudaDeviceProp p;
+  if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return p.major == 10 ? 1 : 0;
+}
+
+extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
+  B200_REQUIRE(cfg && out, B200_ERR_INVALID, "ctx_create: null argument");
+  B200_REQUIRE(cfg->head_dim == kHeadDim, B200_ERR_UNSUPPORTED, "ctx_create: head_dim must be 128 (got %d)", cfg->head_dim);
+  B200_REQUIRE(cfg->tp_world >= 1 && cfg->tp_rank >= 0 && cfg->tp_rank < cfg->tp_world, B200_ERR_INVALID,
+               "ctx_create: bad tp rank/world %d/%d", cfg->tp_rank, cfg->tp_world);
+  B200_REQUIRE(cfg->n_q_heads % cfg->tp_world == 0 && cfg->n_kv_heads % cfg->tp_world == 0 &&
+                   cfg->intermediate % cfg->tp_world == 0 && cfg->vocab % cfg->tp_world == 0,
+               B200_ERR_UNSUPPORTED, "ctx_create: heads/intermediate/vocab must divide by tp_world=%d", cfg->tp_world);
+  B200_REQUIRE(cfg->hidden % 8 == 0 && cfg->intermediate % (8 * cfg->tp_world) == 0 && cfg->max_tokens > 0 &&
+                   cfg->n_layers > 0 && cfg->block_size > 0 && cfg->max_blocks_per_seq > 0,
+               B200_ERR_INVALID, "ctx_create: bad sizes");
+  b200_ctx* c = new b200_ctx();
+  c->cfg = *cfg;
+  const int W = cfg->tp_world;
+  c->hq = cfg->n_q_heads / W;
+  c->hkv = cfg->n_kv_heads / W;
+  c->inter = cfg->intermediate / W;
+  c->vocab_local = cfg->vocab / W;
+  c->qkv_w = (c->hq + 2 * c->hkv) * kHeadDim;
+  c->max_logit_rows = cfg->max_tokens < 512 ? cfg->max_tokens : 512;
+  c->layers.resize(cfg->n_layers);
+  if (const char* e = getenv("B200_GEMV_MAX_T")) c->gemv_max_t = atoi(e);
+  if (const char* e = getenv("B200_GRAPHS")) c->graphs = atoi(e) != 0;
+
+  const int64_t T = cfg->max_tokens, h = cfg->hidden, R = c->max_logit_rows;
+  const int max_ctx = cfg->max_blocks_per_seq * cfg->block_size;
+  c->attn_ws_bytes = 0;
+  for (int t = 1; t <= T; t = t < 64 ? t + 1 : t * 2) {  // the bound is not monotone in T: scan
+    const int64_t b = paged_attn_workspace_bytes(t, c->hq, max_ctx, cfg->block_size);
+    if (b > c->attn_ws_bytes) c->attn_ws_bytes = b;
+  }
+  c->attn_ws_bytes = std::max<int64_t>(c->attn_ws_bytes, paged_attn_workspace_bytes((int)T, c->hq, max_ctx, cfg->block_size));
+  int64_t lw = 0;
+  const int outs[5] = {c->qkv_w, (int)h, 2 * c->inter, (int)h, c->vocab_local};
+  const int ks[5] = {(int)h, c->hq * kHeadDim, (int)h, c->inter, (int)h};
+  for (int i = 0; i < 5; ++i) lw = std::max<int64_t>(lw, linear_tc_workspace_bytes((int)T, outs[i], ks[i]));
+  c->lin_ws_bytes = lw;
+  c->meta_ints = 6 * T + (int64_t)T * cfg->max_blocks_per_seq;
+
+  struct Item {
+    void** p;
+    int64_t bytes;
+  };
+  std::vector<Item> items = {
+      {(void**)&c->x, T * h * 2},
+      {(void**)&c->res, T * h * 2},
+      {(void**)&c->normed, T * h * 2},
+      {(void**)&c->qkv_buf, T * c->qkv_w * 2},
+      {(void**)&c->attn_out, T * c->hq * kHeadDim * 2},
+      {(void**)&c->gu_buf, T * 2 * c->inter * 2},
+      {(void**)&c->act, T * c->inter * 2},
+      {(void**)&c->lm_in, R * h * 2},
+      {(void**)&c->logits, R * (int64_t)c->vocab_local * 2},
+      {(void**)&c->attn_ws, c->attn_ws_bytes},
+      {(void**)&c->lin_ws, c->lin_ws_bytes},
+      {(void**)&c->d_meta, c->meta_ints * 4},
+      {(void**)&c->d_tokens, R * 4},
+      {(void**)&c->d_max, R * 4},
+      {(void**)&c->d_pairs, R * 8},
+      {(void**)&c->d_gathered, R * 8 * W},
+  };
+  int64_t total = 0;
+  for (auto& it : items) total += align_up(std::max<int64_t>(it.bytes, 16), 1024);
+  cudaError_t e = cudaMalloc(&c->pool, total);
+  if (e != cudaSuccess) {
+    delete c;
+    return cuda_fail(e, "cudaMalloc(ctx pool)", __FILE__, __LINE__);
+  }
+  e = cudaMemset(c->pool, 0, total);
+  if (e != cudaSuccess) {
+    cudaFree(c->pool);
+    delete c;
+    return cuda_fail(e, "cudaMemset(ctx pool)", __FILE__, __LINE__);
+  }
+  c->pool_bytes = total;
+  int64_t off = 0;
+  for (auto& it : items) {
+    *it.p = static_cast<char*>(c->pool) + off;
+    off += align_up(std::max<int64_t>(it.bytes, 16), 1024);
+  }
+  *out = c;
+  return B200_OK;
+}
+
+extern "C" int b200_ctx_destroy(b200_ctx* c) {
+  if (!c) return B200_OK;
+  for (auto& kv : c->graph_cache) cudaGraphExecDestroy(kv.second);
+  if (c->comm && nccl().ok) nccl().CommDestroy(c->comm);
+  if (c->pool) cudaFree(c->pool);
+  delete c;
+  return B200_OK;
+}
+
+extern "C" int64_t b200_ctx_workspace_bytes(const b200_ctx* c) { return c ? c->pool_bytes : 0; }
+
+extern "C" int b200_set_weight(b200_ctx* c, int32_t layer, int32_t kind, const void* w, int64_t rows, int64_t cols) {
+  B200_REQUIRE(c && w, B200_ERR_INVALID, "set_weight: null argument");
+  B200_REQUIRE(reinterpret_cast<uintptr_t>(w) % 16 == 0, B200_ERR_INVALID, "set_weight: pointer not 16-byte aligned");
+  const int64_t h = c->cfg.hidden;
+  const bool per_layer = !(kind == B200_W_EMBED || kind == B200_W_FINAL_NORM || kind == B200_W_LM_HEAD);
+  if (per_layer) B200_REQUIRE(layer >= 0 && layer < c->cfg.n_layers, B200_ERR_INVALID, "set_weight: layer %d out of range", layer);
+  int64_t er = 0, ec = 0;
+  const __nv_bfloat16* p = static_cast<const __nv_bfloat16*>(w);
+  switch (kind) {
+    case B200_W_EMBED: er = c->cfg.vocab; ec = h; break;
+    case B200_W_LN1: case B200_W_LN2: case B200_W_FINAL_NORM: er = h; ec = 1; break;
+    case B200_W_QKV: er = c->qkv_w; ec = h; break;
+    case B200_W_QKV_BIAS: er = c->qkv_w; ec = 1; break;
+    case B200_W_O: er = h; ec = c->hq * kHeadDim; break;
+    case B200_W_GATE_UP: er = 2 * c->inter; ec = h; break;
+    case B200_W_DOWN: er = h; ec = c->inter; break;
+    case B200_W_LM_HEAD: er = c->vocab_local; ec = h; break;
+    default: B200_REQUIRE(false, B200_ERR_INVALID, "set_weight: unknown kind %d", kind);
+  }
+  B200_REQUIRE(rows == er && cols == ec, B200_ERR_INVALID, "set_weight: kind %d expects [%lld,%lld], got [%lld,%lld]", kind,
+               (long long)er, (long long)ec, (long long)rows, (long long)cols);
+  switch (kind) {
+    case B200_W_EMBED: c->embed = p; break;
+    case B200_W_FINAL_NORM: c->final_norm = p; break;
+    case B200_W_LM_HEAD: c->lm_head = p; break;
+    case B200_W_LN1: c->layers[layer].ln1 = p; break;
+    case B200_W_LN2: c->layers[layer].ln2 = p; break;
+    case B200_W_QKV: c->layers[layer].qkv = p; break;
+    case B200_W_QKV_BIAS: c->layers[layer].qkv_b = p; break;
+    case B200_W_O: c->layers[layer].o = p; break;
+    case B200_W_GATE_UP: c->layers[layer].gu = p; break;
+    case B200_W_DOWN: c->layers[layer].down = p; break;
+  }
+  return B200_OK;
+}
+
+extern "C" int b200_set_kv_cache(b200_ctx* c, void* k_cache, void* v_cache, int64_t n_blocks) {
+  B200_REQUIRE(c && k_cache && v_cache && n_blocks > 0, B200_ERR_INVALID, "set_kv_cache: bad argument");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(k_cache) | reinterpret_cast<uintptr_t>(v_cache)) % 128 == 0, B200_ERR_INVALID,
+               "set_kv_cache: caches must be 128-byte aligned");
+  c->kc = static_cast<__nv_bfloat16*>(k_cache);
+  c->vc = static_cast<__nv_bfloat16*>(v_cache);
+  c->n_blocks = n_blocks;
+  return B200_OK;
+}
+
+extern "C" int b200_set_rope_cache(b200_ctx* c, const void* cos_sin, int64_t max_pos) {
+  B200_REQUIRE(c && cos_sin && max_pos > 0, B200_ERR_INVALID, "set_rope_cache: bad argument");
+  c->cos_sin = static_cast<const __nv_bfloat16*>(cos_sin);
+  c->max_pos = max_pos;
+  return B200_OK;
+}
+
+extern "C" int b200_nccl_unique_id(void* host_id128) {
+  B200_REQUIRE(host_id128, B200_ERR_INVALID, "nccl_unique_id: null");
+  B200_REQUIRE(nccl().ok, B200_ERR_NCCL, "libnccl.so.2 not found in the process");
+  ncclUniqueId id;
+  B200_NCCL(nccl().GetUniqueId(&id));
+  memcpy(host_id128, &id, sizeof(id));
+  return B200_OK;
+}
+
+extern "C" int b200_nccl_init(b200_ctx* c, const void* host_id128) {
+  B200_REQUIRE(c && host_id128, B200_ERR_INVALID, "nccl_init: null");
+  B200_REQUIRE(nccl().ok, B200_ERR_NCCL, "libnccl.so.2 not found in the process");
+  ncclUniqueId id;
+  memcpy(&id, host_id128, sizeof(id));
+  B200_NCCL(nccl().CommInitRank(&c->comm, c->cfg.tp_world, id, c->cfg.tp_rank));
+  return B200_OK;
+}
+
+extern "C" int b200_allreduce_bf16(b200_ctx* c, void* buf, int64_t count, void* stream) {
+  B200_REQUIRE(c && buf, B200_ERR_INVALID, "allreduce: null");
+  if (c->cfg.tp_world == 1) return B200_OK;
+  B200_REQUIRE(c->comm, B200_ERR_STATE, "allreduce: b200_nccl_init not called");
+  ++launch_counter();
+  B200_NCCL(nccl().AllReduce(buf, buf, (size_t)count, ncclBfloat16, ncclSum, c->comm, (cudaStream_t)stream));
+  return B200_OK;
+}
+
+extern "C" int b200_ctx_set_graphs(b200_ctx* c, int32_t enabled) {
+  B200_REQUIRE(c, B200_ERR_INVALID, "null ctx");
+  c->graphs = enabled != 0;
+  return B200_OK;
+}
+extern "C" int b200_ctx_last_step_launches(const b200_ctx* c) { return c ? c->last_launches : 0; }
+extern "C" int b200_ctx_set_tap(b200_ctx* c, int32_t layer, void* out_hidden, void* out_residual) {
+  B200_REQUIRE(c, B200_ERR_INVALID, "null ctx");
+  c->tap_layer = layer;
+  c->tap_hidden = out_hidden;
+  c->tap_res = out_residual;
+  return B200_OK;
+}
+
+// ---- linear dispatch ----------------------------------------------------------------------------
+static int linear_any(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
+                      __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, int impl, int gemv_max_t, void* ws,
+                      int64_t ws_bytes, cudaStream_t s) {
+  if (T == 0) return B200_OK;
+  if (impl == 0) impl = (T <= gemv_max_t || !linear_tc_supported(T, n_out, k)) ? 1 : 2;
+  if (impl == 1) return linear_gemv(x, ldx, w, bias, y, ldy, T, n_out, k, s);
+  B200_REQUIRE(linear_tc_supported(T, n_out, k), B200_ERR_UNSUPPORTED,
+               "linear: tcgen05 path does not support T=%d n_out=%d k=%d", T, n_out, k);
+  return linear_tc(x, ldx, w, bias, y, ldy, T, n_out, k, ws, ws_bytes, s);
+}
+
+extern "C" int64_t b200_linear_workspace_bytes(int32_t T, int32_t n_out, int32_t k) {
+  return linear_tc_workspace_bytes(T, n_out, k);
+}
+
+extern "C" int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y, int64_t ldy,
+                                int32_t T, int32_t n_out, int32_t k, int32_t impl, void* ws, int64_t ws_bytes,
+                                void* stream) {
+  B200_REQUIRE(x && w && y && T >= 0 && n_out > 0 && k > 0, B200_ERR_INVALID, "linear: bad argument");
+  int gm = 4;
+  if (const char* e = getenv("B200_GEMV_MAX_T")) gm = atoi(e);
+  return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias,
+                    (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int b200_rmsnorm(const void* x, void* res, const void* w, void* y, int32_t T, int32_t hidden, float eps,
+                            void* stream) {
+  B200_REQUIRE(x && w && y, B200_ERR_INVALID, "rmsnorm: null");
+  return rmsnorm((const __nv_bfloat16*)x, (__nv_bfloat16*)res, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, T, hidden,
+                 eps, (cudaStream_t)stream);
+}
+
+extern "C" int b200_embed(const int32_t* ids, const void* table, void* out, int32_t T, int32_t hidden, int32_t vocab,
+                          void* stream) {
+  B200_REQUIRE(ids && table && out, B200_ERR_INVALID, "embed: null");
+  return embed(ids, (const __nv_bfloat16*)table, (__nv_bfloat16*)out, T, hidden, vocab, (cudaStream_t)stream);
+}
+
+extern "C" int b200_rope_kv_append(void* qkv, const int32_t* positions, const int32_t* slot_mapping, const void* cos_sin,
+                                   void* k_cache_layer, void* v_cache_layer, int32_t T, int32_t hq, int32_t hkv,
+                                   int32_t block_size, void* stream) {
+  B200_REQUIRE(qkv && positions && slot_mapping && cos_sin && k_cache_layer && v_cache_layer, B200_ERR_INVALID,
+               "rope_kv_append: null");
+  return rope_kv_append((__nv_bfloat16*)qkv, positions, slot_mapping, (const __nv_bfloat16*)cos_sin,
+                        (__nv_bfloat16*)k_cache_layer, (__nv_bfloat16*)v_cache_layer, T, hq, hkv, block_size,
+                        (cudaStream_t)stream);
+}
+
+extern "C" int64_t b200_paged_attn_workspace_bytes(int32_t T, int32_t hq, int32_t max_ctx, int32_t block_size) {
+  return paged_attn_workspace_bytes(T, hq, max_ctx, block_size);
+}
+
+extern "C" int b200_paged_attn_decode(const void* q, int64_t ldq, const void* kc, const void* vc,
+                                      const int32_t* block_table, int32_t bt_stride, const int32_t* row_to_seq,
+                                      const int32_t* ctx_lens, void* out, int64_t ldo, int32_t T, int32_t hq,
+                                      int32_t hkv, int32_t block_size, int32_t max_ctx, float scale, void* ws,
+                                      int64_t ws_bytes, void* stream) {
+  B200_REQUIRE(q && kc && vc && block_table && ctx_lens && out, B200_ERR_INVALID, "paged_attn: null");
+  return paged_attn((const __nv_bfloat16*)q, ldq, (const __nv_bfloat16*)kc, (const __nv_bfloat16*)vc, block_table,
+                    bt_stride, row_to_seq, ctx_lens, (__nv_bfloat16*)out, ldo, T, hq, hkv, block_size, max_ctx, scale,
+                    ws, ws_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int b200_silu_mul(const void* gu, void* out, int32_t T, int32_t inter, void* stream) {
+  B200_REQUIRE(gu && out, B200_ERR_INVALID, "silu_mul: null");
+  return silu_mul((const __nv_bfloat16*)gu, (__nv_bfloat16*)out, T, inter, (cudaStream_t)stream);
+}
+
+extern "C" int b200_argmax(const void* logits, int64_t ld, int32_t rows, int32_t vocab, int32_t index_offset,
+                           int32_t* out_ids, float* out_max, void* stream) {
+  B200_REQUIRE(logits && out_ids, B200_ERR_INVALID, "argmax: null");
+  return argmax_rows((const __nv_bfloat16*)logits, ld, rows, vocab, index_offset, out_ids, out_max,
+                     (cudaStream_t)stream);
+}
+
+// ---- the step --------------------------------------------------------------------------------------
+struct StepArgs {
+  const int32_t *ids, *positions, *slots, *block_table, *row_to_seq, *ctx_lens, *logit_rows;
+  int bt_stride, T, max_ctx, R;
+  int32_t* out_tokens;
+  void* out_logits;
+};
+
+static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
+  const b200_model_cfg& m = c->cfg;
+  const int T = a.T, h = m.hidden;
+  const bool tp = m.tp_world > 1;
+  const float scale = 1.0f / sqrtf((float)kHeadDim);
+  const int64_t kv_layer_elems = c->n_blocks * c->hkv * (int64_t)m.block_size * kHeadDim;
+  int rc;
+#define STEP(expr)        \
+  do {                    \
+    rc = (expr);          \
+    if (rc) return rc;    \
+  } while (0)
+
+  STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
+  for (int l = 0; l < m.n_layers; ++l) {
+    const LayerW& L = c->layers[l];
+    if (l == 0)
+      STEP(rmsnorm(c->res, nullptr, L.ln1, c->normed, T, h, m.rms_eps, s));
+    else
+      STEP(rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
+    STEP(linear_any(c->normed, h, L.qkv, L.qkv_b, c->qkv_buf, c->qkv_w, T, c->qkv_w, h, 0, c->gemv_max_t, c->lin_ws,
+                    c->lin_ws_bytes, s));
+    __nv_bfloat16* kcl = c->kc + (int64_t)l * kv_layer_elems;
+    __nv_bfloat16* vcl = c->vc + (int64_t)l * kv_layer_elems;
+    STEP(rope_kv_append(c->qkv_buf, a.positions, a.slots, c->cos_sin, kcl, vcl, T, c->hq, c->hkv, m.block_size, s));
+    STEP(paged_attn(c->qkv_buf, c->qkv_w, kcl, vcl, a.block_table, a.bt_stride, a.row_to_seq, a.ctx_lens, c->attn_out,
+                    c->hq * kHeadDim, T, c->hq, c->hkv, m.block_size, a.max_ctx, scale, c->attn_ws, c->attn_ws_bytes, s));
+    STEP(linear_any(c->attn_out, c->hq * kHeadDim, L.o, nullptr, c->x, h, T, h, c->hq * kHeadDim, 0, c->gemv_max_t,
+                    c->lin_ws, c->lin_ws_bytes, s));
+    if (tp) STEP(b200_allreduce_bf16(c, c->x, (int64_t)T * h, s));
+    STEP(rmsnorm(c->x, c->res, L.ln2, c->normed, T, h, m.rms_eps, s));
+    STEP(linear_any(c->normed, h, L.gu, nullptr, c->gu_buf, 2 * c->inter, T, 2 * c->inter, h, 0, c->gemv_max_t,
+                    c->lin_ws, c->lin_ws_bytes, s));
+    STEP(silu_mul(c->gu_buf, c->act, T, c->inter, s));
+    STEP(linear_any(c->act, c->inter, L.down, nullptr, c->x, h, T, h, c->inter, 0, c->gemv_max_t, c->lin_ws,
+                    c->lin_ws_bytes, s));
+    if (tp) STEP(b200_allreduce_bf16(c, c->x, (int64_t)T * h, s));
+    if (l == c->tap_layer && c->tap_hidden) {
+      B200_CUDA(cudaMemcpyAsync(c->tap_hidden, c->x, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));
+      if (c->tap_res) B200_CUDA(cudaMemcpyAsync(c->tap_res, c->res, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));
+    }
+  }
+  STEP(rmsnorm(c->x, c->res, c->final_norm, c->normed, T, h, m.rms_eps, s));
+  const __nv_bfloat16* lm_in = c->normed;
+  if (a.logit_rows) {
+    STEP(embed(a.logit_rows, c->normed, c->lm_in, a.R, h, T, s));  // row gather
+    lm_in = c->lm_in;
+  }
+  STEP(linear_any(lm_in, h, c->lm_head, nullptr, c->logits, c->vocab_local, a.R, c->vocab_local, h, 0, c->gemv_max_t,
+                  c->lin_ws, c->lin_ws_bytes, s));
+  if (!tp) {
+    STEP(argmax_rows(c->logits, c->vocab_local, a.R, c->vocab_local, 0, a.out_tokens, nullptr, s));
+    if (a.out_logits)
+      B200_CUDA(cudaMemcpyAsync(a.out_logits, c->logits, (size_t)a.R * c->vocab_local * 2, cudaMemcpyDeviceToDevice, s));
+  } else {
+    // vocab-parallel greedy: per-rank (max, global index), all-gather of R pairs, pick
+    STEP(argmax_rows(c->logits, c->vocab_local, a.R, c->vocab_local, m.tp_rank * c->vocab_local, c->d_tokens, c->d_max, s));
+    B200_CUDA(launch(tp_pack_kernel, dim3((a.R + 127) / 128), dim3(128), 0, s, (const float*)c->d_max,
+                     (const int32_t*)c->d_tokens, a.R, c->d_pairs));
+    ++launch_counter();
+    B200_NCCL(nccl().AllGather(c->d_pairs, c->d_gathered, (size_t)a.R * 2, ncclFloat32, c->comm, s));
+    B200_CUDA(launch(tp_pick_kernel, dim3((a.R + 127) / 128), dim3(128), 0, s, (const float*)c->d_gathered, m.tp_world,
+                     a.R, a.out_tokens));
+    if (a.out_logits) {
+      // [world][R][vocab_local] rank-major; the host side re-interleaves (test/debug path only)
+      ++launch_counter();
+      B200_NCCL(nccl().AllGather(c->logits, a.out_logits, (size_t)a.R * c->vocab_local, ncclBfloat16, c->comm, s));
+    }
+  }
+#undef STEP
+  return B200_OK;
+}
+
+static uint64_t mix(uint64_t h, uint64_t v) {
+  h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+  return h;
+}
+
+static int pow2_bucket(int v) {
+  int p = 128;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
+  B200_REQUIRE(c->embed && c->final_norm && c->lm_head && c->cos_sin && c->kc, B200_ERR_STATE,
+               "decode_step: weights / rope cache / kv cache not all set");
+  for (int l = 0; l < c->cfg.n_layers; ++l) {
+    const LayerW& L = c->layers[l];
+    B200_REQUIRE(L.ln1 && L.qkv && L.o && L.ln2 && L.gu && L.down && (!c->cfg.qkv_bias || L.qkv_b), B200_ERR_STATE,
+                 "decode_step: layer %d weights incomplete", l);
+  }
+  B200_REQUIRE(a.T > 0 && a.T <= c->cfg.max_tokens, B200_ERR_INVALID, "decode_step: n_tokens=%d outside (0,%d]", a.T,
+               c->cfg.max_tokens);
+  B200_REQUIRE(a.R > 0 && a.R <= c->max_logit_rows && a.R <= a.T, B200_ERR_INVALID,
+               "decode_step: n_logit_rows=%d outside (0,min(%d,n_tokens)]", a.R, c->max_logit_rows);
+  B200_REQUIRE(a.max_ctx > 0 && a.max_ctx <= c->cfg.max_blocks_per_seq * c->cfg.block_size, B200_ERR_INVALID,
+               "decode_step: max_ctx_len=%d outside (0,%d]", a.max_ctx, c->cfg.max_blocks_per_seq * c->cfg.block_size);
+  if (c->cfg.tp_world > 1) B200_REQUIRE(c->comm, B200_ERR_STATE, "decode_step: b200_nccl_init not called");
+
+  const bool use_graph = c->graphs && s != nullptr && c->tap_layer < 0;
+  launch_opts().pdl = getenv("B200_PDL") ? atoi(getenv("B200_PDL")) != 0 : false;
+  int rc = B200_OK;
+  if (!use_graph) {
+    launch_counter() = 0;
+    rc = enqueue_step(c, a, s);
+    c->last_launches = launch_counter();
+    launch_opts().pdl = false;
+    return rc;
+  }
+  uint64_t hsh = 0x1234;
+  const uint64_t parts[] = {(uint64_t)a.ids,        (uint64_t)a.positions,  (uint64_t)a.slots,
+                            (uint64_t)a.block_table, (uint64_t)a.row_to_seq, (uint64_t)a.ctx_lens,
+                            (uint64_t)a.logit_rows,  (uint64_t)a.out_tokens, (uint64_t)a.out_logits,
+                            (uint64_t)a.bt_stride,   (uint64_t)a.T,          (uint64_t)pow2_bucket(a.max_ctx),
+                            (uint64_t)a.R,           (uint64_t)launch_opts().pdl};
+  for (uint64_t p : parts) hsh = mix(hsh, p);
+  GraphKey key{hsh};
+  auto it = c->graph_cache.find(key);
+  if (it == c->graph_cache.end()) {
+    StepArgs b = a;
+    b.max_ctx = pow2_bucket(a.max_ctx);
+    cudaGraph_t g = nullptr;
+    B200_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    launch_counter() = 0;
+    rc = enqueue_step(c, b, s);
+    const int n = launch_counter();
+    cudaError_t e = cudaStreamEndCapture(s, &g);
+    launch_opts().pdl = false;
+    if (rc) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture", __FILE__, __LINE__);
+    cudaGraphExec_t ge = nullptr;
+    e = cudaGraphInstantiate(&ge, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__);
+    if (c->graph_cache.size() > 256) {  // bound the cache: drop everything, shapes re-capture on demand
+      for (auto& kv : c->graph_cache) cudaGraphExecDestroy(kv.second);
+      c->graph_cache.clear();
+    }
+    it = c->graph_cache.emplace(key, ge).first;
+    c->last_launches = n;
+  }
+  launch_opts().pdl = false;
+  B200_CUDA(cudaGraphLaunch(it->second, s));
+  return B200_OK;
+}
+
+extern "C" int b200_decode_step(b200_ctx* c, const int32_t* ids, const int32_t* positions, const int32_t* slot_mapping,
+                                const int32_t* block_table, int32_t bt_stride, const int32_t* row_to_seq,
+                                const int32_t* ctx_lens, int32_t n_tokens, int32_t max_ctx_len,
+                                const int32_t* logit_rows, int32_t n_logit_rows, int32_t* out_token_ids,
+                                void* out_logits, void* stream) {
+  B200_REQUIRE(c && ids && positions && slot_mapping && block_table && ctx_lens && out_token_ids, B200_ERR_INVALID,
+               "decode_step: null argument");
+  StepArgs a{ids, positions, slot_mapping, block_table, row_to_seq, ctx_lens, logit_rows, bt_stride, n_tokens,
+             max_ctx_len, logit_rows ? n_logit_rows : n_tokens, out_token_ids, out_logits};
+  return run_step(c, a, (cudaStream_t)stream);
+}
+
+extern "C" int b200_decode_step_host(b200_ctx* c, const int32_t* host_packed, int32_t n_tokens, int32_t n_seqs,
+                                     int32_t bt_stride, int32_t max_ctx_len, int32_t n_logit_rows,
+                                     int32_t* host_out_token_ids, void* stream) {
+  B200_REQUIRE(c && host_packed && host_out_token_ids, B200_ERR_INVALID, "decode_step_host: null argument");
+  B200_REQUIRE(n_tokens > 0 && n_tokens <= c->cfg.max_tokens && n_seqs > 0 && n_seqs <= n_tokens && bt_stride > 0 &&
+                   bt_stride <= c->cfg.max_blocks_per_seq && n_logit_rows > 0 && n_logit_rows <= n_tokens,
+               B200_ERR_INVALID, "decode_step_host: bad sizes (T=%d seqs=%d bt_stride=%d rows=%d)", n_tokens, n_seqs,
+               bt_stride, n_logit_rows);
+  cudaStream_t s = (cudaStream_t)stream;
+  // ONE host->device copy of the dense packed buffer; the device pointers are functions of
+  // (T, rows, seqs, bt_stride) only, so steps of the same shape replay the same captured graph.
+  const int64_t T = n_tokens;
+  int32_t* d = c->d_meta;
+  const int64_t n_ints = 5 * T + n_logit_rows + (int64_t)n_seqs * bt_stride;
+  B200_REQUIRE(n_ints <= c->meta_ints, B200_ERR_INVALID, "decode_step_host: metadata larger than the ctx buffer");
+  B200_CUDA(cudaMemcpyAsync(d, host_packed, (size_t)n_ints * 4, cudaMemcpyHostToDevice, s));
+  StepArgs a{d, d + T, d + 2 * T, d + 5 * T + n_logit_rows, d + 4 * T, d + 3 * T, d + 5 * T, bt_stride, n_tokens,
+             max_ctx_len, n_logit_rows, c->d_tokens, nullptr};
+  int rc = run_step(c, a, s);
+  if (rc) return rc;
+  B200_CUDA(cudaMemcpyAsync(host_out_token_ids, c->d_tokens, (size_t)n_logit_rows * 4, cudaMemcpyDeviceToHost, s));
+  return B200_OK;
+}

@@ -1,0 +1,360 @@
+// (a6) Paged attention for single-query rows (decode, and prefill rows seen as independent
+// queries with their own context length), split-KV with log-sum-exp merge.
+//
+// Roofline: HBM.  Algorithmic bytes per launch = sum over rows of ctx_len * n_kv_heads * 128 * 2 * 2
+// (every cached K and V element of the row's context read once; q/out are noise).
+//
+// Data path: the cache layout [block][kv head][block_size][128] makes a 64-token K (or V) tile of
+// one kv head one contiguous 16 KiB run, so a tile is ONE bulk-async copy (cp.async.bulk ->
+// SASS UBLKCP) completing on an mbarrier; a 3-stage ring keeps 64 KiB of KV in flight per CTA and
+// two CTAs fit per SM.  One CTA = (row, kv head, split); the G = hq/hkv query heads of the group
+// share every K/V byte fetched (GQA).  Scores, softmax and the P.V accumulation are fp32 (R4 of
+// oracle/decode_oracle.py); the online-softmax running max/sum are kept per head per CTA.
+//
+// Replaces: paged_attention_v1/v2 CPU kernels / IPEX single_query_cached_kv_attention of the
+// vLLM-CPU image ([V22] vllm/v1/attention/backends/cpu_attn.py:377-396).
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int kTile = 64;                        // tokens per smem tile
+constexpr int kStages = 3;
+constexpr int kAttnThreads = 128;
+constexpr int kTileBytes = kTile * kHeadDim * 2;  // 16 KiB per K or V tile
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra.uni WAIT_DONE;\n"
+      "bra.uni WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+struct AttnSmem {
+  alignas(128) unsigned char k[kStages][kTileBytes];
+  alignas(128) unsigned char v[kStages][kTileBytes];
+  alignas(8) uint64_t full[kStages];
+  float p[8][kTile];  // scores, then probabilities, [head][token]
+  float alpha[8];
+  float m[8];
+  float l[8];
+};
+
+template <int G>
+__global__ void __launch_bounds__(kAttnThreads)
+paged_attn_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_bfloat16* __restrict__ kc,
+                  const __nv_bfloat16* __restrict__ vc, const int32_t* __restrict__ block_table, int bt_stride,
+                  const int32_t* __restrict__ row_to_seq, const int32_t* __restrict__ ctx_lens,
+                  __nv_bfloat16* __restrict__ out, int64_t ldo, int hkv, int block_size, int tiles_per_split,
+                  int n_splits, float scale, float* __restrict__ part_o, float* __restrict__ part_ml) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  AttnSmem& sm = *reinterpret_cast<AttnSmem*>(smem_raw);
+  const int split = blockIdx.x, kvh = blockIdx.y, t = blockIdx.z;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int hq = hkv * G;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) mbar_init(&sm.full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (tid < 8) {
+    sm.m[tid] = -INFINITY;
+    sm.l[tid] = 0.f;
+  }
+  __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int ctx = ctx_lens[t];
+  const int seq = row_to_seq ? row_to_seq[t] : t;
+  const int n_tiles_total = (ctx + kTile - 1) / kTile;
+  const int tile_begin = split * tiles_per_split;
+  const int tile_end = min(tile_begin + tiles_per_split, n_tiles_total);
+  const int n_tiles = max(tile_end - tile_begin, 0);
+  const int32_t* bt = block_table + (int64_t)seq * bt_stride;
+
+  auto issue = [&](int i) {  // called by thread 0: fetch tile (tile_begin + i) into stage i % kStages
+    const int st = i % kStages;
+    const int tok0 = (tile_begin + i) * kTile;
+    const int64_t blk = bt[tok0 / block_size];
+    const int off = tok0 % block_size;
+    const int64_t e = ((blk * hkv + kvh) * block_size + off) * kHeadDim;
+    mbar_expect_tx(&sm.full[st], 2 * kTileBytes);
+    bulk_g2s(sm.k[st], kc + e, kTileBytes, &sm.full[st]);
+    bulk_g2s(sm.v[st], vc + e, kTileBytes, &sm.full[st]);
+  };
+  if (tid == 0)
+    for (int i = 0; i < min(kStages, n_tiles); ++i) issue(i);
+
+  // QK mapping: 8 lanes per token, lane j owns dims [8j,8j+8) and [64+8j,64+8j+8): each 16-byte
+  // shared load of a quarter warp is one contiguous 128 bytes (conflict free).
+  const int j8 = lane & 7, tsub = lane >> 3;
+  float qr[G][16];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const __nv_bfloat16* qp = q + (int64_t)t * ldq + (kvh * G + g) * kHeadDim;
+    const uint4 a = *reinterpret_cast<const uint4*>(qp + 8 * j8);
+    const uint4 b = *reinterpret_cast<const uint4*>(qp + 64 + 8 * j8);
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      qr[g][2 * i] = bf16lo(w[i]);
+      qr[g][2 * i + 1] = bf16hi(w[i]);
+    }
+  }
+  // PV mapping: 16 threads per token (8 dims each), 8 token streams.
+  const int dg = tid & 15, ts = tid >> 4;
+  float acc[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[g][i] = 0.f;
+
+  for (int it = 0; it < n_tiles; ++it) {
+    const int st = it % kStages;
+    const int tok0 = (tile_begin + it) * kTile;
+    const int n_valid = min(kTile, ctx - tok0);
+    mbar_wait(&sm.full[st], (it / kStages) & 1);
+
+    // ---- scores ----
+    const unsigned char* kt = sm.k[st];
+#pragma unroll
+    for (int i = 0; i < kTile / 16; ++i) {
+      const int tok = warp * (kTile / 4) + i * 4 + tsub;
+      const uint4 a = *reinterpret_cast<const uint4*>(kt + tok * 256 + 16 * j8);
+      const uint4 b = *reinterpret_cast<const uint4*>(kt + tok * 256 + 128 + 16 * j8);
+      const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      float kf[16];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        kf[2 * e] = bf16lo(w[e]);
+        kf[2 * e + 1] = bf16hi(w[e]);
+      }
+      float sc[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        float d = 0.f;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) d = fmaf(qr[g][e], kf[e], d);
+        d += __shfl_xor_sync(0xffffffffu, d, 1);
+        d += __shfl_xor_sync(0xffffffffu, d, 2);
+        d += __shfl_xor_sync(0xffffffffu, d, 4);
+        sc[g] = d;
+      }
+#pragma unroll
+      for (int g = 0; g < G; ++g)
+        if (j8 == g) sm.p[g][tok] = tok < n_valid ? sc[g] * scale : -INFINITY;
+    }
+    __syncthreads();
+
+    // ---- online softmax: warp w owns heads w, w+4 ----
+    for (int g = warp; g < G; g += 4) {
+      const float s0 = sm.p[g][lane], s1 = sm.p[g][lane + 32];
+      const float m_old = sm.m[g];
+      const float m_new = fmaxf(m_old, warp_max(fmaxf(s0, s1)));  // finite: token tok0 is always valid
+      const float p0 = __expf(s0 - m_new), p1 = __expf(s1 - m_new);
+      sm.p[g][lane] = p0;
+      sm.p[g][lane + 32] = p1;
+      const float a = __expf(m_old - m_new);  // exp(-inf) = 0 on the first tile
+      const float lsum = warp_sum(p0 + p1);
+      if (lane == 0) {
+        sm.alpha[g] = a;
+        sm.m[g] = m_new;
+        sm.l[g] = sm.l[g] * a + lsum;
+      }
+    }
+    __syncthreads();
+
+    // ---- P.V ----
+    const unsigned char* vt = sm.v[st];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const float a = sm.alpha[g];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[g][i] *= a;
+    }
+#pragma unroll 2
+    for (int tok = ts; tok < n_valid; tok += 8) {
+      const uint4 a = *reinterpret_cast<const uint4*>(vt + tok * 256 + 16 * dg);
+      const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+      float vf[8];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        vf[2 * e] = bf16lo(w[e]);
+        vf[2 * e + 1] = bf16hi(w[e]);
+      }
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const float p = sm.p[g][tok];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[g][e] = fmaf(p, vf[e], acc[g][e]);
+      }
+    }
+    __syncthreads();  // everyone is done with stage st and with sm.p
+    if (tid == 0 && it + kStages < n_tiles) issue(it + kStages);
+  }
+
+  // ---- reduce the 8 token streams through shared memory (reuse K stage 0: 8*G*128*4 <= 32 KiB) ----
+  float* red = reinterpret_cast<float*>(sm.k[0]);  // [8][G][128]; G=8 spills into k[1], also idle now
+#pragma unroll
+  for (int g = 0; g < G; ++g)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) red[(ts * G + g) * kHeadDim + dg * 8 + e] = acc[g][e];
+  __syncthreads();
+  const int d = tid;  // 128 threads = 128 dims
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    float o = 0.f;
+#pragma unroll
+    for (int s = 0; s < 8; ++s) o += red[(s * G + g) * kHeadDim + d];
+    const int head = kvh * G + g;
+    if (n_splits == 1) {
+      const float l = sm.l[g];
+      out[(int64_t)t * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? o / l : 0.f);
+    } else {
+      const int64_t pi = ((int64_t)t * hq + head) * n_splits + split;
+      part_o[pi * kHeadDim + d] = o;
+      if (d == 0) {
+        part_ml[pi * 2] = sm.m[g];
+        part_ml[pi * 2 + 1] = sm.l[g];
+      }
+    }
+  }
+}
+
+// Merge the splits of one (row, head): o = sum_s o_s * exp(m_s - m) / sum_s l_s * exp(m_s - m).
+__global__ void __launch_bounds__(kHeadDim)
+attn_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml, __nv_bfloat16* __restrict__ out,
+                  int64_t ldo, int hq, int n_splits) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int head = blockIdx.x, t = blockIdx.y, d = threadIdx.x;
+  const int64_t base = ((int64_t)t * hq + head) * n_splits;
+  float m = -INFINITY;
+  for (int s = 0; s < n_splits; ++s) m = fmaxf(m, part_ml[(base + s) * 2]);
+  float o = 0.f, l = 0.f;
+  for (int s = 0; s < n_splits; ++s) {
+    const float ms = part_ml[(base + s) * 2], ls = part_ml[(base + s) * 2 + 1];
+    if (ls > 0.f) {
+      const float w = __expf(ms - m);
+      l = fmaf(ls, w, l);
+      o = fmaf(part_o[(base + s) * kHeadDim + d], w, o);
+    }
+  }
+  out[(int64_t)t * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? o / l : 0.f);
+}
+
+inline int pow2_at_least(int v, int lo) {
+  int p = lo;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// Split count is a pure function of (T, hkv, bucketed max_ctx) so that a captured graph stays valid
+// for every step in the same bucket.
+void split_plan(int T, int hkv, int max_ctx, int* n_splits, int* tiles_per_split) {
+  const int tiles = pow2_at_least(max(max_ctx, 1), 128) / kTile;
+  const int ctas = max(T * hkv, 1);
+  int s = (2 * kNumSMs + ctas - 1) / ctas;
+  s = max(1, min(s, tiles / 2));  // at least 2 tiles (128 tokens) per split
+  s = min(s, 64);
+  *tiles_per_split = (tiles + s - 1) / s;
+  *n_splits = (tiles + *tiles_per_split - 1) / *tiles_per_split;
+}
+
+template <int G>
+int launch_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+                const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tiles_per_split,
+                float scale, float* part_o, float* part_ml, cudaStream_t s) {
+  static bool attr_set = false;
+  const size_t smem = sizeof(AttnSmem);
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(paged_attn_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  B200_CUDA(launch(paged_attn_kernel<G>, dim3(n_splits, hkv, T), dim3(kAttnThreads), smem, s, q, ldq, kc, vc,
+                   block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tiles_per_split, n_splits,
+                   scale, part_o, part_ml));
+  return B200_OK;
+}
+
+}  // namespace
+
+int64_t paged_attn_workspace_bytes(int T, int hq, int max_ctx, int block_size) {
+  (void)block_size;
+  // upper bound over every hkv >= 1: n_splits <= 64
+  int ns, tps;
+  split_plan(T, 1, max_ctx, &ns, &tps);
+  return (int64_t)T * hq * ns * (kHeadDim + 2) * sizeof(float) + 256;
+}
+
+int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+               const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+               __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
+               void* ws, int64_t ws_bytes, cudaStream_t s) {
+  B200_REQUIRE(hkv > 0 && hq % hkv == 0, B200_ERR_INVALID, "attn: hq=%d not a multiple of hkv=%d", hq, hkv);
+  B200_REQUIRE(block_size % kTile == 0, B200_ERR_UNSUPPORTED, "attn: block_size=%d must be a multiple of %d",
+               block_size, kTile);
+  B200_REQUIRE(ldq % 8 == 0 && ldo % 8 == 0, B200_ERR_INVALID, "attn: ldq/ldo must be multiples of 8");
+  B200_REQUIRE(T <= 65535, B200_ERR_UNSUPPORTED, "attn: more than 65535 rows in one launch");
+  if (T == 0) return B200_OK;
+  int n_splits, tps;
+  split_plan(T, hkv, max_ctx, &n_splits, &tps);
+  float* part_o = nullptr;
+  float* part_ml = nullptr;
+  if (n_splits > 1) {
+    const int64_t need = (int64_t)T * hq * n_splits * (kHeadDim + 2) * sizeof(float);
+    B200_REQUIRE(ws && ws_bytes >= need, B200_ERR_INVALID, "attn: workspace too small (%lld < %lld)",
+                 (long long)ws_bytes, (long long)need);
+    part_o = static_cast<float*>(ws);
+    part_ml = part_o + (int64_t)T * hq * n_splits * kHeadDim;
+  }
+  const int G = hq / hkv;
+  int rc;
+#define B200_ATTN_CASE(g)                                                                                          \
+  case g:                                                                                                          \
+    rc = launch_attn<g>(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv, block_size, \
+                        n_splits, tps, scale, part_o, part_ml, s);                                                 \
+    break;
+  switch (G) {
+    B200_ATTN_CASE(1)
+    B200_ATTN_CASE(2)
+    B200_ATTN_CASE(4)
+    B200_ATTN_CASE(5)
+    B200_ATTN_CASE(8)
+    default:
+      B200_REQUIRE(false, B200_ERR_UNSUPPORTED, "attn: GQA group %d not built (1,2,4,5,8)", G);
+  }
+#undef B200_ATTN_CASE
+  if (rc) return rc;
+  if (n_splits > 1)
+    B200_CUDA(launch(attn_merge_kernel, dim3(hq, T), dim3(kHeadDim), 0, s, (const float*)part_o,
+                     (const float*)part_ml, out, ldo, hq, n_splits));
+  return B200_OK;
+}
+
+}  // namespace b200

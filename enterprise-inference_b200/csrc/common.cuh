@@ -1,0 +1,125 @@
+// Shared device/host helpers for the sm_100a decode kernels.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "b200_decode.h"
+
+namespace b200 {
+
+// ---- error plumbing (never throw across the C ABI) --------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define B200_CUDA(expr)                                                        \
+  do {                                                                         \
+    cudaError_t _e = (expr);                                                   \
+    if (_e != cudaSuccess) return ::b200::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define B200_REQUIRE(cond, code, ...)          \
+  do {                                         \
+    if (!(cond)) {                             \
+      ::b200::set_error(__VA_ARGS__);          \
+      return (code);                           \
+    }                                          \
+  } while (0)
+
+#define B200_LAUNCH_CHECK() B200_CUDA(cudaGetLastError())
+
+constexpr int kHeadDim = 128;
+constexpr int kNumSMs = 148;
+
+// ---- bf16 helpers -----------------------------------------------------------------------
+// A bf16 is the top half of an fp32: widening is a shift / mask (exact).
+__device__ __forceinline__ float bf16lo(uint32_t p) { return __uint_as_float(p << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
+// Streaming 128-bit load that does not allocate in L1 (weights / KV are read once).
+__device__ __forceinline__ uint4 ld_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+// Cached 128-bit read-only load (activations re-read by every warp).
+__device__ __forceinline__ uint4 ld_ro(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---- Programmatic dependent launch -------------------------------------------------------
+// Every kernel of the step waits for its predecessor's memory here and lets its successor
+// start its prologue early; with no PDL attribute on the launch both are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+
+// ---- launch helper -----------------------------------------------------------------------
+struct LaunchOpts {
+  bool pdl = false;  // programmatic stream serialization (set by the ctx inside a step)
+};
+LaunchOpts& launch_opts();
+int& launch_counter();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                          Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  int na = 0;
+  if (launch_opts().pdl) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = na;
+  ++launch_counter();
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+// ---- kernels' host entry points (internal, C++ linkage) ----------------------------------
+int linear_gemv(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
+                __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, cudaStream_t s);
+bool linear_tc_supported(int T, int n_out, int k);
+int64_t linear_tc_workspace_bytes(int T, int n_out, int k);
+int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
+              __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, void* ws, int64_t ws_bytes,
+              cudaStream_t s);
+int rmsnorm(const __nv_bfloat16* x, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int T,
+            int hidden, float eps, cudaStream_t s);
+int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, int T, int hidden, int vocab,
+          cudaStream_t s);
+int rope_kv_append(__nv_bfloat16* qkv, const int32_t* positions, const int32_t* slots,
+                   const __nv_bfloat16* cos_sin, __nv_bfloat16* kc, __nv_bfloat16* vc, int T, int hq,
+                   int hkv, int block_size, cudaStream_t s);
+int64_t paged_attn_workspace_bytes(int T, int hq, int max_ctx, int block_size);
+int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+               const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+               __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx,
+               float scale, void* ws, int64_t ws_bytes, cudaStream_t s);
+int silu_mul(const __nv_bfloat16* gu, __nv_bfloat16* out, int T, int inter, cudaStream_t s);
+int argmax_rows(const __nv_bfloat16* logits, int64_t ld, int rows, int vocab, int index_offset,
+                int32_t* out_ids, float* out_max, cudaStream_t s);
+
+}  // namespace b200

@@ -1,0 +1,280 @@
+// The small ops of the decode step: embedding gather (a1), (add+)RMSNorm (a2), RoPE + KV append
+// (a4+a5), SiLU*mul (a8), greedy argmax (a10).  All are latency/launch bound at decode sizes;
+// their bytes are noise next to the weight stream, so the design goal is: vectorised 16-byte
+// accesses, one pass over the data, rounding points identical to oracle/decode_oracle.py R1/R3/R5/R6.
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------
+// (a1) embedding
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+embed_kernel(const int32_t* __restrict__ ids, const __nv_bfloat16* __restrict__ table,
+             __nv_bfloat16* __restrict__ out, int hidden, int vocab) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int t = blockIdx.x;
+  int id = ids[t];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);  // ids are validated on the host; clamp, never fault
+  const uint4* src = reinterpret_cast<const uint4*>(table + (int64_t)id * hidden);
+  uint4* dst = reinterpret_cast<uint4*>(out + (int64_t)t * hidden);
+  for (int c = threadIdx.x; c < hidden / 8; c += blockDim.x) dst[c] = __ldg(src + c);
+}
+
+// ---------------------------------------------------------------------------------------
+// (a2) RMSNorm / fused add + RMSNorm.  One CTA per token row, the row lives in registers.
+//   s = x (+ res) in fp32; res' = bf16(s); var over UNROUNDED s; n = bf16(s / sqrt(var+eps));
+//   y = bf16(n * w)                                   [V22] vllm/ir/ops/layernorm.py:10-21,40-58
+// ---------------------------------------------------------------------------------------
+constexpr int kNormThreads = 256;
+constexpr int kNormMaxChunks = 4;  // hidden <= 8192
+
+template <bool HAS_RES>
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* res, const __nv_bfloat16* __restrict__ w,
+               __nv_bfloat16* y, int hidden, float eps) {
+  __shared__ float red[kNormThreads / 32];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int t = blockIdx.x;
+  const int nchunk = hidden >> 3;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + (int64_t)t * hidden);
+  uint4* rr = HAS_RES ? reinterpret_cast<uint4*>(res + (int64_t)t * hidden) : nullptr;
+  float v[kNormMaxChunks][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormMaxChunks; ++i) {
+    const int c = threadIdx.x + i * kNormThreads;
+    if (c < nchunk) {
+      const uint4 a = xr[c];
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+      if (HAS_RES) {
+        const uint4 b = rr[c];
+        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[i][2 * j] = bf16lo(aw[j]) + bf16lo(bw[j]);
+          v[i][2 * j + 1] = bf16hi(aw[j]) + bf16hi(bw[j]);
+          o[j] = pack_bf16(v[i][2 * j], v[i][2 * j + 1]);
+        }
+        rr[c] = make_uint4(o[0], o[1], o[2], o[3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[i][2 * j] = bf16lo(aw[j]);
+          v[i][2 * j + 1] = bf16hi(aw[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss = fmaf(v[i][j], v[i][j], ss);
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormThreads / 32; ++i) tot += red[i];
+  const float r = 1.0f / sqrtf(tot / (float)hidden + eps);
+  const uint4* wr = reinterpret_cast<const uint4*>(w);
+  uint4* yr = reinterpret_cast<uint4*>(y + (int64_t)t * hidden);
+#pragma unroll
+  for (int i = 0; i < kNormMaxChunks; ++i) {
+    const int c = threadIdx.x + i * kNormThreads;
+    if (c < nchunk) {
+      const uint4 wq = __ldg(wr + c);
+      const uint32_t ww[4] = {wq.x, wq.y, wq.z, wq.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float n0 = round_bf16(v[i][2 * j] * r), n1 = round_bf16(v[i][2 * j + 1] * r);
+        o[j] = pack_bf16(n0 * bf16lo(ww[j]), n1 * bf16hi(ww[j]));
+      }
+      yr[c] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// (a4+a5) NeoX RoPE in bf16 arithmetic on q and k heads, then K/V rows into the paged cache.
+// grid (token, head), 64 threads: thread i owns the pair (i, i+64).
+// cache layout per layer: [block][kv head][block_size][128].
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64)
+rope_kv_kernel(__nv_bfloat16* qkv, const int32_t* __restrict__ positions, const int32_t* __restrict__ slots,
+               const __nv_bfloat16* __restrict__ cos_sin, __nv_bfloat16* kc, __nv_bfloat16* vc, int hq, int hkv,
+               int block_size) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int t = blockIdx.x, head = blockIdx.y, i = threadIdx.x;
+  const int row_w = (hq + 2 * hkv) * kHeadDim;
+  __nv_bfloat16* hp = qkv + (int64_t)t * row_w + head * kHeadDim;
+  const int slot = slots[t];
+  if (head < hq + hkv) {
+    const int pos = positions[t];
+    const __nv_bfloat16* cs = cos_sin + (int64_t)pos * kHeadDim;
+    const float c = __bfloat162float(cs[i]), s = __bfloat162float(cs[i + 64]);
+    const float x1 = __bfloat162float(hp[i]), x2 = __bfloat162float(hp[i + 64]);
+    // every elementwise op rounds to bf16 (R3)
+    const float o1 = round_bf16(round_bf16(x1 * c) - round_bf16(x2 * s));
+    const float o2 = round_bf16(round_bf16(x2 * c) + round_bf16(x1 * s));
+    if (head < hq) {
+      hp[i] = __float2bfloat16_rn(o1);
+      hp[i + 64] = __float2bfloat16_rn(o2);
+    } else if (slot >= 0) {
+      const int kvh = head - hq;
+      const int64_t blk = slot / block_size, off = slot % block_size;
+      __nv_bfloat16* dst = kc + ((blk * hkv + kvh) * block_size + off) * kHeadDim;
+      dst[i] = __float2bfloat16_rn(o1);
+      dst[i + 64] = __float2bfloat16_rn(o2);
+    }
+  } else if (slot >= 0) {
+    const int kvh = head - hq - hkv;
+    const int64_t blk = slot / block_size, off = slot % block_size;
+    __nv_bfloat16* dst = vc + ((blk * hkv + kvh) * block_size + off) * kHeadDim;
+    dst[i] = hp[i];
+    dst[i + 64] = hp[i + 64];
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// (a8) SiLU*mul: a = bf16(bf16(silu(g)) * u)             [V22] activation.py:137-141
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float silu_bf16(float g) { return round_bf16(g / (1.0f + expf(-g))); }
+
+__global__ void __launch_bounds__(256)
+silu_mul_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ out, int inter, int64_t total_chunks) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int cpr = inter >> 3;  // chunks per row
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total_chunks;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t t = idx / cpr;
+    const int c = (int)(idx % cpr);
+    const uint4 g = *reinterpret_cast<const uint4*>(gu + t * 2 * inter + c * 8);
+    const uint4 u = *reinterpret_cast<const uint4*>(gu + t * 2 * inter + inter + c * 8);
+    const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, uw[4] = {u.x, u.y, u.z, u.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      o[j] = pack_bf16(silu_bf16(bf16lo(gw[j])) * bf16lo(uw[j]), silu_bf16(bf16hi(gw[j])) * bf16hi(uw[j]));
+    *reinterpret_cast<uint4*>(out + t * inter + c * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// (a10) greedy argmax per row, fp32 compare, ties -> lowest index.  [V22] sampler.py:90-91,235-236
+// ---------------------------------------------------------------------------------------
+constexpr int kArgmaxThreads = 1024;
+
+__device__ __forceinline__ void take(float& bv, int& bi, float v, int i) {
+  if (v > bv || (v == bv && i < bi)) {
+    bv = v;
+    bi = i;
+  }
+}
+
+__global__ void __launch_bounds__(kArgmaxThreads)
+argmax_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, int index_offset,
+              int32_t* __restrict__ out_ids, float* __restrict__ out_max) {
+  __shared__ float sv[kArgmaxThreads / 32];
+  __shared__ int si[kArgmaxThreads / 32];
+  pdl_wait();
+  pdl_launch_dependents();
+  const __nv_bfloat16* row = logits + (int64_t)blockIdx.x * ld;
+  float bv = -INFINITY;
+  int bi = 0x7fffffff;
+  const int nchunk = vocab >> 3;
+  for (int c = threadIdx.x; c < nchunk; c += kArgmaxThreads) {
+    const uint4 q = *reinterpret_cast<const uint4*>(row + c * 8);
+    const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      take(bv, bi, bf16lo(qw[j]), c * 8 + 2 * j);
+      take(bv, bi, bf16hi(qw[j]), c * 8 + 2 * j + 1);
+    }
+  }
+  for (int i = nchunk * 8 + threadIdx.x; i < vocab; i += kArgmaxThreads) take(bv, bi, __bfloat162float(row[i]), i);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    take(bv, bi, ov, oi);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    sv[threadIdx.x >> 5] = bv;
+    si[threadIdx.x >> 5] = bi;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    bv = sv[threadIdx.x];
+    bi = si[threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      take(bv, bi, ov, oi);
+    }
+    if (threadIdx.x == 0) {
+      out_ids[blockIdx.x] = bi + index_offset;
+      if (out_max) out_max[blockIdx.x] = bv;
+    }
+  }
+}
+
+}  // namespace
+
+int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, int T, int hidden, int vocab,
+          cudaStream_t s) {
+  B200_REQUIRE(hidden % 8 == 0, B200_ERR_UNSUPPORTED, "embed: hidden %% 8 != 0");
+  if (T == 0) return B200_OK;
+  B200_CUDA(launch(embed_kernel, dim3(T), dim3(128), 0, s, ids, table, out, hidden, vocab));
+  return B200_OK;
+}
+
+int rmsnorm(const __nv_bfloat16* x, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int T,
+            int hidden, float eps, cudaStream_t s) {
+  B200_REQUIRE(hidden % 8 == 0 && hidden <= 8 * kNormThreads * kNormMaxChunks, B200_ERR_UNSUPPORTED,
+               "rmsnorm: hidden=%d unsupported (multiple of 8, <= %d)", hidden, 8 * kNormThreads * kNormMaxChunks);
+  if (T == 0) return B200_OK;
+  if (res)
+    B200_CUDA(launch(rmsnorm_kernel<true>, dim3(T), dim3(kNormThreads), 0, s, x, res, w, y, hidden, eps));
+  else
+    B200_CUDA(launch(rmsnorm_kernel<false>, dim3(T), dim3(kNormThreads), 0, s, x, res, w, y, hidden, eps));
+  return B200_OK;
+}
+
+int rope_kv_append(__nv_bfloat16* qkv, const int32_t* positions, const int32_t* slots,
+                   const __nv_bfloat16* cos_sin, __nv_bfloat16* kc, __nv_bfloat16* vc, int T, int hq,
+                   int hkv, int block_size, cudaStream_t s) {
+  if (T == 0) return B200_OK;
+  B200_CUDA(launch(rope_kv_kernel, dim3(T, hq + 2 * hkv), dim3(64), 0, s, qkv, positions, slots, cos_sin, kc, vc,
+                   hq, hkv, block_size));
+  return B200_OK;
+}
+
+int silu_mul(const __nv_bfloat16* gu, __nv_bfloat16* out, int T, int inter, cudaStream_t s) {
+  B200_REQUIRE(inter % 8 == 0, B200_ERR_UNSUPPORTED, "silu_mul: intermediate %% 8 != 0");
+  if (T == 0) return B200_OK;
+  const int64_t chunks = (int64_t)T * (inter / 8);
+  int64_t grid64 = (chunks + 255) / 256;
+  if (grid64 > (int64_t)kNumSMs * 8) grid64 = (int64_t)kNumSMs * 8;
+  const int grid = (int)grid64;
+  B200_CUDA(launch(silu_mul_kernel, dim3(grid), dim3(256), 0, s, gu, out, inter, chunks));
+  return B200_OK;
+}
+
+int argmax_rows(const __nv_bfloat16* logits, int64_t ld, int rows, int vocab, int index_offset,
+                int32_t* out_ids, float* out_max, cudaStream_t s) {
+  B200_REQUIRE(ld % 8 == 0, B200_ERR_UNSUPPORTED, "argmax: ld %% 8 != 0");
+  if (rows == 0) return B200_OK;
+  B200_CUDA(launch(argmax_kernel, dim3(rows), dim3(kArgmaxThreads), 0, s, logits, ld, vocab, index_offset, out_ids,
+                   out_max));
+  return B200_OK;
+}
+
+}  // namespace b200

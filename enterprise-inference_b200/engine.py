@@ -1,0 +1,246 @@
+"""Host-side engine: KV block manager + continuous-batching scheduler with chunked prefill.
+
+Mirrors the scheduler of the image the chart deploys, as parameterised by the chart's flags
+(/root/reference/core/helm-charts/vllm/xeon-values.yaml:70-89): --block-size 128,
+--max-num-batched-tokens 2048 (token budget of one step), --max-num-seqs 256,
+--enable_chunked_prefill, --max-model-len 8192.  Greedy only on the device
+(clients send "temperature": 0, /root/reference/docs/accessing-deployed-models.md:176).
+Pure host logic: unit-tested on CPU with a fake runner.
+"""
+from __future__ import annotations
+
+import time
+from collections import deque
+from dataclasses import dataclass, field
+from typing import Deque, Dict, List, Optional
+
+from .runner import StepBatch
+
+
+class OutOfBlocks(RuntimeError):
+    pass
+
+
+class BlockManager:
+    """Free-list allocator of fixed-size KV blocks; block tables are per sequence."""
+
+    def __init__(self, n_blocks: int, block_size: int):
+        self.n_blocks, self.block_size = n_blocks, block_size
+        self.free: List[int] = list(range(n_blocks - 1, -1, -1))
+
+    def blocks_needed(self, n_tokens: int) -> int:
+        return (n_tokens + self.block_size - 1) // self.block_size
+
+    def can_grow(self, table: List[int], n_tokens: int) -> bool:
+        return self.blocks_needed(n_tokens) - len(table) <= len(self.free)
+
+    def grow(self, table: List[int], n_tokens: int) -> None:
+        need = self.blocks_needed(n_tokens) - len(table)
+        if need > len(self.free):
+            raise OutOfBlocks(f"need {need} blocks, {len(self.free)} free")
+        for _ in range(need):
+            table.append(self.free.pop())
+
+    def release(self, table: List[int]) -> None:
+        self.free.extend(reversed(table))
+        table.clear()
+
+    @property
+    def usage(self) -> float:
+        return 1.0 - len(self.free) / max(self.n_blocks, 1)
+
+
+@dataclass
+class Request:
+    request_id: str
+    prompt_ids: List[int]
+    max_tokens: int = 16
+    ignore_eos: bool = False
+    eos_token_ids: tuple = ()
+    stop_token_ids: tuple = ()
+    min_tokens: int = 0
+    arrival: float = field(default_factory=time.monotonic)
+    # state
+    output_ids: List[int] = field(default_factory=list)
+    n_computed: int = 0                 # tokens whose KV is in the cache
+    block_table: List[int] = field(default_factory=list)
+    finished: bool = False
+    finish_reason: Optional[str] = None
+    first_token_time: Optional[float] = None
+    finish_time: Optional[float] = None
+    token_times: List[float] = field(default_factory=list)
+
+    @property
+    def all_ids(self) -> List[int]:
+        return self.prompt_ids + self.output_ids
+
+    @property
+    def n_total(self) -> int:
+        return len(self.prompt_ids) + len(self.output_ids)
+
+
+@dataclass
+class Scheduled:
+    req: Request
+    n_new: int          # token rows this step
+    samples: bool       # the last row produces a token
+
+
+class Scheduler:
+    def __init__(self, blocks: BlockManager, *, max_num_batched_tokens: int = 2048, max_num_seqs: int = 256,
+                 max_model_len: int = 8192, max_logit_rows: int = 512):
+        self.blocks = blocks
+        self.max_tokens = max_num_batched_tokens
+        self.max_seqs = min(max_num_seqs, max_logit_rows)
+        self.max_model_len = max_model_len
+        self.waiting: Deque[Request] = deque()
+        self.running: List[Request] = []
+
+    def add(self, req: Request) -> None:
+        if len(req.prompt_ids) == 0:
+            raise ValueError("empty prompt")
+        if len(req.prompt_ids) + req.max_tokens > self.max_model_len:
+            raise ValueError(f"prompt ({len(req.prompt_ids)}) + max_tokens ({req.max_tokens}) exceeds "
+                             f"max-model-len {self.max_model_len}")
+        self.waiting.append(req)
+
+    def has_work(self) -> bool:
+        return bool(self.waiting or self.running)
+
+    def schedule(self) -> List[Scheduled]:
+        """Decode rows first (one per running, fully-prefilled sequence), then prefill chunks of the
+        running and newly admitted sequences until the token budget is spent."""
+        budget = self.max_tokens
+        out: List[Scheduled] = []
+        # running: decode or continue prefill
+        for req in list(self.running):
+            if budget == 0:
+                break
+            if req not in self.running:   # preempted earlier in this pass
+                continue
+            remaining = req.n_total - req.n_computed
+            n_new = min(remaining, budget)
+            if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
+                # preempt the youngest running request (recompute later), vLLM's default policy
+                victim = self.running[-1]
+                if victim is req and len(self.running) == 1:
+                    raise OutOfBlocks("a single sequence does not fit the KV cache")
+                self._preempt(victim)
+                if victim is req:
+                    continue
+                if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
+                    continue
+            self.blocks.grow(req.block_table, req.n_computed + n_new)
+            out.append(Scheduled(req, n_new, n_new == remaining))
+            budget -= n_new
+        # admit
+        while self.waiting and budget > 0 and len(self.running) < self.max_seqs:
+            req = self.waiting[0]
+            n_new = min(req.n_total - req.n_computed, budget)
+            if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
+                break
+            self.waiting.popleft()
+            self.blocks.grow(req.block_table, req.n_computed + n_new)
+            self.running.append(req)
+            out.append(Scheduled(req, n_new, n_new == req.n_total - req.n_computed))
+            budget -= n_new
+        return out
+
+    def _preempt(self, req: Request) -> None:
+        self.running.remove(req)
+        self.blocks.release(req.block_table)
+        req.n_computed = 0
+        self.waiting.appendleft(req)
+
+    def build_batch(self, sched: List[Scheduled]) -> StepBatch:
+        b = StepBatch()
+        bs = self.blocks.block_size
+        for si, s in enumerate(sched):
+            r = s.req
+            ids = r.all_ids
+            for p in range(r.n_computed, r.n_computed + s.n_new):
+                b.ids.append(ids[p])
+                b.positions.append(p)
+                b.slots.append(r.block_table[p // bs] * bs + p % bs)
+                b.ctx_lens.append(p + 1)
+                b.row_to_seq.append(si)
+            if s.samples:
+                b.logit_rows.append(len(b.ids) - 1)
+            b.block_tables.append(r.block_table)
+        return b
+
+    def commit(self, sched: List[Scheduled], sampled: List[int], now: Optional[float] = None) -> List[Request]:
+        """Apply a step's results; returns the requests that finished."""
+        now = time.monotonic() if now is None else now
+        done, k = [], 0
+        for s in sched:
+            r = s.req
+            r.n_computed += s.n_new
+            if not s.samples:
+                continue
+            tok = int(sampled[k])
+            k += 1
+            r.output_ids.append(tok)
+            r.token_times.append(now)
+            if r.first_token_time is None:
+                r.first_token_time = now
+            n_out = len(r.output_ids)
+            reason = None
+            if n_out >= r.min_tokens:
+                if tok in r.stop_token_ids:
+                    reason = "stop"
+                elif not r.ignore_eos and tok in r.eos_token_ids:
+                    reason = "stop"
+            if reason is None and n_out >= r.max_tokens:
+                reason = "length"
+            if reason:
+                r.finished, r.finish_reason, r.finish_time = True, reason, now
+                self.running.remove(r)
+                self.blocks.release(r.block_table)
+                done.append(r)
+        return done
+
+
+class LLMEngine:
+    """add_request / step loop around a ModelRunner (or anything with .step(StepBatch))."""
+
+    def __init__(self, runner, *, max_num_batched_tokens: int = 2048, max_num_seqs: int = 256,
+                 max_model_len: int = 8192):
+        self.runner = runner
+        self.blocks = BlockManager(runner.n_blocks, runner.block_size)
+        self.scheduler = Scheduler(self.blocks, max_num_batched_tokens=min(max_num_batched_tokens, runner.max_tokens),
+                                   max_num_seqs=max_num_seqs, max_model_len=min(max_model_len, runner.max_model_len))
+        self.requests: Dict[str, Request] = {}
+        self.steps = 0
+
+    def add_request(self, req: Request) -> None:
+        self.scheduler.add(req)
+        self.requests[req.request_id] = req
+
+    def has_work(self) -> bool:
+        return self.scheduler.has_work()
+
+    def step(self) -> List[Request]:
+        sched = self.scheduler.schedule()
+        if not sched:
+            return []
+        batch = self.scheduler.build_batch(sched)
+        if batch.logit_rows:
+            sampled = self.runner.step(batch)
+        else:  # a prefill chunk that samples nothing still needs one logit row for the ABI
+            batch.logit_rows.append(batch.n_tokens - 1)
+            self.runner.step(batch)
+            sampled = []
+        self.steps += 1
+        done = self.scheduler.commit(sched, list(sampled))
+        for r in done:
+            self.requests.pop(r.request_id, None)
+        return done
+
+    def generate(self, prompts: List[List[int]], max_tokens: int, ignore_eos: bool = True) -> List[List[int]]:
+        reqs = [Request(f"gen-{i}", list(p), max_tokens=max_tokens, ignore_eos=ignore_eos) for i, p in enumerate(prompts)]
+        for r in reqs:
+            self.add_request(r)
+        while self.has_work():
+            self.step()
+        return [r.output_ids for r in reqs]

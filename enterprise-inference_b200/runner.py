@@ -1,0 +1,234 @@
+"""Device state of one TP rank and one scheduler step through the C-ABI.
+
+Mirrors the worker/model-runner of the image the chart deploys (one worker process per TP rank,
+/root/reference/core/helm-charts/vllm/xeon-values.yaml:78-79; [V22] vllm/v1/worker/*model_runner*):
+it owns the weights, the paged KV cache and the step inputs, and runs `execute_model` — here
+`b200_decode_step_host` — once per scheduler iteration.  torch allocates; CUDA computes.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _abi
+from .config import ModelConfig, rope_cos_sin
+
+
+@dataclass
+class StepBatch:
+    """Step inputs.  One entry per token row; block_tables one row per sequence."""
+    ids: List[int] = field(default_factory=list)
+    positions: List[int] = field(default_factory=list)
+    slots: List[int] = field(default_factory=list)
+    ctx_lens: List[int] = field(default_factory=list)
+    row_to_seq: List[int] = field(default_factory=list)
+    logit_rows: List[int] = field(default_factory=list)
+    block_tables: List[Sequence[int]] = field(default_factory=list)
+
+    @property
+    def n_tokens(self):
+        return len(self.ids)
+
+
+class ModelRunner:
+    def __init__(self, cfg: ModelConfig, device: Optional[torch.device] = None, *, max_tokens: int = 2048,
+                 max_model_len: int = 8192, block_size: int = 128, n_blocks: Optional[int] = None,
+                 kv_cache_gib: Optional[float] = None, tp_rank: int = 0, tp_world: int = 1,
+                 graphs: bool = True):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ModelRunner needs a CUDA device (B200, sm_100a); there is no CPU path")
+        self.lib = _abi.lib()
+        self.cfg = cfg
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        torch.cuda.set_device(self.device)
+        if not self.lib.b200_device_ok():
+            raise RuntimeError("the current CUDA device is not compute capability 10.x (B200)")
+        self.block_size = block_size
+        self.max_tokens = max_tokens
+        self.max_model_len = max_model_len
+        self.max_blocks_per_seq = (max_model_len + block_size - 1) // block_size
+        self.tp_rank, self.tp_world = tp_rank, tp_world
+        self.hq = cfg.n_q_heads // tp_world
+        self.hkv = cfg.n_kv_heads // tp_world
+        self.inter = cfg.intermediate // tp_world
+        self.vocab_local = cfg.vocab // tp_world
+        self.stream = torch.cuda.Stream(device=self.device)
+
+        mc = _abi.ModelCfg(hidden=cfg.hidden, n_layers=cfg.n_layers, n_q_heads=cfg.n_q_heads,
+                           n_kv_heads=cfg.n_kv_heads, head_dim=cfg.head_dim, intermediate=cfg.intermediate,
+                           vocab=cfg.vocab, qkv_bias=int(cfg.qkv_bias), rms_eps=cfg.rms_eps,
+                           block_size=block_size, max_tokens=max_tokens,
+                           max_blocks_per_seq=self.max_blocks_per_seq, tp_rank=tp_rank, tp_world=tp_world)
+        h = C.c_void_p()
+        _abi.check(self.lib.b200_ctx_create(C.byref(mc), C.byref(h)))
+        self.ctx = h
+        _abi.check(self.lib.b200_ctx_set_graphs(self.ctx, int(graphs)))
+
+        # KV cache [L][n_blocks][hkv][block][128] bf16, zero-filled (a masked tail never reads NaNs)
+        per_block = cfg.n_layers * self.hkv * block_size * cfg.head_dim * 2 * 2
+        if n_blocks is None:
+            if kv_cache_gib is None:
+                free, _ = torch.cuda.mem_get_info(self.device)
+                kv_cache_gib = max(free / 2 ** 30 * 0.5, 0.25)
+            n_blocks = max(int(kv_cache_gib * 2 ** 30) // per_block, 2)
+        self.n_blocks = n_blocks
+        shape = (cfg.n_layers, n_blocks, self.hkv, block_size, cfg.head_dim)
+        self.k_cache = torch.zeros(shape, dtype=torch.bfloat16, device=self.device)
+        self.v_cache = torch.zeros(shape, dtype=torch.bfloat16, device=self.device)
+        _abi.check(self.lib.b200_set_kv_cache(self.ctx, self.k_cache.data_ptr(), self.v_cache.data_ptr(), n_blocks))
+        self.cos_sin = rope_cos_sin(cfg, max(max_model_len, 16)).to(self.device)
+        _abi.check(self.lib.b200_set_rope_cache(self.ctx, self.cos_sin.data_ptr(), self.cos_sin.shape[0]))
+
+        self._weights: List[torch.Tensor] = []   # keeps the borrowed device tensors alive
+        meta_ints = 6 * max_tokens + max_tokens * self.max_blocks_per_seq
+        self._h_meta = torch.empty(meta_ints, dtype=torch.int32).pin_memory()
+        self._h_meta_np = self._h_meta.numpy()
+        self._h_out = torch.empty(max(max_tokens, 1), dtype=torch.int32).pin_memory()
+        self._h_out_np = self._h_out.numpy()
+        self.h2d_bytes_last = 0
+        self.d2h_bytes_last = 0
+
+    # ---- weights ---------------------------------------------------------------------------
+    def _set(self, layer: int, kind: int, t: torch.Tensor):
+        t = t.to(device=self.device, dtype=torch.bfloat16).contiguous()
+        self._weights.append(t)
+        rows, cols = (t.shape[0], t.shape[1]) if t.dim() == 2 else (t.shape[0], 1)
+        _abi.check(self.lib.b200_set_weight(self.ctx, layer, kind, t.data_ptr(), rows, cols))
+
+    def load_weights(self, w: Dict[str, torch.Tensor]):
+        """HF-named tensors ([V22] llama.py:437-444 packing: q|k|v -> qkv, gate|up -> gate_up),
+        sharded Megatron-style for this TP rank."""
+        c, r, d = self.cfg, self.tp_rank, self.cfg.head_dim
+        qs = slice(r * self.hq * d, (r + 1) * self.hq * d)
+        ks = slice(r * self.hkv * d, (r + 1) * self.hkv * d)
+        is_ = slice(r * self.inter, (r + 1) * self.inter)
+        vs = slice(r * self.vocab_local, (r + 1) * self.vocab_local)
+        self._set(0, _abi.W_EMBED, w["model.embed_tokens.weight"])
+        for l in range(c.n_layers):
+            p = f"model.layers.{l}."
+            self._set(l, _abi.W_LN1, w[p + "input_layernorm.weight"])
+            self._set(l, _abi.W_QKV, torch.cat([w[p + "self_attn.q_proj.weight"][qs],
+                                                w[p + "self_attn.k_proj.weight"][ks],
+                                                w[p + "self_attn.v_proj.weight"][ks]], 0))
+            if c.qkv_bias:
+                self._set(l, _abi.W_QKV_BIAS, torch.cat([w[p + "self_attn.q_proj.bias"][qs],
+                                                         w[p + "self_attn.k_proj.bias"][ks],
+                                                         w[p + "self_attn.v_proj.bias"][ks]], 0))
+            self._set(l, _abi.W_O, w[p + "self_attn.o_proj.weight"][:, qs])
+            self._set(l, _abi.W_LN2, w[p + "post_attention_layernorm.weight"])
+            self._set(l, _abi.W_GATE_UP, torch.cat([w[p + "mlp.gate_proj.weight"][is_],
+                                                    w[p + "mlp.up_proj.weight"][is_]], 0))
+            self._set(l, _abi.W_DOWN, w[p + "mlp.down_proj.weight"][:, is_])
+        self._set(0, _abi.W_FINAL_NORM, w["model.norm.weight"])
+        self._set(0, _abi.W_LM_HEAD, w["lm_head.weight"][vs])
+
+    def init_random_weights(self, seed: int = 1234, std: float = 0.02):
+        """Random-init N(0, std^2) weights generated on the device (benchmarks; no checkpoint
+        is reachable without network).  Norm weights are 1."""
+        c = self.cfg
+        g = torch.Generator(device=self.device)
+        g.manual_seed(seed + 7919 * self.tp_rank)
+
+        def rnd(*shape):
+            t = torch.empty(shape, dtype=torch.bfloat16, device=self.device)
+            t.normal_(0.0, std, generator=g)
+            return t
+
+        ones = torch.ones(c.hidden, dtype=torch.bfloat16, device=self.device)
+        ge = torch.Generator(device=self.device)
+        ge.manual_seed(seed)  # the embedding is replicated: same bytes on every rank
+        emb = torch.empty((c.vocab, c.hidden), dtype=torch.bfloat16, device=self.device)
+        emb.normal_(0.0, std, generator=ge)
+        self._set(0, _abi.W_EMBED, emb)
+        qkv_rows = (self.hq + 2 * self.hkv) * c.head_dim
+        for l in range(c.n_layers):
+            self._set(l, _abi.W_LN1, ones)
+            self._set(l, _abi.W_QKV, rnd(qkv_rows, c.hidden))
+            if c.qkv_bias:
+                self._set(l, _abi.W_QKV_BIAS, rnd(qkv_rows))
+            self._set(l, _abi.W_O, rnd(c.hidden, self.hq * c.head_dim))
+            self._set(l, _abi.W_LN2, ones)
+            self._set(l, _abi.W_GATE_UP, rnd(2 * self.inter, c.hidden))
+            self._set(l, _abi.W_DOWN, rnd(c.hidden, self.inter))
+        self._set(0, _abi.W_FINAL_NORM, ones)
+        self._set(0, _abi.W_LM_HEAD, rnd(self.vocab_local, c.hidden))
+
+    # ---- TP --------------------------------------------------------------------------------
+    def init_tp(self, group=None):
+        """Create the ctx's NCCL communicator; the 128-byte id travels over torch.distributed."""
+        if self.tp_world == 1:
+            return
+        import torch.distributed as dist
+        buf = (C.c_char * 128)()
+        if self.tp_rank == 0:
+            _abi.check(self.lib.b200_nccl_unique_id(buf))
+        obj = [bytes(buf)]
+        dist.broadcast_object_list(obj, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        idb = (C.c_char * 128).from_buffer_copy(obj[0])
+        _abi.check(self.lib.b200_nccl_init(self.ctx, idb))
+
+    # ---- one step ---------------------------------------------------------------------------
+    def pack(self, b: StepBatch):
+        """Write the dense packed int32 buffer b200_decode_step_host expects into pinned memory."""
+        T, R, S = b.n_tokens, len(b.logit_rows), len(b.block_tables)
+        bt_stride = max(max(len(r) for r in b.block_tables), 1)
+        a = self._h_meta_np
+        a[0:T] = b.ids
+        a[T:2 * T] = b.positions
+        a[2 * T:3 * T] = b.slots
+        a[3 * T:4 * T] = b.ctx_lens
+        a[4 * T:5 * T] = b.row_to_seq
+        a[5 * T:5 * T + R] = b.logit_rows
+        o = 5 * T + R
+        bt = a[o:o + S * bt_stride].reshape(S, bt_stride)
+        bt.fill(0)
+        for i, row in enumerate(b.block_tables):
+            bt[i, :len(row)] = row
+        return T, R, S, bt_stride, o + S * bt_stride
+
+    def step(self, b: StepBatch, sync: bool = True) -> np.ndarray:
+        """Host-buffer step (the serving path and bench.py's e2e): pinned H2D, step, D2H."""
+        T, R, S, bt_stride, n_ints = self.pack(b)
+        max_ctx = max(b.ctx_lens)
+        _abi.check(self.lib.b200_decode_step_host(self.ctx, self._h_meta.data_ptr(), T, S, bt_stride, max_ctx, R,
+                                                  self._h_out.data_ptr(), self.stream.cuda_stream))
+        self.h2d_bytes_last, self.d2h_bytes_last = n_ints * 4, R * 4
+        if sync:
+            self.stream.synchronize()
+        return self._h_out_np[:R]
+
+    def step_device(self, ids, positions, slots, block_table, ctx_lens, max_ctx, *, row_to_seq=None,
+                    logit_rows=None, out_tokens=None, out_logits=None, stream=None):
+        """Device-pointer step (inputs already resident in HBM): bench.py's `value`, and tests."""
+        T = ids.numel()
+        R = logit_rows.numel() if logit_rows is not None else T
+        if out_tokens is None:
+            out_tokens = torch.empty(R, dtype=torch.int32, device=self.device)
+        s = (stream or self.stream).cuda_stream
+        _abi.check(self.lib.b200_decode_step(
+            self.ctx, ids.data_ptr(), positions.data_ptr(), slots.data_ptr(), block_table.data_ptr(),
+            block_table.stride(0), _abi.ptr(row_to_seq), ctx_lens.data_ptr(), T, int(max_ctx),
+            _abi.ptr(logit_rows), R, out_tokens.data_ptr(), _abi.ptr(out_logits), s))
+        return out_tokens
+
+    def last_step_launches(self) -> int:
+        return int(self.lib.b200_ctx_last_step_launches(self.ctx))
+
+    def set_graphs(self, on: bool):
+        _abi.check(self.lib.b200_ctx_set_graphs(self.ctx, int(on)))
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            torch.cuda.synchronize(self.device)
+            self.lib.b200_ctx_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,199 @@
+/*
+ * b200_decode.h — C-ABI of the B200-native decode path.
+ *
+ * The reference (psurabh/Enterprise-Inference v1.3.0) has NO in-process FFI for this path:
+ * its boundary is the container contract of core/helm-charts/vllm (image + args + env + HTTP,
+ * /root/reference/core/helm-charts/vllm/templates/deployment.yaml:57,66-87 and
+ * /root/reference/docs/api-spec.yaml:6-49).  The arithmetic runs inside the third-party
+ * image vllm-cpu-release-repo:v0.10.2 (values.yaml:23-28).  Each entry point below therefore
+ * cites the step of that image's decode loop it replaces (the
+ * [V22] citations are the vLLM 0.22 wheel used as the readable statement of the math).
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative b200_status otherwise; the text of the
+ *    last error of the calling thread is b200_last_error(); nothing throws across the ABI;
+ *  - every tensor is a CALLER-OWNED DEVICE pointer (e.g. torch tensor.data_ptr()) unless the
+ *    parameter name starts with host_; bf16 unless stated; row-major; explicit leading dims;
+ *  - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing syncs
+ *    unless documented;
+ *  - no hidden allocation after b200_ctx_create(): scratch is either inside the ctx or passed
+ *    by the caller as (workspace, workspace_bytes) with a *_workspace_bytes() query;
+ *  - a ctx is not re-entrant: one engine thread per rank drives it; TP ranks are processes.
+ */
+#ifndef B200_DECODE_H
+#define B200_DECODE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+typedef struct b200_ctx b200_ctx;
+
+typedef enum b200_status {
+  B200_OK = 0,
+  B200_ERR_INVALID = -1,      /* bad argument / shape */
+  B200_ERR_CUDA = -2,         /* a CUDA runtime/driver call failed */
+  B200_ERR_UNSUPPORTED = -3,  /* shape outside what the kernels were built for */
+  B200_ERR_NCCL = -4,
+  B200_ERR_STATE = -5         /* call order (weights not set, ...) */
+} b200_status;
+
+B200_API const char* b200_last_error(void);
+B200_API int b200_abi_version(void);
+/* 1 when a CUDA device of compute capability 10.x is current, else 0 (no error text). */
+B200_API int b200_device_ok(void);
+
+/* ---- model / context ------------------------------------------------------------------ */
+typedef struct b200_model_cfg {
+  int32_t hidden, n_layers, n_q_heads, n_kv_heads, head_dim; /* GLOBAL sizes; head_dim == 128 */
+  int32_t intermediate, vocab;
+  int32_t qkv_bias;            /* Qwen2: 1 */
+  float rms_eps;
+  int32_t block_size;          /* KV block, tokens: 128 (xeon-values.yaml:72-73 --block-size) */
+  int32_t max_tokens;          /* max token rows in one step (--max-num-batched-tokens 2048) */
+  int32_t max_blocks_per_seq;  /* ceil(max-model-len / block_size) */
+  int32_t tp_rank, tp_world;   /* tensor parallel (deployment.yaml:72-78 --tensor-parallel-size) */
+} b200_model_cfg;
+
+typedef enum b200_weight_kind {
+  B200_W_EMBED = 0,     /* [vocab, hidden]                      (a1)  replicated on every rank */
+  B200_W_LN1 = 1,       /* [hidden]                             (a2)  */
+  B200_W_QKV = 2,       /* [(hq+2hkv)_local*128, hidden]        (a3)  q|k|v rows, column-parallel */
+  B200_W_QKV_BIAS = 3,  /* [(hq+2hkv)_local*128]                      */
+  B200_W_O = 4,         /* [hidden, hq_local*128]               (a7)  row-parallel */
+  B200_W_LN2 = 5,       /* [hidden]                                   */
+  B200_W_GATE_UP = 6,   /* [2*I_local, hidden] gate rows then up rows (a8) */
+  B200_W_DOWN = 7,      /* [hidden, I_local]                    (a8)  row-parallel */
+  B200_W_FINAL_NORM = 8,/* [hidden]                             (a9)  */
+  B200_W_LM_HEAD = 9    /* [vocab_local, hidden]                (a9)  vocab-parallel */
+} b200_weight_kind;
+
+/* Replaces: model construction inside the image's worker (one per TP rank,
+ * xeon-values.yaml:78-79 --distributed_executor_backend mp).  Allocates the ctx's private
+ * activation/scratch buffers (the only cudaMalloc calls in the library). */
+B200_API int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out);
+B200_API int b200_ctx_destroy(b200_ctx* ctx);
+/* Bytes of device memory the ctx allocated in b200_ctx_create(). */
+B200_API int64_t b200_ctx_workspace_bytes(const b200_ctx* ctx);
+
+/* Replaces: weight loading ([V22] vllm/model_executor/models/llama.py:437-444 packing map).
+ * The pointer is borrowed for the life of the ctx; `layer` is ignored for EMBED/FINAL_NORM/
+ * LM_HEAD.  rows/cols are checked against the cfg (local TP shard sizes). */
+B200_API int b200_set_weight(b200_ctx* ctx, int32_t layer, int32_t kind, const void* w, int64_t rows, int64_t cols);
+
+/* KV cache, caller-owned, one allocation per K and V:
+ *   [n_layers][n_blocks][n_kv_heads_local][block_size][head_dim] bf16
+ * so one (block, kv head) is a contiguous 32 KiB tile — one bulk-async copy per tile.
+ * Replaces the image-internal cache ([V22] vllm/v1/attention/backends/cpu_attn.py:88-100). */
+B200_API int b200_set_kv_cache(b200_ctx* ctx, void* k_cache, void* v_cache, int64_t n_blocks);
+
+/* cos|sin cache [max_pos][head_dim] bf16 ([V22] rotary_embedding/base.py:58-63,82-92). */
+B200_API int b200_set_rope_cache(b200_ctx* ctx, const void* cos_sin, int64_t max_pos);
+
+/* NCCL communicator for TP (replaces the image's shm all-reduce,
+ * [V22] vllm/distributed/device_communicators/cpu_communicator.py:229-276).
+ * b200_nccl_unique_id writes 128 bytes to host_id (rank 0 calls it and shares the bytes);
+ * b200_nccl_init is collective over the tp_world ranks of the ctx. */
+B200_API int b200_nccl_unique_id(void* host_id128);
+B200_API int b200_nccl_init(b200_ctx* ctx, const void* host_id128);
+
+/* ---- the hot path: one scheduler step ----------------------------
+ * Replaces ModelRunner.execute_model of the image for one batch of token rows
+ * ([V22] vllm/model_executor/models/llama.py:395-434 + sampler.py:235-236).
+ * Row t is one new token: ids[t], positions[t], slot_mapping[t] = block_id*block_size+off,
+ * ctx_lens[t] = tokens it attends to (position+1), row_to_seq[t] = its row of block_table
+ * (NULL: row t).  Decode rows and (chunked) prefill rows have the same form, a prefill chunk
+ * being T rows of one sequence with ctx_lens 1..T (+offset).
+ * logit_rows[n_logit_rows] selects the rows that get lm_head + greedy sampling (NULL: all).
+ * out_token_ids[n_logit_rows] int32; out_logits (nullable) bf16 [n_logit_rows][vocab].
+ * max_ctx_len is a HOST hint >= max(ctx_lens) that sizes the split-KV grid.
+ * With tp_world > 1 it is collective over the ranks. */
+B200_API int b200_decode_step(b200_ctx* ctx, const int32_t* ids, const int32_t* positions,
+                     const int32_t* slot_mapping, const int32_t* block_table, int32_t bt_stride,
+                     const int32_t* row_to_seq, const int32_t* ctx_lens, int32_t n_tokens,
+                     int32_t max_ctx_len, const int32_t* logit_rows, int32_t n_logit_rows,
+                     int32_t* out_token_ids, void* out_logits, void* stream);
+
+/* Same step, driven from PINNED HOST memory: one packed int32 buffer
+ *   [ids | positions | slot_mapping | ctx_lens | row_to_seq | logit_rows](each n_tokens, the
+ *   last n_logit_rows) followed by block_table [n_seqs][bt_stride],
+ * copied H2D, the step, and the sampled ids copied D2H into host_out_token_ids.  The copies
+ * are enqueued on `stream`; the caller synchronises.  This is the call the serving engine
+ * makes every iteration (the `e2e` figure of bench.py). */
+B200_API int b200_decode_step_host(b200_ctx* ctx, const int32_t* host_packed, int32_t n_tokens,
+                          int32_t n_seqs, int32_t bt_stride, int32_t max_ctx_len,
+                          int32_t n_logit_rows, int32_t* host_out_token_ids, void* stream);
+
+/* Graph replay: 1 (default) captures each distinct step shape into a CUDA graph; 0 = eager
+ * launches (the chart's --enforce-eager is accepted by the server but does not force this). */
+B200_API int b200_ctx_set_graphs(b200_ctx* ctx, int32_t enabled);
+/* Number of kernels one step of the given shape launches (bench.py's gpu_launches). */
+B200_API int b200_ctx_last_step_launches(const b200_ctx* ctx);
+/* Per-layer hidden/residual taps for parity tests: after a step, copies the layer's MLP
+ * output and residual rows ([n_tokens][hidden] bf16 each) — only valid with graphs off. */
+B200_API int b200_ctx_set_tap(b200_ctx* ctx, int32_t layer, void* out_hidden, void* out_residual);
+
+/* ---- per-kernel entry points (unit tests, ncu) ------------------------------------------ */
+
+/* y[T][n_out] = x[T][k] . w[n_out][k]^T (+bias), fp32 accumulate, one rounding to bf16.
+ * Replaces sgl-kernel weight_packed_linear / oneDNN matmul of the image
+ * ([V22] vllm/model_executor/layers/utils.py:277-299).  impl: 0 auto, 1 CUDA-core GEMV
+ * (HBM-bound, T small), 2 tcgen05/TMEM weight-streaming GEMM.  Scratch (split-K partials
+ * and tile counters) comes from the caller. */
+B200_API int64_t b200_linear_workspace_bytes(int32_t n_tokens, int32_t n_out, int32_t k);
+B200_API int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y,
+                     int64_t ldy, int32_t n_tokens, int32_t n_out, int32_t k, int32_t impl,
+                     void* workspace, int64_t workspace_bytes, void* stream);
+
+/* (a2) y = rmsnorm(x)*w, or with res != NULL: s=x+res; res=bf16(s); y=rmsnorm(s)*w
+ * ([V22] vllm/ir/ops/layernorm.py:10-21,40-58). y may alias x. */
+B200_API int b200_rmsnorm(const void* x, void* res, const void* w, void* y, int32_t n_tokens,
+                 int32_t hidden, float eps, void* stream);
+
+/* (a1) x[t] = table[ids[t]] ([V22] llama.py:371-375,392-393). */
+B200_API int b200_embed(const int32_t* ids, const void* table, void* out, int32_t n_tokens,
+               int32_t hidden, int32_t vocab, void* stream);
+
+/* (a4+a5) in-place NeoX RoPE on the q and k heads of qkv[T][(hq+2hkv)*128] in bf16
+ * arithmetic, then k,v rows written to the paged cache at slot_mapping[t]
+ * ([V22] rotary_embedding/common.py:160-183; cpu_attn.py:342-362 reshape_and_cache). */
+B200_API int b200_rope_kv_append(void* qkv, const int32_t* positions, const int32_t* slot_mapping,
+                        const void* cos_sin, void* k_cache_layer, void* v_cache_layer,
+                        int32_t n_tokens, int32_t n_q_heads, int32_t n_kv_heads,
+                        int32_t block_size, void* stream);
+
+/* (a6) paged attention, one query row per token, split-KV with LSE merge
+ * ([V22] cpu_attn.py:377-396).  q rows are the first hq*128 columns of a [T][ldq] buffer. */
+B200_API int64_t b200_paged_attn_workspace_bytes(int32_t n_tokens, int32_t n_q_heads, int32_t max_ctx_len,
+                                        int32_t block_size);
+B200_API int b200_paged_attn_decode(const void* q, int64_t ldq, const void* k_cache_layer,
+                           const void* v_cache_layer, const int32_t* block_table, int32_t bt_stride,
+                           const int32_t* row_to_seq, const int32_t* ctx_lens, void* out,
+                           int64_t ldo, int32_t n_tokens, int32_t n_q_heads, int32_t n_kv_heads,
+                           int32_t block_size, int32_t max_ctx_len, float scale, void* workspace,
+                           int64_t workspace_bytes, void* stream);
+
+/* (a8) out[T][I] = bf16(bf16(silu(g))*u), gu = [T][2I] gate|up ([V22] activation.py:137-141). */
+B200_API int b200_silu_mul(const void* gu, void* out, int32_t n_tokens, int32_t intermediate, void* stream);
+
+/* (a10) greedy: fp32 argmax of bf16 logits, ties -> lowest index ([V22] sampler.py:90-91,235-236).
+ * Also writes the winning value (fp32) when out_max != NULL (used by the TP (max,idx) reduce). */
+B200_API int b200_argmax(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, int32_t index_offset,
+                int32_t* out_ids, float* out_max, void* stream);
+
+/* (a11) sum all-reduce of a bf16 buffer over the ctx's TP communicator. */
+B200_API int b200_allreduce_bf16(b200_ctx* ctx, void* buf, int64_t count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_DECODE_H */

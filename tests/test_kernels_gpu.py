@@ -1,0 +1,241 @@
+"""GPU parity, kernel by kernel, through the C-ABI, against oracle/decode_oracle.py.
+Tolerances: bit-exact for integer/index/copy work (embed, KV append, argmax) and for the bf16
+elementwise arithmetic of RoPE; for fp32-accumulated ops the only freedom is summation order, so
+the bar is <= 1 bf16 ulp on a small fraction of elements (stated per test)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import pkg
+from oracle import decode_oracle as O
+
+pytestmark = pytest.mark.gpu
+BF = torch.bfloat16
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return pkg("_abi").lib()
+
+
+@pytest.fixture(scope="module")
+def abi():
+    return pkg("_abi")
+
+
+def dev(t):
+    return t.cuda().contiguous()
+
+
+def ulp_close(got, want, max_ulp=1, max_frac=0.01, atol_small=2 ** -9):
+    """bf16 tensors: every element within max_ulp bf16 ulps of `want` (or atol_small near zero),
+    at most max_frac of them different at all."""
+    g, w = got.float().cpu(), want.float().cpu()
+    diff = (g - w).abs()
+    ulp = torch.maximum(w.abs(), torch.tensor(2.0 ** -126)).log2().floor().exp2() * 2.0 ** -7
+    bad = diff > torch.maximum(max_ulp * ulp, torch.tensor(atol_small))
+    assert not bad.any(), f"{int(bad.sum())} elements beyond {max_ulp} ulp; max diff {diff.max():.4g}"
+    frac = (diff > 0).float().mean().item()
+    assert frac <= max_frac, f"{frac:.4f} of elements differ (allowed {max_frac})"
+
+
+def sync_check(abi, rc):
+    abi.check(rc)
+    torch.cuda.synchronize()
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,n_out,k,bias", [(1, 512, 512, False), (1, 6144, 4096, False), (2, 1536, 640, True),
+                                             (3, 1000, 1024, True), (4, 4096, 14336, False), (7, 264, 2048, False),
+                                             (1, 2, 8, False), (9, 128256 // 8, 512, False)])
+def test_linear_gemv(lib, abi, T, n_out, k, bias):
+    g = torch.Generator().manual_seed(T * 1000 + n_out + k)
+    x = torch.randn(T, k, generator=g).to(BF)
+    w = (0.05 * torch.randn(n_out, k, generator=g)).to(BF)
+    b = torch.randn(n_out, generator=g).to(BF) if bias else None
+    want = O.linear(x, w, b)
+    xd, wd, bd = dev(x), dev(w), (dev(b) if bias else None)
+    y = torch.zeros(T, n_out, dtype=BF, device="cuda")
+    sync_check(abi, lib.b200_linear_bf16(xd.data_ptr(), k, wd.data_ptr(), abi.ptr(bd), y.data_ptr(), n_out, T, n_out, k,
+                                         1, None, 0, None))
+    ulp_close(y, want, max_ulp=1, max_frac=0.02)
+
+
+def test_linear_is_linear_at_full_width(lib, abi):
+    """Size-independent property at the 8B down-proj shape: W(a*x) == a*W(x) for a power of two
+    (exact in bf16/fp32), and column-sliced leading dimension works."""
+    k, n_out = 14336, 4096
+    g = torch.Generator().manual_seed(1)
+    w = dev((0.02 * torch.randn(n_out, k, generator=g)).to(BF))
+    x = dev(torch.randn(2, k + 64, generator=g).to(BF))        # ldx = k + 64
+    y1 = torch.empty(2, n_out, dtype=BF, device="cuda")
+    y2 = torch.empty_like(y1)
+    sync_check(abi, lib.b200_linear_bf16(x.data_ptr(), k + 64, w.data_ptr(), None, y1.data_ptr(), n_out, 2, n_out, k, 1, None, 0, None))
+    x4 = (x.float() * 4).to(BF)
+    sync_check(abi, lib.b200_linear_bf16(x4.data_ptr(), k + 64, w.data_ptr(), None, y2.data_ptr(), n_out, 2, n_out, k, 1, None, 0, None))
+    assert torch.equal((y1.float() * 4).to(BF), y2)
+    ulp_close(y1, O.linear(x[:, :k].cpu(), w.cpu()), max_frac=0.02)
+
+
+@pytest.mark.parametrize("T,h", [(1, 512), (5, 4096), (64, 5120), (3, 8192), (2, 640)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_rmsnorm(lib, abi, T, h, with_res):
+    g = torch.Generator().manual_seed(h + T)
+    x = torch.randn(T, h, generator=g).to(BF)
+    r = torch.randn(T, h, generator=g).to(BF)
+    w = (1 + 0.1 * torch.randn(h, generator=g)).to(BF)
+    xd, rd, wd = dev(x), dev(r), dev(w)
+    y = torch.empty(T, h, dtype=BF, device="cuda")
+    if with_res:
+        want, want_res = O.add_rms_norm(x, r, w, 1e-5)
+        sync_check(abi, lib.b200_rmsnorm(xd.data_ptr(), rd.data_ptr(), wd.data_ptr(), y.data_ptr(), T, h, 1e-5, None))
+        assert torch.equal(rd.cpu(), want_res), "residual must be bit-exact (one fp32 add, one rounding)"
+    else:
+        want = O.rms_norm(x, w, 1e-5)
+        sync_check(abi, lib.b200_rmsnorm(xd.data_ptr(), None, wd.data_ptr(), y.data_ptr(), T, h, 1e-5, None))
+    # the variance's summation order moves rsqrt by an fp32 ulp: rare 1-ulp bf16 flips at each rounding
+    ulp_close(y, want, max_ulp=2, max_frac=0.01)
+
+
+def test_embed_exact(lib, abi):
+    tab = torch.randn(1000, 512).to(BF)
+    ids = torch.tensor([0, 999, 5, 5, 17], dtype=torch.int32)
+    out = torch.empty(5, 512, dtype=BF, device="cuda")
+    sync_check(abi, lib.b200_embed(dev(ids).data_ptr(), dev(tab).data_ptr(), out.data_ptr(), 5, 512, 1000, None))
+    assert torch.equal(out.cpu(), tab[ids.long()])
+
+
+@pytest.mark.parametrize("cfgname", ["tiny", "tiny-qwen", "tiny-g8"])
+def test_rope_kv_append_exact(lib, abi, cfgname):
+    cfg = O.CONFIGS[cfgname]
+    hq, hkv, d, bs, nb = cfg.n_q_heads, cfg.n_kv_heads, 128, 128, 5
+    T = 7
+    g = torch.Generator().manual_seed(3)
+    qkv = torch.randn(T, (hq + 2 * hkv) * d, generator=g).to(BF)
+    pos = torch.tensor([0, 1, 127, 128, 129, 300, 511], dtype=torch.int32)
+    blocks = [3, 0, 4, 1]
+    slots = torch.tensor([blocks[p // bs] * bs + p % bs for p in pos.tolist()], dtype=torch.int32)
+    slots[5] = -1                                              # padding row: nothing written
+    cs = O.cos_sin_cache(cfg, 1024)
+    kc = torch.zeros(nb, hkv, bs, d, dtype=BF, device="cuda")
+    vc = torch.zeros_like(kc)
+    qd = dev(qkv)
+    sync_check(abi, lib.b200_rope_kv_append(qd.data_ptr(), dev(pos).data_ptr(), dev(slots).data_ptr(), dev(cs).data_ptr(),
+                                            kc.data_ptr(), vc.data_ptr(), T, hq, hkv, bs, None))
+    q = qkv[:, :hq * d].view(T, hq, d)
+    k = qkv[:, hq * d:(hq + hkv) * d].view(T, hkv, d)
+    v = qkv[:, (hq + hkv) * d:].view(T, hkv, d)
+    cos, sin = cs[pos.long(), :64], cs[pos.long(), 64:]
+    qr, kr = O.rope_apply(q, cos, sin), O.rope_apply(k, cos, sin)
+    assert torch.equal(qd.cpu()[:, :hq * d].view(T, hq, d), qr), "RoPE(q) must be bit-exact (bf16 arithmetic)"
+    want_k = torch.zeros(nb, hkv, bs, d, dtype=BF)
+    want_v = torch.zeros_like(want_k)
+    for t in range(T):
+        s = int(slots[t])
+        if s >= 0:
+            want_k[s // bs, :, s % bs] = kr[t]
+            want_v[s // bs, :, s % bs] = v[t]
+    assert torch.equal(kc.cpu(), want_k) and torch.equal(vc.cpu(), want_v)
+
+
+@pytest.mark.parametrize("T,I", [(1, 1024), (3, 14336), (64, 1536)])
+def test_silu_mul(lib, abi, T, I):
+    gu = (2 * torch.randn(T, 2 * I, generator=torch.Generator().manual_seed(I))).to(BF)
+    out = torch.empty(T, I, dtype=BF, device="cuda")
+    sync_check(abi, lib.b200_silu_mul(dev(gu).data_ptr(), out.data_ptr(), T, I, None))
+    ulp_close(out, O.silu_mul(gu), max_ulp=1, max_frac=0.005)   # expf vs the host libm: rare 1-ulp flips
+
+
+def test_argmax_exact_with_ties(lib, abi):
+    V = 128256
+    lg = torch.randn(6, V, generator=torch.Generator().manual_seed(9)).to(BF)
+    lg[1, 77] = 9.0; lg[1, 100000] = 9.0                       # tie -> lowest index
+    lg[2, V - 1] = 50.0                                        # last element
+    lg[3, :] = -1.0                                            # all equal -> 0
+    lg[4, 0] = 60.0
+    ids = torch.empty(6, dtype=torch.int32, device="cuda")
+    mx = torch.empty(6, dtype=torch.float32, device="cuda")
+    sync_check(abi, lib.b200_argmax(dev(lg).data_ptr(), V, 6, V, 0, ids.data_ptr(), mx.data_ptr(), None))
+    assert ids.cpu().tolist() == O.greedy(lg).tolist()
+    assert torch.equal(mx.cpu(), lg.float().max(-1).values)
+    # ragged vocab (not a multiple of 8 handled by the tail loop) and an index offset
+    lg2 = lg[:, :1003].contiguous()
+    ld = 1008
+    pad = torch.full((6, ld), -100.0, dtype=BF); pad[:, :1003] = lg2
+    sync_check(abi, lib.b200_argmax(dev(pad).data_ptr(), ld, 6, 1003, 5000, ids.data_ptr(), None, None))
+    assert ids.cpu().tolist() == (O.greedy(lg2) + 5000).tolist()
+
+
+# ---------------------------------------------------------------------------------------------
+def run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv, max_ctx_hint=None, seed=0):
+    """q [T,hq,128]; K,V per row: list of [n,hkv,128] -> scatter into a shuffled paged cache."""
+    T, bs = q.shape[0], 128
+    nblk = [(n + bs - 1) // bs for n in ctx_lens]
+    total = sum(nblk) + 3
+    perm = torch.randperm(total, generator=torch.Generator().manual_seed(seed)).tolist()
+    kc = torch.full((total, hkv, bs, 128), float("nan"), dtype=BF)   # unwritten slots are NaN on purpose
+    vc = torch.full_like(kc, float("nan"))
+    stride = max(nblk)
+    bt = torch.zeros(T, stride, dtype=torch.int32)
+    it = iter(perm)
+    for t in range(T):
+        for j in range(nblk[t]):
+            b = next(it)
+            bt[t, j] = b
+            n = min(bs, ctx_lens[t] - j * bs)
+            kc[b, :, :n] = K[t][j * bs:j * bs + n].permute(1, 0, 2)
+            vc[b, :, :n] = V[t][j * bs:j * bs + n].permute(1, 0, 2)
+    max_ctx = max_ctx_hint or max(ctx_lens)
+    ws_bytes = lib.b200_paged_attn_workspace_bytes(T, hq, max_ctx, bs)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
+    out = torch.empty(T, hq * 128, dtype=BF, device="cuda")
+    qd = dev(q.reshape(T, hq * 128))
+    sync_check(abi, lib.b200_paged_attn_decode(qd.data_ptr(), hq * 128, dev(kc).data_ptr(), dev(vc).data_ptr(),
+                                               dev(bt).data_ptr(), stride, None, dev(torch.tensor(ctx_lens, dtype=torch.int32)).data_ptr(),
+                                               out.data_ptr(), hq * 128, T, hq, hkv, bs, max_ctx, 128 ** -0.5,
+                                               ws.data_ptr(), ws_bytes, None))
+    return out.cpu().view(T, hq, 128)
+
+
+@pytest.mark.parametrize("hq,hkv", [(4, 1), (5, 1), (16, 2), (8, 8), (4, 2)])
+@pytest.mark.parametrize("ctx_lens", [[1], [63, 64, 65], [128, 129, 1], [1000, 17, 4097]])
+def test_paged_attention_vs_oracle(lib, abi, hq, hkv, ctx_lens):
+    g = torch.Generator().manual_seed(hq * 100 + hkv + len(ctx_lens))
+    T = len(ctx_lens)
+    q = torch.randn(T, hq, 128, generator=g).to(BF)
+    K = [torch.randn(n, hkv, 128, generator=g).to(BF) for n in ctx_lens]
+    V = [torch.randn(n, hkv, 128, generator=g).to(BF) for n in ctx_lens]
+    got = run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv)
+    want = torch.stack([O.attend(q[t], K[t], V[t], ctx_lens[t], 128 ** -0.5) for t in range(T)])
+    assert torch.isfinite(got.float()).all()
+    ulp_close(got, want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
+
+
+def test_paged_attention_split_invariance_long_context(lib, abi):
+    """Config-3 scale (ctx 32768, G=4): the split-KV result must not depend on the split plan —
+    compare the plan for max_ctx=32768 with a larger hint (different split count) and the oracle."""
+    hq, hkv, n = 4, 1, 32768
+    g = torch.Generator().manual_seed(5)
+    q = torch.randn(1, hq, 128, generator=g).to(BF)
+    K = [torch.randn(n, hkv, 128, generator=g).to(BF)]
+    V = [torch.randn(n, hkv, 128, generator=g).to(BF)]
+    a = run_attn(lib, abi, q, K, V, [n], hq, hkv)
+    b = run_attn(lib, abi, q, K, V, [n], hq, hkv, max_ctx_hint=65536, seed=1)
+    want = O.attend(q[0], K[0], V[0], n, 128 ** -0.5)[None]
+    ulp_close(a, want, max_ulp=2, max_frac=0.2, atol_small=2 ** -9)
+    ulp_close(b, a, max_ulp=1, max_frac=0.05, atol_small=2 ** -9)
+
+
+def test_empty_inputs_are_noops(lib, abi):
+    assert lib.b200_silu_mul(1, 1, 0, 1024, None) == 0
+    assert lib.b200_rmsnorm(1, None, 1, 1, 0, 512, 1e-5, None) == 0
+    assert lib.b200_embed(1, 1, 1, 0, 512, 10, None) == 0
+    assert lib.b200_argmax(1, 8, 0, 8, 0, 1, None, None) == 0
+    torch.cuda.synchronize()
+
+
+def test_unsupported_shapes_error(lib, abi):
+    x = torch.zeros(1, 12, dtype=BF, device="cuda")
+    assert lib.b200_linear_bf16(x.data_ptr(), 12, x.data_ptr(), None, x.data_ptr(), 1, 1, 1, 12, 1, None, 0, None) == -3
+    assert b"multiples of 8" in lib.b200_last_error()
+    assert lib.b200_rmsnorm(x.data_ptr(), None, x.data_ptr(), x.data_ptr(), 1, 16384, 1e-5, None) == -3

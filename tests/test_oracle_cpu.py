@@ -1,0 +1,79 @@
+"""CPU: the oracle against its frozen golden vectors (and through them the HF stand-in), the
+product-side config/rope restatement against the oracle's, and size-independent properties."""
+import ast
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import pkg
+from oracle import decode_oracle as O
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny-qwen", "tiny-g8"])
+def test_oracle_reproduces_golden(name, golden_dir):
+    g = np.load(f"{golden_dir}/{name}.npz")
+    cfg = O.CONFIGS[name]
+    assert ast.literal_eval(str(g["cfg"])) == cfg.to_dict()
+    w = O.make_weights(cfg, seed=int(g["seed"]), norm_jitter=float(g["norm_jitter"]))
+    assert O.weights_digest(w) == str(g["digest"]), "torch CPU RNG stream drifted: regenerate fixtures"
+    om = O.OracleModel(cfg, w, capacity=256)
+    prompt = g["prompt"].tolist()
+    toks, logits = om.generate(prompt, len(g["tokens"]), keep_logits=True)
+    assert toks == g["tokens"].tolist()
+    np.testing.assert_array_equal(logits.numpy(), g["gen_logits"])
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny-qwen", "tiny-g8"])
+def test_golden_within_north_star_tolerance_of_hf(name, golden_dir):
+    """The frozen HF (transformers 5.5.0, CPU bf16) logits bound the oracle: softmax max abs
+    error <= 2e-2 (north_star); greedy picks agree wherever the oracle's margin is not tiny."""
+    g = np.load(f"{golden_dir}/{name}.npz")
+    a, b = torch.from_numpy(g["tf_logits"]), torch.from_numpy(g["hf_logits"])
+    assert (torch.softmax(a, -1) - torch.softmax(b, -1)).abs().max() <= 2e-2
+    margin = O.top2_margin(a)
+    dis = a.argmax(-1) != b.argmax(-1)
+    assert (margin[dis] < 0.07).all(), "greedy disagreement outside near-ties"
+
+
+def test_chunked_prefill_equals_token_at_a_time():
+    cfg = O.CONFIGS["tiny"]
+    om = O.OracleModel(cfg, O.make_weights(cfg), capacity=64)
+    ids = O.make_prompt(cfg, 3, 20)
+    a = om.forward(om.new_seq(), ids)
+    st = om.new_seq()
+    b = torch.cat([om.forward(st, ids[:7]), om.forward(st, ids[7:8]), om.forward(st, ids[8:])])
+    # not bit-equal: the fp32 GEMM's summation order depends on the row count (as it does in the
+    # reference image); the difference must stay at bf16-ulp level
+    assert (a.float() - b.float()).abs().max() <= 2 ** -5
+    assert (torch.softmax(a.float(), -1) - torch.softmax(b.float(), -1)).abs().max() <= 1e-3
+
+
+def test_product_config_and_rope_match_oracle():
+    C = pkg("config")
+    for oname, pname in (("llama-3.1-8b", "llama-3.1-8b"), ("qwen2-32b", "qwen2-32b"), ("llama-3.1-70b", "llama-3.1-70b"),
+                         ("tiny", "tiny")):
+        o, p = O.CONFIGS[oname].to_dict(), C.get_config(pname).to_dict()
+        o.pop("name"), p.pop("name")
+        assert o == p
+    # SURVEY §8 shape table
+    assert C.get_config("llama-3.1-8b").decode_params() == 7_504_658_432
+    assert C.get_config("qwen2-32b").decode_params() == 31_984_189_440
+    assert C.get_config("llama-3.1-70b").decode_params() == 69_501_714_432
+    assert C.get_config("llama-3.1-8b").kv_bytes_per_token() == 131072
+    for name in ("tiny", "qwen2-32b"):
+        assert torch.equal(C.rope_cos_sin(C.get_config(name), 4096), O.cos_sin_cache(O.CONFIGS[name], 4096))
+
+
+def test_rounding_points():
+    """R1/R5: the bf16 intermediate roundings are really there (a 'better' fp32 path differs)."""
+    torch.manual_seed(0)
+    x = torch.randn(4, 512).to(torch.bfloat16)
+    w = (1 + 0.1 * torch.randn(512)).to(torch.bfloat16)
+    y = O.rms_norm(x, w, 1e-5)
+    xf = x.float()
+    better = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5) * w.float()).to(torch.bfloat16)
+    assert not torch.equal(y, better)
+    y2, r2 = O.add_rms_norm(x, x, w, 1e-5)
+    assert torch.equal(r2, (x.float() * 2).to(torch.bfloat16))
+    assert O.greedy(torch.tensor([[1.0, 3.0, 3.0, 2.0]]).to(torch.bfloat16)).item() == 1  # ties -> lowest
