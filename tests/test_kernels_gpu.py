@@ -23,8 +23,22 @@ def abi():
     return pkg("_abi")
 
 
+_keep = []
+
+
 def dev(t):
-    return t.cuda().contiguous()
+    """Upload and keep alive until the test ends (a temporary would be freed — and its memory
+    reused — before the asynchronous kernel reads it)."""
+    d = t.cuda().contiguous()
+    _keep.append(d)
+    return d
+
+
+@pytest.fixture(autouse=True)
+def _release_uploads():
+    yield
+    torch.cuda.synchronize()
+    _keep.clear()
 
 
 def ulp_close(got, want, max_ulp=1, max_frac=0.01, atol_small=2 ** -9):
