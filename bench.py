@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""bench.py — the decode hot path on B200, next to the reference's CPU path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl b200|reference]
+
+A "step" is one scheduler iteration of the decode path over one batch of sequences (every
+sequence emits one token).  Default workload = BASELINE.json configs[1]: Llama-3.1-8B-Instruct
+bf16, continuous batch of 64 requests, 512-token prompts / 256 output tokens, random-init weights,
+synthetic prompt KV (prefill flops are not part of the decode metric).  8B fits one
+GPU and does not shard (SURVEY.md §8e "replicas only"), so --gpus N runs N independent replicas
+(weak scaling, no data-path collective); `--workload llama70b-tp` is the tensor-parallel path.
+
+Printed line (rank 0): metric/value/unit per the driver contract plus
+  roofline      dominant kernel's achieved HBM GB/s (CUDA events, live) vs MEASURED_PEAKS.json
+  cpu_baseline  the oracle (CPU port of the reference image's algorithm) timed on this host
+  e2e           same metric through the engine API with pinned HOST buffers (H2D + step + D2H)
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "enterprise-inference_b200"
+
+WORKLOADS = {
+    # name: (model, batch, ctx_start, description)
+    "llama8b-bs64": ("llama-3.1-8b", 64, 512,
+                     "Llama-3.1-8B-Instruct bf16 decode, continuous batch of 64, 512-in/256-out (BASELINE configs[1])"),
+    "llama8b-bs1": ("llama-3.1-8b", 1, 128, "Llama-3.1-8B-Instruct bf16 decode, batch 1, 128-in/128-out (configs[0])"),
+    "llama8b-ctx32k": ("llama-3.1-8b", 8, 32768 - 64, "Llama-3.1-8B-Instruct bf16 decode, batch 8 at 32k context (configs[2])"),
+    "llama70b-tp": ("llama-3.1-70b", 64, 512, "Llama-3.1-70B-Instruct bf16 decode, TP=N, batch 64 (configs[4])"),
+    "qwen32b-tp": ("qwen2-32b", 32, 512, "DeepSeek-R1-Distill-Qwen-32B bf16 decode, TP=N, batch 32 (configs[3])"),
+    "tiny": ("tiny", 4, 16, "tiny config (self-test)"),
+}
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append((time.monotonic(), ln.strip()))
+
+    def stop(self, t0: float, t1: float):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [l for (t, l) in self.lines if t0 - 0.05 <= t <= t1 + 0.15] or [l for (_, l) in self.lines]
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in rows:
+            f = [x.strip() for x in l.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+                for n, v in zip(names, f[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_decode_baseline(model: str, batch: int, ctx: int, steps: int, warmup: int, budget_s: float):
+    """Times the CPU oracle (oracle/decode_oracle.py, the port of the algorithm the reference's
+    vLLM-CPU image runs; the image itself is unavailable: no network, no container runtime) for
+    `steps` decode steps of the workload.  Returns (tok_s, ms_per_step, steps_run, info)."""
+    import torch
+    from oracle import decode_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = O.CONFIGS[model]
+    g = torch.Generator().manual_seed(1234)
+
+    def rnd(*shape):
+        return torch.empty(shape, dtype=torch.bfloat16).normal_(0.0, 0.02, generator=g)
+
+    # One layer's random weights aliased across all layers: bounds host RAM and init time; a layer
+    # (436 MB for 8B) is far larger than the host LLC, so every layer still streams from DRAM.
+    layer = {"input_layernorm.weight": torch.ones(cfg.hidden, dtype=torch.bfloat16),
+             "post_attention_layernorm.weight": torch.ones(cfg.hidden, dtype=torch.bfloat16),
+             "self_attn.q_proj.weight": rnd(cfg.q_size, cfg.hidden), "self_attn.k_proj.weight": rnd(cfg.kv_size, cfg.hidden),
+             "self_attn.v_proj.weight": rnd(cfg.kv_size, cfg.hidden), "self_attn.o_proj.weight": rnd(cfg.hidden, cfg.q_size),
+             "mlp.gate_proj.weight": rnd(cfg.intermediate, cfg.hidden), "mlp.up_proj.weight": rnd(cfg.intermediate, cfg.hidden),
+             "mlp.down_proj.weight": rnd(cfg.hidden, cfg.intermediate)}
+    if cfg.qkv_bias:
+        for x, n in (("q", cfg.q_size), ("k", cfg.kv_size), ("v", cfg.kv_size)):
+            layer[f"self_attn.{x}_proj.bias"] = rnd(n)
+    w = {"model.embed_tokens.weight": rnd(cfg.vocab, cfg.hidden), "model.norm.weight": torch.ones(cfg.hidden, dtype=torch.bfloat16),
+         "lm_head.weight": rnd(cfg.vocab, cfg.hidden)}
+    for l in range(cfg.n_layers):
+        for k, v in layer.items():
+            w[f"model.layers.{l}.{k}"] = v
+    cap = ctx + steps + warmup + 2
+    om = O.OracleModel(cfg, w, capacity=cap)
+    # packed qkv / gate_up copies are per layer in OracleModel: alias them too
+    for L in om.layers[1:]:
+        L.update(om.layers[0])
+    states = []
+    for b in range(batch):
+        st = O.SeqState()
+        kv = torch.zeros(cap, cfg.n_kv_heads, cfg.head_dim, dtype=torch.bfloat16)
+        kv[:ctx].normal_(0.0, 0.5, generator=g)
+        st.K = [kv] * cfg.n_layers           # synthetic prompt KV, shared storage across layers
+        st.V = [kv] * cfg.n_layers
+        st.n = ctx
+        states.append(st)
+    toks = torch.randint(0, cfg.vocab, (batch,), generator=g).tolist()
+    times, t_begin = [], time.monotonic()
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            t0 = time.monotonic()
+            logits = om.step_batch(states, toks, fast_linear=True)
+            toks = O.greedy(logits).tolist()
+            dt = time.monotonic() - t0
+            if i >= warmup:
+                times.append(dt)
+            done = i + 1
+            if i + 1 >= min(warmup, 1) + 1 and (time.monotonic() - t_begin) + dt > budget_s:
+                break
+    if not times:
+        times = [dt]
+    ms = 1e3 * sum(times) / len(times)
+    info = {"cores": cores, "kind": "port",
+            "sample": (f"{len(times)} decode step(s) of {batch} seqs at ctx {ctx} (+{max(done - len(times), 0)} warm-up), oracle "
+                       f"step_batch with bf16 oneDNN linears, torch {torch.__version__}, {cores} threads; one layer's "
+                       "random weights aliased across layers (layer >> LLC); reference image vllm-cpu v0.10.2 "
+                       "unavailable on this box")}
+    return batch / ms * 1e3, ms, len(times), info
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    model, batch, ctx0, desc = WORKLOADS[args.workload]
+    tok_s, ms, steps_run, info = cpu_decode_baseline(model, batch, ctx0 + 128 if args.workload == "llama8b-bs64" else ctx0,
+                                                     args.steps, args.warmup, budget_s=200.0)
+    line = {"impl": "reference", "metric": "output tok/s (decode)", "value": round(tok_s, 3), "unit": "tok/s",
+            "n_gpus": args.gpus, "steps": steps_run, "warmup": args.warmup, "ms_per_step": round(ms, 2),
+            "p50_tpot_ms": round(ms, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic (random-init weights, synthetic prompt KV)",
+            "config": {"workload": desc, "batch": batch},
+            "cpu_baseline": {"value": round(tok_s, 3), "unit": "tok/s", **info},
+            "e2e": {"value": round(tok_s, 3), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# the B200 arm
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    Cfg = importlib.import_module(PKG + ".config")
+    R = importlib.import_module(PKG + ".runner")
+    E = importlib.import_module(PKG + ".engine")
+    abi = importlib.import_module(PKG + "._abi")
+    lib = abi.lib()
+
+    model, B, ctx0, desc = WORKLOADS[args.workload]
+    tp = args.workload.endswith("-tp")
+    cfg = Cfg.get_config(model)
+    K, W = args.steps, args.warmup
+    total_steps = 2 * (K + W) + 8
+    max_len = ctx0 + total_steps + 1
+    bs = 128
+    blocks_per_seq = (max_len + bs - 1) // bs
+    n_blocks = B * blocks_per_seq + 2
+    r = R.ModelRunner(cfg, max_tokens=max(B, 8), max_model_len=blocks_per_seq * bs, n_blocks=n_blocks,
+                      tp_rank=rank if tp else 0, tp_world=world if tp else 1)
+    r.init_random_weights(seed=1234)
+    if tp:
+        r.init_tp()
+    gk = torch.Generator(device="cuda").manual_seed(99 + rank)
+    r.k_cache.normal_(0.0, 0.5, generator=gk)   # synthetic prompt KV
+    r.v_cache.normal_(0.0, 0.5, generator=gk)
+    hbm_peak, peak_src = peaks()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- (1) device-resident: inputs already in HBM, the sampled token feeds the next step ----
+    bt = torch.arange(B * blocks_per_seq, dtype=torch.int32, device="cuda").view(B, blocks_per_seq).contiguous()
+    ids = torch.randint(0, cfg.vocab, (B,), dtype=torch.int32, device="cuda")
+    pos = torch.full((B,), ctx0 - 1, dtype=torch.int32, device="cuda")
+    slots = (bt[:, (ctx0 - 1) // bs] * bs + (ctx0 - 1) % bs).to(torch.int32).contiguous()
+    ctxl = (pos + 1).contiguous()
+    out = torch.empty(B, dtype=torch.int32, device="cuda")
+    stream = r.stream
+    step_no = [0]
+
+    def dev_step():
+        max_ctx = ctx0 + step_no[0] + 1
+        r.step_device(ids, pos, slots, bt, ctxl, max_ctx, out_tokens=out, stream=stream)
+        abi.check(lib.b200_advance_decode_rows(ids.data_ptr(), pos.data_ptr(), slots.data_ptr(), ctxl.data_ptr(),
+                                               bt.data_ptr(), blocks_per_seq, None, out.data_ptr(), B, bs,
+                                               stream.cuda_stream))
+        step_no[0] += 1
+
+    with torch.cuda.stream(stream):
+        for _ in range(W):
+            dev_step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    t_wall0 = time.monotonic()
+    with torch.cuda.stream(stream):
+        evs[0].record(stream)
+        for i in range(K):
+            dev_step()
+            evs[i + 1].record(stream)
+    barrier()
+    t_wall1 = time.monotonic()
+    clocks = sampler.stop(t_wall0, t_wall1)
+    total_ms = max_over_ranks(evs[0].elapsed_time(evs[K]))
+    per_step = [evs[i].elapsed_time(evs[i + 1]) for i in range(K)]
+    launches_per_step = r.last_step_launches() + 1
+    n_eff = 1 if tp else world
+    value = n_eff * B * K / total_ms * 1e3
+    mean_ctx = ctx0 + W + K / 2.0
+    step_bytes = (cfg.weight_bytes() + B * mean_ctx * cfg.kv_bytes_per_token()) / (world if tp else 1)
+    step_gbs = step_bytes / (total_ms / K) / 1e6
+
+    # ---- (2) roofline of the dominant kernel: the gate_up projection (31% of the weight bytes), ----
+    # launched back to back over the 32 layers' distinct weights (7.5 GB >> L2), CUDA events on its stream
+    gu = [t for t in r._weights if t.dim() == 2 and t.shape[0] == 2 * r.inter and t.shape[1] == cfg.hidden]
+    x = torch.randn(B, cfg.hidden, device="cuda", dtype=torch.bfloat16)
+    y = torch.empty(B, 2 * r.inter, device="cuda", dtype=torch.bfloat16)
+    wsb = int(lib.b200_linear_workspace_bytes(B, 2 * r.inter, cfg.hidden))
+    wsp = torch.empty(max(wsb, 16), dtype=torch.uint8, device="cuda")
+    reps = max(1, 64 // len(gu))
+
+    def gu_pass():
+        for _ in range(reps):
+            for wt in gu:
+                abi.check(lib.b200_linear_bf16(x.data_ptr(), cfg.hidden, wt.data_ptr(), None, y.data_ptr(), 2 * r.inter, B,
+                                               2 * r.inter, cfg.hidden, 0, wsp.data_ptr(), wsb, stream.cuda_stream))
+    with torch.cuda.stream(stream):
+        gu_pass()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        gu_pass()
+        e1.record(stream)
+    barrier()
+    k_ms = e0.elapsed_time(e1) / (reps * len(gu))
+    k_bytes = 2 * r.inter * cfg.hidden * 2
+    achieved = k_bytes / k_ms / 1e6
+    roofline = {"bound": "hbm", "kernel": "linear gate_up [2I x h] weight stream, T=%d" % B, "achieved": round(achieved, 1),
+                "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": None,
+                "peak_source": peak_src, "bytes_per_launch": k_bytes, "us_per_launch": round(k_ms * 1e3, 2),
+                "whole_step": {"bytes": int(step_bytes), "GBps": round(step_gbs, 1), "frac": round(step_gbs / hbm_peak, 4)}}
+
+    # ---- (3) end to end through the engine API: host scheduling, pinned H2D, step, D2H ----
+    eng = E.LLMEngine(r, max_num_batched_tokens=max(B, 8), max_num_seqs=max(B, 8), max_model_len=blocks_per_seq * bs)
+    gp = torch.Generator().manual_seed(1000 + rank)
+    for i in range(B):
+        prompt = torch.randint(0, cfg.vocab, (ctx0,), generator=gp).tolist()
+        req = E.Request(f"r{i}", prompt, max_tokens=K + W + 4, ignore_eos=True)
+        eng.add_prefilled(req, ctx0 - 1)   # prompt KV is the synthetic cache content
+    for _ in range(W):
+        eng.step()
+    barrier()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record(stream)
+    for _ in range(K):
+        eng.step()
+    a1.record(stream)
+    barrier()
+    e2e_ms = max_over_ranks(a0.elapsed_time(a1))
+    e2e_val = n_eff * B * K / e2e_ms * 1e3
+    e2e = {"value": round(e2e_val, 1), "unit": "tok/s", "h2d_bytes_per_step": int(r.h2d_bytes_last),
+           "d2h_bytes_per_step": int(r.d2h_bytes_last), "ms_per_step": round(e2e_ms / K, 4)}
+
+    # ---- (4) the CPU port timed on this host (rank 0, N=1 only) ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            tok_s, ms, n, info = cpu_decode_baseline(model, B, int(mean_ctx), steps=2, warmup=1, budget_s=30.0)
+            cpu = {"value": round(tok_s, 3), "unit": "tok/s", "ms_per_step": round(ms, 1), **info}
+        except Exception as ex:  # host RAM etc.
+            cpu = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "port", "sample": f"not run: {ex}"}
+
+    if rank == 0:
+        line = {"metric": "output tok/s (decode)", "value": round(value, 1), "unit": "tok/s", "n_gpus": world,
+                "steps": K, "warmup": W, "ms_per_step": round(total_ms / K, 4),
+                "p50_tpot_ms": round(statistics.median(per_step), 4), "higher_is_better": True,
+                "scaling": "strong" if tp else "weak", "vs_baseline": None, "dtype": "bf16",
+                "data": "synthetic (random-init weights N(0,0.02), synthetic prompt KV, greedy, ignore_eos)",
+                "config": {"workload": desc, "batch_per_gpu": B, "ctx_start": ctx0, "mean_ctx": mean_ctx,
+                           "parallelism": (f"tp{world}" if tp else f"replicas x{world}"), "kv_block": bs,
+                           "l2": "inputs larger than L2: %.1f GB of weights+KV streamed per step" % (step_bytes / 1e9)},
+                "clocks": clocks, "gpu_launches": launches_per_step * K, "launches_per_step": launches_per_step,
+                "roofline": roofline, "e2e": e2e}
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    r.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="llama8b-bs64", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -55,6 +55,7 @@ SIGNATURES = {
                                          _i32, _i32, _f32, _vp, _i64, _vp]),
     "b200_silu_mul": (C.c_int, [_vp, _vp, _i32, _i32, _vp]),
     "b200_argmax": (C.c_int, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "b200_advance_decode_rows": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _vp]),
     "b200_allreduce_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
 }
 

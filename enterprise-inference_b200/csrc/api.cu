@@ -442,6 +442,15 @@ extern "C" int b200_argmax(const void* logits, int64_t ld, int32_t rows, int32_t
                      (cudaStream_t)stream);
 }
 
+extern "C" int b200_advance_decode_rows(int32_t* ids, int32_t* positions, int32_t* slot_mapping, int32_t* ctx_lens,
+                                        const int32_t* block_table, int32_t bt_stride, const int32_t* row_to_seq,
+                                        const int32_t* sampled, int32_t n_rows, int32_t block_size, void* stream) {
+  B200_REQUIRE(ids && positions && slot_mapping && ctx_lens && block_table && sampled && block_size > 0, B200_ERR_INVALID,
+               "advance_decode_rows: bad argument");
+  return advance_rows(ids, positions, slot_mapping, ctx_lens, block_table, bt_stride, row_to_seq, sampled, n_rows,
+                      block_size, (cudaStream_t)stream);
+}
+
 // ---- the step --------------------------------------------------------------------------------------
 struct StepArgs {
   const int32_t *ids, *positions, *slots, *block_table, *row_to_seq, *ctx_lens, *logit_rows;

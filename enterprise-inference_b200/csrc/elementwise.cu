@@ -226,7 +226,37 @@ argmax_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, i
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// (a0) device-side advance of pure-decode rows: the sampled token becomes the next input, position
+// and context grow by one, the slot follows the block table.  Lets a caller run several decode
+// steps without a host round trip (inputs stay resident in HBM).
+// ---------------------------------------------------------------------------------------
+__global__ void advance_rows_kernel(int32_t* ids, int32_t* positions, int32_t* slots, int32_t* ctx_lens,
+                                    const int32_t* __restrict__ block_table, int bt_stride,
+                                    const int32_t* __restrict__ row_to_seq, const int32_t* __restrict__ sampled, int n,
+                                    int block_size) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int p = positions[t] + 1;
+  const int seq = row_to_seq ? row_to_seq[t] : t;
+  ids[t] = sampled[t];
+  positions[t] = p;
+  ctx_lens[t] = p + 1;
+  slots[t] = block_table[(int64_t)seq * bt_stride + p / block_size] * block_size + p % block_size;
+}
+
 }  // namespace
+
+int advance_rows(int32_t* ids, int32_t* positions, int32_t* slots, int32_t* ctx_lens, const int32_t* block_table,
+                 int bt_stride, const int32_t* row_to_seq, const int32_t* sampled, int n, int block_size,
+                 cudaStream_t s) {
+  if (n == 0) return B200_OK;
+  B200_CUDA(launch(advance_rows_kernel, dim3((n + 127) / 128), dim3(128), 0, s, ids, positions, slots, ctx_lens,
+                   block_table, bt_stride, row_to_seq, sampled, n, block_size));
+  return B200_OK;
+}
 
 int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, int T, int hidden, int vocab,
           cudaStream_t s) {

@@ -217,6 +217,15 @@ class LLMEngine:
         self.scheduler.add(req)
         self.requests[req.request_id] = req
 
+    def add_prefilled(self, req: Request, n_computed: int) -> None:
+        """Benchmark/test utility: admit a request whose first n_computed tokens are taken as already
+        in the KV cache (synthetic prompt KV) — blocks are allocated, nothing is computed."""
+        assert 0 <= n_computed < req.n_total
+        self.blocks.grow(req.block_table, n_computed)
+        req.n_computed = n_computed
+        self.scheduler.running.append(req)
+        self.requests[req.request_id] = req
+
     def has_work(self) -> bool:
         return self.scheduler.has_work()
 

@@ -190,6 +190,16 @@ B200_API int b200_silu_mul(const void* gu, void* out, int32_t n_tokens, int32_t 
 B200_API int b200_argmax(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, int32_t index_offset,
                 int32_t* out_ids, float* out_max, void* stream);
 
+/* (a0) device-side scheduler advance for pure-decode rows: ids[t]=sampled[t], positions[t]+=1,
+ * ctx_lens[t]=positions[t]+1, slot_mapping[t] from the block table.  The image's scheduler does this
+ * on the host every iteration ([V22] vllm/v1/attention/backends/cpu_attn.py:107-117 metadata build);
+ * on the device it lets several decode steps run without a host round trip.  The caller guarantees
+ * the block table already covers the next position. */
+B200_API int b200_advance_decode_rows(int32_t* ids, int32_t* positions, int32_t* slot_mapping,
+                                      int32_t* ctx_lens, const int32_t* block_table, int32_t bt_stride,
+                                      const int32_t* row_to_seq, const int32_t* sampled, int32_t n_rows,
+                                      int32_t block_size, void* stream);
+
 /* (a11) sum all-reduce of a bf16 buffer over the ctx's TP communicator. */
 B200_API int b200_allreduce_bf16(b200_ctx* ctx, void* buf, int64_t count, void* stream);
 

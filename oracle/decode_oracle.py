@@ -352,6 +352,42 @@ class OracleModel:
         st.n += T
         return (logits, hidden) if return_hidden else logits
 
+    def step_batch(self, states: List[SeqState], token_ids: List[int], fast_linear: bool = False):
+        """One decode step for B sequences (one new token each), linears batched over the rows —
+        the shape of work the image's CPU model runner does per scheduler iteration.  With
+        fast_linear the projections run as bf16 torch F.linear (oneDNN: fp32 accumulate, one
+        rounding — still R2) instead of an explicit fp32 matmul; used by the timed CPU baseline."""
+        c = self.cfg
+        B = len(states)
+        lin = (lambda x, w, b=None: torch.nn.functional.linear(x, w, b)) if fast_linear else linear
+        pos = torch.tensor([st.n for st in states])
+        cos, sin = self.cs[pos, : c.head_dim // 2], self.cs[pos, c.head_dim // 2:]
+        x = self.w["model.embed_tokens.weight"][torch.tensor(token_ids)]
+        res = None
+        for l, L in enumerate(self.layers):
+            if res is None:
+                res = x
+                y = rms_norm(x, L["ln1"], c.rms_eps)
+            else:
+                y, res = add_rms_norm(x, res, L["ln1"], c.rms_eps)
+            qkv = lin(y, L["qkv_w"], L["qkv_b"])
+            q = rope_apply(qkv[:, : c.q_size].view(B, c.n_q_heads, c.head_dim), cos, sin)
+            k = rope_apply(qkv[:, c.q_size: c.q_size + c.kv_size].view(B, c.n_kv_heads, c.head_dim), cos, sin)
+            v = qkv[:, c.q_size + c.kv_size:].view(B, c.n_kv_heads, c.head_dim)
+            outs = []
+            for b, st in enumerate(states):
+                st.K[l][st.n] = k[b]
+                st.V[l][st.n] = v[b]
+                outs.append(attend(q[b], st.K[l], st.V[l], st.n + 1, self.scale))
+            x = lin(torch.stack(outs).view(B, c.q_size), L["o_w"])
+            y, res = add_rms_norm(x, res, L["ln2"], c.rms_eps)
+            x = lin(silu_mul(lin(y, L["gu_w"])), L["d_w"])
+        y, _ = add_rms_norm(x, res, self.w["model.norm.weight"], c.rms_eps)
+        logits = lin(y, self.w["lm_head.weight"])
+        for st in states:
+            st.n += 1
+        return logits
+
     def generate(self, prompt: List[int], n_new: int, keep_logits: bool = False):
         """Greedy, ignore_eos: exactly n_new tokens."""
         st = self.new_seq()

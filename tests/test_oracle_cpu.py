@@ -77,3 +77,17 @@ def test_rounding_points():
     y2, r2 = O.add_rms_norm(x, x, w, 1e-5)
     assert torch.equal(r2, (x.float() * 2).to(torch.bfloat16))
     assert O.greedy(torch.tensor([[1.0, 3.0, 3.0, 2.0]]).to(torch.bfloat16)).item() == 1  # ties -> lowest
+
+
+def test_batched_step_matches_per_sequence_forward():
+    cfg = O.CONFIGS["tiny"]
+    om = O.OracleModel(cfg, O.make_weights(cfg, norm_jitter=0.1), capacity=64)
+    prompts = [O.make_prompt(cfg, i, n) for i, n in enumerate((3, 9, 17))]
+    sts, ref = [], []
+    for p in prompts:
+        st = om.new_seq(); om.forward(st, p[:-1]); sts.append(st)
+        st2 = om.new_seq(); ref.append(om.forward(st2, p)[-1])
+    for fast in (False, True):
+        import copy
+        got = om.step_batch(copy.deepcopy(sts), [p[-1] for p in prompts], fast_linear=fast)
+        assert (torch.softmax(got.float(), -1) - torch.softmax(torch.stack(ref).float(), -1)).abs().max() <= 1e-3
