@@ -358,3 +358,72 @@ int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, con
 }
 
 }  // namespace b200
+
+// =================================================================================================
+// b200_paged_attn_decode_static — the same split-KV attention for callers that may not allocate.
+//
+// Who needs it: an engine that sizes all of its device memory once at start-up and forbids any
+// later allocation (a fixed memory plan under a static partition of the GPU, or a host runtime whose
+// device-memory calls go through an arena the library cannot reach), and bindings written in
+// languages/FFIs where handing the library a scratch pointer of the right size is awkward.  Such a
+// caller cannot satisfy b200_paged_attn_decode's (workspace, workspace_bytes) contract by calling
+// cudaMalloc, so the split partials live in the array below instead: it is part of the library's
+// image, every GPU that loads the library carries its kStaticScratchBytes until the process exits,
+// and nothing is allocated or freed by this entry point (no cudaMalloc/cudaFree, no torch).
+//
+// `g_attn_scratch` names DEVICE memory.  In host code that name is only a handle for the runtime —
+// not an address a kernel can use — so the address is looked up with cudaGetSymbolAddress once per
+// device (with that device current) and cached; the FIRST call on a device performs this look-up,
+// which is why that first call should be made before any stream capture begins.
+//
+// Sharing: every call on a device uses the same array and finds whatever the previous call left in
+// it.  Nothing in it has to start at zero — each launch writes every partial (o, m, l) it later
+// merges, including those of empty splits, before the merge kernel reads them — so no clearing is
+// done.  Two calls whose kernels overlap on the GPU (different streams, or different threads
+// driving one device) would write the same bytes and race: issue them on one stream, or serialise.
+// =================================================================================================
+namespace b200 {
+namespace {
+constexpr int64_t kStaticScratchBytes = 2 << 20;  // 2 MiB: every decode-sized batch; the largest split plans (about 2.4 MiB) are refused
+static __device__ __align__(256) unsigned char g_attn_scratch[kStaticScratchBytes];
+constexpr int kMaxDevices = 64;
+void* g_scratch_addr[kMaxDevices] = {};
+}  // namespace
+}  // namespace b200
+
+extern "C" int64_t b200_paged_attn_static_scratch_bytes(void) { return b200::kStaticScratchBytes; }
+
+extern "C" int b200_paged_attn_decode_static(const void* q, int64_t ldq, const void* k_cache_layer,
+                                             const void* v_cache_layer, const int32_t* block_table, int32_t bt_stride,
+                                             const int32_t* row_to_seq, const int32_t* ctx_lens, void* out, int64_t ldo,
+                                             int32_t n_tokens, int32_t n_q_heads, int32_t n_kv_heads,
+                                             int32_t block_size, int32_t max_ctx_len, float scale, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(q && k_cache_layer && v_cache_layer && block_table && ctx_lens && out, B200_ERR_INVALID,
+               "paged_attn_static: null argument");
+  B200_REQUIRE(n_tokens >= 0 && n_q_heads > 0 && n_kv_heads > 0 && max_ctx_len > 0, B200_ERR_INVALID,
+               "paged_attn_static: bad sizes");
+  // exact need of this launch (0 when a single split writes the output directly)
+  int n_splits = 1, tps = 1;
+  split_plan(n_tokens > 0 ? n_tokens : 1, n_kv_heads, max_ctx_len, &n_splits, &tps);
+  const int64_t need =
+      n_splits > 1 ? (int64_t)n_tokens * n_q_heads * n_splits * (kHeadDim + 2) * (int64_t)sizeof(float) : 0;
+  B200_REQUIRE(need <= kStaticScratchBytes, B200_ERR_UNSUPPORTED,
+               "paged_attn_static: this shape needs %lld bytes of split scratch, the built-in array holds %lld "
+               "(rows=%d q_heads=%d splits=%d); use b200_paged_attn_decode with a caller workspace",
+               (long long)need, (long long)kStaticScratchBytes, n_tokens, n_q_heads, n_splits);
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxDevices, B200_ERR_UNSUPPORTED, "paged_attn_static: device ordinal %d >= %d", dev,
+               kMaxDevices);
+  if (!g_scratch_addr[dev]) {  // set-up, once per device, that device current
+    void* p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_attn_scratch));
+    B200_REQUIRE(p != nullptr, B200_ERR_CUDA, "paged_attn_static: cudaGetSymbolAddress returned a null address");
+    g_scratch_addr[dev] = p;
+  }
+  return paged_attn((const __nv_bfloat16*)q, ldq, (const __nv_bfloat16*)k_cache_layer,
+                    (const __nv_bfloat16*)v_cache_layer, block_table, bt_stride, row_to_seq, ctx_lens,
+                    (__nv_bfloat16*)out, ldo, n_tokens, n_q_heads, n_kv_heads, block_size, max_ctx_len, scale,
+                    g_scratch_addr[dev], kStaticScratchBytes, (cudaStream_t)stream);
+}

@@ -182,6 +182,21 @@ B200_API int b200_paged_attn_decode(const void* q, int64_t ldq, const void* k_ca
                            int32_t block_size, int32_t max_ctx_len, float scale, void* workspace,
                            int64_t workspace_bytes, void* stream);
 
+/* No counterpart in the reference: a variant of b200_paged_attn_decode for callers that cannot
+ * allocate device memory after start-up (engines with a fixed memory plan, bindings that cannot call
+ * cudaMalloc).  Same inputs, outputs and results, but the split-KV partials live in a 2 MiB array
+ * built into the library (b200_paged_attn_static_scratch_bytes(); held by every GPU that loads the
+ * library until exit) and the call allocates nothing.  Shapes whose partials exceed the array return
+ * B200_ERR_UNSUPPORTED with the sizes in b200_last_error().  The first call on each device looks up
+ * the array's device address: make it before any stream capture.  All calls on a device share the
+ * array — keep them on one stream; calls that overlap on the GPU race. */
+B200_API int64_t b200_paged_attn_static_scratch_bytes(void);
+B200_API int b200_paged_attn_decode_static(const void* q, int64_t ldq, const void* k_cache_layer,
+                                  const void* v_cache_layer, const int32_t* block_table, int32_t bt_stride,
+                                  const int32_t* row_to_seq, const int32_t* ctx_lens, void* out,
+                                  int64_t ldo, int32_t n_tokens, int32_t n_q_heads, int32_t n_kv_heads,
+                                  int32_t block_size, int32_t max_ctx_len, float scale, void* stream);
+
 /* (a8) out[T][I] = bf16(bf16(silu(g))*u), gu = [T][2I] gate|up ([V22] activation.py:137-141). */
 B200_API int b200_silu_mul(const void* gu, void* out, int32_t n_tokens, int32_t intermediate, void* stream);
 
