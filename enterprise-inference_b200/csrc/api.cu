@@ -212,6 +212,9 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
   int64_t lw = 0;
   const int outs[5] = {c->qkv_w, (int)h, 2 * c->inter, (int)h, c->vocab_local};
   const int ks[5] = {(int)h, c->hq * kHeadDim, (int)h, c->inter, (int)h};
+  for (int t = 1; t <= T; t = (t < 16 ? 16 : (t % 2 == 0 ? t + 1 : (t - 1) * 2))) {  // 1,16,17,32,33,64,65,...
+    for (int i = 0; i < 5; ++i) lw = std::max<int64_t>(lw, linear_tc_workspace_bytes(t, outs[i], ks[i]));
+  }
   for (int i = 0; i < 5; ++i) lw = std::max<int64_t>(lw, linear_tc_workspace_bytes((int)T, outs[i], ks[i]));
   c->lin_ws_bytes = lw;
   c->meta_ints = 6 * T + (int64_t)T * cfg->max_blocks_per_seq;

@@ -1,11 +1,434 @@
-// placeholder until the tcgen05 kernel lands
+// tcgen05 / TMEM weight-streaming linear: y[T][n_out] = x[T][k] . w[n_out][k]^T (+bias), T >= 5.
+//
+// Decode GEMMs are skinny (T = 8..256 token rows against n_out = 4096..128256 weight rows), so the
+// operands are SWAPPED: a 128-row slab of W is the UMMA "A" operand (M = 128, fills the tensor
+// core's M), the token rows are "B" (N = 16..256), and the fp32 accumulator D[128 features][N
+// tokens] lives in TMEM (lane = feature, column = token).  Bound: HBM — algorithmic bytes per
+// launch = n_out*k*2, each weight element crosses HBM once; the tensor pipe needs
+// max(128,M)*N/256 cycles per K=16 step = 32 cycles for N = 64 against 4 KiB of W, i.e. it can
+// absorb 128 B/clk/SM where HBM delivers ~23 B/clk/SM, so tensor utilisation is expected to be
+// low (~15-20 %) and HBM GB/s is the figure of merit.
+//
+// Pipeline per CTA (192 threads): warp 0 = TMA producer (cp.async.bulk.tensor, SWIZZLE_128B,
+// W with an evict-first L2 policy, x evict-last), warp 1 = TMEM allocator + single-thread
+// tcgen05.mma issuer (tcgen05.commit releases smem stages and signals the epilogue), warps 2-5 =
+// epilogue (tcgen05.ld 32x32b -> bias -> bf16 -> global).  A CTA owns (128-row slab, token tile,
+// K split).  Split-K is deterministic: partials go to an fp32 workspace, the LAST CTA of a slab
+// (atomic ticket) sums them in split order, so results do not depend on scheduling.
+// W tiles of the first stages are requested BEFORE griddepcontrol.wait (they do not depend on the
+// previous kernel) so that under programmatic dependent launch the weight stream never drains.
+//
+// Replaces: sgl-kernel weight_packed_linear (AMX) / oneDNN bf16 matmul of the vLLM-CPU image
+// ([V22] vllm/model_executor/layers/utils.py:277-299); rounding R2 of oracle/decode_oracle.py.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
 #include "common.cuh"
+
 namespace b200 {
-bool linear_tc_supported(int, int, int) { return false; }
-int64_t linear_tc_workspace_bytes(int, int, int) { return 256; }
-int linear_tc(const __nv_bfloat16*, int64_t, const __nv_bfloat16*, const __nv_bfloat16*, __nv_bfloat16*, int64_t, int,
-              int, int, void*, int64_t, cudaStream_t) {
-  set_error("tcgen05 linear not built");
-  return B200_ERR_UNSUPPORTED;
+
+namespace {
+
+constexpr int kBlockM = 128;   // weight rows per CTA = UMMA M
+constexpr int kBlockK = 64;    // bf16 elements per stage row = 128 bytes = one swizzle span
+constexpr int kUmmaK = 16;
+constexpr int kTcThreads = 192;
+constexpr int kCounterBytes = 64 * 1024;  // slab tickets at the head of the workspace (16384 slabs x token tiles)
+constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
+constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
+
+__host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? 5 : (N <= 64 ? 4 : (N <= 128 ? 3 : 4)); }
+__host__ __device__ constexpr int stage_bytes(int N) { return kBlockM * kBlockK * 2 + N * kBlockK * 2; }
+__host__ __device__ constexpr int smem_bytes_for(int N) { return stages_for(N) * stage_bytes(N) + 1024 + 256; }
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra.uni WAIT_DONE;\n"
+      "bra.uni WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
+                                            uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], bf16 x bf16 -> fp32, issued by ONE thread
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+// start>>4 [0,14) | LBO>>4 [16,30) (ignored for swizzled K-major, 1) | SBO>>4 [32,46) = 1024 B between
+// 8-row groups | version=1 [46,48) | layout_type=2 (SWIZZLE_128B) [61,64)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// cute::UMMA::InstrDescriptor: c_format F32 (1)<<4 | a_format BF16 (1)<<7 | b_format BF16 (1)<<10 |
+// a_major K (0)<<15 | b_major K (0)<<16 | N>>3 <<17 | M>>4 <<24
+__host__ __device__ constexpr uint32_t make_idesc(int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct TcParams {
+  const __nv_bfloat16* bias;
+  __nv_bfloat16* y;
+  int64_t ldy;
+  int T, n_out, n_kblocks, splits;
+  float* partials;      // [splits][tok_tiles*N][n_out_pad] fp32
+  unsigned int* tickets;  // [m_tiles * tok_tiles], zero on entry, zero on exit
+  int n_out_pad;
+};
+
+template <int N>
+__global__ void __launch_bounds__(kTcThreads)
+linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, TcParams p) {
+  constexpr int S = stages_for(N);
+  constexpr int kStageBytes = stage_bytes(N);
+  constexpr int kABytes = kBlockM * kBlockK * 2;
+  constexpr int kTmemCols = N < 32 ? 32 : N;
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + S * kStageBytes);
+  uint64_t* empty = full + S;
+  uint64_t* tmem_full = empty + S;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  int* ticket_slot = reinterpret_cast<int*>(tmem_slot + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_tile = blockIdx.x, split = blockIdx.y, tok_tile = blockIdx.z;
+  // K range of this split (balanced: the first `rem` splits get one more block)
+  const int base = p.n_kblocks / p.splits, rem = p.n_kblocks % p.splits;
+  const int kb0 = split * base + min(split, rem);
+  const int nkb = base + (split < rem ? 1 : 0);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+      const int pre = min(S, nkb);
+      // weights first: they do not depend on the producer of x
+      for (int i = 0; i < pre; ++i) {
+        mbar_expect_tx(&full[i], kStageBytes);
+        tma_load_2d(smem + i * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[i], kEvictFirst);
+      }
+      pdl_wait();
+      pdl_launch_dependents();
+      for (int i = 0; i < pre; ++i)
+        tma_load_2d(smem + i * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[i], kEvictLast);
+      for (int i = pre; i < nkb; ++i) {
+        const int st = i % S;
+        mbar_wait(&empty[st], ((i / S) - 1) & 1);
+        mbar_expect_tx(&full[st], kStageBytes);
+        tma_load_2d(smem + st * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[st], kEvictFirst);
+        tma_load_2d(smem + st * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[st], kEvictLast);
+      }
+    } else {
+      pdl_wait();
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    pdl_wait();
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(N);
+      for (int i = 0; i < nkb; ++i) {
+        const int st = i % S;
+        mbar_wait(&full[st], (i / S) & 1);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + st * kStageBytes);
+        const uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // advancing K inside the 128-byte swizzle span = +32 bytes on the start address
+          tc_mma(tmem_base, make_desc(a_addr + k * kUmmaK * 2), make_desc(b_addr + k * kUmmaK * 2), idesc,
+                 (i | k) ? 1u : 0u);
+        }
+        tc_commit(&empty[st]);  // arrives when the MMAs above have finished reading this stage
+      }
+      tc_commit(tmem_full);     // accumulator complete
+    }
+  } else {
+    // ===== epilogue: 4 warps, TMEM lane quadrant = warp % 4 =====
+    pdl_wait();
+    const int quad = warp & 3;
+    const int row = m_tile * kBlockM + quad * 32 + lane;   // output feature owned by this thread
+    const int tok0 = tok_tile * N;
+    if (nkb > 0) {
+      mbar_wait(tmem_full, 0);
+      tc_fence_after();
+    }
+    const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const bool direct = p.splits == 1;
+    const float b = (direct && p.bias && row < p.n_out) ? __bfloat162float(p.bias[row]) : 0.f;
+#pragma unroll
+    for (int c = 0; c < N; c += 16) {
+      uint32_t r[16];
+      if (nkb > 0) {
+        tmem_ld16(taddr + c, r);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) r[j] = 0u;
+      }
+      if (direct) {
+        if (row < p.n_out) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int t = tok0 + c + j;
+            if (t < p.T) p.y[(int64_t)t * p.ldy + row] = __float2bfloat16_rn(__uint_as_float(r[j]) + b);
+          }
+        }
+      } else {
+        float* dst = p.partials + ((int64_t)split * gridDim.z * N + tok0 + c) * p.n_out_pad + row;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) dst[(int64_t)j * p.n_out_pad] = __uint_as_float(r[j]);
+      }
+    }
+    if (!direct) {
+      // deterministic split-K: the last CTA of this (slab, token tile) reduces in split order
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const int tile_id = m_tile * gridDim.z + tok_tile;
+      if (warp == 2 && lane == 0) *ticket_slot = (int)atomicAdd(&p.tickets[tile_id], 1u);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*ticket_slot == p.splits - 1) {
+        __threadfence();
+        if (row < p.n_out) {
+          const float bb = p.bias ? __bfloat162float(p.bias[row]) : 0.f;
+          const int tmax = min(N, p.T - tok0);
+          for (int t = 0; t < tmax; ++t) {
+            float acc = 0.f;
+            for (int s = 0; s < p.splits; ++s)
+              acc += __ldcg(p.partials + ((int64_t)s * gridDim.z * N + tok0 + t) * p.n_out_pad + row);
+            p.y[(int64_t)(tok0 + t) * p.ldy + row] = __float2bfloat16_rn(acc + bb);
+          }
+        }
+        if (warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+    else
+      cudaGetLastError();
+  }
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  uint64_t rows, cols, ld;
+  uint32_t box_rows;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    return std::hash<const void*>()(k.ptr) ^ (k.rows * 1315423911ull) ^ (k.cols << 7) ^ (k.ld << 17) ^ k.box_rows;
+  }
+};
+
+// 2D bf16 tensor map [rows][cols] (row stride ld elements), box [box_rows][64], SWIZZLE_128B, zero OOB fill.
+int get_map(const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows, CUtensorMap* out) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  MapKey key{ptr, rows, cols, ld, box_rows};
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) {
+    *out = it->second;
+    return B200_OK;
+  }
+  EncodeTiledFn fn = encode_fn();
+  B200_REQUIRE(fn != nullptr, B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kBlockK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, B200_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] ld %llu", (int)r,
+               (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld);
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, m);
+  *out = m;
+  return B200_OK;
+}
+
+inline int n_tile_for(int T) { return T <= 16 ? 16 : (T <= 32 ? 32 : (T <= 64 ? 64 : (T <= 128 ? 128 : 256))); }
+
+struct Plan {
+  int N, m_tiles, tok_tiles, n_kblocks, splits, n_out_pad;
+};
+
+Plan make_plan(int T, int n_out, int k) {
+  Plan pl;
+  pl.N = n_tile_for(T);
+  pl.m_tiles = (n_out + kBlockM - 1) / kBlockM;
+  pl.tok_tiles = (T + pl.N - 1) / pl.N;
+  pl.n_kblocks = (k + kBlockK - 1) / kBlockK;
+  pl.n_out_pad = pl.m_tiles * kBlockM;
+  const int ctas_per_sm = smem_bytes_for(pl.N) * 2 <= 227 * 1024 ? 2 : 1;
+  const int slots = kNumSMs * ctas_per_sm;
+  const int tiles = pl.m_tiles * pl.tok_tiles;
+  int s = 1;
+  if (tiles < slots) {
+    s = slots / tiles;                       // fill one wave of resident CTAs
+    s = min(s, max(pl.n_kblocks / 4, 1));    // at least 4 K blocks (64 KiB of W) per split
+    s = max(1, min(s, 32));
+  }
+  pl.splits = s;
+  return pl;
+}
+
+template <int N>
+int launch_tc(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
+  static bool attr_set = false;
+  const int smem = smem_bytes_for(N);
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  B200_CUDA(launch(linear_tc_kernel<N>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads), (size_t)smem, s,
+                   mw, mx, p));
+  return B200_OK;
+}
+
+}  // namespace
+
+bool linear_tc_supported(int T, int n_out, int k) {
+  if (T < 1 || n_out < 1) return false;
+  if (k % 8 != 0) return false;  // TMA global strides are multiples of 16 bytes
+  const Plan pl = make_plan(T, n_out, k);
+  return (int64_t)pl.m_tiles * pl.tok_tiles * 4 <= kCounterBytes && pl.tok_tiles <= 65535 && pl.splits <= 65535;
+}
+
+int64_t linear_tc_workspace_bytes(int T, int n_out, int k) {
+  if (T < 1) T = 1;
+  const Plan pl = make_plan(T, n_out, k);
+  const int64_t part = pl.splits > 1 ? (int64_t)pl.splits * pl.tok_tiles * pl.N * pl.n_out_pad * 4 : 0;
+  return kCounterBytes + part + 256;
+}
+
+int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
+              __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, void* ws, int64_t ws_bytes, cudaStream_t s) {
+  B200_REQUIRE(k % 8 == 0 && ldx % 8 == 0, B200_ERR_UNSUPPORTED, "linear_tc: k and ldx must be multiples of 8");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) % 16 == 0, B200_ERR_INVALID,
+               "linear_tc: x and w must be 16-byte aligned");
+  const Plan pl = make_plan(T, n_out, k);
+  const int64_t need = linear_tc_workspace_bytes(T, n_out, k);
+  B200_REQUIRE(pl.splits == 1 || (ws && ws_bytes >= need), B200_ERR_INVALID,
+               "linear_tc: workspace too small (%lld < %lld)", (long long)ws_bytes, (long long)need);
+  CUtensorMap mw, mx;
+  int rc = get_map(w, (uint64_t)n_out, (uint64_t)k, (uint64_t)k, kBlockM, &mw);
+  if (rc) return rc;
+  rc = get_map(x, (uint64_t)T, (uint64_t)k, (uint64_t)ldx, (uint32_t)pl.N, &mx);
+  if (rc) return rc;
+  TcParams p;
+  p.bias = bias;
+  p.y = y;
+  p.ldy = ldy;
+  p.T = T;
+  p.n_out = n_out;
+  p.n_kblocks = pl.n_kblocks;
+  p.splits = pl.splits;
+  p.tickets = reinterpret_cast<unsigned int*>(ws);
+  p.partials = ws ? reinterpret_cast<float*>(static_cast<char*>(ws) + kCounterBytes) : nullptr;
+  p.n_out_pad = pl.n_out_pad;
+  switch (pl.N) {
+    case 16: return launch_tc<16>(mw, mx, p, pl, s);
+    case 32: return launch_tc<32>(mw, mx, p, pl, s);
+    case 64: return launch_tc<64>(mw, mx, p, pl, s);
+    case 128: return launch_tc<128>(mw, mx, p, pl, s);
+    default: return launch_tc<256>(mw, mx, p, pl, s);
+  }
+}
+
 }  // namespace b200

@@ -148,7 +148,8 @@ B200_API int b200_ctx_set_tap(b200_ctx* ctx, int32_t layer, void* out_hidden, vo
  * Replaces sgl-kernel weight_packed_linear / oneDNN matmul of the image
  * ([V22] vllm/model_executor/layers/utils.py:277-299).  impl: 0 auto, 1 CUDA-core GEMV
  * (HBM-bound, T small), 2 tcgen05/TMEM weight-streaming GEMM.  Scratch (split-K partials
- * and tile counters) comes from the caller. */
+ * and slab tickets) comes from the caller: the first 64 KiB of the workspace must be ZERO before
+ * its first use (cudaMemset once); every launch leaves them zero again. */
 B200_API int64_t b200_linear_workspace_bytes(int32_t n_tokens, int32_t n_out, int32_t k);
 B200_API int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y,
                      int64_t ldy, int32_t n_tokens, int32_t n_out, int32_t k, int32_t impl,

@@ -75,6 +75,45 @@ def test_linear_gemv(lib, abi, T, n_out, k, bias):
     ulp_close(y, want, max_ulp=1, max_frac=0.02)
 
 
+@pytest.mark.parametrize("T,n_out,k,bias", [(16, 128, 64, False), (5, 256, 128, True), (64, 6144, 4096, False),
+                                             (17, 264, 512, True), (100, 1000, 1024, True), (64, 4096, 14336, False),
+                                             (256, 512, 4096, False), (300, 384, 2048, True), (8, 128, 200, False),
+                                             (1, 1024, 4096, False), (33, 5120 + 2048, 5120, True)])
+def test_linear_tcgen05(lib, abi, T, n_out, k, bias):
+    """The tcgen05/TMEM weight-streaming GEMM (impl=2): ragged T / n_out / k (TMA zero-fills the
+    out-of-bounds part of a box), split-K and direct epilogues, twice in a row on the same
+    workspace (the slab tickets must be left at zero)."""
+    g = torch.Generator().manual_seed(T * 7 + n_out + k)
+    x = torch.randn(T, k, generator=g).to(BF)
+    w = (0.05 * torch.randn(n_out, k, generator=g)).to(BF)
+    b = torch.randn(n_out, generator=g).to(BF) if bias else None
+    want = O.linear(x, w, b)
+    xd, wd, bd = dev(x), dev(w), (dev(b) if bias else None)
+    wsb = lib.b200_linear_workspace_bytes(T, n_out, k)
+    ws = torch.zeros(wsb, dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        y = torch.full((T, n_out), float("nan"), dtype=BF, device="cuda")
+        sync_check(abi, lib.b200_linear_bf16(xd.data_ptr(), k, wd.data_ptr(), abi.ptr(bd), y.data_ptr(), n_out, T, n_out, k,
+                                             2, ws.data_ptr(), wsb, None))
+        ulp_close(y, want, max_ulp=1, max_frac=0.02)
+    assert not ws[:65536].any(), "split-K tickets must be zero again after the launch"
+
+
+def test_linear_tcgen05_matches_gemv_bitwise_up_to_order(lib, abi):
+    """Both linear paths implement R2 (fp32 accumulate, one rounding): they may differ only by
+    summation order."""
+    T, n_out, k = 4, 4096, 4096
+    g = torch.Generator().manual_seed(11)
+    x, w = dev(torch.randn(T, k, generator=g).to(BF)), dev((0.05 * torch.randn(n_out, k, generator=g)).to(BF))
+    y1 = torch.empty(T, n_out, dtype=BF, device="cuda")
+    y2 = torch.empty_like(y1)
+    wsb = lib.b200_linear_workspace_bytes(T, n_out, k)
+    ws = torch.zeros(wsb, dtype=torch.uint8, device="cuda")
+    sync_check(abi, lib.b200_linear_bf16(x.data_ptr(), k, w.data_ptr(), None, y1.data_ptr(), n_out, T, n_out, k, 1, None, 0, None))
+    sync_check(abi, lib.b200_linear_bf16(x.data_ptr(), k, w.data_ptr(), None, y2.data_ptr(), n_out, T, n_out, k, 2, ws.data_ptr(), wsb, None))
+    ulp_close(y2, y1.cpu(), max_ulp=1, max_frac=0.02)
+
+
 def test_linear_is_linear_at_full_width(lib, abi):
     """Size-independent property at the 8B down-proj shape: W(a*x) == a*W(x) for a power of two
     (exact in bf16/fp32), and column-sliced leading dimension works."""
