@@ -284,7 +284,7 @@ def run_b200(args):
     x = torch.randn(B, cfg.hidden, device="cuda", dtype=torch.bfloat16)
     y = torch.empty(B, 2 * r.inter, device="cuda", dtype=torch.bfloat16)
     wsb = int(lib.b200_linear_workspace_bytes(B, 2 * r.inter, cfg.hidden))
-    wsp = torch.empty(max(wsb, 16), dtype=torch.uint8, device="cuda")
+    wsp = torch.zeros(max(wsb, 16), dtype=torch.uint8, device="cuda")
     reps = max(1, 64 // len(gu))
 
     def gu_pass():

@@ -155,7 +155,8 @@ struct b200_ctx {
   void *tap_hidden = nullptr, *tap_res = nullptr;
   // TP
   ncclComm_t comm = nullptr;
-  int gemv_max_t = 4;
+  int gemv_max_t = 0;  // rows <= this use the CUDA-core GEMV; 0: the tcgen05 path serves every T (measured faster)
+  bool pdl = true;
 };
 
 static int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
@@ -200,6 +201,7 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
   c->layers.resize(cfg->n_layers);
   if (const char* e = getenv("B200_GEMV_MAX_T")) c->gemv_max_t = atoi(e);
   if (const char* e = getenv("B200_GRAPHS")) c->graphs = atoi(e) != 0;
+  if (const char* e = getenv("B200_PDL")) c->pdl = atoi(e) != 0;
 
   const int64_t T = cfg->max_tokens, h = cfg->hidden, R = c->max_logit_rows;
   const int max_ctx = cfg->max_blocks_per_seq * cfg->block_size;
@@ -389,7 +391,7 @@ extern "C" int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const
                                 int32_t T, int32_t n_out, int32_t k, int32_t impl, void* ws, int64_t ws_bytes,
                                 void* stream) {
   B200_REQUIRE(x && w && y && T >= 0 && n_out > 0 && k > 0, B200_ERR_INVALID, "linear: bad argument");
-  int gm = 4;
+  int gm = 0;
   if (const char* e = getenv("B200_GEMV_MAX_T")) gm = atoi(e);
   return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias,
                     (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, (cudaStream_t)stream);
@@ -563,7 +565,7 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   if (c->cfg.tp_world > 1) B200_REQUIRE(c->comm, B200_ERR_STATE, "decode_step: b200_nccl_init not called");
 
   const bool use_graph = c->graphs && s != nullptr && c->tap_layer < 0;
-  launch_opts().pdl = getenv("B200_PDL") ? atoi(getenv("B200_PDL")) != 0 : false;
+  launch_opts().pdl = getenv("B200_PDL") ? atoi(getenv("B200_PDL")) != 0 : c->pdl;
   int rc = B200_OK;
   if (!use_graph) {
     launch_counter() = 0;

@@ -21,6 +21,7 @@
 // Replaces: sgl-kernel weight_packed_linear (AMX) / oneDNN bf16 matmul of the vLLM-CPU image
 // ([V22] vllm/model_executor/layers/utils.py:277-299); rounding R2 of oracle/decode_oracle.py.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <unordered_map>
@@ -256,14 +257,51 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (*ticket_slot == p.splits - 1) {
         __threadfence();
-        if (row < p.n_out) {
-          const float bb = p.bias ? __bfloat162float(p.bias[row]) : 0.f;
-          const int tmax = min(N, p.T - tok0);
-          for (int t = 0; t < tmax; ++t) {
-            float acc = 0.f;
-            for (int s = 0; s < p.splits; ++s)
-              acc += __ldcg(p.partials + ((int64_t)s * gridDim.z * N + tok0 + t) * p.n_out_pad + row);
-            p.y[(int64_t)(tok0 + t) * p.ldy + row] = __float2bfloat16_rn(acc + bb);
+        // 4 warps x 32 lanes: lane owns 4 consecutive features (one float4 per partial row), warp wq
+        // owns tokens wq, wq+4, ...; 4 tokens x `splits` 16-byte L2 loads in flight per thread.
+        const int wq = warp - 2;
+        const int r4 = m_tile * kBlockM + lane * 4;
+        const int tmax = min(N, p.T - tok0);
+        float bb[4] = {0.f, 0.f, 0.f, 0.f};
+        if (p.bias) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[r4 + e]);
+        }
+        const int64_t split_stride = (int64_t)gridDim.z * N * p.n_out_pad;
+        const bool vec_ok = (r4 + 3 < p.n_out) && (p.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 7) == 0);
+        for (int t = wq; t < tmax; t += 16) {
+          float4 acc[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          const float* src = p.partials + (int64_t)(tok0 + t) * p.n_out_pad + r4;
+#pragma unroll 3
+          for (int sp = 0; sp < p.splits; ++sp) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              if (t + 4 * u < tmax) {
+                const float4 v = __ldcg(reinterpret_cast<const float4*>(src + sp * split_stride + (int64_t)(4 * u) * p.n_out_pad));
+                acc[u].x += v.x;
+                acc[u].y += v.y;
+                acc[u].z += v.z;
+                acc[u].w += v.w;
+              }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int tt = t + 4 * u;
+            if (tt < tmax) {
+              __nv_bfloat16* dst = p.y + (int64_t)(tok0 + tt) * p.ldy + r4;
+              const float o[4] = {acc[u].x + bb[0], acc[u].y + bb[1], acc[u].z + bb[2], acc[u].w + bb[3]};
+              if (vec_ok) {
+                *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]));
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                  if (r4 + e < p.n_out) dst[e] = __float2bfloat16_rn(o[e]);
+              }
+            }
           }
         }
         if (warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
@@ -355,13 +393,18 @@ Plan make_plan(int T, int n_out, int k) {
   pl.tok_tiles = (T + pl.N - 1) / pl.N;
   pl.n_kblocks = (k + kBlockK - 1) / kBlockK;
   pl.n_out_pad = pl.m_tiles * kBlockM;
-  const int ctas_per_sm = smem_bytes_for(pl.N) * 2 <= 227 * 1024 ? 2 : 1;
-  const int slots = kNumSMs * ctas_per_sm;
+  // Split K until about one CTA per SM exists (two kernels of the step can then be co-resident
+  // under programmatic dependent launch: the next one prefetches its first weight stages while
+  // this one drains).  Tunable for experiments: B200_TC_SLOTS, B200_TC_MIN_KB.
+  static const int slots_env = getenv("B200_TC_SLOTS") ? atoi(getenv("B200_TC_SLOTS")) : 0;
+  static const int minkb_env = getenv("B200_TC_MIN_KB") ? atoi(getenv("B200_TC_MIN_KB")) : 0;
+  const int slots = slots_env > 0 ? slots_env : kNumSMs;
+  const int min_kb = minkb_env > 0 ? minkb_env : 4;
   const int tiles = pl.m_tiles * pl.tok_tiles;
   int s = 1;
   if (tiles < slots) {
-    s = slots / tiles;                       // fill one wave of resident CTAs
-    s = min(s, max(pl.n_kblocks / 4, 1));    // at least 4 K blocks (64 KiB of W) per split
+    s = (slots + tiles / 2) / tiles;                  // nearest to one wave
+    s = min(s, max(pl.n_kblocks / min_kb, 1));        // at least min_kb K blocks (64 KiB of W each) per split
     s = max(1, min(s, 32));
   }
   pl.splits = s;

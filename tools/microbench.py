@@ -44,7 +44,7 @@ def bench_linear(impls=(1,), Ts=(1, 2, 4)):
             x = torch.randn(T, k, device="cuda", dtype=BF)
             y = torch.empty(T, n, device="cuda", dtype=BF)
             wsb = lib.b200_linear_workspace_bytes(T, n, k)
-            wsp = torch.empty(max(wsb, 16), dtype=torch.uint8, device="cuda")
+            wsp = torch.zeros(max(wsb, 16), dtype=torch.uint8, device="cuda")
             for impl in impls:
                 i = [0]
 
