@@ -23,7 +23,7 @@ class ModelCfg(C.Structure):
                [(n, C.c_int32) for n in ("block_size", "max_tokens", "max_blocks_per_seq", "tp_rank", "tp_world")]
 
 
-W_EMBED, W_LN1, W_QKV, W_QKV_BIAS, W_O, W_LN2, W_GATE_UP, W_DOWN, W_FINAL_NORM, W_LM_HEAD = range(10)
+W_EMBED, W_LN1, W_QKV, W_QKV_BIAS, W_O, W_LN2, W_GATE_UP, W_DOWN, W_FINAL_NORM, W_LM_HEAD, W_GATE_UP_INTERLEAVED = range(11)
 
 _vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
@@ -47,6 +47,8 @@ SIGNATURES = {
     "b200_ctx_set_tap": (C.c_int, [_vp, _i32, _vp, _vp]),
     "b200_linear_workspace_bytes": (_i64, [_i32, _i32, _i32]),
     "b200_linear_bf16": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _i64, _vp]),
+    "b200_linear_fused_bf16": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
+                                         _i32, _i32, _i32, _vp, _i64, _vp]),
     "b200_rmsnorm": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _f32, _vp]),
     "b200_embed": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
     "b200_rope_kv_append": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),

@@ -113,6 +113,7 @@ using namespace b200;
 struct LayerW {
   const __nv_bfloat16 *ln1 = nullptr, *qkv = nullptr, *qkv_b = nullptr, *o = nullptr, *ln2 = nullptr, *gu = nullptr,
                       *down = nullptr;
+  bool gu_interleaved = false;  // gu holds 128-row slabs of 64 gate rows + the 64 matching up rows
 };
 
 struct GraphKey {
@@ -157,6 +158,8 @@ struct b200_ctx {
   ncclComm_t comm = nullptr;
   int gemv_max_t = 0;  // rows <= this use the CUDA-core GEMV; 0: the tcgen05 path serves every T (measured faster)
   bool pdl = true;
+  bool fuse = true;                    // epilogue fusion (RoPE+KV, SiLU*mul) on the tcgen05 path
+  int64_t prefetch_cap = 0;   // bytes of the NEXT linear's weights pulled into L2 per linear (0: off)
 };
 
 static int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
@@ -202,6 +205,8 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
   if (const char* e = getenv("B200_GEMV_MAX_T")) c->gemv_max_t = atoi(e);
   if (const char* e = getenv("B200_GRAPHS")) c->graphs = atoi(e) != 0;
   if (const char* e = getenv("B200_PDL")) c->pdl = atoi(e) != 0;
+  if (const char* e = getenv("B200_FUSE")) c->fuse = atoi(e) != 0;
+  if (const char* e = getenv("B200_PREFETCH_MB")) c->prefetch_cap = (int64_t)atoi(e) << 20;
 
   const int64_t T = cfg->max_tokens, h = cfg->hidden, R = c->max_logit_rows;
   const int max_ctx = cfg->max_blocks_per_seq * cfg->block_size;
@@ -291,7 +296,7 @@ extern "C" int b200_set_weight(b200_ctx* c, int32_t layer, int32_t kind, const v
     case B200_W_QKV: er = c->qkv_w; ec = h; break;
     case B200_W_QKV_BIAS: er = c->qkv_w; ec = 1; break;
     case B200_W_O: er = h; ec = c->hq * kHeadDim; break;
-    case B200_W_GATE_UP: er = 2 * c->inter; ec = h; break;
+    case B200_W_GATE_UP: case B200_W_GATE_UP_INTERLEAVED: er = 2 * c->inter; ec = h; break;
     case B200_W_DOWN: er = h; ec = c->inter; break;
     case B200_W_LM_HEAD: er = c->vocab_local; ec = h; break;
     default: B200_REQUIRE(false, B200_ERR_INVALID, "set_weight: unknown kind %d", kind);
@@ -307,7 +312,10 @@ extern "C" int b200_set_weight(b200_ctx* c, int32_t layer, int32_t kind, const v
     case B200_W_QKV: c->layers[layer].qkv = p; break;
     case B200_W_QKV_BIAS: c->layers[layer].qkv_b = p; break;
     case B200_W_O: c->layers[layer].o = p; break;
-    case B200_W_GATE_UP: c->layers[layer].gu = p; break;
+    case B200_W_GATE_UP: c->layers[layer].gu = p; c->layers[layer].gu_interleaved = false; break;
+    case B200_W_GATE_UP_INTERLEAVED:
+      B200_REQUIRE(c->inter % 64 == 0, B200_ERR_UNSUPPORTED, "interleaved gate_up needs intermediate_local %% 64 == 0");
+      c->layers[layer].gu = p; c->layers[layer].gu_interleaved = true; break;
     case B200_W_DOWN: c->layers[layer].down = p; break;
   }
   return B200_OK;
@@ -372,15 +380,22 @@ extern "C" int b200_ctx_set_tap(b200_ctx* c, int32_t layer, void* out_hidden, vo
 }
 
 // ---- linear dispatch ----------------------------------------------------------------------------
+static bool tc_path(int T, int n_out, int k, int gemv_max_t) {
+  return T > gemv_max_t && linear_tc_supported(T, n_out, k);
+}
+
 static int linear_any(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
                       __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, int impl, int gemv_max_t, void* ws,
-                      int64_t ws_bytes, cudaStream_t s) {
+                      int64_t ws_bytes, const LinearExtra* ex, cudaStream_t s) {
   if (T == 0) return B200_OK;
-  if (impl == 0) impl = (T <= gemv_max_t || !linear_tc_supported(T, n_out, k)) ? 1 : 2;
-  if (impl == 1) return linear_gemv(x, ldx, w, bias, y, ldy, T, n_out, k, s);
+  if (impl == 0) impl = tc_path(T, n_out, k, gemv_max_t) ? 2 : 1;
+  if (impl == 1) {
+    B200_REQUIRE(!ex || ex->mode == 0, B200_ERR_UNSUPPORTED, "linear: fused epilogues need the tcgen05 path");
+    return linear_gemv(x, ldx, w, bias, y, ldy, T, n_out, k, s);
+  }
   B200_REQUIRE(linear_tc_supported(T, n_out, k), B200_ERR_UNSUPPORTED,
                "linear: tcgen05 path does not support T=%d n_out=%d k=%d", T, n_out, k);
-  return linear_tc(x, ldx, w, bias, y, ldy, T, n_out, k, ws, ws_bytes, s);
+  return linear_tc(x, ldx, w, bias, y, ldy, T, n_out, k, ws, ws_bytes, ex, s);
 }
 
 extern "C" int64_t b200_linear_workspace_bytes(int32_t T, int32_t n_out, int32_t k) {
@@ -394,7 +409,28 @@ extern "C" int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const
   int gm = 0;
   if (const char* e = getenv("B200_GEMV_MAX_T")) gm = atoi(e);
   return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias,
-                    (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, (cudaStream_t)stream);
+                    (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int b200_linear_fused_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y, int64_t ldy,
+                                      int32_t T, int32_t n_out, int32_t k, int32_t mode, const int32_t* positions,
+                                      const int32_t* slot_mapping, const void* cos_sin, void* k_cache_layer,
+                                      void* v_cache_layer, int32_t n_q_heads, int32_t n_kv_heads, int32_t block_size,
+                                      void* ws, int64_t ws_bytes, void* stream) {
+  B200_REQUIRE(x && w && y && T >= 0 && n_out > 0 && k > 0, B200_ERR_INVALID, "linear_fused: bad argument");
+  B200_REQUIRE(mode == 1 || mode == 2, B200_ERR_INVALID, "linear_fused: mode must be 1 (silu*mul) or 2 (rope+kv)");
+  LinearExtra ex;
+  ex.mode = mode;
+  ex.positions = positions;
+  ex.slots = slot_mapping;
+  ex.cos_sin = (const __nv_bfloat16*)cos_sin;
+  ex.kc = (__nv_bfloat16*)k_cache_layer;
+  ex.vc = (__nv_bfloat16*)v_cache_layer;
+  ex.hq = n_q_heads;
+  ex.hkv = n_kv_heads;
+  ex.block_size = block_size;
+  return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias,
+                    (__nv_bfloat16*)y, ldy, T, n_out, k, 2, 0, ws, ws_bytes, &ex, (cudaStream_t)stream);
 }
 
 extern "C" int b200_rmsnorm(const void* x, void* res, const void* w, void* y, int32_t T, int32_t hidden, float eps,
@@ -477,6 +513,15 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     if (rc) return rc;    \
   } while (0)
 
+  // Each tcgen05 linear pulls (a prefix of) the NEXT linear's weights into L2 so that HBM keeps
+  // streaming while the small dependent kernels between two linears run.
+  auto pf = [&](LinearExtra& ex, const void* next, int64_t elems) {
+    if (c->prefetch_cap > 0 && next) {
+      ex.pf_ptr = next;
+      ex.pf_bytes = std::min<int64_t>(elems * 2, c->prefetch_cap);
+    }
+  };
+  const int qn = c->qkv_w, on = h, ok = c->hq * kHeadDim, gn = 2 * c->inter, dn = h, dk = c->inter;
   STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
   for (int l = 0; l < m.n_layers; ++l) {
     const LayerW& L = c->layers[l];
@@ -484,22 +529,64 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       STEP(rmsnorm(c->res, nullptr, L.ln1, c->normed, T, h, m.rms_eps, s));
     else
       STEP(rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
-    STEP(linear_any(c->normed, h, L.qkv, L.qkv_b, c->qkv_buf, c->qkv_w, T, c->qkv_w, h, 0, c->gemv_max_t, c->lin_ws,
-                    c->lin_ws_bytes, s));
     __nv_bfloat16* kcl = c->kc + (int64_t)l * kv_layer_elems;
     __nv_bfloat16* vcl = c->vc + (int64_t)l * kv_layer_elems;
-    STEP(rope_kv_append(c->qkv_buf, a.positions, a.slots, c->cos_sin, kcl, vcl, T, c->hq, c->hkv, m.block_size, s));
+    {  // QKV (+ RoPE + KV append in the epilogue when on the tcgen05 path)
+      LinearExtra ex;
+      const bool tcp = tc_path(T, qn, h, c->gemv_max_t);
+      if (tcp) pf(ex, L.o, (int64_t)on * ok);
+      if (tcp && c->fuse) {
+        ex.mode = 2;
+        ex.positions = a.positions;
+        ex.slots = a.slots;
+        ex.cos_sin = c->cos_sin;
+        ex.kc = kcl;
+        ex.vc = vcl;
+        ex.hq = c->hq;
+        ex.hkv = c->hkv;
+        ex.block_size = m.block_size;
+      }
+      STEP(linear_any(c->normed, h, L.qkv, L.qkv_b, c->qkv_buf, qn, T, qn, h, 0, c->gemv_max_t, c->lin_ws,
+                      c->lin_ws_bytes, &ex, s));
+      if (ex.mode != 2)
+        STEP(rope_kv_append(c->qkv_buf, a.positions, a.slots, c->cos_sin, kcl, vcl, T, c->hq, c->hkv, m.block_size, s));
+    }
     STEP(paged_attn(c->qkv_buf, c->qkv_w, kcl, vcl, a.block_table, a.bt_stride, a.row_to_seq, a.ctx_lens, c->attn_out,
                     c->hq * kHeadDim, T, c->hq, c->hkv, m.block_size, a.max_ctx, scale, c->attn_ws, c->attn_ws_bytes, s));
-    STEP(linear_any(c->attn_out, c->hq * kHeadDim, L.o, nullptr, c->x, h, T, h, c->hq * kHeadDim, 0, c->gemv_max_t,
-                    c->lin_ws, c->lin_ws_bytes, s));
+    {  // O
+      LinearExtra ex;
+      if (tc_path(T, on, ok, c->gemv_max_t)) pf(ex, L.gu, (int64_t)gn * h);
+      STEP(linear_any(c->attn_out, ok, L.o, nullptr, c->x, h, T, on, ok, 0, c->gemv_max_t, c->lin_ws, c->lin_ws_bytes,
+                      &ex, s));
+    }
     if (tp) STEP(b200_allreduce_bf16(c, c->x, (int64_t)T * h, s));
     STEP(rmsnorm(c->x, c->res, L.ln2, c->normed, T, h, m.rms_eps, s));
-    STEP(linear_any(c->normed, h, L.gu, nullptr, c->gu_buf, 2 * c->inter, T, 2 * c->inter, h, 0, c->gemv_max_t,
-                    c->lin_ws, c->lin_ws_bytes, s));
-    STEP(silu_mul(c->gu_buf, c->act, T, c->inter, s));
-    STEP(linear_any(c->act, c->inter, L.down, nullptr, c->x, h, T, h, c->inter, 0, c->gemv_max_t, c->lin_ws,
-                    c->lin_ws_bytes, s));
+    {  // gate_up (+ SiLU*mul in the epilogue over interleaved slabs)
+      LinearExtra ex;
+      const bool tcp = tc_path(T, gn, h, c->gemv_max_t);
+      if (tcp) pf(ex, L.down, (int64_t)dn * dk);
+      if (L.gu_interleaved) {
+        B200_REQUIRE(tcp, B200_ERR_UNSUPPORTED, "interleaved gate_up weights need the tcgen05 path");
+        ex.mode = 1;
+        STEP(linear_any(c->normed, h, L.gu, nullptr, c->act, c->inter, T, gn, h, 0, c->gemv_max_t, c->lin_ws,
+                        c->lin_ws_bytes, &ex, s));
+      } else {
+        STEP(linear_any(c->normed, h, L.gu, nullptr, c->gu_buf, gn, T, gn, h, 0, c->gemv_max_t, c->lin_ws,
+                        c->lin_ws_bytes, &ex, s));
+        STEP(silu_mul(c->gu_buf, c->act, T, c->inter, s));
+      }
+    }
+    {  // down
+      LinearExtra ex;
+      if (tc_path(T, dn, dk, c->gemv_max_t)) {
+        if (l + 1 < m.n_layers)
+          pf(ex, c->layers[l + 1].qkv, (int64_t)qn * h);
+        else
+          pf(ex, c->lm_head, (int64_t)c->vocab_local * h);
+      }
+      STEP(linear_any(c->act, dk, L.down, nullptr, c->x, h, T, dn, dk, 0, c->gemv_max_t, c->lin_ws, c->lin_ws_bytes,
+                      &ex, s));
+    }
     if (tp) STEP(b200_allreduce_bf16(c, c->x, (int64_t)T * h, s));
     if (l == c->tap_layer && c->tap_hidden) {
       B200_CUDA(cudaMemcpyAsync(c->tap_hidden, c->x, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));
@@ -513,7 +600,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     lm_in = c->lm_in;
   }
   STEP(linear_any(lm_in, h, c->lm_head, nullptr, c->logits, c->vocab_local, a.R, c->vocab_local, h, 0, c->gemv_max_t,
-                  c->lin_ws, c->lin_ws_bytes, s));
+                  c->lin_ws, c->lin_ws_bytes, nullptr, s));
   if (!tp) {
     STEP(argmax_rows(c->logits, c->vocab_local, a.R, c->vocab_local, 0, a.out_tokens, nullptr, s));
     if (a.out_logits)

@@ -103,9 +103,22 @@ int linear_gemv(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, con
                 __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, cudaStream_t s);
 bool linear_tc_supported(int T, int n_out, int k);
 int64_t linear_tc_workspace_bytes(int T, int n_out, int k);
+// Optional epilogue fusion / prefetch of the tcgen05 linear (modes: 0 plain, 1 silu*mul over an
+// interleaved gate|up slab, 2 RoPE + KV append over a fused qkv projection).
+struct LinearExtra {
+  int mode = 0;
+  const void* pf_ptr = nullptr;  // next weights to pull into L2
+  int64_t pf_bytes = 0;
+  const int32_t* positions = nullptr;
+  const int32_t* slots = nullptr;
+  const __nv_bfloat16* cos_sin = nullptr;
+  __nv_bfloat16* kc = nullptr;
+  __nv_bfloat16* vc = nullptr;
+  int hq = 0, hkv = 0, block_size = 0;
+};
 int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
               __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, void* ws, int64_t ws_bytes,
-              cudaStream_t s);
+              const LinearExtra* ex, cudaStream_t s);
 int rmsnorm(const __nv_bfloat16* x, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int T,
             int hidden, float eps, cudaStream_t s);
 int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, int T, int hidden, int vocab,

@@ -124,9 +124,99 @@ struct TcParams {
   float* partials;      // [splits][tok_tiles*N][n_out_pad] fp32
   unsigned int* tickets;  // [m_tiles * tok_tiles], zero on entry, zero on exit
   int n_out_pad;
+  // next weights to pull into L2 while this kernel (and the small kernels after it) run
+  const char* pf_ptr;
+  long long pf_bytes;
+  // MODE_ROPE_KV (slab == one 128-wide head of the fused qkv projection)
+  const int32_t* positions;
+  const int32_t* slots;
+  const __nv_bfloat16* cos_sin;
+  __nv_bfloat16* kc;
+  __nv_bfloat16* vc;
+  int hq, hkv, block_size;
 };
 
-template <int N>
+// Epilogue modes (template parameter):
+//  kPlain    y[t][row] = bf16(acc + bias)
+//  kSiluMul  the slab holds 64 gate rows then the 64 matching up rows (B200_W_GATE_UP_INTERLEAVED):
+//            y[t][m_tile*64 + i] = bf16(bf16(silu(bf16(g_i))) * bf16(u_i))          (R5)
+//  kRopeKv   the slab is one head of the fused qkv projection: NeoX RoPE in bf16 arithmetic (R3) on q
+//            and k heads, q rows to y, k/v rows straight into the paged cache at slots[t]
+enum { kPlain = 0, kSiluMul = 1, kRopeKv = 2 };
+
+__device__ __forceinline__ float silu_bf16_dev(float g) { return round_bf16(g / (1.0f + expf(-g))); }
+
+// One thread finalises 4 consecutive slab rows (r4..r4+3, lane = r4/4) of one token.
+template <int MODE>
+__device__ __forceinline__ void finalize4(const TcParams& p, int m_tile, int lane, int tok, float4 a, const float (&bb)[4]) {
+  const int r4 = lane * 4;
+  float v[4] = {round_bf16(a.x + bb[0]), round_bf16(a.y + bb[1]), round_bf16(a.z + bb[2]), round_bf16(a.w + bb[3])};
+  if (MODE == kPlain) {
+    const int row = m_tile * kBlockM + r4;
+    __nv_bfloat16* dst = p.y + (int64_t)tok * p.ldy + row;
+    if (row + 3 < p.n_out && (p.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 7) == 0)) {
+      *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (row + e < p.n_out) dst[e] = __float2bfloat16_rn(v[e]);
+    }
+  } else if (MODE == kSiluMul) {
+    float u[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) u[e] = __shfl_xor_sync(0xffffffffu, v[e], 16);  // lanes 16..31 hold the up rows
+    if (lane < 16) {
+      const int f = m_tile * 64 + r4;                                           // output feature
+      float o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o[e] = silu_bf16_dev(v[e]) * u[e];
+      __nv_bfloat16* dst = p.y + (int64_t)tok * p.ldy + f;
+      if ((p.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 7) == 0)) {
+        *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]));
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) dst[e] = __float2bfloat16_rn(o[e]);
+      }
+    }
+  } else {  // kRopeKv
+    const int head = m_tile;
+    float o[4];
+    if (head < p.hq + p.hkv) {
+      float other[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) other[e] = __shfl_xor_sync(0xffffffffu, v[e], 16);
+      const int i0 = r4 & 63;
+      const __nv_bfloat16* cs = p.cos_sin + (int64_t)p.positions[tok] * kHeadDim;
+      const uint2 cq = *reinterpret_cast<const uint2*>(cs + i0);
+      const uint2 sq = *reinterpret_cast<const uint2*>(cs + 64 + i0);
+      const float c[4] = {bf16lo(cq.x), bf16hi(cq.x), bf16lo(cq.y), bf16hi(cq.y)};
+      const float sn[4] = {bf16lo(sq.x), bf16hi(sq.x), bf16lo(sq.y), bf16hi(sq.y)};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        // lanes 0..15 hold x1 (o1 = x1*c - x2*s), lanes 16..31 hold x2 (o2 = x2*c + x1*s); every op rounds
+        const float a0 = round_bf16(v[e] * c[e]), b0 = round_bf16(other[e] * sn[e]);
+        o[e] = lane < 16 ? round_bf16(a0 - b0) : round_bf16(a0 + b0);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o[e] = v[e];
+    }
+    __nv_bfloat16* dst;
+    if (head < p.hq) {
+      dst = p.y + (int64_t)tok * p.ldy + head * kHeadDim + r4;
+    } else {
+      const int slot = p.slots[tok];
+      if (slot < 0) return;
+      const bool is_k = head < p.hq + p.hkv;
+      const int kvh = is_k ? head - p.hq : head - p.hq - p.hkv;
+      const int64_t blk = slot / p.block_size, off = slot % p.block_size;
+      dst = (is_k ? p.kc : p.vc) + ((blk * p.hkv + kvh) * p.block_size + off) * kHeadDim + r4;
+    }
+    *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]));
+  }
+}
+
+template <int N, int MODE>
 __global__ void __launch_bounds__(kTcThreads)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, TcParams p) {
   constexpr int S = stages_for(N);
@@ -214,17 +304,20 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     }
   } else {
     // ===== epilogue: 4 warps, TMEM lane quadrant = warp % 4 =====
-    pdl_wait();
     const int quad = warp & 3;
-    const int row = m_tile * kBlockM + quad * 32 + lane;   // output feature owned by this thread
+    const int srow = quad * 32 + lane;                      // slab row owned while draining TMEM
     const int tok0 = tok_tile * N;
+    const int wq = warp - 2;
+    pdl_wait();
     if (nkb > 0) {
       mbar_wait(tmem_full, 0);
       tc_fence_after();
     }
     const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
     const bool direct = p.splits == 1;
-    const float b = (direct && p.bias && row < p.n_out) ? __bfloat162float(p.bias[row]) : 0.f;
+    // All MMAs have completed (tmem_full), so the pipeline stages are free: stage the fp32 tile
+    // [token][128 rows] there for the direct case, or spill it to the split-K workspace.
+    float* stg = reinterpret_cast<float*>(smem);
 #pragma unroll
     for (int c = 0; c < N; c += 16) {
       uint32_t r[16];
@@ -235,46 +328,49 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         for (int j = 0; j < 16; ++j) r[j] = 0u;
       }
       if (direct) {
-        if (row < p.n_out) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int t = tok0 + c + j;
-            if (t < p.T) p.y[(int64_t)t * p.ldy + row] = __float2bfloat16_rn(__uint_as_float(r[j]) + b);
-          }
-        }
+        for (int j = 0; j < 16; ++j) stg[(c + j) * kBlockM + srow] = __uint_as_float(r[j]);
       } else {
-        float* dst = p.partials + ((int64_t)split * gridDim.z * N + tok0 + c) * p.n_out_pad + row;
+        float* dst = p.partials + ((int64_t)split * gridDim.z * N + tok0 + c) * p.n_out_pad + m_tile * kBlockM + srow;
 #pragma unroll
         for (int j = 0; j < 16; ++j) dst[(int64_t)j * p.n_out_pad] = __uint_as_float(r[j]);
       }
     }
-    if (!direct) {
+    bool finalize = true;
+    const int tile_id = m_tile * gridDim.z + tok_tile;
+    if (direct) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    } else {
       // deterministic split-K: the last CTA of this (slab, token tile) reduces in split order
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      const int tile_id = m_tile * gridDim.z + tok_tile;
       if (warp == 2 && lane == 0) *ticket_slot = (int)atomicAdd(&p.tickets[tile_id], 1u);
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (*ticket_slot == p.splits - 1) {
-        __threadfence();
-        // 4 warps x 32 lanes: lane owns 4 consecutive features (one float4 per partial row), warp wq
-        // owns tokens wq, wq+4, ...; 4 tokens x `splits` 16-byte L2 loads in flight per thread.
-        const int wq = warp - 2;
-        const int r4 = m_tile * kBlockM + lane * 4;
-        const int tmax = min(N, p.T - tok0);
-        float bb[4] = {0.f, 0.f, 0.f, 0.f};
-        if (p.bias) {
+      finalize = (*ticket_slot == p.splits - 1);
+      if (finalize) __threadfence();
+    }
+    if (finalize) {
+      // 4 warps x 32 lanes: lane owns 4 consecutive slab rows, warp wq owns tokens wq, wq+4, ...
+      const int r4 = lane * 4;
+      const int tmax = min(N, p.T - tok0);
+      float bb[4] = {0.f, 0.f, 0.f, 0.f};
+      if (p.bias) {
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[r4 + e]);
-        }
-        const int64_t split_stride = (int64_t)gridDim.z * N * p.n_out_pad;
-        const bool vec_ok = (r4 + 3 < p.n_out) && (p.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 7) == 0);
-        for (int t = wq; t < tmax; t += 16) {
-          float4 acc[4];
+        for (int e = 0; e < 4; ++e)
+          if (m_tile * kBlockM + r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[m_tile * kBlockM + r4 + e]);
+      }
+      const int64_t split_stride = (int64_t)gridDim.z * N * p.n_out_pad;
+      for (int t = wq; t < tmax; t += 16) {
+        float4 acc[4];
+        if (direct) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            acc[u] = (t + 4 * u < tmax) ? *reinterpret_cast<const float4*>(stg + (t + 4 * u) * kBlockM + r4)
+                                        : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
 #pragma unroll
           for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          const float* src = p.partials + (int64_t)(tok0 + t) * p.n_out_pad + r4;
+          const float* src = p.partials + (int64_t)(tok0 + t) * p.n_out_pad + m_tile * kBlockM + r4;
 #pragma unroll 3
           for (int sp = 0; sp < p.splits; ++sp) {
 #pragma unroll
@@ -288,23 +384,26 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
               }
             }
           }
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int tt = t + 4 * u;
-            if (tt < tmax) {
-              __nv_bfloat16* dst = p.y + (int64_t)(tok0 + tt) * p.ldy + r4;
-              const float o[4] = {acc[u].x + bb[0], acc[u].y + bb[1], acc[u].z + bb[2], acc[u].w + bb[3]};
-              if (vec_ok) {
-                *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]));
-              } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e)
-                  if (r4 + e < p.n_out) dst[e] = __float2bfloat16_rn(o[e]);
-              }
-            }
-          }
         }
-        if (warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int tt = t + 4 * u;
+          // warp-uniform condition: the shuffles inside finalize4 stay convergent
+          if (tt < tmax) finalize4<MODE>(p, m_tile, lane, tok0 + tt, acc[u], bb);
+        }
+      }
+      if (!direct && warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
+    }
+    // This CTA is done streaming: pull (a prefix of) the NEXT linear's weights towards L2 so that HBM
+    // keeps working through this kernel's tail and the small kernels that follow (fire and forget).
+    if (p.pf_bytes > 0) {
+      const long long n_ctas = (long long)gridDim.x * gridDim.y * gridDim.z;
+      const long long cta = blockIdx.x + (long long)gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
+      const long long per = ((p.pf_bytes + n_ctas - 1) / n_ctas + 4095) & ~4095ll;
+      const long long lo = cta * per, hi = min(lo + per, p.pf_bytes);
+      for (long long off = lo + (long long)(wq * 32 + lane) * 4096; off < hi; off += 128ll * 4096) {
+        const uint32_t bytes = (uint32_t)min(4096ll, hi - off) & ~15u;
+        if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.pf_ptr + off), "r"(bytes) : "memory");
       }
     }
     tc_fence_before();
@@ -411,17 +510,26 @@ Plan make_plan(int T, int n_out, int k) {
   return pl;
 }
 
-template <int N>
-int launch_tc(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
+template <int N, int MODE>
+int launch_tc2(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
   static bool attr_set = false;
   const int smem = smem_bytes_for(N);
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  B200_CUDA(launch(linear_tc_kernel<N>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads), (size_t)smem, s,
-                   mw, mx, p));
+  B200_CUDA(launch(linear_tc_kernel<N, MODE>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads), (size_t)smem,
+                   s, mw, mx, p));
   return B200_OK;
+}
+
+template <int N>
+int launch_tc(int mode, const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
+  switch (mode) {
+    case kSiluMul: return launch_tc2<N, kSiluMul>(mw, mx, p, pl, s);
+    case kRopeKv: return launch_tc2<N, kRopeKv>(mw, mx, p, pl, s);
+    default: return launch_tc2<N, kPlain>(mw, mx, p, pl, s);
+  }
 }
 
 }  // namespace
@@ -441,7 +549,8 @@ int64_t linear_tc_workspace_bytes(int T, int n_out, int k) {
 }
 
 int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
-              __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, void* ws, int64_t ws_bytes, cudaStream_t s) {
+              __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, void* ws, int64_t ws_bytes,
+              const LinearExtra* ex, cudaStream_t s) {
   B200_REQUIRE(k % 8 == 0 && ldx % 8 == 0, B200_ERR_UNSUPPORTED, "linear_tc: k and ldx must be multiples of 8");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) % 16 == 0, B200_ERR_INVALID,
                "linear_tc: x and w must be 16-byte aligned");
@@ -449,12 +558,36 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
   const int64_t need = linear_tc_workspace_bytes(T, n_out, k);
   B200_REQUIRE(pl.splits == 1 || (ws && ws_bytes >= need), B200_ERR_INVALID,
                "linear_tc: workspace too small (%lld < %lld)", (long long)ws_bytes, (long long)need);
+  const int mode = ex ? ex->mode : 0;
+  TcParams p = {};
+  if (mode == kSiluMul) {
+    B200_REQUIRE(n_out % kBlockM == 0, B200_ERR_UNSUPPORTED, "linear_tc(silu_mul): n_out=%d must be a multiple of 128", n_out);
+  } else if (mode == kRopeKv) {
+    B200_REQUIRE(ex->positions && ex->slots && ex->cos_sin && ex->kc && ex->vc && ex->block_size > 0 &&
+                     n_out == (ex->hq + 2 * ex->hkv) * kHeadDim,
+                 B200_ERR_INVALID, "linear_tc(rope_kv): bad arguments (n_out=%d, hq=%d, hkv=%d)", n_out, ex->hq, ex->hkv);
+    B200_REQUIRE(ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0, B200_ERR_INVALID,
+                 "linear_tc(rope_kv): y must be 8-byte aligned with ldy %% 4 == 0");
+    p.positions = ex->positions;
+    p.slots = ex->slots;
+    p.cos_sin = ex->cos_sin;
+    p.kc = ex->kc;
+    p.vc = ex->vc;
+    p.hq = ex->hq;
+    p.hkv = ex->hkv;
+    p.block_size = ex->block_size;
+  } else {
+    B200_REQUIRE(mode == kPlain, B200_ERR_INVALID, "linear_tc: unknown epilogue mode %d", mode);
+  }
+  if (ex && ex->pf_ptr && ex->pf_bytes > 0) {
+    p.pf_ptr = static_cast<const char*>(ex->pf_ptr);
+    p.pf_bytes = ex->pf_bytes & ~15ll;
+  }
   CUtensorMap mw, mx;
   int rc = get_map(w, (uint64_t)n_out, (uint64_t)k, (uint64_t)k, kBlockM, &mw);
   if (rc) return rc;
   rc = get_map(x, (uint64_t)T, (uint64_t)k, (uint64_t)ldx, (uint32_t)pl.N, &mx);
   if (rc) return rc;
-  TcParams p;
   p.bias = bias;
   p.y = y;
   p.ldy = ldy;
@@ -466,11 +599,11 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
   p.partials = ws ? reinterpret_cast<float*>(static_cast<char*>(ws) + kCounterBytes) : nullptr;
   p.n_out_pad = pl.n_out_pad;
   switch (pl.N) {
-    case 16: return launch_tc<16>(mw, mx, p, pl, s);
-    case 32: return launch_tc<32>(mw, mx, p, pl, s);
-    case 64: return launch_tc<64>(mw, mx, p, pl, s);
-    case 128: return launch_tc<128>(mw, mx, p, pl, s);
-    default: return launch_tc<256>(mw, mx, p, pl, s);
+    case 16: return launch_tc<16>(mode, mw, mx, p, pl, s);
+    case 32: return launch_tc<32>(mode, mw, mx, p, pl, s);
+    case 64: return launch_tc<64>(mode, mw, mx, p, pl, s);
+    case 128: return launch_tc<128>(mode, mw, mx, p, pl, s);
+    default: return launch_tc<256>(mode, mw, mx, p, pl, s);
   }
 }
 

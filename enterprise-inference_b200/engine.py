@@ -14,6 +14,8 @@ from collections import deque
 from dataclasses import dataclass, field
 from typing import Deque, Dict, List, Optional
 
+import numpy as np
+
 from .runner import StepBatch
 
 
@@ -64,6 +66,7 @@ class Request:
     output_ids: List[int] = field(default_factory=list)
     n_computed: int = 0                 # tokens whose KV is in the cache
     block_table: List[int] = field(default_factory=list)
+    row: int = -1                       # row of the scheduler's block-table mirror while running
     finished: bool = False
     finish_reason: Optional[str] = None
     first_token_time: Optional[float] = None
@@ -77,6 +80,10 @@ class Request:
     @property
     def n_total(self) -> int:
         return len(self.prompt_ids) + len(self.output_ids)
+
+    def token_at(self, p: int) -> int:
+        n = len(self.prompt_ids)
+        return self.prompt_ids[p] if p < n else self.output_ids[p - n]
 
 
 @dataclass
@@ -95,6 +102,27 @@ class Scheduler:
         self.max_model_len = max_model_len
         self.waiting: Deque[Request] = deque()
         self.running: List[Request] = []
+        # numpy mirror of the running sequences' block tables (one row each): the decode fast path
+        # gathers from it instead of walking Python lists
+        self.max_blocks = blocks.blocks_needed(max_model_len) + 1
+        self.bt_np = np.zeros((self.max_seqs + 1, self.max_blocks), dtype=np.int32)
+        self.free_rows: List[int] = list(range(self.max_seqs, -1, -1))
+
+    def _grow(self, req: Request, n_tokens: int) -> None:
+        old = len(req.block_table)
+        self.blocks.grow(req.block_table, n_tokens)
+        if req.row < 0:
+            req.row = self.free_rows.pop()
+            old = 0
+        new = len(req.block_table)
+        if new > old:
+            self.bt_np[req.row, old:new] = req.block_table[old:new]
+
+    def _release(self, req: Request) -> None:
+        self.blocks.release(req.block_table)
+        if req.row >= 0:
+            self.free_rows.append(req.row)
+            req.row = -1
 
     def add(self, req: Request) -> None:
         if len(req.prompt_ids) == 0:
@@ -130,7 +158,7 @@ class Scheduler:
                     continue
                 if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
                     continue
-            self.blocks.grow(req.block_table, req.n_computed + n_new)
+            self._grow(req, req.n_computed + n_new)
             out.append(Scheduled(req, n_new, n_new == remaining))
             budget -= n_new
         # admit
@@ -140,7 +168,7 @@ class Scheduler:
             if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
                 break
             self.waiting.popleft()
-            self.blocks.grow(req.block_table, req.n_computed + n_new)
+            self._grow(req, req.n_computed + n_new)
             self.running.append(req)
             out.append(Scheduled(req, n_new, n_new == req.n_total - req.n_computed))
             budget -= n_new
@@ -148,13 +176,23 @@ class Scheduler:
 
     def _preempt(self, req: Request) -> None:
         self.running.remove(req)
-        self.blocks.release(req.block_table)
+        self._release(req)
         req.n_computed = 0
         self.waiting.appendleft(req)
 
     def build_batch(self, sched: List[Scheduled]) -> StepBatch:
-        b = StepBatch()
         bs = self.blocks.block_size
+        n = len(sched)
+        if all(s.n_new == 1 and s.samples for s in sched):
+            # decode fast path: one row per sequence, vectorised
+            rows = np.fromiter((s.req.row for s in sched), dtype=np.int64, count=n)
+            pos = np.fromiter((s.req.n_computed for s in sched), dtype=np.int32, count=n)
+            ids = np.fromiter((s.req.token_at(s.req.n_computed) for s in sched), dtype=np.int32, count=n)
+            ar = np.arange(n, dtype=np.int32)
+            stride = int(pos.max()) // bs + 1
+            return StepBatch(ids=ids, positions=pos, slots=self.bt_np[rows, pos // bs] * bs + pos % bs,
+                             ctx_lens=pos + 1, row_to_seq=ar, logit_rows=ar, block_tables=self.bt_np[rows, :stride])
+        b = StepBatch()
         for si, s in enumerate(sched):
             r = s.req
             ids = r.all_ids
@@ -196,7 +234,7 @@ class Scheduler:
             if reason:
                 r.finished, r.finish_reason, r.finish_time = True, reason, now
                 self.running.remove(r)
-                self.blocks.release(r.block_table)
+                self._release(r)
                 done.append(r)
         return done
 
@@ -221,7 +259,7 @@ class LLMEngine:
         """Benchmark/test utility: admit a request whose first n_computed tokens are taken as already
         in the KV cache (synthetic prompt KV) — blocks are allocated, nothing is computed."""
         assert 0 <= n_computed < req.n_total
-        self.blocks.grow(req.block_table, n_computed)
+        self.scheduler._grow(req, max(n_computed, 1))
         req.n_computed = n_computed
         self.scheduler.running.append(req)
         self.requests[req.request_id] = req
@@ -234,7 +272,7 @@ class LLMEngine:
         if not sched:
             return []
         batch = self.scheduler.build_batch(sched)
-        if batch.logit_rows:
+        if len(batch.logit_rows):
             sampled = self.runner.step(batch)
         else:  # a prefill chunk that samples nothing still needs one logit row for the ABI
             batch.logit_rows.append(batch.n_tokens - 1)

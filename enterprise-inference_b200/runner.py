@@ -33,6 +33,11 @@ class StepBatch:
     def n_tokens(self):
         return len(self.ids)
 
+    @property
+    def max_ctx(self):
+        c = self.ctx_lens
+        return int(c.max()) if isinstance(c, np.ndarray) else max(c)
+
 
 class ModelRunner:
     def __init__(self, cfg: ModelConfig, device: Optional[torch.device] = None, *, max_tokens: int = 2048,
@@ -99,6 +104,16 @@ class ModelRunner:
         rows, cols = (t.shape[0], t.shape[1]) if t.dim() == 2 else (t.shape[0], 1)
         _abi.check(self.lib.b200_set_weight(self.ctx, layer, kind, t.data_ptr(), rows, cols))
 
+    def _set_gate_up(self, layer: int, gate: torch.Tensor, up: torch.Tensor):
+        """gate|up as 128-row slabs of 64 gate rows + the 64 matching up rows, so that the gate_up
+        linear applies SiLU*mul in its epilogue; plain gate-then-up when I_local is not a multiple of 64."""
+        I, h = gate.shape
+        if I % 64 == 0:
+            il = torch.stack([gate.reshape(I // 64, 64, h), up.reshape(I // 64, 64, h)], dim=1).reshape(2 * I, h)
+            self._set(layer, _abi.W_GATE_UP_INTERLEAVED, il)
+        else:
+            self._set(layer, _abi.W_GATE_UP, torch.cat([gate, up], 0))
+
     def load_weights(self, w: Dict[str, torch.Tensor]):
         """HF-named tensors ([V22] llama.py:437-444 packing: q|k|v -> qkv, gate|up -> gate_up),
         sharded Megatron-style for this TP rank."""
@@ -120,8 +135,7 @@ class ModelRunner:
                                                          w[p + "self_attn.v_proj.bias"][ks]], 0))
             self._set(l, _abi.W_O, w[p + "self_attn.o_proj.weight"][:, qs])
             self._set(l, _abi.W_LN2, w[p + "post_attention_layernorm.weight"])
-            self._set(l, _abi.W_GATE_UP, torch.cat([w[p + "mlp.gate_proj.weight"][is_],
-                                                    w[p + "mlp.up_proj.weight"][is_]], 0))
+            self._set_gate_up(l, w[p + "mlp.gate_proj.weight"][is_], w[p + "mlp.up_proj.weight"][is_])
             self._set(l, _abi.W_DOWN, w[p + "mlp.down_proj.weight"][:, is_])
         self._set(0, _abi.W_FINAL_NORM, w["model.norm.weight"])
         self._set(0, _abi.W_LM_HEAD, w["lm_head.weight"][vs])
@@ -152,7 +166,8 @@ class ModelRunner:
                 self._set(l, _abi.W_QKV_BIAS, rnd(qkv_rows))
             self._set(l, _abi.W_O, rnd(c.hidden, self.hq * c.head_dim))
             self._set(l, _abi.W_LN2, ones)
-            self._set(l, _abi.W_GATE_UP, rnd(2 * self.inter, c.hidden))
+            self._set(l, _abi.W_GATE_UP_INTERLEAVED if self.inter % 64 == 0 else _abi.W_GATE_UP,
+                      rnd(2 * self.inter, c.hidden))
             self._set(l, _abi.W_DOWN, rnd(c.hidden, self.inter))
         self._set(0, _abi.W_FINAL_NORM, ones)
         self._set(0, _abi.W_LM_HEAD, rnd(self.vocab_local, c.hidden))
@@ -175,7 +190,8 @@ class ModelRunner:
     def pack(self, b: StepBatch):
         """Write the dense packed int32 buffer b200_decode_step_host expects into pinned memory."""
         T, R, S = b.n_tokens, len(b.logit_rows), len(b.block_tables)
-        bt_stride = max(max(len(r) for r in b.block_tables), 1)
+        tables = b.block_tables
+        bt_stride = tables.shape[1] if isinstance(tables, np.ndarray) else max(max(len(r) for r in tables), 1)
         a = self._h_meta_np
         a[0:T] = b.ids
         a[T:2 * T] = b.positions
@@ -185,15 +201,18 @@ class ModelRunner:
         a[5 * T:5 * T + R] = b.logit_rows
         o = 5 * T + R
         bt = a[o:o + S * bt_stride].reshape(S, bt_stride)
-        bt.fill(0)
-        for i, row in enumerate(b.block_tables):
-            bt[i, :len(row)] = row
+        if isinstance(tables, np.ndarray):
+            bt[:] = tables
+        else:
+            bt.fill(0)
+            for i, row in enumerate(tables):
+                bt[i, :len(row)] = row
         return T, R, S, bt_stride, o + S * bt_stride
 
     def step(self, b: StepBatch, sync: bool = True) -> np.ndarray:
         """Host-buffer step (the serving path and bench.py's e2e): pinned H2D, step, D2H."""
         T, R, S, bt_stride, n_ints = self.pack(b)
-        max_ctx = max(b.ctx_lens)
+        max_ctx = b.max_ctx
         _abi.check(self.lib.b200_decode_step_host(self.ctx, self._h_meta.data_ptr(), T, S, bt_stride, max_ctx, R,
                                                   self._h_out.data_ptr(), self.stream.cuda_stream))
         self.h2d_bytes_last, self.d2h_bytes_last = n_ints * 4, R * 4

@@ -74,7 +74,10 @@ typedef enum b200_weight_kind {
   B200_W_GATE_UP = 6,   /* [2*I_local, hidden] gate rows then up rows (a8) */
   B200_W_DOWN = 7,      /* [hidden, I_local]                    (a8)  row-parallel */
   B200_W_FINAL_NORM = 8,/* [hidden]                             (a9)  */
-  B200_W_LM_HEAD = 9    /* [vocab_local, hidden]                (a9)  vocab-parallel */
+  B200_W_LM_HEAD = 9,   /* [vocab_local, hidden]                (a9)  vocab-parallel */
+  B200_W_GATE_UP_INTERLEAVED = 10 /* [2*I_local, hidden] in 128-row slabs: 64 gate rows, then the 64 matching
+                                     up rows — lets the gate_up linear apply SiLU*mul in its epilogue (set
+                                     this OR B200_W_GATE_UP; needs I_local % 64 == 0) */
 } b200_weight_kind;
 
 /* Replaces: model construction inside the image's worker (one per TP rank,
@@ -154,6 +157,17 @@ B200_API int64_t b200_linear_workspace_bytes(int32_t n_tokens, int32_t n_out, in
 B200_API int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y,
                      int64_t ldy, int32_t n_tokens, int32_t n_out, int32_t k, int32_t impl,
                      void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Fused epilogues of the tcgen05 linear (what b200_decode_step uses): mode 1 = a8's SiLU*mul over
+ * interleaved gate|up slabs (w as B200_W_GATE_UP_INTERLEAVED; y is [T][n_out/2]); mode 2 = a4+a5:
+ * w is the fused qkv projection, RoPE is applied to q/k heads, q goes to y[T][ldy], k/v rows go to
+ * the paged cache at slot_mapping[t] (pointers unused by mode 1 may be NULL).  Results are
+ * bit-identical to b200_linear_bf16(impl=2) followed by b200_silu_mul / b200_rope_kv_append. */
+B200_API int b200_linear_fused_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y,
+                           int64_t ldy, int32_t n_tokens, int32_t n_out, int32_t k, int32_t mode,
+                           const int32_t* positions, const int32_t* slot_mapping, const void* cos_sin,
+                           void* k_cache_layer, void* v_cache_layer, int32_t n_q_heads, int32_t n_kv_heads,
+                           int32_t block_size, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* (a2) y = rmsnorm(x)*w, or with res != NULL: s=x+res; res=bf16(s); y=rmsnorm(s)*w
  * ([V22] vllm/ir/ops/layernorm.py:10-21,40-58). y may alias x. */

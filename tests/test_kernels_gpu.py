@@ -114,6 +114,67 @@ def test_linear_tcgen05_matches_gemv_bitwise_up_to_order(lib, abi):
     ulp_close(y2, y1.cpu(), max_ulp=1, max_frac=0.02)
 
 
+@pytest.mark.parametrize("T,I,h", [(3, 1024, 512), (64, 14336, 4096), (40, 1792, 1024), (300, 256, 512)])
+def test_linear_fused_silu_mul_is_bit_identical_to_unfused(lib, abi, T, I, h):
+    """gate_up on interleaved slabs with SiLU*mul in the epilogue == tcgen05 linear + b200_silu_mul."""
+    g = torch.Generator().manual_seed(I + T)
+    x = dev(torch.randn(T, h, generator=g).to(BF))
+    gate = (0.05 * torch.randn(I, h, generator=g)).to(BF)
+    up = (0.05 * torch.randn(I, h, generator=g)).to(BF)
+    w_plain = dev(torch.cat([gate, up], 0))
+    w_il = dev(torch.stack([gate.reshape(I // 64, 64, h), up.reshape(I // 64, 64, h)], dim=1).reshape(2 * I, h))
+    wsb = lib.b200_linear_workspace_bytes(T, 2 * I, h)
+    ws = torch.zeros(wsb, dtype=torch.uint8, device="cuda")
+    gu = torch.empty(T, 2 * I, dtype=BF, device="cuda")
+    ref = torch.empty(T, I, dtype=BF, device="cuda")
+    got = torch.full((T, I), float("nan"), dtype=BF, device="cuda")
+    sync_check(abi, lib.b200_linear_bf16(x.data_ptr(), h, w_plain.data_ptr(), None, gu.data_ptr(), 2 * I, T, 2 * I, h, 2,
+                                         ws.data_ptr(), wsb, None))
+    sync_check(abi, lib.b200_silu_mul(gu.data_ptr(), ref.data_ptr(), T, I, None))
+    sync_check(abi, lib.b200_linear_fused_bf16(x.data_ptr(), h, w_il.data_ptr(), None, got.data_ptr(), I, T, 2 * I, h, 1,
+                                               None, None, None, None, None, 0, 0, 0, ws.data_ptr(), wsb, None))
+    assert torch.equal(got, ref)
+    # and the activation math against the oracle on the same linear output (the linear itself is
+    # checked against the oracle in test_linear_tcgen05; through silu a 1-ulp flip of g is amplified)
+    ulp_close(got, O.silu_mul(gu.cpu()), max_ulp=1, max_frac=0.005)
+
+
+@pytest.mark.parametrize("T,hq,hkv,h,bias", [(5, 4, 1, 512, False), (64, 32, 8, 4096, False), (33, 5, 1, 640, True),
+                                              (200, 16, 2, 1024, False)])
+def test_linear_fused_rope_kv_is_bit_identical_to_unfused(lib, abi, T, hq, hkv, h, bias):
+    """qkv projection with RoPE + paged KV append in the epilogue == tcgen05 linear + b200_rope_kv_append."""
+    g = torch.Generator().manual_seed(T + hq)
+    n_out, bs, nb = (hq + 2 * hkv) * 128, 128, 6
+    x = dev(torch.randn(T, h, generator=g).to(BF))
+    w = dev((0.05 * torch.randn(n_out, h, generator=g)).to(BF))
+    b = dev(torch.randn(n_out, generator=g).to(BF)) if bias else None
+    pos = torch.randint(0, 700, (T,), generator=g).to(torch.int32)
+    slots_all = torch.randperm(nb * bs, generator=g)[:T].to(torch.int32)
+    slots_all[T // 2] = -1
+    posd, slotd = dev(pos), dev(slots_all)
+    cs = dev(O.cos_sin_cache(O.CONFIGS["tiny"], 1024))
+    wsb = lib.b200_linear_workspace_bytes(T, n_out, h)
+    ws = torch.zeros(wsb, dtype=torch.uint8, device="cuda")
+    out = {}
+    for fused in (False, True):
+        y = torch.zeros(T, n_out, dtype=BF, device="cuda")
+        kc = torch.zeros(nb, hkv, bs, 128, dtype=BF, device="cuda")
+        vc = torch.zeros_like(kc)
+        if fused:
+            sync_check(abi, lib.b200_linear_fused_bf16(x.data_ptr(), h, w.data_ptr(), abi.ptr(b), y.data_ptr(), n_out, T, n_out, h,
+                                                       2, posd.data_ptr(), slotd.data_ptr(), cs.data_ptr(), kc.data_ptr(),
+                                                       vc.data_ptr(), hq, hkv, bs, ws.data_ptr(), wsb, None))
+        else:
+            sync_check(abi, lib.b200_linear_bf16(x.data_ptr(), h, w.data_ptr(), abi.ptr(b), y.data_ptr(), n_out, T, n_out, h, 2,
+                                                 ws.data_ptr(), wsb, None))
+            sync_check(abi, lib.b200_rope_kv_append(y.data_ptr(), posd.data_ptr(), slotd.data_ptr(), cs.data_ptr(),
+                                                    kc.data_ptr(), vc.data_ptr(), T, hq, hkv, bs, None))
+        out[fused] = (y[:, :hq * 128].clone(), kc, vc)
+    for a, bb in zip(out[True], out[False]):
+        assert torch.equal(a, bb)
+    assert out[True][1].any() and out[True][2].any()
+
+
 def test_linear_is_linear_at_full_width(lib, abi):
     """Size-independent property at the 8B down-proj shape: W(a*x) == a*W(x) for a power of two
     (exact in bf16/fp32), and column-sliced leading dimension works."""
