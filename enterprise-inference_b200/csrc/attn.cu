@@ -13,6 +13,8 @@
 //
 // Replaces: paged_attention_v1/v2 CPU kernels / IPEX single_query_cached_kv_attention of the
 // vLLM-CPU image ([V22] vllm/v1/attention/backends/cpu_attn.py:377-396).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -304,15 +306,54 @@ int launch_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, co
 
 }  // namespace
 
-int64_t paged_attn_workspace_bytes(int T, int hq, int max_ctx, int block_size) {
-  (void)block_size;
-  // upper bound over every hkv >= 1: n_splits <= 64
-  int ns, tps;
-  split_plan(T, 1, max_ctx, &ns, &tps);
-  return (int64_t)T * hq * ns * (kHeadDim + 2) * sizeof(float) + 256;
+// ---- tcgen05 variant (attn_tc.cu) -----------------------------------------------------------
+bool paged_attn_tc_supported(int hq, int hkv, int block_size);
+int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+                  const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                  __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
+                  void* ws, int64_t ws_bytes, cudaStream_t s);
+
+// 128-token tiles, one CTA per SM: split until about one wave of CTAs exists.
+void attn_split_plan_tc(int T, int hkv, int max_ctx, int* n_splits, int* tiles_per_split) {
+  const int tiles = pow2_at_least(max(max_ctx, 1), 128) / 128;
+  const int ctas = max(T * hkv, 1);
+  int s = (kNumSMs + ctas - 1) / ctas;
+  s = max(1, min(s, tiles));
+  *tiles_per_split = (tiles + s - 1) / s;
+  *n_splits = (tiles + *tiles_per_split - 1) / *tiles_per_split;
 }
 
-int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+int launch_attn_merge(const float* part_o, const float* part_ml, __nv_bfloat16* out, int64_t ldo, int T, int hq,
+                      int n_splits, cudaStream_t s) {
+  B200_CUDA(launch(attn_merge_kernel, dim3(hq, T), dim3(kHeadDim), 0, s, part_o, part_ml, out, ldo, hq, n_splits));
+  return B200_OK;
+}
+
+static bool use_tc_attn(int hq, int hkv, int block_size) {
+  static const int env = getenv("B200_ATTN_TC") ? atoi(getenv("B200_ATTN_TC")) : 1;
+  return env != 0 && paged_attn_tc_supported(hq, hkv, block_size);
+}
+
+// Bytes of split-KV scratch one launch of this shape uses (0: a single split writes the output).
+int64_t paged_attn_scratch_need(int T, int hq, int hkv, int block_size, int max_ctx) {
+  int ns, tps;
+  if (use_tc_attn(hq, hkv, block_size))
+    attn_split_plan_tc(max(T, 1), hkv, max_ctx, &ns, &tps);
+  else
+    split_plan(max(T, 1), hkv, max_ctx, &ns, &tps);
+  return ns > 1 ? (int64_t)T * hq * ns * (kHeadDim + 2) * (int64_t)sizeof(float) : 0;
+}
+
+int64_t paged_attn_workspace_bytes(int T, int hq, int max_ctx, int block_size) {
+  (void)block_size;
+  // upper bound over every hkv >= 1 and both kernels' split plans
+  int ns, tps, ns2;
+  split_plan(T, 1, max_ctx, &ns, &tps);
+  attn_split_plan_tc(T, 1, max_ctx, &ns2, &tps);
+  return (int64_t)T * hq * max(ns, ns2) * (kHeadDim + 2) * sizeof(float) + 256;
+}
+
+static int paged_attn_cc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
                void* ws, int64_t ws_bytes, cudaStream_t s) {
@@ -355,6 +396,19 @@ int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, con
     B200_CUDA(launch(attn_merge_kernel, dim3(hq, T), dim3(kHeadDim), 0, s, (const float*)part_o,
                      (const float*)part_ml, out, ldo, hq, n_splits));
   return B200_OK;
+}
+
+
+
+int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+               const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+               __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
+               void* ws, int64_t ws_bytes, cudaStream_t s) {
+  if (use_tc_attn(hq, hkv, block_size))
+    return paged_attn_tc(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv, block_size,
+                         max_ctx, scale, ws, ws_bytes, s);
+  return paged_attn_cc(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv, block_size,
+                       max_ctx, scale, ws, ws_bytes, s);
 }
 
 }  // namespace b200
@@ -404,14 +458,11 @@ extern "C" int b200_paged_attn_decode_static(const void* q, int64_t ldq, const v
   B200_REQUIRE(n_tokens >= 0 && n_q_heads > 0 && n_kv_heads > 0 && max_ctx_len > 0, B200_ERR_INVALID,
                "paged_attn_static: bad sizes");
   // exact need of this launch (0 when a single split writes the output directly)
-  int n_splits = 1, tps = 1;
-  split_plan(n_tokens > 0 ? n_tokens : 1, n_kv_heads, max_ctx_len, &n_splits, &tps);
-  const int64_t need =
-      n_splits > 1 ? (int64_t)n_tokens * n_q_heads * n_splits * (kHeadDim + 2) * (int64_t)sizeof(float) : 0;
+  const int64_t need = paged_attn_scratch_need(n_tokens, n_q_heads, n_kv_heads, block_size, max_ctx_len);
   B200_REQUIRE(need <= kStaticScratchBytes, B200_ERR_UNSUPPORTED,
                "paged_attn_static: this shape needs %lld bytes of split scratch, the built-in array holds %lld "
-               "(rows=%d q_heads=%d splits=%d); use b200_paged_attn_decode with a caller workspace",
-               (long long)need, (long long)kStaticScratchBytes, n_tokens, n_q_heads, n_splits);
+               "(rows=%d q_heads=%d); use b200_paged_attn_decode with a caller workspace",
+               (long long)need, (long long)kStaticScratchBytes, n_tokens, n_q_heads);
   int dev = -1;
   B200_CUDA(cudaGetDevice(&dev));
   B200_REQUIRE(dev >= 0 && dev < kMaxDevices, B200_ERR_UNSUPPORTED, "paged_attn_static: device ordinal %d >= %d", dev,

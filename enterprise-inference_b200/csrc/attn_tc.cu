@@ -1,0 +1,434 @@
+// (a6) Paged attention for single-query rows on the 5th-gen tensor cores (tcgen05 + TMEM).
+//
+// The CUDA-core kernel in attn.cu is compute bound (fp32 FMA + shuffles per cached token); this
+// one keeps the math on the tensor pipe so that the kernel is bound by the KV stream again.
+// Bound: HBM.  Algorithmic bytes per launch = sum over rows of ctx_len * n_kv_heads * 128 * 2 * 2.
+//
+// Shapes are swapped so that the 128 cached tokens of a tile fill the UMMA M dimension:
+//   S^T[128 tok][16]  = K_tile[128 tok x 128 dim] . Q^T          (A = K, K-major;  B = Q padded to 16 heads)
+//   O^T[128 dim][16]  = V_tile^T[128 dim x 128 tok] . P^T        (A = V, MN-major; B = P, 16 heads x 128 tok)
+// K and V tiles arrive by TMA (cp.async.bulk.tensor, SWIZZLE_128B, two 64-dim halves each) straight
+// from the paged cache — a (block, kv head) tile is one box — into a 3-stage ring (64 KiB per stage).
+// 128 softmax threads own one token (TMEM lane) each for S and one head-dim each for O: scores are
+// read with tcgen05.ld, scaled, masked and exponentiated in fp32 (online softmax, running max per
+// head shared through smem), P is written back to smem as TWO bf16 terms (hi + lo, so that P keeps
+// ~16 mantissa bits: R4 of the oracle keeps P in fp32) and the running output is rescaled in
+// registers, so TMEM never needs a read-modify-write.  GQA: the G query heads of the kv head share
+// every K/V byte.  Split-KV + LSE merge as in attn.cu (same workspace layout, same merge kernel).
+//
+// Replaces: paged_attention_v1/v2 CPU kernels of the vLLM-CPU image
+// ([V22] vllm/v1/attention/backends/cpu_attn.py:377-396).
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+int get_tensor_map_2d(const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows, CUtensorMap* out);
+void attn_split_plan_tc(int T, int hkv, int max_ctx, int* n_splits, int* tiles_per_split);
+int launch_attn_merge(const float* part_o, const float* part_ml, __nv_bfloat16* out, int64_t ldo, int T, int hq,
+                      int n_splits, cudaStream_t s);
+
+namespace {
+
+constexpr int kTileTok = 128;
+constexpr int kKvStages = 3;
+constexpr int kHalfBytes = kTileTok * 64 * 2;     // one [128 tok][64 dim] swizzled sub-tile: 16 KiB
+constexpr int kStageBytes = 4 * kHalfBytes;       // K lo|hi dims, V lo|hi dims: 64 KiB
+constexpr int kSmallTile = 16 * 64 * 2;           // one [16 heads][64] swizzled sub-tile: 2 KiB
+constexpr int kThreads = 192;
+constexpr int kNPad = 16;                         // heads padded to the UMMA N
+constexpr uint32_t kTmemCols = 64;                // S0 | S1 | O | (spare), 16 columns each
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra.uni WAIT_DONE;\n"
+      "bra.uni WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout).
+//  K-major  operand: rows are 128 B, 8-row groups SBO = 1024 B apart, LBO unused (1).
+//  MN-major operand: 64 MN elements (128 B) x 8 K rows per swizzle atom; K groups SBO = 1024 B apart,
+//                    the next 64-element MN atom LBO bytes away.
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// bf16 x bf16 -> fp32, M = 128, N = 16; a_major selects K-major (0) or MN-major (1) for A
+__host__ __device__ constexpr uint32_t make_idesc(int a_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)(kNPad >> 3) << 17) |
+         ((uint32_t)(128 >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// byte offset of element (row r < 16, column c < 128) inside a [16][128] bf16 operand stored as two
+// K-major SWIZZLE_128B sub-tiles of 64 columns (Q and P operands)
+__device__ __forceinline__ uint32_t small_off(int r, int c) {
+  const int sub = c >> 6, cc = c & 63;
+  const int chunk = (cc >> 3) ^ (r & 7);
+  return sub * kSmallTile + (r >> 3) * 1024 + (r & 7) * 128 + chunk * 16 + (cc & 7) * 2;
+}
+
+struct Smem {
+  // dynamic, 1024-aligned: kv[kKvStages][kStageBytes] | q[2*kSmallTile] | p_hi[2][2*kSmallTile] | p_lo[2][...]
+  // followed by the barriers and small exchange areas (see carve-up in the kernel)
+};
+
+template <int G>
+__global__ void __launch_bounds__(kThreads, 1)
+paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
+                     const __nv_bfloat16* __restrict__ q, int64_t ldq, const int32_t* __restrict__ block_table,
+                     int bt_stride, const int32_t* __restrict__ row_to_seq, const int32_t* __restrict__ ctx_lens,
+                     __nv_bfloat16* __restrict__ out, int64_t ldo, int hkv, int block_size, int tiles_per_split,
+                     int n_splits, float scale, float* __restrict__ part_o, float* __restrict__ part_ml) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* kv = smem;
+  unsigned char* qs = kv + kKvStages * kStageBytes;
+  unsigned char* p_hi = qs + 2 * kSmallTile;              // [2 buffers][2 sub-tiles]
+  unsigned char* p_lo = p_hi + 2 * 2 * kSmallTile;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(p_lo + 2 * 2 * kSmallTile);
+  uint64_t* k_full = bars;                   // [kKvStages]
+  uint64_t* v_full = k_full + kKvStages;     // [kKvStages]
+  uint64_t* kv_free = v_full + kKvStages;    // [kKvStages]
+  uint64_t* s_full = kv_free + kKvStages;    // [2]
+  uint64_t* p_ready = s_full + 2;            // [2]
+  uint64_t* o_full = p_ready + 2;            // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+  float* xmax = reinterpret_cast<float*>(tmem_slot + 2);   // [4 warps][8 heads]
+  float* xsum = xmax + 32;                                  // [4 warps][8 heads]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int split = blockIdx.x, kvh = blockIdx.y, t = blockIdx.z;
+  const int hq = hkv * G;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kKvStages; ++s) {
+      mbar_init(&k_full[s], 1);
+      mbar_init(&v_full[s], 1);
+      mbar_init(&kv_free[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&s_full[s], 1);
+      mbar_init(&p_ready[s], 128);
+    }
+    mbar_init(o_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  // zero the small operand tiles (Q, P hi/lo): rows >= G must not feed NaNs into the unused columns
+  for (int i = threadIdx.x; i < (2 + 8) * kSmallTile / 16; i += kThreads)
+    reinterpret_cast<uint4*>(qs)[i] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+  pdl_wait();               // q comes from the previous kernel; everything above overlapped its tail
+  pdl_launch_dependents();
+  // stage Q (G heads x 128 dims) as the swizzled K-major B operand of S^T = K . Q^T
+  for (int i = threadIdx.x; i < G * 16; i += kThreads) {
+    const int g = i >> 4, ch = i & 15;   // 16-byte chunk ch of head g
+    const uint4 v = *reinterpret_cast<const uint4*>(q + (int64_t)blockIdx.z * ldq + (blockIdx.y * G + g) * kHeadDim + ch * 8);
+    *reinterpret_cast<uint4*>(qs + small_off(g, ch * 8)) = v;
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int ctx = ctx_lens[t];
+  const int seq = row_to_seq ? row_to_seq[t] : t;
+  const int n_tiles_total = (ctx + kTileTok - 1) / kTileTok;
+  const int tile_begin = split * tiles_per_split;
+  const int n_tiles = max(min(tile_begin + tiles_per_split, n_tiles_total) - tile_begin, 0);
+  const int32_t* bt = block_table + (int64_t)seq * bt_stride;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0 && n_tiles > 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+      for (int i = 0; i < n_tiles; ++i) {
+        const int st = i % kKvStages;
+        if (i >= kKvStages) mbar_wait(&kv_free[st], ((i / kKvStages) - 1) & 1);
+        const int tok0 = (tile_begin + i) * kTileTok;
+        const int blk = bt[tok0 / block_size];
+        const int row0 = (blk * hkv + kvh) * block_size + (tok0 % block_size);
+        unsigned char* sb = kv + st * kStageBytes;
+        mbar_expect_tx(&k_full[st], 2 * kHalfBytes);
+        tma_load_2d(sb, &map_k, 0, row0, &k_full[st]);
+        tma_load_2d(sb + kHalfBytes, &map_k, 64, row0, &k_full[st]);
+        mbar_expect_tx(&v_full[st], 2 * kHalfBytes);
+        tma_load_2d(sb + 2 * kHalfBytes, &map_v, 0, row0, &v_full[st]);
+        tma_load_2d(sb + 3 * kHalfBytes, &map_v, 64, row0, &v_full[st]);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread), software pipelined: S(i+1) is issued before waiting for P(i) =====
+    if (lane == 0 && n_tiles > 0) {
+      constexpr uint32_t idesc_qk = make_idesc(0);
+      constexpr uint32_t idesc_pv = make_idesc(1);
+      const uint32_t q_addr = smem_u32(qs);
+      auto issue_s = [&](int i) {
+        const int st = i % kKvStages;
+        mbar_wait(&k_full[st], (i / kKvStages) & 1);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(kv + st * kStageBytes);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
+          const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
+          tc_mma(tmem_base + (i & 1) * 16, make_desc(k_addr + ao, 16, 1024), make_desc(q_addr + bo, 16, 1024), idesc_qk,
+                 j ? 1u : 0u);
+        }
+        tc_commit(&s_full[i & 1]);
+      };
+      issue_s(0);
+      for (int i = 0; i < n_tiles; ++i) {
+        if (i + 1 < n_tiles) issue_s(i + 1);
+        const int st = i % kKvStages;
+        mbar_wait(&v_full[st], (i / kKvStages) & 1);
+        mbar_wait(&p_ready[i & 1], (i >> 1) & 1);
+        tc_fence_after();
+        const uint32_t v_addr = smem_u32(kv + st * kStageBytes + 2 * kHalfBytes);
+        const uint32_t ph = smem_u32(p_hi + (i & 1) * 2 * kSmallTile);
+        const uint32_t pl = smem_u32(p_lo + (i & 1) * 2 * kSmallTile);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {  // 16 tokens per step: two 8-token K groups of the MN-major V tile
+          const uint64_t da = make_desc(v_addr + j * 2048, kHalfBytes, 1024);
+          const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
+          tc_mma(tmem_base + 32, da, make_desc(ph + bo, 16, 1024), idesc_pv, j ? 1u : 0u);
+          tc_mma(tmem_base + 32, da, make_desc(pl + bo, 16, 1024), idesc_pv, 1u);
+        }
+        tc_commit(&kv_free[st]);  // K and V of this stage are no longer read
+        tc_commit(o_full);
+      }
+    }
+  } else {
+    // ===== softmax / output: 128 threads; thread = token (S lanes) and = head dim (O lanes) =====
+    const int quad = warp & 3;
+    const int tau = quad * 32 + lane;   // TMEM lane
+    const int wq = warp - 2;
+    float m_run[G], l_run[G], acc[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      m_run[g] = -INFINITY;
+      l_run[g] = 0.f;
+      acc[g] = 0.f;
+    }
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    for (int i = 0; i < n_tiles; ++i) {
+      const int st = i % kKvStages;
+      const int tok0 = (tile_begin + i) * kTileTok;
+      const int n_valid = min(kTileTok, ctx - tok0);
+      mbar_wait(&s_full[i & 1], (i >> 1) & 1);
+      tc_fence_after();
+      uint32_t r[16];
+      tmem_ld16(lane_addr + (i & 1) * 16, r);
+      float sc[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g) sc[g] = tau < n_valid ? __uint_as_float(r[g]) * scale : -INFINITY;
+      // tile max per head over the 128 tokens
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const float wm = warp_max(sc[g]);
+        if (lane == 0) xmax[wq * 8 + g] = wm;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      float alpha[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const float tm = fmaxf(fmaxf(xmax[g], xmax[8 + g]), fmaxf(xmax[16 + g], xmax[24 + g]));
+        const float m_new = fmaxf(m_run[g], tm);   // finite: token tok0 of an active tile is valid
+        alpha[g] = __expf(m_run[g] - m_new);       // 0 on the first tile
+        m_run[g] = m_new;
+        const float pv = __expf(sc[g] - m_new);    // 0 for masked tokens
+        l_run[g] = l_run[g] * alpha[g] + pv;
+        const float hi = round_bf16(pv);
+        const float lo = pv - hi;
+        const uint32_t off = small_off(g, tau) + (i & 1) * 2 * kSmallTile;
+        *reinterpret_cast<__nv_bfloat16*>(p_hi + off) = __float2bfloat16_rn(hi);
+        *reinterpret_cast<__nv_bfloat16*>(p_lo + off) = __float2bfloat16_rn(lo);
+      }
+      if (n_valid < kTileTok) {
+        // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor
+        // core) — wait for the tile, then zero this thread's row if it is past the end
+        mbar_wait(&v_full[st], (i / kKvStages) & 1);
+        if (tau >= n_valid) {
+          unsigned char* vb = kv + st * kStageBytes + 2 * kHalfBytes;
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+              *reinterpret_cast<uint4*>(vb + h2 * kHalfBytes + tau * 128 + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
+      tc_fence_before();
+      mbar_arrive(&p_ready[i & 1]);
+      // O_tile^T[dim = tau][head]: fold into the running output in registers
+      mbar_wait(o_full, i & 1);
+      tc_fence_after();
+      tmem_ld16(lane_addr + 32, r);
+#pragma unroll
+      for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha[g] + __uint_as_float(r[g]);
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // xmax is rewritten by the next tile
+    }
+    // total l per head: sum the per-token partial sums over the 128 threads
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const float ws = warp_sum(l_run[g]);
+      if (lane == 0) xsum[wq * 8 + g] = ws;
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    const int d = tau;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const float l = xsum[g] + xsum[8 + g] + xsum[16 + g] + xsum[24 + g];
+      const int head = kvh * G + g;
+      if (n_splits == 1) {
+        out[(int64_t)t * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? acc[g] / l : 0.f);
+      } else {
+        const int64_t pi = ((int64_t)t * hq + head) * n_splits + split;
+        part_o[pi * kHeadDim + d] = acc[g];
+        if (d == 0) {
+          part_ml[pi * 2] = m_run[g];
+          part_ml[pi * 2 + 1] = l;
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+  }
+}
+
+constexpr int kAttnTcSmem = kKvStages * kStageBytes + (2 + 8) * kSmallTile + 512 + 1024;
+
+template <int G>
+int launch_attn_tc(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
+                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                   __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
+                   float* part_o, float* part_ml, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnTcSmem));
+    attr_set = true;
+  }
+  B200_CUDA(launch(paged_attn_tc_kernel<G>, dim3(n_splits, hkv, T), dim3(kThreads), (size_t)kAttnTcSmem, s, mk, mv, q,
+                   ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, scale,
+                   part_o, part_ml));
+  return B200_OK;
+}
+
+}  // namespace
+
+bool paged_attn_tc_supported(int hq, int hkv, int block_size) {
+  if (hkv <= 0 || hq % hkv) return false;
+  const int G = hq / hkv;
+  return block_size % kTileTok == 0 && (G == 1 || G == 2 || G == 4 || G == 5 || G == 8);
+}
+
+int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+                  const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                  __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
+                  void* ws, int64_t ws_bytes, cudaStream_t s) {
+  B200_REQUIRE(paged_attn_tc_supported(hq, hkv, block_size), B200_ERR_UNSUPPORTED, "attn_tc: unsupported shape");
+  B200_REQUIRE(ldq % 8 == 0, B200_ERR_INVALID, "attn_tc: ldq must be a multiple of 8");
+  if (T == 0) return B200_OK;
+  int n_splits, tps;
+  attn_split_plan_tc(T, hkv, max_ctx, &n_splits, &tps);
+  float* part_o = nullptr;
+  float* part_ml = nullptr;
+  if (n_splits > 1) {
+    const int64_t need = (int64_t)T * hq * n_splits * (kHeadDim + 2) * sizeof(float);
+    B200_REQUIRE(ws && ws_bytes >= need, B200_ERR_INVALID, "attn_tc: workspace too small (%lld < %lld)",
+                 (long long)ws_bytes, (long long)need);
+    part_o = static_cast<float*>(ws);
+    part_ml = part_o + (int64_t)T * hq * n_splits * kHeadDim;
+  }
+  // The cache is addressed as rows of 128 dims; the row bound is only an upper limit for TMA's
+  // out-of-bounds logic (rows actually touched come from the block table).
+  CUtensorMap mk, mv;
+  const uint64_t rows = 1ull << 31;
+  int rc = get_tensor_map_2d(kc, rows, kHeadDim, kHeadDim, kTileTok, &mk);
+  if (rc) return rc;
+  rc = get_tensor_map_2d(vc, rows, kHeadDim, kHeadDim, kTileTok, &mv);
+  if (rc) return rc;
+  const int G = hq / hkv;
+#define B200_ATTN_TC_CASE(g)                                                                                        \
+  case g:                                                                                                           \
+    rc = launch_attn_tc<g>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv, block_size, \
+                           n_splits, tps, scale, part_o, part_ml, s);                                               \
+    break;
+  switch (G) {
+    B200_ATTN_TC_CASE(1)
+    B200_ATTN_TC_CASE(2)
+    B200_ATTN_TC_CASE(4)
+    B200_ATTN_TC_CASE(5)
+    B200_ATTN_TC_CASE(8)
+    default: rc = B200_ERR_UNSUPPORTED;
+  }
+#undef B200_ATTN_TC_CASE
+  if (rc) return rc;
+  if (n_splits > 1) return launch_attn_merge(part_o, part_ml, out, ldo, T, hq, n_splits, s);
+  return B200_OK;
+}
+
+}  // namespace b200

@@ -534,6 +534,11 @@ int launch_tc(int mode, const CUtensorMap& mw, const CUtensorMap& mx, const TcPa
 
 }  // namespace
 
+// shared with attn_tc.cu: [rows][cols] bf16 (row stride ld), box [box_rows][64], SWIZZLE_128B
+int get_tensor_map_2d(const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows, CUtensorMap* out) {
+  return get_map(ptr, rows, cols, ld, box_rows, out);
+}
+
 bool linear_tc_supported(int T, int n_out, int k) {
   if (T < 1 || n_out < 1) return false;
   if (k % 8 != 0) return false;  // TMA global strides are multiples of 16 bytes

@@ -281,9 +281,10 @@ def test_argmax_exact_with_ties(lib, abi):
 
 
 # ---------------------------------------------------------------------------------------------
-def run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv, max_ctx_hint=None, seed=0):
-    """q [T,hq,128]; K,V per row: list of [n,hkv,128] -> scatter into a shuffled paged cache."""
-    T, bs = q.shape[0], 128
+def run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv, max_ctx_hint=None, seed=0, bs=128):
+    """q [T,hq,128]; K,V per row: list of [n,hkv,128] -> scatter into a shuffled paged cache.
+    bs=128 takes the tcgen05 kernel, bs=64 the CUDA-core kernel."""
+    T = q.shape[0]
     nblk = [(n + bs - 1) // bs for n in ctx_lens]
     total = sum(nblk) + 3
     perm = torch.randperm(total, generator=torch.Generator().manual_seed(seed)).tolist()
@@ -311,15 +312,16 @@ def run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv, max_ctx_hint=None, seed=0):
     return out.cpu().view(T, hq, 128)
 
 
+@pytest.mark.parametrize("bs", [128, 64])
 @pytest.mark.parametrize("hq,hkv", [(4, 1), (5, 1), (16, 2), (8, 8), (4, 2)])
 @pytest.mark.parametrize("ctx_lens", [[1], [63, 64, 65], [128, 129, 1], [1000, 17, 4097]])
-def test_paged_attention_vs_oracle(lib, abi, hq, hkv, ctx_lens):
+def test_paged_attention_vs_oracle(lib, abi, hq, hkv, ctx_lens, bs):
     g = torch.Generator().manual_seed(hq * 100 + hkv + len(ctx_lens))
     T = len(ctx_lens)
     q = torch.randn(T, hq, 128, generator=g).to(BF)
     K = [torch.randn(n, hkv, 128, generator=g).to(BF) for n in ctx_lens]
     V = [torch.randn(n, hkv, 128, generator=g).to(BF) for n in ctx_lens]
-    got = run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv)
+    got = run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv, bs=bs)
     want = torch.stack([O.attend(q[t], K[t], V[t], ctx_lens[t], 128 ** -0.5) for t in range(T)])
     assert torch.isfinite(got.float()).all()
     ulp_close(got, want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)

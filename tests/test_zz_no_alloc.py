@@ -20,9 +20,8 @@ pytestmark = pytest.mark.gpu
 BF = torch.bfloat16
 
 
-def make_case(T, hq, hkv, ctx_lens, seed):
+def make_case(T, hq, hkv, ctx_lens, seed, bs=128):
     g = torch.Generator().manual_seed(seed)
-    bs = 128
     nblk = [(n + bs - 1) // bs for n in ctx_lens]
     total = sum(nblk) + 2
     kc = torch.randn(total, hkv, bs, 128, generator=g).to(BF).cuda()
@@ -35,21 +34,22 @@ def make_case(T, hq, hkv, ctx_lens, seed):
             bt[t, j] = next(perm)
     q = torch.randn(T, hq * 128, generator=g).to(BF).cuda()
     return dict(q=q, kc=kc, vc=vc, bt=bt.cuda(), cl=torch.tensor(ctx_lens, dtype=torch.int32).cuda(), stride=stride,
-                T=T, hq=hq, hkv=hkv, max_ctx=max(ctx_lens))
+                T=T, hq=hq, hkv=hkv, max_ctx=max(ctx_lens), bs=bs)
 
 
 def run_both(lib, abi, c):
     T, hq, hkv = c["T"], c["hq"], c["hkv"]
-    ws_bytes = lib.b200_paged_attn_workspace_bytes(T, hq, c["max_ctx"], 128)
+    bs = c["bs"]
+    ws_bytes = lib.b200_paged_attn_workspace_bytes(T, hq, c["max_ctx"], bs)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
     ref = torch.empty(T, hq * 128, dtype=BF, device="cuda")
     got = torch.full_like(ref, float("nan"))
     abi.check(lib.b200_paged_attn_decode(c["q"].data_ptr(), hq * 128, c["kc"].data_ptr(), c["vc"].data_ptr(),
                                          c["bt"].data_ptr(), c["stride"], None, c["cl"].data_ptr(), ref.data_ptr(),
-                                         hq * 128, T, hq, hkv, 128, c["max_ctx"], 128 ** -0.5, ws.data_ptr(), ws_bytes, None))
+                                         hq * 128, T, hq, hkv, bs, c["max_ctx"], 128 ** -0.5, ws.data_ptr(), ws_bytes, None))
     abi.check(lib.b200_paged_attn_decode_static(c["q"].data_ptr(), hq * 128, c["kc"].data_ptr(), c["vc"].data_ptr(),
                                                 c["bt"].data_ptr(), c["stride"], None, c["cl"].data_ptr(), got.data_ptr(),
-                                                hq * 128, T, hq, hkv, 128, c["max_ctx"], 128 ** -0.5, None))
+                                                hq * 128, T, hq, hkv, bs, c["max_ctx"], 128 ** -0.5, None))
     torch.cuda.synchronize()
     return got, ref
 
@@ -74,16 +74,21 @@ def test_static_scratch_attention_matches_workspace_attention_twice_in_a_row():
     # and the first case again gives the first answer again
     got3, _ = run_both(lib, abi, a)
     assert torch.equal(got3, got)
+    # 64-token cache blocks take the library's other attention kernel: same contract
+    c = make_case(T=3, hq=8, hkv=2, ctx_lens=[700, 65, 2049], seed=4, bs=64)
+    got4, ref4 = run_both(lib, abi, c)
+    assert torch.isfinite(got4.float()).all() and torch.equal(got4, ref4)
 
 
 def test_static_scratch_attention_refuses_shapes_beyond_its_array():
     abi = pkg("_abi")
     lib = abi.lib()
-    c = make_case(T=295, hq=8, hkv=1, ctx_lens=[300] * 295, seed=3)   # 295 rows * 8 heads * 2 splits > 2 MiB
+    # 64-token blocks -> the CUDA-core kernel's split plan: 295 rows * 8 heads * 2 splits > 2 MiB
+    c = make_case(T=295, hq=8, hkv=1, ctx_lens=[300] * 295, seed=3, bs=64)
     out = torch.zeros(295, 8 * 128, dtype=BF, device="cuda")
     rc = lib.b200_paged_attn_decode_static(c["q"].data_ptr(), 8 * 128, c["kc"].data_ptr(), c["vc"].data_ptr(),
                                            c["bt"].data_ptr(), c["stride"], None, c["cl"].data_ptr(), out.data_ptr(),
-                                           8 * 128, 295, 8, 1, 128, 300, 128 ** -0.5, None)
+                                           8 * 128, 295, 8, 1, 64, 300, 128 ** -0.5, None)
     assert rc == -3
     msg = lib.b200_last_error().decode()
     assert "built-in array holds" in msg and "b200_paged_attn_decode" in msg
