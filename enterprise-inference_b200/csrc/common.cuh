@@ -98,6 +98,35 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// Same, with a thread-block cluster shape (1,1,1 = no cluster).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                  dim3 cluster, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[2];
+  int na = 0;
+  if (launch_opts().pdl) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (cluster.x * cluster.y * cluster.z > 1) {
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = cluster.x;
+    at[na].val.clusterDim.y = cluster.y;
+    at[na].val.clusterDim.z = cluster.z;
+    ++na;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = na;
+  ++launch_counter();
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---- kernels' host entry points (internal, C++ linkage) ----------------------------------
 int linear_gemv(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
                 __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, cudaStream_t s);

@@ -124,6 +124,7 @@ struct TcParams {
   float* partials;      // [splits][tok_tiles*N][n_out_pad] fp32
   unsigned int* tickets;  // [m_tiles * tok_tiles], zero on entry, zero on exit
   int n_out_pad;
+  int cluster;  // 1: the `splits` CTAs of a slab form a thread-block cluster and reduce through DSMEM
   // next weights to pull into L2 while this kernel (and the small kernels after it) run
   const char* pf_ptr;
   long long pf_bytes;
@@ -314,7 +315,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tc_fence_after();
     }
     const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
-    const bool direct = p.splits == 1;
+    const bool direct = p.splits == 1 || p.cluster;   // the fp32 tile is staged in this CTA's smem
     // All MMAs have completed (tmem_full), so the pipeline stages are free: stage the fp32 tile
     // [token][128 rows] there for the direct case, or spill it to the split-K workspace.
     float* stg = reinterpret_cast<float*>(smem);
@@ -338,10 +339,12 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     }
     bool finalize = true;
     const int tile_id = m_tile * gridDim.z + tok_tile;
-    if (direct) {
+    if (p.cluster) {
+      finalize = false;   // done after the cluster barrier below, by every CTA of the cluster for its share
+    } else if (direct) {
       asm volatile("bar.sync 1, 128;" ::: "memory");
     } else {
-      // deterministic split-K: the last CTA of this (slab, token tile) reduces in split order
+      // deterministic split-K through global memory: the last CTA of this (slab, token tile) reduces
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (warp == 2 && lane == 0) *ticket_slot = (int)atomicAdd(&p.tickets[tile_id], 1u);
@@ -362,7 +365,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const int64_t split_stride = (int64_t)gridDim.z * N * p.n_out_pad;
       for (int t = wq; t < tmax; t += 16) {
         float4 acc[4];
-        if (direct) {
+        if (p.splits == 1) {
 #pragma unroll
           for (int u = 0; u < 4; ++u)
             acc[u] = (t + 4 * u < tmax) ? *reinterpret_cast<const float4*>(stg + (t + 4 * u) * kBlockM + r4)
@@ -392,7 +395,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           if (tt < tmax) finalize4<MODE>(p, m_tile, lane, tok0 + tt, acc[u], bb);
         }
       }
-      if (!direct && warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
+      if (p.splits > 1 && warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
     }
     // This CTA is done streaming: pull (a prefix of) the NEXT linear's weights towards L2 so that HBM
     // keeps working through this kernel's tail and the small kernels that follow (fire and forget).
@@ -407,6 +410,46 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
     }
     tc_fence_before();
+  }
+  if (p.cluster) {
+    // ---- split-K over a thread-block cluster: every CTA staged its fp32 partial tile [token][128] in
+    // its own shared memory; after a cluster barrier CTA `rank` finalises the tokens t = rank (mod S),
+    // summing the S partials in rank order (deterministic) straight out of its peers' smem (DSMEM).
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp >= 2) {
+      const int S2 = p.splits, rank = split, wq = warp - 2, r4 = lane * 4;
+      const int tok0 = tok_tile * N;
+      const int tmax = min(N, p.T - tok0);
+      float bb[4] = {0.f, 0.f, 0.f, 0.f};
+      if (p.bias) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (m_tile * kBlockM + r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[m_tile * kBlockM + r4 + e]);
+      }
+      const uint32_t stg_addr = smem_u32(smem);
+      for (int t = rank + S2 * wq; t < tmax; t += 4 * S2) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint32_t local = stg_addr + (uint32_t)(t * kBlockM + r4) * 4u;
+        for (int pr = 0; pr < S2; ++pr) {
+          uint32_t remote;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(pr));
+          float4 v;
+          asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                       : "r"(remote)
+                       : "memory");
+          acc.x += v.x;
+          acc.y += v.y;
+          acc.z += v.z;
+          acc.w += v.w;
+        }
+        finalize4<MODE>(p, m_tile, lane, tok0 + t, acc, bb);   // warp-uniform: t depends on (rank, wq) only
+      }
+    }
+    // nobody may exit (and release its shared memory) while a peer still reads it
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
   }
   __syncthreads();
   if (warp == 1) {
@@ -518,8 +561,8 @@ int launch_tc2(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, 
     B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  B200_CUDA(launch(linear_tc_kernel<N, MODE>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads), (size_t)smem,
-                   s, mw, mx, p));
+  B200_CUDA(launch_cluster(linear_tc_kernel<N, MODE>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads),
+                           (size_t)smem, s, p.cluster ? dim3(1, pl.splits, 1) : dim3(1, 1, 1), mw, mx, p));
   return B200_OK;
 }
 
@@ -561,10 +604,13 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
                "linear_tc: x and w must be 16-byte aligned");
   const Plan pl = make_plan(T, n_out, k);
   const int64_t need = linear_tc_workspace_bytes(T, n_out, k);
-  B200_REQUIRE(pl.splits == 1 || (ws && ws_bytes >= need), B200_ERR_INVALID,
+  static const int cluster_env = getenv("B200_TC_CLUSTER") ? atoi(getenv("B200_TC_CLUSTER")) : 1;
+  const bool use_cluster = cluster_env != 0 && pl.splits > 1 && pl.splits <= 8;
+  B200_REQUIRE(pl.splits == 1 || use_cluster || (ws && ws_bytes >= need), B200_ERR_INVALID,
                "linear_tc: workspace too small (%lld < %lld)", (long long)ws_bytes, (long long)need);
   const int mode = ex ? ex->mode : 0;
   TcParams p = {};
+  p.cluster = use_cluster ? 1 : 0;
   if (mode == kSiluMul) {
     B200_REQUIRE(n_out % kBlockM == 0, B200_ERR_UNSUPPORTED, "linear_tc(silu_mul): n_out=%d must be a multiple of 128", n_out);
   } else if (mode == kRopeKv) {
