@@ -52,7 +52,7 @@ class BlockManager:
         return 1.0 - len(self.free) / max(self.n_blocks, 1)
 
 
-@dataclass
+@dataclass(eq=False)   # identity semantics: requests live in lists/sets of the scheduler
 class Request:
     request_id: str
     prompt_ids: List[int]
@@ -144,7 +144,7 @@ class Scheduler:
         for req in list(self.running):
             if budget == 0:
                 break
-            if req not in self.running:   # preempted earlier in this pass
+            if req.row < 0:               # preempted earlier in this pass
                 continue
             remaining = req.n_total - req.n_computed
             n_new = min(remaining, budget)

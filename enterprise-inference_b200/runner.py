@@ -104,41 +104,11 @@ class ModelRunner:
         rows, cols = (t.shape[0], t.shape[1]) if t.dim() == 2 else (t.shape[0], 1)
         _abi.check(self.lib.b200_set_weight(self.ctx, layer, kind, t.data_ptr(), rows, cols))
 
-    def _set_gate_up(self, layer: int, gate: torch.Tensor, up: torch.Tensor):
-        """gate|up as 128-row slabs of 64 gate rows + the 64 matching up rows, so that the gate_up
-        linear applies SiLU*mul in its epilogue; plain gate-then-up when I_local is not a multiple of 64."""
-        I, h = gate.shape
-        if I % 64 == 0:
-            il = torch.stack([gate.reshape(I // 64, 64, h), up.reshape(I // 64, 64, h)], dim=1).reshape(2 * I, h)
-            self._set(layer, _abi.W_GATE_UP_INTERLEAVED, il)
-        else:
-            self._set(layer, _abi.W_GATE_UP, torch.cat([gate, up], 0))
-
     def load_weights(self, w: Dict[str, torch.Tensor]):
-        """HF-named tensors ([V22] llama.py:437-444 packing: q|k|v -> qkv, gate|up -> gate_up),
-        sharded Megatron-style for this TP rank."""
-        c, r, d = self.cfg, self.tp_rank, self.cfg.head_dim
-        qs = slice(r * self.hq * d, (r + 1) * self.hq * d)
-        ks = slice(r * self.hkv * d, (r + 1) * self.hkv * d)
-        is_ = slice(r * self.inter, (r + 1) * self.inter)
-        vs = slice(r * self.vocab_local, (r + 1) * self.vocab_local)
-        self._set(0, _abi.W_EMBED, w["model.embed_tokens.weight"])
-        for l in range(c.n_layers):
-            p = f"model.layers.{l}."
-            self._set(l, _abi.W_LN1, w[p + "input_layernorm.weight"])
-            self._set(l, _abi.W_QKV, torch.cat([w[p + "self_attn.q_proj.weight"][qs],
-                                                w[p + "self_attn.k_proj.weight"][ks],
-                                                w[p + "self_attn.v_proj.weight"][ks]], 0))
-            if c.qkv_bias:
-                self._set(l, _abi.W_QKV_BIAS, torch.cat([w[p + "self_attn.q_proj.bias"][qs],
-                                                         w[p + "self_attn.k_proj.bias"][ks],
-                                                         w[p + "self_attn.v_proj.bias"][ks]], 0))
-            self._set(l, _abi.W_O, w[p + "self_attn.o_proj.weight"][:, qs])
-            self._set(l, _abi.W_LN2, w[p + "post_attention_layernorm.weight"])
-            self._set_gate_up(l, w[p + "mlp.gate_proj.weight"][is_], w[p + "mlp.up_proj.weight"][is_])
-            self._set(l, _abi.W_DOWN, w[p + "mlp.down_proj.weight"][:, is_])
-        self._set(0, _abi.W_FINAL_NORM, w["model.norm.weight"])
-        self._set(0, _abi.W_LM_HEAD, w["lm_head.weight"][vs])
+        """HF-named tensors, fused and sharded for this TP rank by weights.shard_weights."""
+        from .weights import shard_weights
+        for layer, kind, t in shard_weights(w, self.cfg, self.tp_rank, self.tp_world):
+            self._set(layer, kind, t)
 
     def init_random_weights(self, seed: int = 1234, std: float = 0.02):
         """Random-init N(0, std^2) weights generated on the device (benchmarks; no checkpoint

@@ -1,0 +1,65 @@
+"""GPU (needs >= 2 devices; skipped otherwise): tensor-parallel decode through the C-ABI with the
+ctx's own NCCL communicator — TP=2 logits and greedy tokens against the single-rank oracle."""
+import os
+
+import pytest
+import torch
+
+from conftest import pkg
+from oracle import decode_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, name, port, out_q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)      # only carries the NCCL unique id
+    C, R = pkg("config"), pkg("runner")
+    ocfg = O.CONFIGS[name]
+    w = O.make_weights(ocfg, seed=1234, norm_jitter=0.1)
+    r = R.ModelRunner(C.ModelConfig(**ocfg.to_dict()), max_tokens=64, max_model_len=512, n_blocks=8,
+                      tp_rank=rank, tp_world=world)
+    r.load_weights(w)
+    r.init_tp()
+    ids = O.make_prompt(ocfg, 5, 40)
+    T = len(ids)
+    bt = torch.tensor([[3]], dtype=torch.int32, device="cuda")
+    pos = torch.arange(T, dtype=torch.int32, device="cuda")
+    logits = torch.empty(world, T, ocfg.vocab // world, dtype=torch.bfloat16, device="cuda")
+    for graphs in (False, True):
+        r.set_graphs(graphs)
+        toks = r.step_device(torch.tensor(ids, dtype=torch.int32).cuda(), pos, 3 * 128 + pos, bt, pos + 1, T,
+                             row_to_seq=torch.zeros(T, dtype=torch.int32).cuda(), out_logits=logits)
+        torch.cuda.synchronize()
+    full = logits.permute(1, 0, 2).reshape(T, ocfg.vocab).float().cpu()
+    if rank == 0:
+        out_q.put((full, toks.cpu()))
+    dist.barrier()
+    r.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_tp2_decode_step_matches_oracle():
+    import torch.multiprocessing as mp
+    name = "tiny-g8"
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, name, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    full, toks = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    cfg = O.CONFIGS[name]
+    w = O.make_weights(cfg, seed=1234, norm_jitter=0.1)
+    om = O.OracleModel(cfg, w, capacity=64)
+    want = om.forward(om.new_seq(), O.make_prompt(cfg, 5, 40)).float()
+    assert (torch.softmax(full, -1) - torch.softmax(want, -1)).abs().max() <= 2e-3
+    assert toks.tolist() == full.argmax(-1).tolist()      # vocab-parallel pick == argmax of the gathered logits
+    dis = toks != want.argmax(-1)
+    assert (O.top2_margin(want)[dis] < 0.08).all()
