@@ -38,6 +38,7 @@ WORKLOADS = {
     "llama8b-bs1": ("llama-3.1-8b", 1, 128, "Llama-3.1-8B-Instruct bf16 decode, batch 1, 128-in/128-out (configs[0])"),
     "llama8b-ctx32k": ("llama-3.1-8b", 8, 32768 - 64, "Llama-3.1-8B-Instruct bf16 decode, batch 8 at 32k context (configs[2])"),
     "llama70b-tp": ("llama-3.1-70b", 64, 512, "Llama-3.1-70B-Instruct bf16 decode, TP=N, batch 64 (configs[4])"),
+    "llama70b-tp-bs1": ("llama-3.1-70b", 1, 128, "Llama-3.1-70B-Instruct bf16 decode, TP=N, batch 1, 128-in/128-out (configs[4])"),
     "qwen32b-tp": ("qwen2-32b", 32, 512, "DeepSeek-R1-Distill-Qwen-32B bf16 decode, TP=N, batch 32 (configs[3])"),
     "tiny": ("tiny", 4, 16, "tiny config (self-test)"),
 }
@@ -203,7 +204,7 @@ def run_b200(args):
     lib = abi.lib()
 
     model, B, ctx0, desc = WORKLOADS[args.workload]
-    tp = args.workload.endswith("-tp")
+    tp = "-tp" in args.workload
     cfg = Cfg.get_config(model)
     K, W = args.steps, args.warmup
     total_steps = 2 * (K + W) + 8
