@@ -1,0 +1,552 @@
+"""OpenAI-compatible model server: the container contract of the reference's vLLM chart.
+
+    python -m enterprise-inference_b200.server --model <hf id> --served-model-name <name> --port 2080 \
+        --block-size 128 --dtype bfloat16 --max-model-len 8192 --tensor-parallel-size 1 ...
+
+What the chart passes (must accept; may no-op): /root/reference/core/helm-charts/vllm/xeon-values.yaml:70-89
+and templates/deployment.yaml:66-87.  HTTP surface: /root/reference/docs/api-spec.yaml (POST
+/v1/completions, /v1/chat/completions; 422 on a bad body, additionalProperties: false), GET /health
+(values.yaml:135-141), GET /metrics with the vllm:* series the Grafana dashboard queries
+(observability/xeon-exporter/grafana-xeon-dashboard.json), GET /v1/models (docs/getting-started-example.md:79-81).
+Sampling on the device is greedy (the reference's clients send "temperature": 0); other sampling
+parameters are accepted and ignored.  /v1/embeddings is served by TEI in the reference, not here.
+"""
+from __future__ import annotations
+
+import argparse
+import asyncio
+import contextlib
+import json
+import os
+import queue
+import signal
+import threading
+import time
+import uuid
+from typing import Any, Dict, List, Optional, Union
+
+from fastapi import FastAPI, HTTPException, Request as HttpRequest
+from fastapi.responses import JSONResponse, PlainTextResponse, StreamingResponse
+from prometheus_client import CollectorRegistry, Counter, Gauge, Histogram, generate_latest
+from pydantic import BaseModel, ConfigDict, Field
+
+from .engine import LLMEngine, Request
+
+
+# ------------------------------------------------------------------------------------------------
+# CLI: every flag the chart emits
+# ------------------------------------------------------------------------------------------------
+def make_arg_parser() -> argparse.ArgumentParser:
+    ap = argparse.ArgumentParser("enterprise-inference_b200.server", allow_abbrev=False)
+    ap.add_argument("--model", required=True)
+    ap.add_argument("--served-model-name", "--served_model_name", dest="served_model_name", default=None)
+    ap.add_argument("--port", type=int, default=2080)
+    ap.add_argument("--host", default="0.0.0.0")
+    ap.add_argument("--block-size", "--block_size", dest="block_size", type=int, default=128)
+    ap.add_argument("--dtype", default="bfloat16")
+    ap.add_argument("--max-model-len", "--max_model_len", dest="max_model_len", type=int, default=8192)
+    ap.add_argument("--max-num-batched-tokens", "--max_num_batched_tokens", dest="max_num_batched_tokens", type=int, default=2048)
+    ap.add_argument("--max-num-seqs", "--max_num_seqs", dest="max_num_seqs", type=int, default=256)
+    ap.add_argument("--tensor-parallel-size", "--tensor_parallel_size", dest="tensor_parallel_size", type=int, default=1)
+    ap.add_argument("--pipeline-parallel-size", "--pipeline_parallel_size", dest="pipeline_parallel_size", type=int, default=1)
+    ap.add_argument("--distributed_executor_backend", "--distributed-executor-backend", dest="distributed_executor_backend", default="mp")
+    ap.add_argument("--enable_chunked_prefill", "--enable-chunked-prefill", dest="enable_chunked_prefill", action="store_true")
+    ap.add_argument("--enforce-eager", "--enforce_eager", dest="enforce_eager", action="store_true")
+    ap.add_argument("--disable-log-requests", "--disable_log_requests", dest="disable_log_requests", action="store_true")
+    ap.add_argument("--enable-auto-tool-choice", dest="enable_auto_tool_choice", action="store_true")
+    ap.add_argument("--tool-call-parser", dest="tool_call_parser", default=None)
+    ap.add_argument("--chat-template", dest="chat_template", default=None)
+    # Gaudi-variant flags of the same chart (gaudi-values.yaml:160): accepted, ignored
+    ap.add_argument("--gpu-memory-util", "--gpu-memory-utilization", dest="gpu_memory_utilization", type=float, default=0.9)
+    ap.add_argument("--max-num-prefill-seqs", dest="max_num_prefill_seqs", type=int, default=None)
+    ap.add_argument("--num_scheduler_steps", "--num-scheduler-steps", dest="num_scheduler_steps", type=int, default=1)
+    ap.add_argument("--use-padding-aware-scheduling", dest="use_padding_aware_scheduling", action="store_true")
+    # ours
+    ap.add_argument("--kv-cache-gib", type=float, default=None, help="KV cache size (default: half of free HBM)")
+    ap.add_argument("--random-weights", action="store_true", help="random-init weights of the model's shape (no checkpoint)")
+    ap.add_argument("--tokenizer", default="auto", help="'auto' (HF tokenizer from the model dir) or 'byte'")
+    return ap
+
+
+def validate_args(args) -> None:
+    if args.dtype not in ("bfloat16", "bf16", "auto"):
+        raise SystemExit(f"--dtype {args.dtype}: this backend computes in bfloat16 only")
+    if args.pipeline_parallel_size != 1:
+        raise SystemExit("--pipeline-parallel-size > 1 is not supported (the reference never sets it, values.yaml:188)")
+    if args.block_size % 64:
+        raise SystemExit("--block-size must be a multiple of 64 (the chart passes 128)")
+    if args.tensor_parallel_size not in (1, 2, 4, 8):
+        raise SystemExit("--tensor-parallel-size must be 1, 2, 4 or 8")
+
+
+# ------------------------------------------------------------------------------------------------
+# tokenizers
+# ------------------------------------------------------------------------------------------------
+class ByteTokenizer:
+    """Ids are UTF-8 bytes (+3 specials); for random-weight smoke runs and tests."""
+    bos_token_id, eos_token_id, pad_token_id = 256, 257, 258
+
+    def __init__(self, vocab: int):
+        self.vocab = vocab
+
+    def encode(self, text: str, add_special_tokens: bool = True) -> List[int]:
+        ids = [b % self.vocab for b in text.encode("utf-8")]
+        return ([self.bos_token_id % self.vocab] if add_special_tokens else []) + ids
+
+    def decode(self, ids: List[int], skip_special_tokens: bool = True) -> str:
+        return bytes(i for i in ids if i < 256).decode("utf-8", errors="replace")
+
+    def apply_chat_template(self, messages, add_generation_prompt=True, **kw) -> str:
+        out = "".join(f"<|{m['role']}|>\n{_content_text(m.get('content'))}\n" for m in messages)
+        return out + ("<|assistant|>\n" if add_generation_prompt else "")
+
+
+def _content_text(c) -> str:
+    if c is None:
+        return ""
+    if isinstance(c, str):
+        return c
+    return "".join(p.get("text", "") for p in c if isinstance(p, dict))
+
+
+def load_tokenizer(kind: str, model_path: Optional[str], vocab: int):
+    if kind == "byte" or model_path is None:
+        return ByteTokenizer(vocab)
+    from transformers import AutoTokenizer
+    return AutoTokenizer.from_pretrained(model_path, local_files_only=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# request / response schema (docs/api-spec.yaml; extra fields are rejected with 422)
+# ------------------------------------------------------------------------------------------------
+class StreamOptions(BaseModel):
+    model_config = ConfigDict(extra="forbid")
+    include_usage: Optional[bool] = True
+    continuous_usage_stats: Optional[bool] = False
+
+
+class _Sampling(BaseModel):
+    model_config = ConfigDict(extra="forbid")
+    model: str
+    max_tokens: Optional[int] = 16
+    temperature: Optional[float] = 0.0
+    top_p: Optional[float] = 1.0
+    top_k: Optional[int] = -1
+    min_p: Optional[float] = 0.0
+    n: Optional[int] = 1
+    best_of: Optional[int] = None
+    seed: Optional[int] = None
+    stop: Optional[Union[str, List[str]]] = None
+    stream: Optional[bool] = False
+    stream_options: Optional[StreamOptions] = None
+    logprobs: Optional[Union[int, bool]] = None
+    logit_bias: Optional[Dict[str, float]] = None
+    frequency_penalty: Optional[float] = 0.0
+    presence_penalty: Optional[float] = 0.0
+    repetition_penalty: Optional[float] = 1.0
+    length_penalty: Optional[float] = 1.0
+    use_beam_search: Optional[bool] = False
+    early_stopping: Optional[bool] = False
+    user: Optional[str] = None
+    stop_token_ids: Optional[List[int]] = None
+    include_stop_str_in_output: Optional[bool] = False
+    ignore_eos: Optional[bool] = False
+    min_tokens: Optional[int] = 0
+    skip_special_tokens: Optional[bool] = True
+    spaces_between_special_tokens: Optional[bool] = True
+    truncate_prompt_tokens: Optional[int] = None
+    add_special_tokens: Optional[bool] = None
+    echo: Optional[bool] = False
+    response_format: Optional[Dict[str, Any]] = None
+    guided_json: Optional[Any] = None
+    guided_regex: Optional[str] = None
+    guided_choice: Optional[List[str]] = None
+    guided_grammar: Optional[str] = None
+    guided_decoding_backend: Optional[str] = None
+    guided_whitespace_pattern: Optional[str] = None
+
+
+class CompletionRequest(_Sampling):
+    prompt: Union[str, List[str], List[int], List[List[int]]]
+    suffix: Optional[str] = None
+    allowed_token_ids: Optional[List[int]] = None
+
+
+class ChatCompletionRequest(_Sampling):
+    messages: List[Dict[str, Any]] = Field(min_length=1)
+    top_logprobs: Optional[int] = None
+    tools: Optional[List[Dict[str, Any]]] = None
+    tool_choice: Optional[Union[str, Dict[str, Any]]] = "none"
+    add_generation_prompt: Optional[bool] = True
+    documents: Optional[List[Dict[str, str]]] = None
+    chat_template: Optional[str] = None
+    chat_template_kwargs: Optional[Dict[str, Any]] = None
+
+
+# ------------------------------------------------------------------------------------------------
+# metrics: the series the reference's Grafana dashboard and ServiceMonitor expect
+# ------------------------------------------------------------------------------------------------
+class Metrics:
+    def __init__(self, model_name: str):
+        self.registry = CollectorRegistry()
+        L = ["model_name"]
+        buckets_t = (0.001, 0.005, 0.01, 0.02, 0.04, 0.06, 0.08, 0.1, 0.25, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0)
+        buckets_l = (0.3, 0.5, 0.8, 1.0, 1.5, 2.0, 2.5, 5.0, 10.0, 15.0, 20.0, 30.0, 40.0, 50.0, 60.0)
+        buckets_n = (1, 2, 5, 10, 20, 50, 100, 200, 500, 1000, 2000, 5000, 10000)
+        r = self.registry
+        self.e2e = Histogram("vllm:e2e_request_latency_seconds", "request latency", L, buckets=buckets_l, registry=r)
+        self.ttft = Histogram("vllm:time_to_first_token_seconds", "TTFT", L, buckets=buckets_t, registry=r)
+        self.tpot = Histogram("vllm:time_per_output_token_seconds", "TPOT", L, buckets=buckets_t, registry=r)
+        self.prompt_tokens = Counter("vllm:prompt_tokens", "prompt tokens", L, registry=r)
+        self.generation_tokens = Counter("vllm:generation_tokens", "generated tokens", L, registry=r)
+        self.req_prompt = Histogram("vllm:request_prompt_tokens", "prompt tokens per request", L, buckets=buckets_n, registry=r)
+        self.req_gen = Histogram("vllm:request_generation_tokens", "generated tokens per request", L, buckets=buckets_n, registry=r)
+        self.success = Counter("vllm:request_success", "finished requests", L + ["finished_reason"], registry=r)
+        self.running = Gauge("vllm:num_requests_running", "running", L, registry=r)
+        self.waiting = Gauge("vllm:num_requests_waiting", "waiting", L, registry=r)
+        self.swapped = Gauge("vllm:num_requests_swapped", "swapped", L, registry=r)
+        self.gpu_cache = Gauge("vllm:gpu_cache_usage_perc", "KV cache usage", L, registry=r)
+        self.cpu_cache = Gauge("vllm:cpu_cache_usage_perc", "CPU KV cache usage (always 0)", L, registry=r)
+        self.m = model_name
+        for g in (self.running, self.waiting, self.swapped, self.gpu_cache, self.cpu_cache):
+            g.labels(self.m).set(0)
+
+    def finished(self, req: Request):
+        m = self.m
+        n_out = len(req.output_ids)
+        self.e2e.labels(m).observe(req.finish_time - req.arrival)
+        if req.first_token_time is not None:
+            self.ttft.labels(m).observe(req.first_token_time - req.arrival)
+        for a, b in zip(req.token_times, req.token_times[1:]):
+            self.tpot.labels(m).observe(b - a)
+        self.prompt_tokens.labels(m).inc(len(req.prompt_ids))
+        self.generation_tokens.labels(m).inc(n_out)
+        self.req_prompt.labels(m).observe(len(req.prompt_ids))
+        self.req_gen.labels(m).observe(n_out)
+        self.success.labels(m, req.finish_reason or "stop").inc()
+
+
+# ------------------------------------------------------------------------------------------------
+# engine thread: the single thread that drives the ctx (the C-ABI is not re-entrant per ctx)
+# ------------------------------------------------------------------------------------------------
+class EngineLoop:
+    def __init__(self, engine: LLMEngine, metrics: Metrics):
+        self.engine, self.metrics = engine, metrics
+        self.inbox: "queue.Queue" = queue.Queue()
+        self.listeners: Dict[str, Any] = {}      # request_id -> (loop, asyncio.Queue)
+        self.alive = True
+        self.error: Optional[str] = None
+        self.draining = False
+        self.thread = threading.Thread(target=self._run, name="b200-engine", daemon=True)
+
+    def start(self):
+        self.thread.start()
+
+    def submit(self, req: Request, loop, q: "asyncio.Queue"):
+        if self.draining:
+            raise HTTPException(503, "server is draining")
+        self.listeners[req.request_id] = (loop, q)
+        self.inbox.put(req)
+
+    def _emit(self, rid: str, item):
+        tgt = self.listeners.get(rid)
+        if tgt:
+            loop, q = tgt
+            loop.call_soon_threadsafe(q.put_nowait, item)
+
+    def _run(self):
+        eng = self.engine
+        try:
+            while self.alive:
+                try:
+                    while True:
+                        req = self.inbox.get(block=not eng.has_work(), timeout=0.05)
+                        try:
+                            eng.add_request(req)
+                        except ValueError as e:
+                            self._emit(req.request_id, ("error", str(e)))
+                            self.listeners.pop(req.request_id, None)
+                except queue.Empty:
+                    pass
+                if not eng.has_work():
+                    continue
+                before = {r.request_id: len(r.output_ids) for r in eng.scheduler.running}
+                done = eng.step()
+                m = self.metrics
+                m.running.labels(m.m).set(len(eng.scheduler.running))
+                m.waiting.labels(m.m).set(len(eng.scheduler.waiting))
+                m.gpu_cache.labels(m.m).set(eng.blocks.usage)
+                for r in list(eng.scheduler.running) + done:
+                    n0 = before.get(r.request_id, 0)
+                    if len(r.output_ids) > n0:
+                        self._emit(r.request_id, ("tokens", r.output_ids[n0:]))
+                for r in done:
+                    m.finished(r)
+                    self._emit(r.request_id, ("done", r.finish_reason))
+                    self.listeners.pop(r.request_id, None)
+        except Exception as e:  # the engine died: /health goes non-200 and the pod is restarted
+            self.error = f"{type(e).__name__}: {e}"
+            for rid in list(self.listeners):
+                self._emit(rid, ("error", self.error))
+
+    def healthy(self) -> bool:
+        return self.error is None and self.thread.is_alive()
+
+
+# ------------------------------------------------------------------------------------------------
+# app
+# ------------------------------------------------------------------------------------------------
+def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_len: int) -> FastAPI:
+    metrics = Metrics(served_model_name)
+    loop_ = EngineLoop(engine, metrics)
+
+    @contextlib.asynccontextmanager
+    async def lifespan(_app):
+        loop_.start()
+        yield
+        loop_.draining = True       # SIGTERM: finish what is running (terminationGracePeriodSeconds: 120)
+        t0 = time.monotonic()
+        while engine.has_work() and loop_.healthy() and time.monotonic() - t0 < 120:
+            await asyncio.sleep(0.05)
+        loop_.alive = False
+
+    app = FastAPI(title="enterprise-inference b200 decode backend", lifespan=lifespan)
+    app.state.engine_loop = loop_
+    app.state.metrics = metrics
+    eos = getattr(tokenizer, "eos_token_id", None)
+    eos_ids = tuple([eos] if isinstance(eos, int) else (eos or []))
+
+    @app.get("/health")
+    async def health():
+        if not loop_.healthy():
+            return PlainTextResponse(loop_.error or "engine thread stopped", status_code=503)
+        return PlainTextResponse("", status_code=200)
+
+    @app.get("/metrics")
+    async def metrics_ep():
+        return PlainTextResponse(generate_latest(metrics.registry).decode(), media_type="text/plain; version=0.0.4")
+
+    @app.get("/v1/models")
+    async def models():
+        return {"object": "list", "data": [{"id": served_model_name, "object": "model", "created": int(time.time()),
+                                            "owned_by": "enterprise-inference-b200", "root": served_model_name,
+                                            "max_model_len": max_model_len}]}
+
+    def error(status: int, msg: str, typ: str = "BadRequestError"):
+        return JSONResponse({"object": "error", "message": msg, "type": typ, "param": None, "code": status}, status_code=status)
+
+    def check_model(name: str):
+        if name != served_model_name:
+            return error(404, f"The model `{name}` does not exist.", "NotFoundError")
+        return None
+
+    def make_request(body: _Sampling, prompt_ids: List[int]) -> Request:
+        if body.truncate_prompt_tokens:
+            prompt_ids = prompt_ids[-body.truncate_prompt_tokens:]
+        max_tokens = body.max_tokens if body.max_tokens is not None else max(max_model_len - len(prompt_ids), 1)
+        return Request(request_id="cmpl-" + uuid.uuid4().hex, prompt_ids=prompt_ids, max_tokens=max_tokens,
+                       ignore_eos=bool(body.ignore_eos), eos_token_ids=eos_ids,
+                       stop_token_ids=tuple(body.stop_token_ids or ()), min_tokens=body.min_tokens or 0)
+
+    class Detok:
+        """Incremental detokenisation + stop strings."""
+        def __init__(self, body: _Sampling):
+            self.ids: List[int] = []
+            self.sent = 0
+            self.stops = [body.stop] if isinstance(body.stop, str) else list(body.stop or [])
+            self.include_stop = bool(body.include_stop_str_in_output)
+            self.skip_special = body.skip_special_tokens is not False
+            self.stopped = False
+
+        def push(self, new_ids: List[int]) -> str:
+            self.ids += new_ids
+            text = tokenizer.decode(self.ids, skip_special_tokens=self.skip_special)
+            for s in self.stops:
+                k = text.find(s, max(self.sent - len(s), 0))
+                if k >= 0:
+                    text = text[:k + (len(s) if self.include_stop else 0)]
+                    self.stopped = True
+            if not self.stopped and text.endswith("�"):     # incomplete UTF-8 sequence: hold it back
+                return ""
+            delta, self.sent = text[self.sent:], max(len(text), self.sent)
+            return delta
+
+    async def run(body: _Sampling, prompt_ids: List[int], chat: bool, prompt_text: str = ""):
+        if len(prompt_ids) == 0:
+            return error(400, "the prompt is empty")
+        if body.n not in (None, 1) or (body.best_of not in (None, 1)) or body.use_beam_search:
+            return error(400, "n > 1, best_of > 1 and beam search are not supported by this backend")
+        req = make_request(body, prompt_ids)
+        if len(prompt_ids) + req.max_tokens > max_model_len:
+            return error(400, f"This model's maximum context length is {max_model_len} tokens. However, you requested "
+                              f"{len(prompt_ids) + req.max_tokens} tokens ({len(prompt_ids)} in the prompt, {req.max_tokens} "
+                              "in the completion).")
+        q: asyncio.Queue = asyncio.Queue()
+        loop_.submit(req, asyncio.get_running_loop(), q)
+        created = int(time.time())
+        rid = req.request_id if not chat else "chat" + req.request_id
+        obj = "chat.completion" if chat else "text_completion"
+        detok = Detok(body)
+
+        def usage():
+            return {"prompt_tokens": len(prompt_ids), "completion_tokens": len(req.output_ids),
+                    "total_tokens": len(prompt_ids) + len(req.output_ids)}
+
+        async def events():
+            while True:
+                kind, val = await q.get()
+                if kind == "tokens":
+                    d = detok.push(val)
+                    if detok.stopped:           # stop string hit: finish the engine request early
+                        req.max_tokens = len(req.output_ids)
+                    yield "delta", d
+                    if detok.stopped:
+                        yield "done", "stop"
+                        return
+                elif kind == "done":
+                    yield "done", val
+                    return
+                else:
+                    yield "error", val
+                    return
+
+        if body.stream:
+            async def sse():
+                first = True
+                include_usage = bool(body.stream_options and body.stream_options.include_usage)
+                cont = bool(body.stream_options and body.stream_options.continuous_usage_stats)
+                async for kind, val in events():
+                    if kind == "error":
+                        yield f"data: {json.dumps({'error': {'message': val, 'type': 'InternalServerError', 'code': 500}})}\n\n"
+                        break
+                    finish = val if kind == "done" else None
+                    text = val if kind == "delta" else ""
+                    if kind == "delta" and not text and not first:
+                        continue
+                    if chat:
+                        delta = {"content": text}
+                        if first:
+                            delta["role"] = "assistant"
+                        choice = {"index": 0, "delta": delta if kind == "delta" else {}, "logprobs": None, "finish_reason": finish}
+                        chunk = {"id": rid, "object": "chat.completion.chunk", "created": created, "model": served_model_name,
+                                 "choices": [choice]}
+                    else:
+                        chunk = {"id": rid, "object": "text_completion", "created": created, "model": served_model_name,
+                                 "choices": [{"index": 0, "text": text, "logprobs": None, "finish_reason": finish, "stop_reason": None}]}
+                    if include_usage:
+                        chunk["usage"] = usage() if cont else None
+                    first = False
+                    yield f"data: {json.dumps(chunk)}\n\n"
+                if include_usage:
+                    yield f"data: {json.dumps({'id': rid, 'object': 'chat.completion.chunk' if chat else 'text_completion', 'created': created, 'model': served_model_name, 'choices': [], 'usage': usage()})}\n\n"
+                yield "data: [DONE]\n\n"
+            return StreamingResponse(sse(), media_type="text/event-stream")
+
+        text, finish = "", None
+        async for kind, val in events():
+            if kind == "delta":
+                text += val
+            elif kind == "done":
+                finish = val
+            else:
+                return error(500, val, "InternalServerError")
+        if chat:
+            choice = {"index": 0, "message": {"role": "assistant", "content": text, "tool_calls": []}, "logprobs": None,
+                      "finish_reason": finish, "stop_reason": None}
+        else:
+            choice = {"index": 0, "text": (prompt_text + text) if body.echo else text, "logprobs": None,
+                      "finish_reason": finish, "stop_reason": None}
+        return {"id": rid, "object": obj, "created": created, "model": served_model_name, "choices": [choice], "usage": usage()}
+
+    @app.post("/v1/completions")
+    async def completions(body: CompletionRequest):
+        bad = check_model(body.model)
+        if bad:
+            return bad
+        p = body.prompt
+        if isinstance(p, list) and p and isinstance(p[0], (list, str)):
+            if len(p) != 1:
+                return error(400, "batched prompts are not supported: send one request per prompt")
+            p = p[0]
+        if isinstance(p, str):
+            ids = tokenizer.encode(p) if body.add_special_tokens is not False else tokenizer.encode(p, add_special_tokens=False)
+            text = p
+        else:
+            ids, text = list(p), ""
+            if any((not isinstance(i, int)) or i < 0 or i >= engine.runner.cfg.vocab for i in ids):
+                return error(400, "prompt token ids out of range")
+        return await run(body, list(ids), chat=False, prompt_text=text)
+
+    @app.post("/v1/chat/completions")
+    async def chat_completions(body: ChatCompletionRequest):
+        bad = check_model(body.model)
+        if bad:
+            return bad
+        for m in body.messages:
+            if "role" not in m:
+                return error(400, "every message needs a role")
+        try:
+            kw = dict(body.chat_template_kwargs or {})
+            if body.tools:
+                kw["tools"] = body.tools
+            if body.chat_template:
+                kw["chat_template"] = body.chat_template
+            prompt = tokenizer.apply_chat_template(body.messages, add_generation_prompt=bool(body.add_generation_prompt),
+                                                   tokenize=False, **kw)
+        except Exception as e:
+            return error(400, f"chat template failed: {e}")
+        ids = tokenizer.encode(prompt, add_special_tokens=False)
+        return await run(body, list(ids), chat=True)
+
+    return app
+
+
+def build_engine(args):
+    """Runner + engine for this rank from the chart's flags (TP workers are launched by main())."""
+    import torch
+    from .config import from_hf_config, get_config
+    from .runner import ModelRunner
+    from .weights import load_safetensors_dir, resolve_hf_snapshot
+    model_path = None
+    try:
+        model_path = resolve_hf_snapshot(args.model)
+        cfg = from_hf_config(model_path)
+    except FileNotFoundError:
+        if not args.random_weights:
+            raise
+        cfg = get_config(args.model)
+    rank = int(os.environ.get("RANK", "0"))
+    world = args.tensor_parallel_size
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    runner = ModelRunner(cfg, max_tokens=args.max_num_batched_tokens, max_model_len=args.max_model_len,
+                         block_size=args.block_size, kv_cache_gib=args.kv_cache_gib, tp_rank=rank, tp_world=world,
+                         graphs=True)
+    if args.random_weights or model_path is None:
+        runner.init_random_weights()
+    else:
+        runner.load_weights(load_safetensors_dir(model_path))
+    if world > 1:
+        runner.init_tp()
+    engine = LLMEngine(runner, max_num_batched_tokens=args.max_num_batched_tokens, max_num_seqs=args.max_num_seqs,
+                       max_model_len=args.max_model_len)
+    tok = load_tokenizer(args.tokenizer if model_path else "byte", model_path, cfg.vocab)
+    return engine, tok
+
+
+def main(argv=None):
+    args, unknown = make_arg_parser().parse_known_args(argv)
+    if unknown:
+        print(f"[b200] ignoring flags this backend does not know: {unknown}", flush=True)
+    validate_args(args)
+    if args.tensor_parallel_size > 1:
+        raise SystemExit("tensor_parallel_size > 1: launch one process per GPU with torchrun; the multi-rank HTTP "
+                         "front end is not wired yet (rank 0 would broadcast each StepBatch) — see DESIGN.md")
+    import uvicorn
+    engine, tok = build_engine(args)
+    app = create_app(engine, tok, args.served_model_name or args.model, args.max_model_len)
+    signal.signal(signal.SIGTERM, lambda *_: (_ for _ in ()).throw(KeyboardInterrupt()))
+    uvicorn.run(app, host=args.host, port=args.port, log_level="warning" if args.disable_log_requests else "info")
+
+
+if __name__ == "__main__":
+    main()

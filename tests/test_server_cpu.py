@@ -1,0 +1,153 @@
+"""CPU: the OpenAI surface and the chart's container contract, with a fake runner behind the engine.
+Shapes of the reference's smoke checks: temperature-0 completions return 200 with
+choices[0].text; /health 200; /metrics exposes the vllm:* series; bad bodies give 422."""
+import json
+import types
+
+import numpy as np
+import pytest
+from fastapi.testclient import TestClient
+
+from conftest import pkg
+
+S = pkg("server")
+E = pkg("engine")
+
+
+class FakeRunner:
+    """next token = (sum of context) % 251 — deterministic, depends on the whole sequence."""
+    def __init__(self):
+        self.n_blocks, self.block_size, self.max_tokens, self.max_model_len = 64, 16, 64, 256
+        self.cfg = types.SimpleNamespace(vocab=512)
+        self.kv = {}
+
+    def step(self, b):
+        for i in range(b.n_tokens):
+            self.kv[int(b.slots[i])] = int(b.ids[i])
+        out = []
+        for r in b.logit_rows:
+            bt = b.block_tables[int(b.row_to_seq[r])]
+            out.append(sum(self.kv[int(bt[p // 16]) * 16 + p % 16] for p in range(int(b.ctx_lens[r]))) % 251)
+        return np.array(out, dtype=np.int32)
+
+
+def expect_ids(prompt_ids, n):
+    ids = list(prompt_ids)
+    for _ in range(n):
+        ids.append(sum(ids) % 251)
+    return ids[len(prompt_ids):]
+
+
+@pytest.fixture()
+def client():
+    eng = E.LLMEngine(FakeRunner(), max_num_batched_tokens=64, max_num_seqs=8, max_model_len=256)
+    tok = S.ByteTokenizer(512)
+    app = S.create_app(eng, tok, "meta-llama/Llama-3.1-8B-Instruct", 256)
+    with TestClient(app) as c:
+        c.tok = tok
+        yield c
+
+
+MODEL = "meta-llama/Llama-3.1-8B-Instruct"
+
+
+def test_health_models_metrics(client):
+    assert client.get("/health").status_code == 200
+    m = client.get("/v1/models").json()
+    assert m["data"][0]["id"] == MODEL
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "What is Deep Learning?", "max_tokens": 5, "temperature": 0})
+    assert r.status_code == 200
+    text = client.get("/metrics").text
+    for series in ("vllm:e2e_request_latency_seconds_bucket", "vllm:prompt_tokens_total", "vllm:generation_tokens_total",
+                   "vllm:time_per_output_token_seconds_bucket", "vllm:time_to_first_token_seconds_bucket",
+                   "vllm:num_requests_running", "vllm:num_requests_swapped", "vllm:num_requests_waiting",
+                   "vllm:gpu_cache_usage_perc", "vllm:cpu_cache_usage_perc", "vllm:request_prompt_tokens_bucket",
+                   "vllm:request_generation_tokens_bucket", "vllm:request_success_total"):
+        assert series in text, series
+    assert f'model_name="{MODEL}"' in text
+    assert 'finished_reason="length"' in text
+
+
+def test_completion_matches_engine_and_usage(client):
+    prompt = "What is Deep Learning?"
+    ids = client.tok.encode(prompt)
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": prompt, "max_tokens": 25, "temperature": 0}).json()
+    want = client.tok.decode(expect_ids(ids, 25))
+    assert r["object"] == "text_completion" and r["choices"][0]["text"] == want
+    assert r["choices"][0]["finish_reason"] == "length"
+    assert r["usage"] == {"prompt_tokens": len(ids), "completion_tokens": 25, "total_tokens": len(ids) + 25}
+    # token-id prompt + echo
+    r2 = client.post("/v1/completions", json={"model": MODEL, "prompt": ids, "max_tokens": 25}).json()
+    assert r2["choices"][0]["text"] == want
+
+
+def test_streaming_sse_with_usage(client):
+    with client.stream("POST", "/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 8, "stream": True,
+                                                        "stream_options": {"include_usage": True}}) as r:
+        assert r.status_code == 200
+        lines = [l for l in r.iter_lines() if l.startswith("data: ")]
+    assert lines[-1] == "data: [DONE]"
+    chunks = [json.loads(l[6:]) for l in lines[:-1]]
+    text = "".join(c["choices"][0]["text"] for c in chunks if c["choices"])
+    assert text == client.tok.decode(expect_ids(client.tok.encode("abc"), 8))
+    assert chunks[-1]["choices"] == [] and chunks[-1]["usage"]["completion_tokens"] == 8
+    assert any(c["choices"] and c["choices"][0]["finish_reason"] == "length" for c in chunks)
+
+
+def test_chat_completion_and_stream(client):
+    body = {"model": MODEL, "messages": [{"role": "system", "content": "You are helpful."}, {"role": "user", "content": "Hi"}],
+            "max_tokens": 6, "temperature": 0}
+    r = client.post("/v1/chat/completions", json=body).json()
+    assert r["object"] == "chat.completion" and r["choices"][0]["message"]["role"] == "assistant"
+    assert r["usage"]["completion_tokens"] == 6
+    with client.stream("POST", "/v1/chat/completions", json={**body, "stream": True}) as s:
+        chunks = [json.loads(l[6:]) for l in s.iter_lines() if l.startswith("data: ") and l != "data: [DONE]"]
+    assert chunks[0]["choices"][0]["delta"].get("role") == "assistant"
+    assert "".join(c["choices"][0]["delta"].get("content", "") for c in chunks if c["choices"]) == r["choices"][0]["message"]["content"]
+
+
+def test_validation_and_errors(client):
+    assert client.post("/v1/completions", json={"model": MODEL}).status_code == 422                     # prompt missing
+    assert client.post("/v1/completions", json={"model": MODEL, "prompt": "x", "bogus_field": 1}).status_code == 422
+    assert client.post("/v1/chat/completions", json={"model": MODEL, "messages": []}).status_code == 422
+    r = client.post("/v1/completions", json={"model": "other", "prompt": "x"})
+    assert r.status_code == 404 and r.json()["object"] == "error"
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "x" * 300, "max_tokens": 10})
+    assert r.status_code == 400 and "maximum context length" in r.json()["message"]
+    assert client.post("/v1/completions", json={"model": MODEL, "prompt": "x", "n": 2}).status_code == 400
+
+
+def test_stop_and_ignore_eos(client):
+    ids = client.tok.encode("hello")
+    first = expect_ids(ids, 1)[0]
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "hello", "max_tokens": 9, "stop_token_ids": [first]}).json()
+    assert r["usage"]["completion_tokens"] == 1 and r["choices"][0]["finish_reason"] == "stop"
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "hello", "max_tokens": 9, "ignore_eos": True}).json()
+    assert r["usage"]["completion_tokens"] == 9
+
+
+def test_chart_flags_are_accepted():
+    """Every arg the chart emits (xeon-values.yaml:70-89 + deployment.yaml:72-87, and the Gaudi variant)."""
+    argv = ["--block-size", "128", "--dtype", "bfloat16", "--max-model-len", "8192", "--distributed_executor_backend", "mp",
+            "--enable_chunked_prefill", "--enforce-eager", "--max-num-batched-tokens", "2048", "--max-num-seqs", "256",
+            "--disable-log-requests", "--enable-auto-tool-choice", "--tool-call-parser", "llama3_json",
+            "--tensor-parallel-size", "1", "--pipeline-parallel-size", "1", "--model", MODEL, "--served-model-name", MODEL,
+            "--port", "2080", "--gpu-memory-util", "0.98", "--max-num-prefill-seqs", "16", "--num_scheduler_steps", "1",
+            "--use-padding-aware-scheduling"]
+    args, unknown = S.make_arg_parser().parse_known_args(argv)
+    assert unknown == [] and args.block_size == 128 and args.port == 2080 and args.max_num_seqs == 256
+    S.validate_args(args)
+    bad, _ = S.make_arg_parser().parse_known_args(argv + ["--pipeline-parallel-size", "2"])
+    with pytest.raises(SystemExit):
+        S.validate_args(bad)
+
+
+def test_health_goes_red_when_the_engine_dies(client):
+    loop = client.app.state.engine_loop
+
+    def boom(_):
+        raise RuntimeError("device lost")
+    loop.engine.runner.step = boom
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "x", "max_tokens": 2})
+    assert r.status_code == 500
+    assert client.get("/health").status_code == 503
