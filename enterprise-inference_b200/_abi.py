@@ -40,6 +40,8 @@ SIGNATURES = {
     "b200_set_rope_cache": (C.c_int, [_vp, _vp, _i64]),
     "b200_nccl_unique_id": (C.c_int, [_vp]),
     "b200_nccl_init": (C.c_int, [_vp, _vp]),
+    "b200_tp_ipc_export": (C.c_int, [_vp, _vp]),
+    "b200_tp_ipc_import": (C.c_int, [_vp, _vp, _i32]),
     "b200_decode_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _vp, _vp]),
     "b200_decode_step_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "b200_ctx_set_graphs": (C.c_int, [_vp, _i32]),

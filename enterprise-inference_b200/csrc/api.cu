@@ -107,6 +107,18 @@ __global__ void tp_pack_kernel(const float* __restrict__ mx, const int32_t* __re
 
 }  // namespace b200
 
+namespace b200 {
+struct ArParams {
+  const __nv_bfloat16* bufs[8];
+  unsigned int* flags[8];
+  unsigned int* state;
+  __nv_bfloat16* out;
+  long long n_chunks;
+  int rank, world, buf_idx;
+};
+int allreduce_oneshot(const ArParams& p, cudaStream_t s);
+}  // namespace b200
+
 using namespace b200;
 
 // ------------------------------------------------------------------------------------------------
@@ -156,6 +168,12 @@ struct b200_ctx {
   void *tap_hidden = nullptr, *tap_res = nullptr;
   // TP
   ncclComm_t comm = nullptr;
+  // one-shot all-reduce over peer memory (allreduce.cu): one IPC-shareable allocation per rank
+  //   [ buffer 0 | buffer 1 | flag block (2 x 8 x 128 B) | state (counter[2], ticket[2]) ]
+  char* ar_mem = nullptr;
+  int64_t ar_buf_bytes = 0, ar_total_bytes = 0;
+  char* ar_peer[8] = {};
+  bool ar_ready = false;
   int gemv_max_t = 0;  // rows <= this use the CUDA-core GEMV; 0: the tcgen05 path serves every T (measured faster)
   bool pdl = true;
   bool fuse = true;                    // epilogue fusion (RoPE+KV, SiLU*mul) on the tcgen05 path
@@ -267,12 +285,54 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
     *it.p = static_cast<char*>(c->pool) + off;
     off += align_up(std::max<int64_t>(it.bytes, 16), 1024);
   }
+  if (W > 1) {
+    c->ar_buf_bytes = align_up(T * h * 2, 1024);
+    c->ar_total_bytes = 2 * c->ar_buf_bytes + 2 * 8 * 128 + 256;
+    e = cudaMalloc((void**)&c->ar_mem, c->ar_total_bytes);
+    if (e == cudaSuccess) e = cudaMemset(c->ar_mem, 0, c->ar_total_bytes);
+    if (e != cudaSuccess) {
+      cudaFree(c->pool);
+      delete c;
+      return cuda_fail(e, "cudaMalloc(all-reduce buffers)", __FILE__, __LINE__);
+    }
+  }
   *out = c;
+  return B200_OK;
+}
+
+extern "C" int b200_tp_ipc_export(b200_ctx* c, void* host_handle64) {
+  B200_REQUIRE(c && host_handle64, B200_ERR_INVALID, "tp_ipc_export: null");
+  B200_REQUIRE(c->ar_mem, B200_ERR_STATE, "tp_ipc_export: tp_world == 1");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t hnd;
+  B200_CUDA(cudaIpcGetMemHandle(&hnd, c->ar_mem));
+  memcpy(host_handle64, &hnd, 64);
+  return B200_OK;
+}
+
+extern "C" int b200_tp_ipc_import(b200_ctx* c, const void* host_handles, int32_t world) {
+  B200_REQUIRE(c && host_handles, B200_ERR_INVALID, "tp_ipc_import: null");
+  B200_REQUIRE(c->ar_mem && world == c->cfg.tp_world && world <= 8, B200_ERR_STATE, "tp_ipc_import: bad world %d", world);
+  for (int r = 0; r < world; ++r) {
+    if (r == c->cfg.tp_rank) {
+      c->ar_peer[r] = c->ar_mem;
+      continue;
+    }
+    cudaIpcMemHandle_t hnd;
+    memcpy(&hnd, static_cast<const char*>(host_handles) + 64 * r, 64);
+    void* ptr = nullptr;
+    B200_CUDA(cudaIpcOpenMemHandle(&ptr, hnd, cudaIpcMemLazyEnablePeerAccess));
+    c->ar_peer[r] = static_cast<char*>(ptr);
+  }
+  c->ar_ready = true;
   return B200_OK;
 }
 
 extern "C" int b200_ctx_destroy(b200_ctx* c) {
   if (!c) return B200_OK;
+  for (int r = 0; r < 8; ++r)
+    if (c->ar_peer[r] && c->ar_peer[r] != c->ar_mem) cudaIpcCloseMemHandle(c->ar_peer[r]);
+  if (c->ar_mem) cudaFree(c->ar_mem);
   for (auto& kv : c->graph_cache) cudaGraphExecDestroy(kv.second);
   if (c->comm && nccl().ok) nccl().CommDestroy(c->comm);
   if (c->pool) cudaFree(c->pool);
@@ -492,6 +552,27 @@ extern "C" int b200_advance_decode_rows(int32_t* ids, int32_t* positions, int32_
                       block_size, (cudaStream_t)stream);
 }
 
+// Row-parallel linears write into partial_dst(); tp_reduce() turns the partials of all ranks into c->x.
+static __nv_bfloat16* partial_dst(b200_ctx* c, int buf_idx) {
+  return c->ar_ready ? reinterpret_cast<__nv_bfloat16*>(c->ar_mem + (int64_t)buf_idx * c->ar_buf_bytes) : c->x;
+}
+static int tp_reduce(b200_ctx* c, int buf_idx, int T, cudaStream_t s) {
+  const int64_t count = (int64_t)T * c->cfg.hidden;
+  if (!c->ar_ready) return b200_allreduce_bf16(c, c->x, count, s);   // NCCL fallback
+  ArParams p = {};
+  for (int r = 0; r < c->cfg.tp_world; ++r) {
+    p.bufs[r] = reinterpret_cast<const __nv_bfloat16*>(c->ar_peer[r] + (int64_t)buf_idx * c->ar_buf_bytes);
+    p.flags[r] = reinterpret_cast<unsigned int*>(c->ar_peer[r] + 2 * c->ar_buf_bytes);
+  }
+  p.state = reinterpret_cast<unsigned int*>(c->ar_mem + 2 * c->ar_buf_bytes + 2 * 8 * 128);
+  p.out = c->x;
+  p.n_chunks = count / 8;
+  p.rank = c->cfg.tp_rank;
+  p.world = c->cfg.tp_world;
+  p.buf_idx = buf_idx;
+  return allreduce_oneshot(p, s);
+}
+
 // ---- the step --------------------------------------------------------------------------------------
 struct StepArgs {
   const int32_t *ids, *positions, *slots, *block_table, *row_to_seq, *ctx_lens, *logit_rows;
@@ -556,10 +637,10 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     {  // O
       LinearExtra ex;
       if (tc_path(T, on, ok, c->gemv_max_t)) pf(ex, L.gu, (int64_t)gn * h);
-      STEP(linear_any(c->attn_out, ok, L.o, nullptr, c->x, h, T, on, ok, 0, c->gemv_max_t, c->lin_ws, c->lin_ws_bytes,
-                      &ex, s));
+      STEP(linear_any(c->attn_out, ok, L.o, nullptr, tp ? partial_dst(c, 0) : c->x, h, T, on, ok, 0, c->gemv_max_t,
+                      c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
-    if (tp) STEP(b200_allreduce_bf16(c, c->x, (int64_t)T * h, s));
+    if (tp) STEP(tp_reduce(c, 0, T, s));
     STEP(rmsnorm(c->x, c->res, L.ln2, c->normed, T, h, m.rms_eps, s));
     {  // gate_up (+ SiLU*mul in the epilogue over interleaved slabs)
       LinearExtra ex;
@@ -584,10 +665,10 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
         else
           pf(ex, c->lm_head, (int64_t)c->vocab_local * h);
       }
-      STEP(linear_any(c->act, dk, L.down, nullptr, c->x, h, T, dn, dk, 0, c->gemv_max_t, c->lin_ws, c->lin_ws_bytes,
-                      &ex, s));
+      STEP(linear_any(c->act, dk, L.down, nullptr, tp ? partial_dst(c, 1) : c->x, h, T, dn, dk, 0, c->gemv_max_t,
+                      c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
-    if (tp) STEP(b200_allreduce_bf16(c, c->x, (int64_t)T * h, s));
+    if (tp) STEP(tp_reduce(c, 1, T, s));
     if (l == c->tap_layer && c->tap_hidden) {
       B200_CUDA(cudaMemcpyAsync(c->tap_hidden, c->x, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));
       if (c->tap_res) B200_CUDA(cudaMemcpyAsync(c->tap_res, c->res, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));

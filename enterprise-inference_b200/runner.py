@@ -143,11 +143,14 @@ class ModelRunner:
         self._set(0, _abi.W_LM_HEAD, rnd(self.vocab_local, c.hidden))
 
     # ---- TP --------------------------------------------------------------------------------
-    def init_tp(self, group=None):
+    def init_tp(self, group=None, peer_allreduce: bool = None):
         """Create the ctx's NCCL communicator; the 128-byte id travels over torch.distributed."""
         if self.tp_world == 1:
             return
+        import os
         import torch.distributed as dist
+        if peer_allreduce is None:
+            peer_allreduce = os.environ.get("B200_PEER_ALLREDUCE", "1") != "0"
         buf = (C.c_char * 128)()
         if self.tp_rank == 0:
             _abi.check(self.lib.b200_nccl_unique_id(buf))
@@ -155,6 +158,16 @@ class ModelRunner:
         dist.broadcast_object_list(obj, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
         idb = (C.c_char * 128).from_buffer_copy(obj[0])
         _abi.check(self.lib.b200_nccl_init(self.ctx, idb))
+        if peer_allreduce:
+            # exchange the CUDA-IPC handles of the all-reduce buffers: from here on the per-layer
+            # all-reduces are one peer-memory kernel per rank instead of NCCL
+            h = (C.c_char * 64)()
+            _abi.check(self.lib.b200_tp_ipc_export(self.ctx, h))
+            handles = [None] * self.tp_world
+            dist.all_gather_object(handles, bytes(h), group=group)
+            allh = (C.c_char * (64 * self.tp_world)).from_buffer_copy(b"".join(handles))
+            _abi.check(self.lib.b200_tp_ipc_import(self.ctx, allh, self.tp_world))
+            dist.barrier(group=group)
 
     # ---- one step ---------------------------------------------------------------------------
     def pack(self, b: StepBatch):

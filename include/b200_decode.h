@@ -109,6 +109,13 @@ B200_API int b200_set_rope_cache(b200_ctx* ctx, const void* cos_sin, int64_t max
 B200_API int b200_nccl_unique_id(void* host_id128);
 B200_API int b200_nccl_init(b200_ctx* ctx, const void* host_id128);
 
+/* Peer-memory all-reduce (optional, after b200_nccl_init): every rank exports the CUDA-IPC handle of its
+ * all-reduce buffers (64 bytes), the ranks exchange them, and each imports all `world` handles (rank
+ * order).  From then on the two all-reduces per layer run as ONE kernel per rank over NVLink peer loads
+ * (flag barrier + rank-ordered fp32 sum) instead of NCCL; NCCL stays the fallback when this is skipped. */
+B200_API int b200_tp_ipc_export(b200_ctx* ctx, void* host_handle64);
+B200_API int b200_tp_ipc_import(b200_ctx* ctx, const void* host_handles, int32_t world);
+
 /* ---- the hot path: one scheduler step ----------------------------
  * Replaces ModelRunner.execute_model of the image for one batch of token rows
  * ([V22] vllm/model_executor/models/llama.py:395-434 + sampler.py:235-236).

@@ -11,7 +11,7 @@ from oracle import decode_oracle as O
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, name, port, out_q):
+def _worker(rank, world, name, port, out_q, peer):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     torch.cuda.set_device(rank)
@@ -22,7 +22,7 @@ def _worker(rank, world, name, port, out_q):
     r = R.ModelRunner(C.ModelConfig(**ocfg.to_dict()), max_tokens=64, max_model_len=512, n_blocks=8,
                       tp_rank=rank, tp_world=world)
     r.load_weights(w)
-    r.init_tp()
+    r.init_tp(peer_allreduce=peer)
     ids = O.make_prompt(ocfg, 5, 40)
     T = len(ids)
     bt = torch.tensor([[3]], dtype=torch.int32, device="cuda")
@@ -42,13 +42,14 @@ def _worker(rank, world, name, port, out_q):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_tp2_decode_step_matches_oracle():
+@pytest.mark.parametrize("peer", [True, False], ids=["peer-memory-allreduce", "nccl-allreduce"])
+def test_tp2_decode_step_matches_oracle(peer):
     import torch.multiprocessing as mp
     name = "tiny-g8"
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29600 + os.getpid() % 2000
-    procs = [ctx.Process(target=_worker, args=(r, 2, name, port, q)) for r in range(2)]
+    port = 29600 + os.getpid() % 2000 + (7 if peer else 0)
+    procs = [ctx.Process(target=_worker, args=(r, 2, name, port, q, peer)) for r in range(2)]
     for p in procs:
         p.start()
     full, toks = q.get(timeout=300)
