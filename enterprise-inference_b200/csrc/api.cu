@@ -553,12 +553,19 @@ extern "C" int b200_advance_decode_rows(int32_t* ids, int32_t* positions, int32_
 }
 
 // Row-parallel linears write into partial_dst(); tp_reduce() turns the partials of all ranks into c->x.
-static __nv_bfloat16* partial_dst(b200_ctx* c, int buf_idx) {
-  return c->ar_ready ? reinterpret_cast<__nv_bfloat16*>(c->ar_mem + (int64_t)buf_idx * c->ar_buf_bytes) : c->x;
+// The one-shot peer-memory kernel wins where the all-reduce is latency bound (small messages); for large
+// messages NCCL's bandwidth-optimal algorithm is faster (measured at TP8: 1 MiB messages 15.0 vs 20.1 ms
+// per 70B step, 16 KiB messages 8.6 vs 9.7 ms) — switch-over tunable with B200_PEER_AR_MAX_KB.
+static bool use_peer_ar(const b200_ctx* c, int T) {
+  static const int64_t max_kb = getenv("B200_PEER_AR_MAX_KB") ? atoi(getenv("B200_PEER_AR_MAX_KB")) : 256;
+  return c->ar_ready && (int64_t)T * c->cfg.hidden * 2 <= max_kb * 1024;
+}
+static __nv_bfloat16* partial_dst(b200_ctx* c, int buf_idx, int T) {
+  return use_peer_ar(c, T) ? reinterpret_cast<__nv_bfloat16*>(c->ar_mem + (int64_t)buf_idx * c->ar_buf_bytes) : c->x;
 }
 static int tp_reduce(b200_ctx* c, int buf_idx, int T, cudaStream_t s) {
   const int64_t count = (int64_t)T * c->cfg.hidden;
-  if (!c->ar_ready) return b200_allreduce_bf16(c, c->x, count, s);   // NCCL fallback
+  if (!use_peer_ar(c, T)) return b200_allreduce_bf16(c, c->x, count, s);   // NCCL
   ArParams p = {};
   for (int r = 0; r < c->cfg.tp_world; ++r) {
     p.bufs[r] = reinterpret_cast<const __nv_bfloat16*>(c->ar_peer[r] + (int64_t)buf_idx * c->ar_buf_bytes);
@@ -637,7 +644,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     {  // O
       LinearExtra ex;
       if (tc_path(T, on, ok, c->gemv_max_t)) pf(ex, L.gu, (int64_t)gn * h);
-      STEP(linear_any(c->attn_out, ok, L.o, nullptr, tp ? partial_dst(c, 0) : c->x, h, T, on, ok, 0, c->gemv_max_t,
+      STEP(linear_any(c->attn_out, ok, L.o, nullptr, tp ? partial_dst(c, 0, T) : c->x, h, T, on, ok, 0, c->gemv_max_t,
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
     if (tp) STEP(tp_reduce(c, 0, T, s));
@@ -665,7 +672,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
         else
           pf(ex, c->lm_head, (int64_t)c->vocab_local * h);
       }
-      STEP(linear_any(c->act, dk, L.down, nullptr, tp ? partial_dst(c, 1) : c->x, h, T, dn, dk, 0, c->gemv_max_t,
+      STEP(linear_any(c->act, dk, L.down, nullptr, tp ? partial_dst(c, 1, T) : c->x, h, T, dn, dk, 0, c->gemv_max_t,
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
     if (tp) STEP(tp_reduce(c, 1, T, s));
