@@ -131,7 +131,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
                      const __nv_bfloat16* __restrict__ q, int64_t ldq, const int32_t* __restrict__ block_table,
                      int bt_stride, const int32_t* __restrict__ row_to_seq, const int32_t* __restrict__ ctx_lens,
                      __nv_bfloat16* __restrict__ out, int64_t ldo, int hkv, int block_size, int tiles_per_split,
-                     int n_splits, float scale, float* __restrict__ part_o, float* __restrict__ part_ml) {
+                     int n_splits, int n_rows, float scale, float* __restrict__ part_o, float* __restrict__ part_ml) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* kv = smem;
@@ -145,13 +145,13 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   uint64_t* s_full = kv_free + kKvStages;    // [2]
   uint64_t* p_ready = s_full + 2;            // [2]
   uint64_t* o_full = p_ready + 2;            // [1]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);   // o_full[1] is q_ready
   float* xmax = reinterpret_cast<float*>(tmem_slot + 2);   // [4 warps][8 heads]
   float* xsum = xmax + 32;                                  // [4 warps][8 heads]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int split = blockIdx.x, kvh = blockIdx.y, t = blockIdx.z;
   const int hq = hkv * G;
+  uint64_t* q_ready = o_full + 1;   // [1], 128 arrivals: Q of the current work item is staged
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kKvStages; ++s) {
@@ -164,6 +164,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       mbar_init(&p_ready[s], 128);
     }
     mbar_init(o_full, 1);
+    mbar_init(q_ready, 128);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -171,90 +172,110 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
                  "r"(kTmemCols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-  // zero the small operand tiles (Q, P hi/lo): rows >= G must not feed NaNs into the unused columns
+  // zero the small operand tiles (Q, P hi/lo) once: rows >= G must not feed NaNs into the unused columns
   for (int i = threadIdx.x; i < (2 + 8) * kSmallTile / 16; i += kThreads)
     reinterpret_cast<uint4*>(qs)[i] = make_uint4(0u, 0u, 0u, 0u);
-  __syncthreads();
-  pdl_wait();               // q comes from the previous kernel; everything above overlapped its tail
-  pdl_launch_dependents();
-  // stage Q (G heads x 128 dims) as the swizzled K-major B operand of S^T = K . Q^T
-  for (int i = threadIdx.x; i < G * 16; i += kThreads) {
-    const int g = i >> 4, ch = i & 15;   // 16-byte chunk ch of head g
-    const uint4 v = *reinterpret_cast<const uint4*>(q + (int64_t)blockIdx.z * ldq + (blockIdx.y * G + g) * kHeadDim + ch * 8);
-    *reinterpret_cast<uint4*>(qs + small_off(g, ch * 8)) = v;
-  }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();               // q and the newest K/V rows come from the previous kernel; the set-up above overlapped its tail
+  pdl_launch_dependents();
 
-  const int ctx = ctx_lens[t];
-  const int seq = row_to_seq ? row_to_seq[t] : t;
-  const int n_tiles_total = (ctx + kTileTok - 1) / kTileTok;
-  const int tile_begin = split * tiles_per_split;
-  const int n_tiles = max(min(tile_begin + tiles_per_split, n_tiles_total) - tile_begin, 0);
-  const int32_t* bt = block_table + (int64_t)seq * bt_stride;
+  // Persistent CTA: work items (row t, kv head, split) are taken round-robin; the K/V ring, the S/P
+  // double buffers and all barrier phases run on ONE tile counter across items, so the TMA producer
+  // streams the next item's tiles while the softmax threads finish the current one.
+  const int n_items = n_splits * hkv * n_rows;
+  struct Item {
+    int t, kvh, split, ctx, tile_begin, n_tiles;
+    const int32_t* bt;
+  };
+  auto get_item = [&](int it) {
+    Item w;
+    w.split = it % n_splits;
+    w.kvh = (it / n_splits) % hkv;
+    w.t = it / (n_splits * hkv);
+    w.ctx = ctx_lens[w.t];
+    const int seq = row_to_seq ? row_to_seq[w.t] : w.t;
+    const int total = (w.ctx + kTileTok - 1) / kTileTok;
+    w.tile_begin = w.split * tiles_per_split;
+    w.n_tiles = max(min(w.tile_begin + tiles_per_split, total) - w.tile_begin, 0);
+    w.bt = block_table + (int64_t)seq * bt_stride;
+    return w;
+  };
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0 && n_tiles > 0) {
+    if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
-      for (int i = 0; i < n_tiles; ++i) {
-        const int st = i % kKvStages;
-        if (i >= kKvStages) mbar_wait(&kv_free[st], ((i / kKvStages) - 1) & 1);
-        const int tok0 = (tile_begin + i) * kTileTok;
-        const int blk = bt[tok0 / block_size];
-        const int row0 = (blk * hkv + kvh) * block_size + (tok0 % block_size);
-        unsigned char* sb = kv + st * kStageBytes;
-        mbar_expect_tx(&k_full[st], 2 * kHalfBytes);
-        tma_load_2d(sb, &map_k, 0, row0, &k_full[st]);
-        tma_load_2d(sb + kHalfBytes, &map_k, 64, row0, &k_full[st]);
-        mbar_expect_tx(&v_full[st], 2 * kHalfBytes);
-        tma_load_2d(sb + 2 * kHalfBytes, &map_v, 0, row0, &v_full[st]);
-        tma_load_2d(sb + 3 * kHalfBytes, &map_v, 64, row0, &v_full[st]);
+      int n = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const Item w = get_item(it);
+        for (int i = 0; i < w.n_tiles; ++i, ++n) {
+          const int st = n % kKvStages;
+          if (n >= kKvStages) mbar_wait(&kv_free[st], ((n / kKvStages) - 1) & 1);
+          const int tok0 = (w.tile_begin + i) * kTileTok;
+          const int blk = w.bt[tok0 / block_size];
+          const int row0 = (blk * hkv + w.kvh) * block_size + (tok0 % block_size);
+          unsigned char* sb = kv + st * kStageBytes;
+          mbar_expect_tx(&k_full[st], 2 * kHalfBytes);
+          tma_load_2d(sb, &map_k, 0, row0, &k_full[st]);
+          tma_load_2d(sb + kHalfBytes, &map_k, 64, row0, &k_full[st]);
+          mbar_expect_tx(&v_full[st], 2 * kHalfBytes);
+          tma_load_2d(sb + 2 * kHalfBytes, &map_v, 0, row0, &v_full[st]);
+          tma_load_2d(sb + 3 * kHalfBytes, &map_v, 64, row0, &v_full[st]);
+        }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread), software pipelined: S(i+1) is issued before waiting for P(i) =====
-    if (lane == 0 && n_tiles > 0) {
+    // ===== MMA issuer (one thread), software pipelined: S(n+1) is issued before waiting for P(n) =====
+    if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc(0);
       constexpr uint32_t idesc_pv = make_idesc(1);
       const uint32_t q_addr = smem_u32(qs);
-      auto issue_s = [&](int i) {
-        const int st = i % kKvStages;
-        mbar_wait(&k_full[st], (i / kKvStages) & 1);
+      auto issue_s = [&](int n) {
+        const int st = n % kKvStages;
+        mbar_wait(&k_full[st], (n / kKvStages) & 1);
         tc_fence_after();
         const uint32_t k_addr = smem_u32(kv + st * kStageBytes);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
           const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
-          tc_mma(tmem_base + (i & 1) * 16, make_desc(k_addr + ao, 16, 1024), make_desc(q_addr + bo, 16, 1024), idesc_qk,
+          tc_mma(tmem_base + (n & 1) * 16, make_desc(k_addr + ao, 16, 1024), make_desc(q_addr + bo, 16, 1024), idesc_qk,
                  j ? 1u : 0u);
         }
-        tc_commit(&s_full[i & 1]);
+        tc_commit(&s_full[n & 1]);
       };
-      issue_s(0);
-      for (int i = 0; i < n_tiles; ++i) {
-        if (i + 1 < n_tiles) issue_s(i + 1);
-        const int st = i % kKvStages;
-        mbar_wait(&v_full[st], (i / kKvStages) & 1);
-        mbar_wait(&p_ready[i & 1], (i >> 1) & 1);
+      int n = 0, active = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const Item w = get_item(it);
+        if (w.n_tiles == 0) continue;
+        mbar_wait(q_ready, active & 1);   // this item's Q is in shared memory
         tc_fence_after();
-        const uint32_t v_addr = smem_u32(kv + st * kStageBytes + 2 * kHalfBytes);
-        const uint32_t ph = smem_u32(p_hi + (i & 1) * 2 * kSmallTile);
-        const uint32_t pl = smem_u32(p_lo + (i & 1) * 2 * kSmallTile);
+        ++active;
+        issue_s(n);
+        for (int i = 0; i < w.n_tiles; ++i, ++n) {
+          if (i + 1 < w.n_tiles) issue_s(n + 1);
+          const int st = n % kKvStages;
+          mbar_wait(&v_full[st], (n / kKvStages) & 1);
+          mbar_wait(&p_ready[n & 1], (n >> 1) & 1);
+          tc_fence_after();
+          const uint32_t v_addr = smem_u32(kv + st * kStageBytes + 2 * kHalfBytes);
+          const uint32_t ph = smem_u32(p_hi + (n & 1) * 2 * kSmallTile);
+          const uint32_t pl = smem_u32(p_lo + (n & 1) * 2 * kSmallTile);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {  // 16 tokens per step: two 8-token K groups of the MN-major V tile
-          const uint64_t da = make_desc(v_addr + j * 2048, kHalfBytes, 1024);
-          const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
-          tc_mma(tmem_base + 32, da, make_desc(ph + bo, 16, 1024), idesc_pv, j ? 1u : 0u);
-          tc_mma(tmem_base + 32, da, make_desc(pl + bo, 16, 1024), idesc_pv, 1u);
+          for (int j = 0; j < 8; ++j) {  // 16 tokens per step: two 8-token K groups of the MN-major V tile
+            const uint64_t da = make_desc(v_addr + j * 2048, kHalfBytes, 1024);
+            const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
+            tc_mma(tmem_base + 32, da, make_desc(ph + bo, 16, 1024), idesc_pv, j ? 1u : 0u);
+            tc_mma(tmem_base + 32, da, make_desc(pl + bo, 16, 1024), idesc_pv, 1u);
+          }
+          tc_commit(&kv_free[st]);  // K and V of this stage are no longer read
+          tc_commit(o_full);
         }
-        tc_commit(&kv_free[st]);  // K and V of this stage are no longer read
-        tc_commit(o_full);
       }
     }
   } else {
@@ -262,93 +283,109 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     const int quad = warp & 3;
     const int tau = quad * 32 + lane;   // TMEM lane
     const int wq = warp - 2;
-    float m_run[G], l_run[G], acc[G];
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      m_run[g] = -INFINITY;
-      l_run[g] = 0.f;
-      acc[g] = 0.f;
-    }
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
-    for (int i = 0; i < n_tiles; ++i) {
-      const int st = i % kKvStages;
-      const int tok0 = (tile_begin + i) * kTileTok;
-      const int n_valid = min(kTileTok, ctx - tok0);
-      mbar_wait(&s_full[i & 1], (i >> 1) & 1);
-      tc_fence_after();
-      uint32_t r[16];
-      tmem_ld16(lane_addr + (i & 1) * 16, r);
-      float sc[G];
-#pragma unroll
-      for (int g = 0; g < G; ++g) sc[g] = tau < n_valid ? __uint_as_float(r[g]) * scale : -INFINITY;
-      // tile max per head over the 128 tokens
+    int n = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      const Item w = get_item(it);
+      float m_run[G], l_run[G], acc[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) {
-        const float wm = warp_max(sc[g]);
-        if (lane == 0) xmax[wq * 8 + g] = wm;
+        m_run[g] = -INFINITY;
+        l_run[g] = 0.f;
+        acc[g] = 0.f;
+      }
+      if (w.n_tiles > 0) {
+        // stage Q (G heads x 128 dims) as the swizzled K-major B operand of S^T = K . Q^T.  The previous
+        // item's MMAs are complete (its last o_full was waited on), so the buffer is free.
+        for (int i = wq * 32 + lane; i < G * 16; i += 128) {
+          const int g = i >> 4, ch = i & 15;   // 16-byte chunk ch of head g
+          const uint4 v = *reinterpret_cast<const uint4*>(q + (int64_t)w.t * ldq + (w.kvh * G + g) * kHeadDim + ch * 8);
+          *reinterpret_cast<uint4*>(qs + small_off(g, ch * 8)) = v;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_arrive(q_ready);
+      }
+      for (int i = 0; i < w.n_tiles; ++i, ++n) {
+        const int st = n % kKvStages;
+        const int tok0 = (w.tile_begin + i) * kTileTok;
+        const int n_valid = min(kTileTok, w.ctx - tok0);
+        mbar_wait(&s_full[n & 1], (n >> 1) & 1);
+        tc_fence_after();
+        uint32_t r[16];
+        tmem_ld16(lane_addr + (n & 1) * 16, r);
+        float sc[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) sc[g] = tau < n_valid ? __uint_as_float(r[g]) * scale : -INFINITY;
+        // tile max per head over the 128 tokens
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const float wm = warp_max(sc[g]);
+          if (lane == 0) xmax[wq * 8 + g] = wm;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        float alpha[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const float tm = fmaxf(fmaxf(xmax[g], xmax[8 + g]), fmaxf(xmax[16 + g], xmax[24 + g]));
+          const float m_new = fmaxf(m_run[g], tm);   // finite: token tok0 of an active tile is valid
+          alpha[g] = __expf(m_run[g] - m_new);       // 0 on the first tile
+          m_run[g] = m_new;
+          const float pv = __expf(sc[g] - m_new);    // 0 for masked tokens
+          l_run[g] = l_run[g] * alpha[g] + pv;
+          const float hi = round_bf16(pv);
+          const float lo = pv - hi;
+          const uint32_t off = small_off(g, tau) + (n & 1) * 2 * kSmallTile;
+          *reinterpret_cast<__nv_bfloat16*>(p_hi + off) = __float2bfloat16_rn(hi);
+          *reinterpret_cast<__nv_bfloat16*>(p_lo + off) = __float2bfloat16_rn(lo);
+        }
+        if (n_valid < kTileTok) {
+          // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor
+          // core) — wait for the tile, then zero this thread's row if it is past the end
+          mbar_wait(&v_full[st], (n / kKvStages) & 1);
+          if (tau >= n_valid) {
+            unsigned char* vb = kv + st * kStageBytes + 2 * kHalfBytes;
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+              for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(vb + h2 * kHalfBytes + tau * 128 + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
+        tc_fence_before();
+        mbar_arrive(&p_ready[n & 1]);
+        // O_tile^T[dim = tau][head]: fold into the running output in registers
+        mbar_wait(o_full, n & 1);
+        tc_fence_after();
+        tmem_ld16(lane_addr + 32, r);
+#pragma unroll
+        for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha[g] + __uint_as_float(r[g]);
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // xmax is rewritten by the next tile
+      }
+      // total l per head: sum the per-token partial sums over the 128 threads
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const float ws = warp_sum(l_run[g]);
+        if (lane == 0) xsum[wq * 8 + g] = ws;
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      float alpha[G];
+      const int d = tau;
 #pragma unroll
       for (int g = 0; g < G; ++g) {
-        const float tm = fmaxf(fmaxf(xmax[g], xmax[8 + g]), fmaxf(xmax[16 + g], xmax[24 + g]));
-        const float m_new = fmaxf(m_run[g], tm);   // finite: token tok0 of an active tile is valid
-        alpha[g] = __expf(m_run[g] - m_new);       // 0 on the first tile
-        m_run[g] = m_new;
-        const float pv = __expf(sc[g] - m_new);    // 0 for masked tokens
-        l_run[g] = l_run[g] * alpha[g] + pv;
-        const float hi = round_bf16(pv);
-        const float lo = pv - hi;
-        const uint32_t off = small_off(g, tau) + (i & 1) * 2 * kSmallTile;
-        *reinterpret_cast<__nv_bfloat16*>(p_hi + off) = __float2bfloat16_rn(hi);
-        *reinterpret_cast<__nv_bfloat16*>(p_lo + off) = __float2bfloat16_rn(lo);
-      }
-      if (n_valid < kTileTok) {
-        // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor
-        // core) — wait for the tile, then zero this thread's row if it is past the end
-        mbar_wait(&v_full[st], (i / kKvStages) & 1);
-        if (tau >= n_valid) {
-          unsigned char* vb = kv + st * kStageBytes + 2 * kHalfBytes;
-#pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2)
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-              *reinterpret_cast<uint4*>(vb + h2 * kHalfBytes + tau * 128 + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+        const float l = xsum[g] + xsum[8 + g] + xsum[16 + g] + xsum[24 + g];
+        const int head = w.kvh * G + g;
+        if (n_splits == 1) {
+          out[(int64_t)w.t * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? acc[g] / l : 0.f);
+        } else {
+          const int64_t pi = ((int64_t)w.t * hq + head) * n_splits + w.split;
+          part_o[pi * kHeadDim + d] = acc[g];
+          if (d == 0) {
+            part_ml[pi * 2] = m_run[g];
+            part_ml[pi * 2 + 1] = l;
+          }
         }
       }
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
-      tc_fence_before();
-      mbar_arrive(&p_ready[i & 1]);
-      // O_tile^T[dim = tau][head]: fold into the running output in registers
-      mbar_wait(o_full, i & 1);
-      tc_fence_after();
-      tmem_ld16(lane_addr + 32, r);
-#pragma unroll
-      for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha[g] + __uint_as_float(r[g]);
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // xmax is rewritten by the next tile
-    }
-    // total l per head: sum the per-token partial sums over the 128 threads
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      const float ws = warp_sum(l_run[g]);
-      if (lane == 0) xsum[wq * 8 + g] = ws;
-    }
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    const int d = tau;
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      const float l = xsum[g] + xsum[8 + g] + xsum[16 + g] + xsum[24 + g];
-      const int head = kvh * G + g;
-      if (n_splits == 1) {
-        out[(int64_t)t * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? acc[g] / l : 0.f);
-      } else {
-        const int64_t pi = ((int64_t)t * hq + head) * n_splits + split;
-        part_o[pi * kHeadDim + d] = acc[g];
-        if (d == 0) {
-          part_ml[pi * 2] = m_run[g];
-          part_ml[pi * 2 + 1] = l;
-        }
-      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // xsum is rewritten by the next item
     }
     tc_fence_before();
   }
@@ -371,8 +408,10 @@ int launch_attn_tc(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bflo
     B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnTcSmem));
     attr_set = true;
   }
-  B200_CUDA(launch(paged_attn_tc_kernel<G>, dim3(n_splits, hkv, T), dim3(kThreads), (size_t)kAttnTcSmem, s, mk, mv, q,
-                   ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, scale,
+  const int64_t items = (int64_t)n_splits * hkv * T;
+  const int grid = (int)(items < kNumSMs ? items : kNumSMs);   // persistent: one CTA per SM, items round-robin
+  B200_CUDA(launch(paged_attn_tc_kernel<G>, dim3(grid), dim3(kThreads), (size_t)kAttnTcSmem, s, mk, mv, q, ldq,
+                   block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, T, scale,
                    part_o, part_ml));
   return B200_OK;
 }
