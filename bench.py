@@ -307,8 +307,11 @@ def run_b200(args):
     k_ms = e0.elapsed_time(e1) / (reps * len(gu))
     k_bytes = 2 * r.inter * cfg.hidden * 2
     achieved = k_bytes / k_ms / 1e6
+    # dram__bytes_read+write per launch from the committed `ncu --set full` capture of this kernel
+    # (profiles/r01_ncu_linear_gate_up.md: 235.45 MB + 3.4 MB at the 8B shape, T=64); null for other shapes
+    traffic = 238.9e6 if (model == "llama-3.1-8b" and B == 64) else None
     roofline = {"bound": "hbm", "kernel": "linear gate_up [2I x h] weight stream, T=%d" % B, "achieved": round(achieved, 1),
-                "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": None,
+                "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": traffic,
                 "peak_source": peak_src, "bytes_per_launch": k_bytes, "us_per_launch": round(k_ms * 1e3, 2),
                 "whole_step": {"bytes": int(step_bytes), "GBps": round(step_gbs, 1), "frac": round(step_gbs / hbm_peak, 4)}}
 
