@@ -313,11 +313,18 @@ int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
                   void* ws, int64_t ws_bytes, cudaStream_t s);
 
-// 128-token tiles, one CTA per SM: split until about one wave of CTAs exists.
+// 128-token tiles, persistent CTAs (one per SM) that take work items round-robin in split-major
+// order.  Rows are cut into chunks of C tiles so that there are several items per CTA (about 8 per
+// SM): chunks cost the same, later splits of shorter rows are empty and skipped, so the static
+// round-robin is balanced without a device-side queue.  Pure function of (T, hkv, bucketed max_ctx).
 void attn_split_plan_tc(int T, int hkv, int max_ctx, int* n_splits, int* tiles_per_split) {
   const int tiles = pow2_at_least(max(max_ctx, 1), 128) / 128;
-  const int ctas = max(T * hkv, 1);
-  int s = (kNumSMs + ctas - 1) / ctas;
+  const int64_t base = max((int64_t)T * hkv, (int64_t)1);
+  int s = 1;
+  if (base < 2 * kNumSMs) {   // enough rows x kv heads already: splitting only adds partials and a merge launch
+    const int64_t chunk = max((int64_t)4, (int64_t)tiles * base / (8 * kNumSMs));   // >= 512 tokens per item
+    s = (int)min((int64_t)64, (tiles + chunk - 1) / chunk);
+  }
   s = max(1, min(s, tiles));
   *tiles_per_split = (tiles + s - 1) / s;
   *n_splits = (tiles + *tiles_per_split - 1) / *tiles_per_split;

@@ -38,7 +38,7 @@ constexpr int kStageBytes = 4 * kHalfBytes;       // K lo|hi dims, V lo|hi dims:
 constexpr int kSmallTile = 16 * 64 * 2;           // one [16 heads][64] swizzled sub-tile: 2 KiB
 constexpr int kThreads = 192;
 constexpr int kNPad = 16;                         // heads padded to the UMMA N
-constexpr uint32_t kTmemCols = 64;                // S0 | S1 | O | (spare), 16 columns each
+constexpr uint32_t kTmemCols = 64;                // S0 | S1 | O0 | O1, 16 columns each
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -144,14 +144,14 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   uint64_t* kv_free = v_full + kKvStages;    // [kKvStages]
   uint64_t* s_full = kv_free + kKvStages;    // [2]
   uint64_t* p_ready = s_full + 2;            // [2]
-  uint64_t* o_full = p_ready + 2;            // [1]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);   // o_full[1] is q_ready
+  uint64_t* o_full = p_ready + 2;            // [2] one per O buffer
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 3);   // o_full[2] is q_ready
   float* xmax = reinterpret_cast<float*>(tmem_slot + 2);   // [4 warps][8 heads]
   float* xsum = xmax + 32;                                  // [4 warps][8 heads]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int hq = hkv * G;
-  uint64_t* q_ready = o_full + 1;   // [1], 128 arrivals: Q of the current work item is staged
+  uint64_t* q_ready = o_full + 2;   // [1], 128 arrivals: Q of the current work item is staged
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kKvStages; ++s) {
@@ -162,8 +162,8 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     for (int s = 0; s < 2; ++s) {
       mbar_init(&s_full[s], 1);
       mbar_init(&p_ready[s], 128);
+      mbar_init(&o_full[s], 1);
     }
-    mbar_init(o_full, 1);
     mbar_init(q_ready, 128);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -192,10 +192,11 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     const int32_t* bt;
   };
   auto get_item = [&](int it) {
-    Item w;
-    w.split = it % n_splits;
-    w.kvh = (it / n_splits) % hkv;
-    w.t = it / (n_splits * hkv);
+    Item w;   // split-major: all first chunks, then all second chunks, ... (long items first)
+    const int n_base = hkv * n_rows;
+    w.split = it / n_base;
+    w.kvh = (it % n_base) % hkv;
+    w.t = (it % n_base) / hkv;
     w.ctx = ctx_lens[w.t];
     const int seq = row_to_seq ? row_to_seq[w.t] : w.t;
     const int total = (w.ctx + kTileTok - 1) / kTileTok;
@@ -270,11 +271,11 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
           for (int j = 0; j < 8; ++j) {  // 16 tokens per step: two 8-token K groups of the MN-major V tile
             const uint64_t da = make_desc(v_addr + j * 2048, kHalfBytes, 1024);
             const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
-            tc_mma(tmem_base + 32, da, make_desc(ph + bo, 16, 1024), idesc_pv, j ? 1u : 0u);
-            tc_mma(tmem_base + 32, da, make_desc(pl + bo, 16, 1024), idesc_pv, 1u);
+            tc_mma(tmem_base + 32 + (n & 1) * 16, da, make_desc(ph + bo, 16, 1024), idesc_pv, j ? 1u : 0u);
+            tc_mma(tmem_base + 32 + (n & 1) * 16, da, make_desc(pl + bo, 16, 1024), idesc_pv, 1u);
           }
           tc_commit(&kv_free[st]);  // K and V of this stage are no longer read
-          tc_commit(o_full);
+          tc_commit(&o_full[n & 1]);
         }
       }
     }
@@ -287,12 +288,13 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     int n = 0;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const Item w = get_item(it);
-      float m_run[G], l_run[G], acc[G];
+      float m_run[G], l_run[G], acc[G], alpha_prev[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) {
         m_run[g] = -INFINITY;
         l_run[g] = 0.f;
         acc[g] = 0.f;
+        alpha_prev[g] = 0.f;
       }
       if (w.n_tiles > 0) {
         // stage Q (G heads x 128 dims) as the swizzled K-major B operand of S^T = K . Q^T.  The previous
@@ -354,13 +356,26 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
         tc_fence_before();
         mbar_arrive(&p_ready[n & 1]);
-        // O_tile^T[dim = tau][head]: fold into the running output in registers
-        mbar_wait(o_full, n & 1);
-        tc_fence_after();
-        tmem_ld16(lane_addr + 32, r);
+        // Fold the PREVIOUS tile's O_tile^T[dim = tau][head] into the running output (O is double
+        // buffered in TMEM): the P.V MMAs of this tile run while the next tile's softmax is computed.
+        if (i > 0) {
+          mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
+          tc_fence_after();
+          tmem_ld16(lane_addr + 32 + ((n - 1) & 1) * 16, r);
 #pragma unroll
-        for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha[g] + __uint_as_float(r[g]);
+          for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha_prev[g] + __uint_as_float(r[g]);
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) alpha_prev[g] = alpha[g];
         asm volatile("bar.sync 1, 128;" ::: "memory");  // xmax is rewritten by the next tile
+      }
+      if (w.n_tiles > 0) {   // the last tile's O
+        uint32_t r[16];
+        mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
+        tc_fence_after();
+        tmem_ld16(lane_addr + 32 + ((n - 1) & 1) * 16, r);
+#pragma unroll
+        for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha_prev[g] + __uint_as_float(r[g]);
       }
       // total l per head: sum the per-token partial sums over the 128 threads
 #pragma unroll
