@@ -36,7 +36,7 @@ constexpr int kKvStages = 3;
 constexpr int kHalfBytes = kTileTok * 64 * 2;     // one [128 tok][64 dim] swizzled sub-tile: 16 KiB
 constexpr int kStageBytes = 4 * kHalfBytes;       // K lo|hi dims, V lo|hi dims: 64 KiB
 constexpr int kSmallTile = 16 * 64 * 2;           // one [16 heads][64] swizzled sub-tile: 2 KiB
-constexpr int kThreads = 192;
+constexpr int kThreads = 224;                     // TMA warp, MMA warp, 4 softmax warps, Q-staging warp
 constexpr int kNPad = 16;                         // heads padded to the UMMA N
 constexpr uint32_t kTmemCols = 64;                // S0 | S1 | O0 | O1, 16 columns each
 
@@ -136,7 +136,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* kv = smem;
   unsigned char* qs = kv + kKvStages * kStageBytes;
-  unsigned char* p_hi = qs + 2 * kSmallTile;              // [2 buffers][2 sub-tiles]
+  unsigned char* p_hi = qs + 2 * 2 * kSmallTile;          // qs: [2 buffers][2 sub-tiles]; p: [2 buffers][2 sub-tiles]
   unsigned char* p_lo = p_hi + 2 * 2 * kSmallTile;
   uint64_t* bars = reinterpret_cast<uint64_t*>(p_lo + 2 * 2 * kSmallTile);
   uint64_t* k_full = bars;                   // [kKvStages]
@@ -145,13 +145,14 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   uint64_t* s_full = kv_free + kKvStages;    // [2]
   uint64_t* p_ready = s_full + 2;            // [2]
   uint64_t* o_full = p_ready + 2;            // [2] one per O buffer
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 3);   // o_full[2] is q_ready
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 6);   // o_full[2..3] q_ready[2], o_full[4..5] q_free[2]
   float* xmax = reinterpret_cast<float*>(tmem_slot + 2);   // [4 warps][8 heads]
   float* xsum = xmax + 32;                                  // [4 warps][8 heads]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int hq = hkv * G;
-  uint64_t* q_ready = o_full + 2;   // [1], 128 arrivals: Q of the current work item is staged
+  uint64_t* q_ready = o_full + 2;   // [2], 32 arrivals: Q of work item j is staged in qs[j & 1]
+  uint64_t* q_free = o_full + 4;    // [2], tcgen05.commit: the S MMAs of item j no longer read qs[j & 1]
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kKvStages; ++s) {
@@ -163,8 +164,9 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       mbar_init(&s_full[s], 1);
       mbar_init(&p_ready[s], 128);
       mbar_init(&o_full[s], 1);
+      mbar_init(&q_ready[s], 32);
+      mbar_init(&q_free[s], 1);
     }
-    mbar_init(q_ready, 128);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -173,7 +175,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   // zero the small operand tiles (Q, P hi/lo) once: rows >= G must not feed NaNs into the unused columns
-  for (int i = threadIdx.x; i < (2 + 8) * kSmallTile / 16; i += kThreads)
+  for (int i = threadIdx.x; i < (4 + 8) * kSmallTile / 16; i += kThreads)
     reinterpret_cast<uint4*>(qs)[i] = make_uint4(0u, 0u, 0u, 0u);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   tc_fence_before();
@@ -188,7 +190,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   // streams the next item's tiles while the softmax threads finish the current one.
   const int n_items = n_splits * hkv * n_rows;
   struct Item {
-    int t, kvh, split, ctx, tile_begin, n_tiles;
+    int t, kvh, split, ctx, tile_begin, n_tiles, blk0;
     const int32_t* bt;
   };
   auto get_item = [&](int it) {
@@ -203,8 +205,12 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     w.tile_begin = w.split * tiles_per_split;
     w.n_tiles = max(min(w.tile_begin + tiles_per_split, total) - w.tile_begin, 0);
     w.bt = block_table + (int64_t)seq * bt_stride;
+    w.blk0 = w.n_tiles > 0 ? w.bt[(w.tile_begin * kTileTok) / block_size] : 0;   // first tile's block, fetched early
     return w;
   };
+  // Every role walks the same item sequence; an item's metadata (context length, block-table row,
+  // first block id: dependent global loads, ~1 us each) is fetched one item AHEAD (`nxt`) so that an
+  // item switch never stalls the TMA stream.
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -212,13 +218,16 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
       int n = 0;
+      Item nxt = {};
+      if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-        const Item w = get_item(it);
+        const Item w = nxt;
+        if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
         for (int i = 0; i < w.n_tiles; ++i, ++n) {
           const int st = n % kKvStages;
           if (n >= kKvStages) mbar_wait(&kv_free[st], ((n / kKvStages) - 1) & 1);
           const int tok0 = (w.tile_begin + i) * kTileTok;
-          const int blk = w.bt[tok0 / block_size];
+          const int blk = i == 0 ? w.blk0 : w.bt[tok0 / block_size];
           const int row0 = (blk * hkv + w.kvh) * block_size + (tok0 % block_size);
           unsigned char* sb = kv + st * kStageBytes;
           mbar_expect_tx(&k_full[st], 2 * kHalfBytes);
@@ -235,7 +244,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc(0);
       constexpr uint32_t idesc_pv = make_idesc(1);
-      const uint32_t q_addr = smem_u32(qs);
+      uint32_t q_addr = smem_u32(qs);
       auto issue_s = [&](int n) {
         const int st = n % kKvStages;
         mbar_wait(&k_full[st], (n / kKvStages) & 1);
@@ -251,15 +260,22 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         tc_commit(&s_full[n & 1]);
       };
       int n = 0, active = 0;
+      Item nxt = {};
+      if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-        const Item w = get_item(it);
+        const Item w = nxt;
+        if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
         if (w.n_tiles == 0) continue;
-        mbar_wait(q_ready, active & 1);   // this item's Q is in shared memory
+        mbar_wait(&q_ready[active & 1], (active >> 1) & 1);   // this item's Q is in shared memory
         tc_fence_after();
-        ++active;
+        q_addr = smem_u32(qs + (active & 1) * 2 * kSmallTile);
         issue_s(n);
+        if (w.n_tiles == 1) tc_commit(&q_free[active & 1]);
         for (int i = 0; i < w.n_tiles; ++i, ++n) {
-          if (i + 1 < w.n_tiles) issue_s(n + 1);
+          if (i + 1 < w.n_tiles) {
+            issue_s(n + 1);
+            if (i + 2 == w.n_tiles) tc_commit(&q_free[active & 1]);   // last S of this item issued
+          }
           const int st = n % kKvStages;
           mbar_wait(&v_full[st], (n / kKvStages) & 1);
           mbar_wait(&p_ready[n & 1], (n >> 1) & 1);
@@ -277,7 +293,29 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
           tc_commit(&kv_free[st]);  // K and V of this stage are no longer read
           tc_commit(&o_full[n & 1]);
         }
+        ++active;
       }
+    }
+  } else if (warp == 6) {
+    // ===== Q stager: item j's G x 128 query rows -> qs[j & 1] as the swizzled K-major B operand of
+    // S^T = K . Q^T, one item ahead of the MMA warp so that item boundaries cost no bubble =====
+    int active = 0;
+    Item nxt = {};
+    if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      const Item w = nxt;
+      if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
+      if (w.n_tiles == 0) continue;
+      if (active >= 2) mbar_wait(&q_free[active & 1], ((active >> 1) - 1) & 1);
+      unsigned char* qb = qs + (active & 1) * 2 * kSmallTile;
+      for (int i = lane; i < G * 16; i += 32) {
+        const int g = i >> 4, ch = i & 15;   // 16-byte chunk ch of head g
+        const uint4 v = *reinterpret_cast<const uint4*>(q + (int64_t)w.t * ldq + (w.kvh * G + g) * kHeadDim + ch * 8);
+        *reinterpret_cast<uint4*>(qb + small_off(g, ch * 8)) = v;
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      mbar_arrive(&q_ready[active & 1]);
+      ++active;
     }
   } else {
     // ===== softmax / output: 128 threads; thread = token (S lanes) and = head dim (O lanes) =====
@@ -286,8 +324,11 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     const int wq = warp - 2;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
     int n = 0;
+    Item nxt = {};
+    if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-      const Item w = get_item(it);
+      const Item w = nxt;
+      if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
       float m_run[G], l_run[G], acc[G], alpha_prev[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) {
@@ -295,17 +336,6 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         l_run[g] = 0.f;
         acc[g] = 0.f;
         alpha_prev[g] = 0.f;
-      }
-      if (w.n_tiles > 0) {
-        // stage Q (G heads x 128 dims) as the swizzled K-major B operand of S^T = K . Q^T.  The previous
-        // item's MMAs are complete (its last o_full was waited on), so the buffer is free.
-        for (int i = wq * 32 + lane; i < G * 16; i += 128) {
-          const int g = i >> 4, ch = i & 15;   // 16-byte chunk ch of head g
-          const uint4 v = *reinterpret_cast<const uint4*>(q + (int64_t)w.t * ldq + (w.kvh * G + g) * kHeadDim + ch * 8);
-          *reinterpret_cast<uint4*>(qs + small_off(g, ch * 8)) = v;
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_arrive(q_ready);
       }
       for (int i = 0; i < w.n_tiles; ++i, ++n) {
         const int st = n % kKvStages;
@@ -411,7 +441,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   }
 }
 
-constexpr int kAttnTcSmem = kKvStages * kStageBytes + (2 + 8) * kSmallTile + 512 + 1024;
+constexpr int kAttnTcSmem = kKvStages * kStageBytes + (4 + 8) * kSmallTile + 512 + 1024;
 
 template <int G>
 int launch_attn_tc(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
