@@ -458,6 +458,12 @@ static int linear_any(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* 
   return linear_tc(x, ldx, w, bias, y, ldy, T, n_out, k, ws, ws_bytes, ex, s);
 }
 
+namespace b200 { int linear_tc_read_trace(unsigned long long* host16); }
+// debug helper (not in the public header): timestamps of CTA 0 of the last tcgen05 linear, B200_TC_TRACE=1
+extern "C" __attribute__((visibility("default"))) int b200_debug_linear_trace(unsigned long long* host16) {
+  return b200::linear_tc_read_trace(host16);
+}
+
 extern "C" int64_t b200_linear_workspace_bytes(int32_t T, int32_t n_out, int32_t k) {
   return linear_tc_workspace_bytes(T, n_out, k);
 }

@@ -135,7 +135,16 @@ struct TcParams {
   __nv_bfloat16* kc;
   __nv_bfloat16* vc;
   int hq, hkv, block_size;
+  unsigned long long* trace;  // debug (B200_TC_TRACE=1): %globaltimer stamps of CTA 0, else null
 };
+
+__device__ __forceinline__ void tc_trace(const TcParams& p, int slot) {
+  if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[slot] = t;
+  }
+}
 
 // Epilogue modes (template parameter):
 //  kPlain    y[t][row] = bf16(acc + bias)
@@ -234,6 +243,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tile = blockIdx.x, split = blockIdx.y, tok_tile = blockIdx.z;
+  if (threadIdx.x == 0) tc_trace(p, 0);   // CTA start
   // K range of this split (balanced: the first `rem` splits get one more block)
   const int base = p.n_kblocks / p.splits, rem = p.n_kblocks % p.splits;
   const int kb0 = split * base + min(split, rem);
@@ -268,7 +278,9 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         mbar_expect_tx(&full[i], kStageBytes);
         tma_load_2d(smem + i * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[i], kEvictFirst);
       }
+      tc_trace(p, 1);   // W of the first stages requested
       pdl_wait();
+      tc_trace(p, 2);   // previous kernel complete
       pdl_launch_dependents();
       for (int i = 0; i < pre; ++i)
         tma_load_2d(smem + i * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[i], kEvictLast);
@@ -290,6 +302,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       for (int i = 0; i < nkb; ++i) {
         const int st = i % S;
         mbar_wait(&full[st], (i / S) & 1);
+        if (i == 0) tc_trace(p, 3);   // first stage landed
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + st * kStageBytes);
         const uint32_t b_addr = a_addr + kABytes;
@@ -301,6 +314,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
         tc_commit(&empty[st]);  // arrives when the MMAs above have finished reading this stage
       }
+      tc_trace(p, 4);           // last MMA issued
       tc_commit(tmem_full);     // accumulator complete
     }
   } else {
@@ -314,6 +328,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       mbar_wait(tmem_full, 0);
       tc_fence_after();
     }
+    if (warp == 2 && lane == 0) tc_trace(p, 5);   // accumulator complete (epilogue starts)
     const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
     const bool direct = p.splits == 1 || p.cluster;   // the fp32 tile is staged in this CTA's smem
     // All MMAs have completed (tmem_full), so the pipeline stages are free: stage the fp32 tile
@@ -337,6 +352,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         for (int j = 0; j < 16; ++j) dst[(int64_t)j * p.n_out_pad] = __uint_as_float(r[j]);
       }
     }
+    if (warp == 2 && lane == 0) tc_trace(p, 6);   // tile staged
     bool finalize = true;
     const int tile_id = m_tile * gridDim.z + tok_tile;
     if (p.cluster) {
@@ -411,6 +427,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     }
     tc_fence_before();
   }
+  if (threadIdx.x == 64) tc_trace(p, 7);   // before the cluster phase
   if (p.cluster) {
     // ---- split-K over a thread-block cluster: every CTA staged its fp32 partial tile [token][128] in
     // its own shared memory; after a cluster barrier CTA `rank` finalises the tokens t = rank (mod S),
@@ -428,30 +445,51 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           if (m_tile * kBlockM + r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[m_tile * kBlockM + r4 + e]);
       }
       const uint32_t stg_addr = smem_u32(smem);
-      for (int t = rank + S2 * wq; t < tmax; t += 4 * S2) {
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        const uint32_t local = stg_addr + (uint32_t)(t * kBlockM + r4) * 4u;
-        for (int pr = 0; pr < S2; ++pr) {
-          uint32_t remote;
-          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(pr));
-          float4 v;
-          asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];"
-                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                       : "r"(remote)
-                       : "memory");
-          acc.x += v.x;
-          acc.y += v.y;
-          acc.z += v.z;
-          acc.w += v.w;
+      // two tokens per pass: all 2 x S remote 16-byte loads are issued before the first use, so the
+      // DSMEM latency (~1 us) is paid once per pass instead of once per peer
+      for (int t = rank + S2 * wq; t < tmax; t += 8 * S2) {
+        const int t1 = t + 4 * S2;
+        float4 v[2][8];
+#pragma unroll
+        for (int pr = 0; pr < 8; ++pr) {
+          if (pr < S2) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int tt = u ? t1 : t;
+              const uint32_t local = stg_addr + (uint32_t)((tt < tmax ? tt : t) * kBlockM + r4) * 4u;
+              uint32_t remote;
+              asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(pr));
+              asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];"
+                           : "=f"(v[u][pr].x), "=f"(v[u][pr].y), "=f"(v[u][pr].z), "=f"(v[u][pr].w)
+                           : "r"(remote)
+                           : "memory");
+            }
+          }
         }
-        finalize4<MODE>(p, m_tile, lane, tok0 + t, acc, bb);   // warp-uniform: t depends on (rank, wq) only
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int tt = u ? t1 : t;
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int pr = 0; pr < 8; ++pr) {
+            if (pr < S2) {   // rank order: deterministic and identical to the global-memory path
+              acc.x += v[u][pr].x;
+              acc.y += v[u][pr].y;
+              acc.z += v[u][pr].z;
+              acc.w += v[u][pr].w;
+            }
+          }
+          if (tt < tmax) finalize4<MODE>(p, m_tile, lane, tok0 + tt, acc, bb);   // warp-uniform condition
+        }
       }
     }
     // nobody may exit (and release its shared memory) while a peer still reads it
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
   }
+  if (threadIdx.x == 64) tc_trace(p, 8);   // reduce + finalize done
   __syncthreads();
+  if (threadIdx.x == 0) tc_trace(p, 9);    // CTA end
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
@@ -522,6 +560,15 @@ int get_map(const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t
   return B200_OK;
 }
 
+unsigned long long* g_trace = nullptr;
+unsigned long long* trace_buffer() {
+  static const bool on = getenv("B200_TC_TRACE") && atoi(getenv("B200_TC_TRACE"));
+  if (on && !g_trace) {
+    if (cudaMalloc((void**)&g_trace, 16 * sizeof(unsigned long long)) != cudaSuccess) g_trace = nullptr;
+  }
+  return on ? g_trace : nullptr;
+}
+
 inline int n_tile_for(int T) { return T <= 16 ? 16 : (T <= 32 ? 32 : (T <= 64 ? 64 : (T <= 128 ? 128 : 256))); }
 
 struct Plan {
@@ -577,6 +624,13 @@ int launch_tc(int mode, const CUtensorMap& mw, const CUtensorMap& mx, const TcPa
 
 }  // namespace
 
+// debug: copy the 16 %globaltimer stamps of the last traced launch (B200_TC_TRACE=1) to the host
+int linear_tc_read_trace(unsigned long long* host16) {
+  if (!g_trace) return B200_ERR_STATE;
+  B200_CUDA(cudaMemcpy(host16, g_trace, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return B200_OK;
+}
+
 // shared with attn_tc.cu: [rows][cols] bf16 (row stride ld), box [box_rows][64], SWIZZLE_128B
 int get_tensor_map_2d(const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows, CUtensorMap* out) {
   return get_map(ptr, rows, cols, ld, box_rows, out);
@@ -611,6 +665,7 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
   const int mode = ex ? ex->mode : 0;
   TcParams p = {};
   p.cluster = use_cluster ? 1 : 0;
+  p.trace = trace_buffer();
   if (mode == kSiluMul) {
     B200_REQUIRE(n_out % kBlockM == 0, B200_ERR_UNSUPPORTED, "linear_tc(silu_mul): n_out=%d must be a multiple of 128", n_out);
   } else if (mode == kRopeKv) {
