@@ -296,6 +296,7 @@ def run_b200(args):
             for wt in gu:
                 abi.check(lib.b200_linear_bf16(x.data_ptr(), cfg.hidden, wt.data_ptr(), None, y.data_ptr(), 2 * r.inter, B,
                                                2 * r.inter, cfg.hidden, 0, wsp.data_ptr(), wsb, stream.cuda_stream))
+    abi.check(lib.b200_set_launch_pdl(1))   # same launch attribute as inside the step
     with torch.cuda.stream(stream):
         gu_pass()
         barrier()
@@ -304,6 +305,7 @@ def run_b200(args):
         gu_pass()
         e1.record(stream)
     barrier()
+    abi.check(lib.b200_set_launch_pdl(0))
     k_ms = e0.elapsed_time(e1) / (reps * len(gu))
     k_bytes = 2 * r.inter * cfg.hidden * 2
     achieved = k_bytes / k_ms / 1e6

@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libb200decode.so")
+LIB_PATH = os.environ.get("B200_LIB") or os.path.join(HERE, "lib", "libb200decode.so")   # B200_LIB: A/B builds
 
 
 class B200Error(RuntimeError):
@@ -44,6 +44,7 @@ SIGNATURES = {
     "b200_tp_ipc_import": (C.c_int, [_vp, _vp, _i32]),
     "b200_decode_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _vp, _vp]),
     "b200_decode_step_host": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "b200_set_launch_pdl": (C.c_int, [_i32]),
     "b200_ctx_set_graphs": (C.c_int, [_vp, _i32]),
     "b200_ctx_last_step_launches": (C.c_int, [_vp]),
     "b200_ctx_set_tap": (C.c_int, [_vp, _i32, _vp, _vp]),

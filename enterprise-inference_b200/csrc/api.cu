@@ -425,6 +425,21 @@ extern "C" int b200_allreduce_bf16(b200_ctx* c, void* buf, int64_t count, void* 
   return B200_OK;
 }
 
+static thread_local const void* g_pf_hint_ptr = nullptr;
+static thread_local int64_t g_pf_hint_bytes = 0;
+// experiment hook (not in the public header): the next b200_linear_bf16 on this thread also pulls
+// [ptr, ptr+bytes) towards L2 when its CTAs finish streaming
+extern "C" __attribute__((visibility("default"))) int b200_debug_prefetch_hint(const void* ptr, int64_t bytes) {
+  g_pf_hint_ptr = ptr;
+  g_pf_hint_bytes = bytes;
+  return B200_OK;
+}
+
+extern "C" int b200_set_launch_pdl(int32_t enabled) {
+  launch_opts().pdl = enabled != 0;
+  return B200_OK;
+}
+
 extern "C" int b200_ctx_set_graphs(b200_ctx* c, int32_t enabled) {
   B200_REQUIRE(c, B200_ERR_INVALID, "null ctx");
   c->graphs = enabled != 0;
@@ -458,7 +473,10 @@ static int linear_any(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* 
   return linear_tc(x, ldx, w, bias, y, ldy, T, n_out, k, ws, ws_bytes, ex, s);
 }
 
-namespace b200 { int linear_tc_read_trace(unsigned long long* host16); }
+namespace b200 { int linear_tc_read_trace(unsigned long long* host16); int attn_tc_read_trace(unsigned long long* host64); }
+extern "C" __attribute__((visibility("default"))) int b200_debug_attn_trace(unsigned long long* host64) {
+  return b200::attn_tc_read_trace(host64);
+}
 // debug helper (not in the public header): timestamps of CTA 0 of the last tcgen05 linear, B200_TC_TRACE=1
 extern "C" __attribute__((visibility("default"))) int b200_debug_linear_trace(unsigned long long* host16) {
   return b200::linear_tc_read_trace(host16);
@@ -474,8 +492,14 @@ extern "C" int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const
   B200_REQUIRE(x && w && y && T >= 0 && n_out > 0 && k > 0, B200_ERR_INVALID, "linear: bad argument");
   int gm = 0;
   if (const char* e = getenv("B200_GEMV_MAX_T")) gm = atoi(e);
+  LinearExtra ex;
+  ex.pf_ptr = g_pf_hint_ptr;
+  ex.pf_bytes = g_pf_hint_bytes;
+  g_pf_hint_ptr = nullptr;
+  g_pf_hint_bytes = 0;
   return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias,
-                    (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, nullptr, (cudaStream_t)stream);
+                    (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, (impl == 1 || !ex.pf_ptr) ? nullptr : &ex,
+                    (cudaStream_t)stream);
 }
 
 extern "C" int b200_linear_fused_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y, int64_t ldy,
@@ -616,12 +640,14 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     }
   };
   const int qn = c->qkv_w, on = h, ok = c->hq * kHeadDim, gn = 2 * c->inter, dn = h, dk = c->inter;
+  // timing experiments only (results are wrong): B200_DEBUG_SKIP bit 0 = skip the per-layer norms, bit 1 = skip attention
+  static const int dbg_skip = getenv("B200_DEBUG_SKIP") ? atoi(getenv("B200_DEBUG_SKIP")) : 0;
   STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
   for (int l = 0; l < m.n_layers; ++l) {
     const LayerW& L = c->layers[l];
     if (l == 0)
       STEP(rmsnorm(c->res, nullptr, L.ln1, c->normed, T, h, m.rms_eps, s));
-    else
+    else if (!(dbg_skip & 1))
       STEP(rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
     __nv_bfloat16* kcl = c->kc + (int64_t)l * kv_layer_elems;
     __nv_bfloat16* vcl = c->vc + (int64_t)l * kv_layer_elems;
@@ -645,6 +671,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       if (ex.mode != 2)
         STEP(rope_kv_append(c->qkv_buf, a.positions, a.slots, c->cos_sin, kcl, vcl, T, c->hq, c->hkv, m.block_size, s));
     }
+    if (!(dbg_skip & 2))
     STEP(paged_attn(c->qkv_buf, c->qkv_w, kcl, vcl, a.block_table, a.bt_stride, a.row_to_seq, a.ctx_lens, c->attn_out,
                     c->hq * kHeadDim, T, c->hq, c->hkv, m.block_size, a.max_ctx, scale, c->attn_ws, c->attn_ws_bytes, s));
     {  // O
@@ -654,7 +681,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
     if (tp) STEP(tp_reduce(c, 0, T, s));
-    STEP(rmsnorm(c->x, c->res, L.ln2, c->normed, T, h, m.rms_eps, s));
+    if (!(dbg_skip & 1)) STEP(rmsnorm(c->x, c->res, L.ln2, c->normed, T, h, m.rms_eps, s));
     {  // gate_up (+ SiLU*mul in the epilogue over interleaved slabs)
       LinearExtra ex;
       const bool tcp = tc_path(T, gn, h, c->gemv_max_t);
@@ -730,6 +757,7 @@ static int pow2_bucket(int v) {
 }
 
 static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
+  const bool pdl_prev = launch_opts().pdl;   // the caller's per-thread setting is restored on every exit
   B200_REQUIRE(c->embed && c->final_norm && c->lm_head && c->cos_sin && c->kc, B200_ERR_STATE,
                "decode_step: weights / rope cache / kv cache not all set");
   for (int l = 0; l < c->cfg.n_layers; ++l) {
@@ -752,7 +780,7 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     launch_counter() = 0;
     rc = enqueue_step(c, a, s);
     c->last_launches = launch_counter();
-    launch_opts().pdl = false;
+    launch_opts().pdl = pdl_prev;
     return rc;
   }
   uint64_t hsh = 0x1234;
@@ -773,7 +801,7 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     rc = enqueue_step(c, b, s);
     const int n = launch_counter();
     cudaError_t e = cudaStreamEndCapture(s, &g);
-    launch_opts().pdl = false;
+    launch_opts().pdl = pdl_prev;
     if (rc) {
       if (g) cudaGraphDestroy(g);
       return rc;
@@ -790,7 +818,7 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     it = c->graph_cache.emplace(key, ge).first;
     c->last_launches = n;
   }
-  launch_opts().pdl = false;
+  launch_opts().pdl = pdl_prev;
   B200_CUDA(cudaGraphLaunch(it->second, s));
   return B200_OK;
 }

@@ -19,6 +19,7 @@
 // Replaces: paged_attention_v1/v2 CPU kernels of the vLLM-CPU image
 // ([V22] vllm/v1/attention/backends/cpu_attn.py:377-396).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -120,6 +121,17 @@ __device__ __forceinline__ uint32_t small_off(int r, int c) {
   return sub * kSmallTile + (r >> 3) * 1024 + (r & 7) * 128 + chunk * 16 + (cc & 7) * 2;
 }
 
+// debug (B200_ATTN_TRACE=1): %globaltimer stamps of CTA 0's first softmax thread
+__device__ unsigned long long g_attn_trace[64];
+__device__ int g_attn_trace_on;
+__device__ __forceinline__ void attn_trace(int slot) {
+  if (g_attn_trace_on && blockIdx.x == 0 && slot < 64) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_attn_trace[slot] = t;
+  }
+}
+
 struct Smem {
   // dynamic, 1024-aligned: kv[kKvStages][kStageBytes] | q[2*kSmallTile] | p_hi[2][2*kSmallTile] | p_lo[2][...]
   // followed by the barriers and small exchange areas (see carve-up in the kernel)
@@ -133,6 +145,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
                      __nv_bfloat16* __restrict__ out, int64_t ldo, int hkv, int block_size, int tiles_per_split,
                      int n_splits, int n_rows, float scale, float* __restrict__ part_o, float* __restrict__ part_ml) {
   extern __shared__ unsigned char smem_raw[];
+  if (threadIdx.x == 64) attn_trace(0);
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* kv = smem;
   unsigned char* qs = kv + kKvStages * kStageBytes;
@@ -184,6 +197,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();               // q and the newest K/V rows come from the previous kernel; the set-up above overlapped its tail
   pdl_launch_dependents();
+  if (threadIdx.x == 64) attn_trace(1);
 
   // Persistent CTA: work items (row t, kv head, split) are taken round-robin; the K/V ring, the S/P
   // double buffers and all barrier phases run on ONE tile counter across items, so the TMA producer
@@ -323,12 +337,13 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     const int tau = quad * 32 + lane;   // TMEM lane
     const int wq = warp - 2;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
-    int n = 0;
+    int n = 0, item_no = 0;
     Item nxt = {};
     if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++item_no) {
       const Item w = nxt;
       if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
+      if (tau == 0) attn_trace(2 + 3 * item_no);
       float m_run[G], l_run[G], acc[G], alpha_prev[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) {
@@ -342,6 +357,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         const int tok0 = (w.tile_begin + i) * kTileTok;
         const int n_valid = min(kTileTok, w.ctx - tok0);
         mbar_wait(&s_full[n & 1], (n >> 1) & 1);
+        if (i == 0 && tau == 0) attn_trace(3 + 3 * item_no);
         tc_fence_after();
         uint32_t r[16];
         tmem_ld16(lane_addr + (n & 1) * 16, r);
@@ -431,6 +447,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         }
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");  // xsum is rewritten by the next item
+      if (tau == 0) attn_trace(4 + 3 * item_no);
     }
     tc_fence_before();
   }
@@ -453,6 +470,8 @@ int launch_attn_tc(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bflo
     B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnTcSmem));
     attr_set = true;
   }
+  static const int trace_on = getenv("B200_ATTN_TRACE") ? atoi(getenv("B200_ATTN_TRACE")) : 0;
+  if (trace_on) cudaMemcpyToSymbol(g_attn_trace_on, &trace_on, sizeof(int));
   const int64_t items = (int64_t)n_splits * hkv * T;
   const int grid = (int)(items < kNumSMs ? items : kNumSMs);   // persistent: one CTA per SM, items round-robin
   B200_CUDA(launch(paged_attn_tc_kernel<G>, dim3(grid), dim3(kThreads), (size_t)kAttnTcSmem, s, mk, mv, q, ldq,
@@ -462,6 +481,11 @@ int launch_attn_tc(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bflo
 }
 
 }  // namespace
+
+int attn_tc_read_trace(unsigned long long* host64) {
+  B200_CUDA(cudaMemcpyFromSymbol(host64, g_attn_trace, 64 * sizeof(unsigned long long)));
+  return B200_OK;
+}
 
 bool paged_attn_tc_supported(int hq, int hkv, int block_size) {
   if (hkv <= 0 || hq % hkv) return false;

@@ -154,6 +154,11 @@ B200_API int b200_ctx_set_tap(b200_ctx* ctx, int32_t layer, void* out_hidden, vo
 
 /* ---- per-kernel entry points (unit tests, ncu) ------------------------------------------ */
 
+/* Launch attribute for the per-kernel entry points called from THIS thread: 1 = programmatic dependent
+ * launch (the kernels of b200_decode_step always use it unless B200_PDL=0): a kernel's prologue and first
+ * weight tiles overlap the previous kernel's tail.  Default 0. */
+B200_API int b200_set_launch_pdl(int32_t enabled);
+
 /* y[T][n_out] = x[T][k] . w[n_out][k]^T (+bias), fp32 accumulate, one rounding to bf16.
  * Replaces sgl-kernel weight_packed_linear / oneDNN matmul of the image
  * ([V22] vllm/model_executor/layers/utils.py:277-299).  impl: 0 auto, 1 CUDA-core GEMV

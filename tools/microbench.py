@@ -138,3 +138,31 @@ if __name__ == "__main__":
         bench_attn()
     if "step" in what:
         bench_step()
+
+
+def bench_prefill(model="llama-3.1-8b", T=2048, n_chunks=2):
+    """One sequence prefilled in chunks of T rows (the --max-num-batched-tokens budget): rows/s."""
+    Cfg = importlib.import_module(PKG + ".config")
+    R = importlib.import_module(PKG + ".runner")
+    cfg = Cfg.get_config(model)
+    r = R.ModelRunner(cfg, max_tokens=T, max_model_len=8192, kv_cache_gib=4)
+    r.init_random_weights()
+    nb = (T * n_chunks + 127) // 128
+    bt = torch.arange(nb, dtype=torch.int32, device="cuda").view(1, nb)
+    for c in range(n_chunks):
+        pos = torch.arange(c * T, (c + 1) * T, dtype=torch.int32, device="cuda")
+        ids = torch.randint(0, cfg.vocab, (T,), dtype=torch.int32, device="cuda")
+        rows = torch.tensor([T - 1], dtype=torch.int32, device="cuda")
+        z = torch.zeros(T, dtype=torch.int32, device="cuda")
+
+        def fn():
+            r.step_device(ids, pos, pos, bt, pos + 1, (c + 1) * T, row_to_seq=z, logit_rows=rows, stream=torch.cuda.current_stream())
+        ms = time_ms(fn, iters=3, warmup=1)
+        flops = 2 * cfg.decode_params() * T
+        print(json.dumps({"kernel": "prefill_chunk", "model": model, "T": T, "ctx_end": (c + 1) * T, "ms": round(ms, 2),
+                          "rows_per_s": round(T / ms * 1e3), "TFLOPs": round(flops / ms / 1e9, 1), "launches": r.last_step_launches()}))
+    r.close()
+
+
+if __name__ == "__main__" and "prefill" in sys.argv[1:]:
+    bench_prefill()
