@@ -44,6 +44,28 @@ WORKLOADS = {
 }
 
 
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """Rank 0 prints ONE JSON line on stdout: route everything else that libraries write to fd 1
+    (NCCL's version banner, torchrun chatter) to stderr and keep the real stdout for the result."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def peaks():
     try:
         p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -181,7 +203,7 @@ def run_reference(args):
             "config": {"workload": desc, "batch": batch},
             "cpu_baseline": {"value": round(tok_s, 3), "unit": "tok/s", **info},
             "e2e": {"value": round(tok_s, 3), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -360,7 +382,7 @@ def run_b200(args):
                 "roofline": roofline, "e2e": e2e}
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
     r.close()
     if dist is not None:
         dist.destroy_process_group()
@@ -375,6 +397,7 @@ def main():
     ap.add_argument("--workload", default="llama8b-bs64", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args)
