@@ -195,7 +195,11 @@ class ModelRunner:
     def step(self, b: StepBatch, sync: bool = True) -> np.ndarray:
         """Host-buffer step (the serving path and bench.py's e2e): pinned H2D, step, D2H."""
         T, R, S, bt_stride, n_ints = self.pack(b)
-        max_ctx = b.max_ctx
+        return self.step_packed(T, R, S, bt_stride, b.max_ctx, n_ints, sync)
+
+    def step_packed(self, T: int, R: int, S: int, bt_stride: int, max_ctx: int, n_ints: int, sync: bool = True) -> np.ndarray:
+        """The step over whatever is in the pinned packed buffer (filled by pack(), or by a broadcast
+        from rank 0 on a tensor-parallel worker)."""
         _abi.check(self.lib.b200_decode_step_host(self.ctx, self._h_meta.data_ptr(), T, S, bt_stride, max_ctx, R,
                                                   self._h_out.data_ptr(), self.stream.cuda_stream))
         self.h2d_bytes_last, self.d2h_bytes_last = n_ints * 4, R * 4

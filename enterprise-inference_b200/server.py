@@ -501,36 +501,57 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
     return app
 
 
+class _RunnerFactory:
+    """Picklable recipe for one rank's ModelRunner (used in this process and in spawned TP workers)."""
+
+    def __init__(self, args):
+        self.args = args
+
+    def resolve(self):
+        from .config import from_hf_config, get_config
+        from .weights import resolve_hf_snapshot
+        a = self.args
+        try:
+            path = resolve_hf_snapshot(a.model)
+            return path, from_hf_config(path)
+        except FileNotFoundError:
+            if not a.random_weights:
+                raise
+            return None, get_config(a.model)
+
+    def __call__(self, rank: int, world: int):
+        import torch
+        from .runner import ModelRunner
+        from .weights import load_safetensors_dir
+        a = self.args
+        path, cfg = self.resolve()
+        torch.cuda.set_device(rank)
+        runner = ModelRunner(cfg, max_tokens=a.max_num_batched_tokens, max_model_len=a.max_model_len,
+                             block_size=a.block_size, kv_cache_gib=a.kv_cache_gib, n_blocks=getattr(a, "n_blocks", None),
+                             tp_rank=rank, tp_world=world, graphs=True)
+        if a.random_weights or path is None:
+            runner.init_random_weights()
+        else:
+            runner.load_weights(load_safetensors_dir(path))
+        return runner
+
+
 def build_engine(args):
-    """Runner + engine for this rank from the chart's flags (TP workers are launched by main())."""
-    import torch
-    from .config import from_hf_config, get_config
-    from .runner import ModelRunner
-    from .weights import load_safetensors_dir, resolve_hf_snapshot
-    model_path = None
-    try:
-        model_path = resolve_hf_snapshot(args.model)
-        cfg = from_hf_config(model_path)
-    except FileNotFoundError:
-        if not args.random_weights:
-            raise
-        cfg = get_config(args.model)
-    rank = int(os.environ.get("RANK", "0"))
+    """Runner(s) + engine from the chart's flags.  tensor_parallel_size > 1: this process is rank 0 and
+    spawns one worker process per further GPU (the chart's `--distributed_executor_backend mp`)."""
+    factory = _RunnerFactory(args)
+    path, cfg = factory.resolve()
     world = args.tensor_parallel_size
-    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
-    runner = ModelRunner(cfg, max_tokens=args.max_num_batched_tokens, max_model_len=args.max_model_len,
-                         block_size=args.block_size, kv_cache_gib=args.kv_cache_gib, tp_rank=rank, tp_world=world,
-                         graphs=True)
-    if args.random_weights or model_path is None:
-        runner.init_random_weights()
-    else:
-        runner.load_weights(load_safetensors_dir(model_path))
+    workers = []
     if world > 1:
-        runner.init_tp()
+        from .tp_exec import launch_workers
+        runner, workers = launch_workers(world, factory)
+    else:
+        runner = factory(0, 1)
     engine = LLMEngine(runner, max_num_batched_tokens=args.max_num_batched_tokens, max_num_seqs=args.max_num_seqs,
                        max_model_len=args.max_model_len)
-    tok = load_tokenizer(args.tokenizer if model_path else "byte", model_path, cfg.vocab)
-    return engine, tok
+    tok = load_tokenizer(args.tokenizer if path else "byte", path, cfg.vocab)
+    return engine, tok, workers
 
 
 def main(argv=None):
@@ -538,14 +559,17 @@ def main(argv=None):
     if unknown:
         print(f"[b200] ignoring flags this backend does not know: {unknown}", flush=True)
     validate_args(args)
-    if args.tensor_parallel_size > 1:
-        raise SystemExit("tensor_parallel_size > 1: launch one process per GPU with torchrun; the multi-rank HTTP "
-                         "front end is not wired yet (rank 0 would broadcast each StepBatch) — see DESIGN.md")
     import uvicorn
-    engine, tok = build_engine(args)
+    engine, tok, workers = build_engine(args)
     app = create_app(engine, tok, args.served_model_name or args.model, args.max_model_len)
     signal.signal(signal.SIGTERM, lambda *_: (_ for _ in ()).throw(KeyboardInterrupt()))
-    uvicorn.run(app, host=args.host, port=args.port, log_level="warning" if args.disable_log_requests else "info")
+    try:
+        uvicorn.run(app, host=args.host, port=args.port, log_level="warning" if args.disable_log_requests else "info")
+    finally:
+        if workers:
+            engine.runner.stop()
+            for p in workers:
+                p.join(timeout=30)
 
 
 if __name__ == "__main__":

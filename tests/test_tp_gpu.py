@@ -64,3 +64,39 @@ def test_tp2_decode_step_matches_oracle(peer):
     assert toks.tolist() == full.argmax(-1).tolist()      # vocab-parallel pick == argmax of the gathered logits
     dis = toks != want.argmax(-1)
     assert (O.top2_margin(want)[dis] < 0.08).all()
+
+
+def _build_tiny_g8(rank, world):
+    C, R = pkg("config"), pkg("runner")
+    ocfg = O.CONFIGS["tiny-g8"]
+    r = R.ModelRunner(C.ModelConfig(**ocfg.to_dict()), max_tokens=64, max_model_len=512, n_blocks=16, tp_rank=rank, tp_world=world)
+    r.load_weights(O.make_weights(ocfg, seed=1234, norm_jitter=0.1))
+    return r
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_tp2_serving_executor_generates_oracle_tokens():
+    """The server's multi-process executor: rank 0 schedules and broadcasts each step, a spawned worker
+    rank executes it on its shard; greedy tokens through the engine match the oracle."""
+    TP, E = pkg("tp_exec"), pkg("engine")
+    leader, procs = TP.launch_workers(2, _build_tiny_g8, port=29800 + os.getpid() % 1000)
+    try:
+        eng = E.LLMEngine(leader, max_num_batched_tokens=64, max_num_seqs=4, max_model_len=512)
+        cfg = O.CONFIGS["tiny-g8"]
+        prompts = [O.make_prompt(cfg, 7, 20), O.make_prompt(cfg, 8, 70)]
+        outs = eng.generate(prompts, max_tokens=12)
+        om = O.OracleModel(cfg, O.make_weights(cfg, seed=1234, norm_jitter=0.1), capacity=128)
+        for p, got in zip(prompts, outs):
+            want, logits = om.generate(p, 12, keep_logits=True)
+            for i, (a, b) in enumerate(zip(got, want)):
+                if a != b:
+                    assert float(O.top2_margin(logits[i])) < 0.08
+                    break
+    finally:
+        leader.stop()
+        for p in procs:
+            p.join(timeout=60)
+        import torch.distributed as dist
+        leader.runner.close()
+        dist.destroy_process_group()
+    assert all(p.exitcode == 0 for p in procs)
