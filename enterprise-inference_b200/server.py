@@ -567,9 +567,8 @@ def main(argv=None):
         uvicorn.run(app, host=args.host, port=args.port, log_level="warning" if args.disable_log_requests else "info")
     finally:
         if workers:
-            engine.runner.stop()
-            for p in workers:
-                p.join(timeout=30)
+            from .tp_exec import shutdown
+            shutdown(engine.runner, workers)
 
 
 if __name__ == "__main__":

@@ -87,3 +87,13 @@ def launch_workers(world: int, build_runner, port: Optional[int] = None):
     for _ in procs:
         ready.get(timeout=600)
     return TPLeader(runner), procs
+
+
+def shutdown(leader: TPLeader, procs) -> None:
+    """Stop the workers, tear down this rank, then reap the worker processes (in this order: the
+    process-group teardown is collective, so rank 0 must not wait for the workers before joining it)."""
+    leader.stop()
+    leader.runner.close()
+    dist.destroy_process_group()
+    for p in procs:
+        p.join(timeout=60)

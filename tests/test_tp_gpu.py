@@ -93,10 +93,5 @@ def test_tp2_serving_executor_generates_oracle_tokens():
                     assert float(O.top2_margin(logits[i])) < 0.08
                     break
     finally:
-        leader.stop()
-        for p in procs:
-            p.join(timeout=60)
-        import torch.distributed as dist
-        leader.runner.close()
-        dist.destroy_process_group()
+        TP.shutdown(leader, procs)
     assert all(p.exitcode == 0 for p in procs)
