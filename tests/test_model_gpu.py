@@ -152,6 +152,22 @@ def test_full_width_8b_two_layers_vs_oracle():
     r.close()
 
 
+@pytest.mark.parametrize("name,layers,vocab", [("qwen2-32b", 2, 8192), ("llama-3.1-70b", 1, 8192)])
+def test_full_width_other_families_vs_oracle(name, layers, vocab):
+    """Shape-faithful DeepSeek-R1-Distill-Qwen-32B (h 5120, 40/8 heads = G 5, qkv bias, I 27648) and
+    Llama-3.1-70B (h 8192, 64/8 heads = G 8, I 28672) layers, truncated in depth and vocabulary so that the
+    CPU oracle finishes in seconds: decode rows and a prefill chunk against the oracle run live."""
+    cfg = O.truncated(O.CONFIGS[name], layers, vocab=vocab)
+    w = O.make_weights(cfg, seed=11, norm_jitter=0.05)
+    r = make_runner(cfg, w, max_tokens=32, max_model_len=256, n_blocks=4)
+    ids = O.make_prompt(cfg, 0, 12)
+    om = O.OracleModel(cfg, w, capacity=32)
+    want = om.forward(om.new_seq(), ids).float()
+    assert_logits_close(teacher_forced_logits(r, ids, chunk=1), want, softmax_tol=2e-3)
+    assert_logits_close(teacher_forced_logits(r, ids, chunk=12), want, softmax_tol=2e-3)
+    r.close()
+
+
 def test_step_argument_validation():
     cfg = O.CONFIGS["tiny"]
     r = make_runner(cfg, O.make_weights(cfg), max_tokens=8)
