@@ -1,0 +1,63 @@
+"""CPU: the deploy/ files against the reference chart (skipped where /root/reference is absent, e.g. on
+the GPU box): b200-values.yaml keeps the schema of xeon-values.yaml, and the server's CLI accepts every
+argument any of the reference's values files can put on the command line."""
+import os
+
+import pytest
+import yaml
+
+from conftest import ROOT, pkg
+
+REF = "/root/reference/core/helm-charts/vllm"
+needs_ref = pytest.mark.skipif(not os.path.isdir(REF), reason="reference checkout not present")
+
+
+def load(path):
+    with open(path) as f:
+        return yaml.safe_load(f)
+
+
+@needs_ref
+def test_b200_values_keep_the_reference_schema():
+    ours = load(os.path.join(ROOT, "deploy", "helm-charts", "vllm", "b200-values.yaml"))
+    ref = load(os.path.join(REF, "xeon-values.yaml"))
+    for key in ("accelDevice", "image", "modelConfigs", "defaultModelConfigs", "LLM_MODEL_ID"):
+        assert key in ours, key
+    assert set(ours["image"]) >= {"repository", "tag", "pullPolicy"}
+    ref_model = next(iter(ref["modelConfigs"].values()))
+    for name, mc in ours["modelConfigs"].items():
+        assert set(mc) <= set(ref_model), f"{name}: keys outside the reference schema: {set(mc) - set(ref_model)}"
+        assert {"extraCmdArgs", "tensor_parallel_size"} <= set(mc)
+    assert set(ours["defaultModelConfigs"]) <= set(ref["defaultModelConfigs"])
+    assert "meta-llama/Llama-3.1-8B-Instruct" in ours["modelConfigs"]      # the reference's default CPU model
+
+
+@needs_ref
+@pytest.mark.parametrize("values", ["xeon-values.yaml", "gaudi-values.yaml", "gaudi3-values.yaml"])
+def test_every_reference_cmd_arg_is_accepted(values):
+    S = pkg("server")
+    ref = load(os.path.join(REF, values))
+    arg_lists = [mc.get("extraCmdArgs") or [] for mc in (ref.get("modelConfigs") or {}).values()]
+    arg_lists.append((ref.get("defaultModelConfigs") or {}).get("extraCmdArgs") or [])
+    seen = 0
+    for argv in arg_lists:
+        argv = [str(a) for a in argv]
+        args, unknown = S.make_arg_parser().parse_known_args(argv + ["--model", "m", "--port", "2080"])
+        # flags this backend has no use for may be unknown, but they must be ignorable (never an error),
+        # and the ones that shape the decode path must be understood
+        assert args.block_size == 128 or "--block-size" not in argv
+        for must in ("--block-size", "--dtype", "--max-model-len", "--max-num-seqs", "--max-num-batched-tokens"):
+            assert must not in unknown
+        seen += 1
+    assert seen >= 2
+
+
+def test_our_values_args_parse_and_validate():
+    S = pkg("server")
+    ours = load(os.path.join(ROOT, "deploy", "helm-charts", "vllm", "b200-values.yaml"))
+    for name, mc in ours["modelConfigs"].items():
+        argv = [str(a) for a in mc["extraCmdArgs"]] + ["--tensor-parallel-size", str(mc["tensor_parallel_size"]),
+                                                       "--model", name, "--served-model-name", name, "--port", "2080"]
+        args, unknown = S.make_arg_parser().parse_known_args(argv)
+        assert unknown == []
+        S.validate_args(args)
