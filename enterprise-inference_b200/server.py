@@ -176,7 +176,7 @@ class ChatCompletionRequest(_Sampling):
     messages: List[Dict[str, Any]] = Field(min_length=1)
     top_logprobs: Optional[int] = None
     tools: Optional[List[Dict[str, Any]]] = None
-    tool_choice: Optional[Union[str, Dict[str, Any]]] = "none"
+    tool_choice: Optional[Union[str, Dict[str, Any]]] = "auto"
     add_generation_prompt: Optional[bool] = True
     documents: Optional[List[Dict[str, str]]] = None
     chat_template: Optional[str] = None
@@ -296,7 +296,7 @@ class EngineLoop:
 # ------------------------------------------------------------------------------------------------
 # app
 # ------------------------------------------------------------------------------------------------
-def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_len: int) -> FastAPI:
+def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_len: int, tool_parser=None) -> FastAPI:
     metrics = Metrics(served_model_name)
     loop_ = EngineLoop(engine, metrics)
 
@@ -451,8 +451,13 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
             else:
                 return error(500, val, "InternalServerError")
         if chat:
-            choice = {"index": 0, "message": {"role": "assistant", "content": text, "tool_calls": []}, "logprobs": None,
-                      "finish_reason": finish, "stop_reason": None}
+            content, tool_calls = text, []
+            if tool_parser is not None and getattr(body, "tools", None) and body.tool_choice != "none":
+                content, tool_calls = tool_parser(text, body.tools)
+                if tool_calls:
+                    finish = "tool_calls"
+            choice = {"index": 0, "message": {"role": "assistant", "content": content, "tool_calls": tool_calls},
+                      "logprobs": None, "finish_reason": finish, "stop_reason": None}
         else:
             choice = {"index": 0, "text": (prompt_text + text) if body.echo else text, "logprobs": None,
                       "finish_reason": finish, "stop_reason": None}
@@ -561,7 +566,9 @@ def main(argv=None):
     validate_args(args)
     import uvicorn
     engine, tok, workers = build_engine(args)
-    app = create_app(engine, tok, args.served_model_name or args.model, args.max_model_len)
+    from .tool_parsers import get_parser
+    parser = get_parser(args.tool_call_parser) if args.enable_auto_tool_choice else None
+    app = create_app(engine, tok, args.served_model_name or args.model, args.max_model_len, tool_parser=parser)
     signal.signal(signal.SIGTERM, lambda *_: (_ for _ in ()).throw(KeyboardInterrupt()))
     try:
         uvicorn.run(app, host=args.host, port=args.port, log_level="warning" if args.disable_log_requests else "info")

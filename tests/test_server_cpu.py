@@ -151,3 +151,46 @@ def test_health_goes_red_when_the_engine_dies(client):
     r = client.post("/v1/completions", json={"model": MODEL, "prompt": "x", "max_tokens": 2})
     assert r.status_code == 500
     assert client.get("/health").status_code == 503
+
+
+def test_tool_call_parsers():
+    T = pkg("tool_parsers")
+    tools = [{"type": "function", "function": {"name": "get_weather", "parameters": {}}}]
+    c, calls = T.parse_llama3_json('{"name": "get_weather", "parameters": {"city": "Paris"}}', tools)
+    assert c is None and calls[0]["function"]["name"] == "get_weather" and json.loads(calls[0]["function"]["arguments"]) == {"city": "Paris"}
+    c, calls = T.parse_llama3_json('<|python_tag|>{"name": "get_weather", "parameters": {}}; {"name": "get_weather", "arguments": {"city": "Rome"}}', tools)
+    assert len(calls) == 2
+    assert T.parse_llama3_json("The weather is nice.", tools) == ("The weather is nice.", [])
+    assert T.parse_llama3_json('{"name": "unknown_fn", "parameters": {}}', tools)[1] == []
+    c, calls = T.parse_hermes('Let me check.\n<tool_call>\n{"name": "get_weather", "arguments": {"city": "Oslo"}}\n</tool_call>', tools)
+    assert c == "Let me check." and calls[0]["type"] == "function" and calls[0]["id"].startswith("chatcmpl-tool-")
+    assert T.parse_hermes("<tool_call>not json</tool_call>", tools) == ("<tool_call>not json</tool_call>", [])
+    assert T.get_parser(None) is None and T.get_parser("hermes") is T.parse_hermes
+    with pytest.raises(SystemExit):
+        T.get_parser("mistral")
+
+
+def test_chat_tool_calls_through_the_server():
+    """With --enable-auto-tool-choice the parser turns a JSON assistant turn into tool_calls."""
+    class Scripted(FakeRunner):
+        script = list(b'{"name": "get_weather", "parameters": {"city": "Paris"}}')
+
+        def step(self, b):
+            out = super().step(b)
+            for j, r in enumerate(b.logit_rows):
+                n_prompt = self.prompt_len
+                k = int(b.ctx_lens[r]) - n_prompt
+                out[j] = self.script[k] if 0 <= k < len(self.script) else 257
+            return out
+    fr = Scripted()
+    eng = E.LLMEngine(fr, max_num_batched_tokens=64, max_num_seqs=8, max_model_len=256)
+    tok = S.ByteTokenizer(512)
+    app = S.create_app(eng, tok, MODEL, 256, tool_parser=pkg("tool_parsers").parse_llama3_json)
+    msgs = [{"role": "user", "content": "Weather in Paris?"}]
+    fr.prompt_len = len(tok.encode(tok.apply_chat_template(msgs), add_special_tokens=False))
+    tools = [{"type": "function", "function": {"name": "get_weather", "parameters": {"type": "object"}}}]
+    with TestClient(app) as c:
+        r = c.post("/v1/chat/completions", json={"model": MODEL, "messages": msgs, "tools": tools, "max_tokens": 80}).json()
+    ch = r["choices"][0]
+    assert ch["finish_reason"] == "tool_calls" and ch["message"]["content"] is None
+    assert ch["message"]["tool_calls"][0]["function"]["name"] == "get_weather"
