@@ -75,6 +75,10 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
       : "memory");
 }
+// TMA prefetch of one tile into L2 (no shared-memory destination, no completion to wait for)
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
@@ -127,6 +131,7 @@ struct TcParams {
   float* partials;      // [splits][tok_tiles*N][n_out_pad] fp32
   unsigned int* tickets;  // [m_tiles * tok_tiles], zero on entry, zero on exit
   int n_out_pad;
+  int l2_ahead; // weight tiles (16 KiB each) a CTA prefetches into L2 before griddepcontrol.wait
   int cluster;  // 1: the `splits` CTAs of a slab form a thread-block cluster and reduce through DSMEM
   // next weights to pull into L2 while this kernel (and the small kernels after it) run
   const char* pf_ptr;
@@ -282,6 +287,10 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         tma_load_2d(smem + i * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[i], kEvictFirst);
       }
       tc_trace(p, 1);   // W of the first stages requested
+      // While the previous kernel drains (its epilogue, then the small kernels that produce x), HBM would
+      // idle: pull this CTA's NEXT weight tiles into L2 now, so that the loads issued after the wait hit L2.
+      for (int i = pre; i < min(nkb, pre + p.l2_ahead); ++i)
+        tma_prefetch_2d(&map_w, (kb0 + i) * kBlockK, m_tile * kBlockM);
       pdl_wait();
       tc_trace(p, 2);   // previous kernel complete
       pdl_launch_dependents();
@@ -668,6 +677,8 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
   const int mode = ex ? ex->mode : 0;
   TcParams p = {};
   p.cluster = use_cluster ? 1 : 0;
+  static const int l2_ahead_env = getenv("B200_TC_L2_AHEAD") ? atoi(getenv("B200_TC_L2_AHEAD")) : 0;   // measured: every depth > 0 is slower (the predecessor is still streaming)
+  p.l2_ahead = launch_opts().pdl ? l2_ahead_env : 0;   // only useful when this kernel starts before its predecessor ends
   p.trace = trace_buffer();
   if (mode == kSiluMul) {
     B200_REQUIRE(n_out % kBlockM == 0, B200_ERR_UNSUPPORTED, "linear_tc(silu_mul): n_out=%d must be a multiple of 128", n_out);
