@@ -58,6 +58,8 @@ SIGNATURES = {
     "b200_paged_attn_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
     "b200_paged_attn_decode": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i64, _i32, _i32, _i32,
                                          _i32, _i32, _f32, _vp, _i64, _vp]),
+    "b200_paged_attn_prefill": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i64, _i32, _i32, _i32,
+                                          _i32, _i32, _f32, _vp, _i64, _vp]),
     "b200_paged_attn_static_scratch_bytes": (_i64, []),
     "b200_paged_attn_decode_static": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i64, _i32, _i32, _i32,
                                                 _i32, _i32, _f32, _vp]),

@@ -561,6 +561,17 @@ extern "C" int b200_paged_attn_decode(const void* q, int64_t ldq, const void* kc
                     ws, ws_bytes, (cudaStream_t)stream);
 }
 
+extern "C" int b200_paged_attn_prefill(const void* q, int64_t ldq, const void* kc, const void* vc,
+                                       const int32_t* block_table, int32_t bt_stride, const int32_t* row_to_seq,
+                                       const int32_t* ctx_lens, void* out, int64_t ldo, int32_t T, int32_t hq,
+                                       int32_t hkv, int32_t block_size, int32_t max_ctx, float scale, void* ws,
+                                       int64_t ws_bytes, void* stream) {
+  B200_REQUIRE(q && kc && vc && block_table && ctx_lens && out, B200_ERR_INVALID, "paged_attn_prefill: null");
+  return paged_attn_ex((const __nv_bfloat16*)q, ldq, (const __nv_bfloat16*)kc, (const __nv_bfloat16*)vc, block_table,
+                       bt_stride, row_to_seq, ctx_lens, (__nv_bfloat16*)out, ldo, T, hq, hkv, block_size, max_ctx, scale,
+                       ws, ws_bytes, 1, (cudaStream_t)stream);
+}
+
 extern "C" int b200_silu_mul(const void* gu, void* out, int32_t T, int32_t inter, void* stream) {
   B200_REQUIRE(gu && out, B200_ERR_INVALID, "silu_mul: null");
   return silu_mul((const __nv_bfloat16*)gu, (__nv_bfloat16*)out, T, inter, (cudaStream_t)stream);
@@ -616,6 +627,7 @@ struct StepArgs {
   int bt_stride, T, max_ctx, R;
   int32_t* out_tokens;
   void* out_logits;
+  int n_seqs = 0;   // sequences in the step when the caller knows it (host-buffer entry), else 0
 };
 
 static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
@@ -642,6 +654,9 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   const int qn = c->qkv_w, on = h, ok = c->hq * kHeadDim, gn = 2 * c->inter, dn = h, dk = c->inter;
   // timing experiments only (results are wrong): B200_DEBUG_SKIP bit 0 = skip the per-layer norms, bit 1 = skip attention
   static const int dbg_skip = getenv("B200_DEBUG_SKIP") ? atoi(getenv("B200_DEBUG_SKIP")) : 0;
+  // Prefill-heavy steps (many more rows than sequences) pack consecutive rows of a sequence into one pass
+  // over its K/V; decode steps keep one row per work item.
+  const int attn_pack = a.row_to_seq && (a.n_seqs > 0 ? (T >= 4 * a.n_seqs && T >= 32) : T >= 512);
   STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
   for (int l = 0; l < m.n_layers; ++l) {
     const LayerW& L = c->layers[l];
@@ -672,8 +687,9 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
         STEP(rope_kv_append(c->qkv_buf, a.positions, a.slots, c->cos_sin, kcl, vcl, T, c->hq, c->hkv, m.block_size, s));
     }
     if (!(dbg_skip & 2))
-    STEP(paged_attn(c->qkv_buf, c->qkv_w, kcl, vcl, a.block_table, a.bt_stride, a.row_to_seq, a.ctx_lens, c->attn_out,
-                    c->hq * kHeadDim, T, c->hq, c->hkv, m.block_size, a.max_ctx, scale, c->attn_ws, c->attn_ws_bytes, s));
+    STEP(paged_attn_ex(c->qkv_buf, c->qkv_w, kcl, vcl, a.block_table, a.bt_stride, a.row_to_seq, a.ctx_lens, c->attn_out,
+                       c->hq * kHeadDim, T, c->hq, c->hkv, m.block_size, a.max_ctx, scale, c->attn_ws, c->attn_ws_bytes,
+                       attn_pack, s));
     {  // O
       LinearExtra ex;
       if (tc_path(T, on, ok, c->gemv_max_t)) pf(ex, L.gu, (int64_t)gn * h);
@@ -788,7 +804,7 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
                             (uint64_t)a.block_table, (uint64_t)a.row_to_seq, (uint64_t)a.ctx_lens,
                             (uint64_t)a.logit_rows,  (uint64_t)a.out_tokens, (uint64_t)a.out_logits,
                             (uint64_t)a.bt_stride,   (uint64_t)a.T,          (uint64_t)pow2_bucket(a.max_ctx),
-                            (uint64_t)a.R,           (uint64_t)launch_opts().pdl};
+                            (uint64_t)a.R,           (uint64_t)launch_opts().pdl, (uint64_t)a.n_seqs};
   for (uint64_t p : parts) hsh = mix(hsh, p);
   GraphKey key{hsh};
   auto it = c->graph_cache.find(key);
@@ -853,6 +869,7 @@ extern "C" int b200_decode_step_host(b200_ctx* c, const int32_t* host_packed, in
   B200_CUDA(cudaMemcpyAsync(d, host_packed, (size_t)n_ints * 4, cudaMemcpyHostToDevice, s));
   StepArgs a{d, d + T, d + 2 * T, d + 5 * T + n_logit_rows, d + 4 * T, d + 3 * T, d + 5 * T, bt_stride, n_tokens,
              max_ctx_len, n_logit_rows, c->d_tokens, nullptr};
+  a.n_seqs = n_seqs;
   int rc = run_step(c, a, s);
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(host_out_token_ids, c->d_tokens, (size_t)n_logit_rows * 4, cudaMemcpyDeviceToHost, s));

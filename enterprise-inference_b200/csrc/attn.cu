@@ -311,7 +311,8 @@ bool paged_attn_tc_supported(int hq, int hkv, int block_size);
 int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
-                  void* ws, int64_t ws_bytes, cudaStream_t s);
+                  void* ws, int64_t ws_bytes, int pack, cudaStream_t s);
+int attn_tc_pack_rows(int G);
 
 // 128-token tiles, persistent CTAs (one per SM) that take work items round-robin in split-major
 // order.  Rows are cut into chunks of C tiles so that there are several items per CTA (about 8 per
@@ -356,8 +357,11 @@ int64_t paged_attn_workspace_bytes(int T, int hq, int max_ctx, int block_size) {
   // upper bound over every hkv >= 1 and both kernels' split plans
   int ns, tps, ns2;
   split_plan(T, 1, max_ctx, &ns, &tps);
-  attn_split_plan_tc(T, 1, max_ctx, &ns2, &tps);
-  return (int64_t)T * hq * max(ns, ns2) * (kHeadDim + 2) * sizeof(float) + 256;
+  for (int r = 1; r <= 4; ++r) {   // row-at-a-time and every packed group size
+    attn_split_plan_tc((T + r - 1) / r, 1, max_ctx, &ns2, &tps);
+    ns = max(ns, ns2);
+  }
+  return (int64_t)T * hq * ns * (kHeadDim + 2) * sizeof(float) + 256;
 }
 
 static int paged_attn_cc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
@@ -407,13 +411,27 @@ static int paged_attn_cc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat1
 
 
 
+// pack != 0: consecutive query rows of one sequence (a prefill chunk) share one pass over the K/V cache
+int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+                  const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                  __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
+                  void* ws, int64_t ws_bytes, int pack, cudaStream_t s);
+
 int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
                void* ws, int64_t ws_bytes, cudaStream_t s) {
+  return paged_attn_ex(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv, block_size,
+                       max_ctx, scale, ws, ws_bytes, 0, s);
+}
+
+int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+                  const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                  __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
+                  void* ws, int64_t ws_bytes, int pack, cudaStream_t s) {
   if (use_tc_attn(hq, hkv, block_size))
     return paged_attn_tc(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv, block_size,
-                         max_ctx, scale, ws, ws_bytes, s);
+                         max_ctx, scale, ws, ws_bytes, pack, s);
   return paged_attn_cc(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv, block_size,
                        max_ctx, scale, ws, ws_bytes, s);
 }

@@ -137,7 +137,7 @@ struct Smem {
   // followed by the barriers and small exchange areas (see carve-up in the kernel)
 };
 
-template <int G>
+template <int G, int R>
 __global__ void __launch_bounds__(kThreads, 1)
 paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
                      const __nv_bfloat16* __restrict__ q, int64_t ldq, const int32_t* __restrict__ block_table,
@@ -159,9 +159,11 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   uint64_t* p_ready = s_full + 2;            // [2]
   uint64_t* o_full = p_ready + 2;            // [2] one per O buffer
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 6);   // o_full[2..3] q_ready[2], o_full[4..5] q_free[2]
-  float* xmax = reinterpret_cast<float*>(tmem_slot + 2);   // [4 warps][8 heads]
-  float* xsum = xmax + 32;                                  // [4 warps][8 heads]
+  float* xmax = reinterpret_cast<float*>(tmem_slot + 2);   // [4 warps][16 columns]
+  float* xsum = xmax + 64;                                  // [4 warps][16 columns]
 
+  constexpr int NC = G * R;   // live columns of the N = 16 MMA
+  static_assert(NC <= kNPad, "row group does not fit the MMA N");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int hq = hkv * G;
   uint64_t* q_ready = o_full + 2;   // [2], 32 arrivals: Q of work item j is staged in qs[j & 1]
@@ -199,32 +201,66 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   pdl_launch_dependents();
   if (threadIdx.x == 64) attn_trace(1);
 
-  // Persistent CTA: work items (row t, kv head, split) are taken round-robin; the K/V ring, the S/P
+  // Persistent CTA: work items (row group, kv head, split) are taken round-robin; the K/V ring, the S/P
   // double buffers and all barrier phases run on ONE tile counter across items, so the TMA producer
   // streams the next item's tiles while the softmax threads finish the current one.
-  const int n_items = n_splits * hkv * n_rows;
+  //
+  // A row group is R consecutive query rows: their R*G (<= 16) query heads fill the columns of the
+  // N = 16 MMA.  When the R rows belong to ONE sequence (a prefill chunk) the group is one pass over that
+  // sequence's K/V with a per-column causal mask (1/R of the cache traffic of row-at-a-time); otherwise
+  // (decode rows of different sequences, a chunk boundary) it degrades to R single-row passes ("runs").
+  const int n_groups = (n_rows + R - 1) / R;
+  const int n_items = n_splits * hkv * n_groups;
   struct Item {
-    int t, kvh, split, ctx, tile_begin, n_tiles, blk0;
-    const int32_t* bt;
+    int r0, kvh, split, tile_begin, nrun, total_tiles;
+    int ctx[R];            // context length per row (0: row absent)
+    int run_tiles[R];      // tiles of run u inside this split
+    int run_ctx[R];        // longest context of run u
+    const int32_t* run_bt[R];
   };
   auto get_item = [&](int it) {
     Item w;   // split-major: all first chunks, then all second chunks, ... (long items first)
-    const int n_base = hkv * n_rows;
+    const int n_base = hkv * n_groups;
     w.split = it / n_base;
     w.kvh = (it % n_base) % hkv;
-    w.t = (it % n_base) / hkv;
-    w.ctx = ctx_lens[w.t];
-    const int seq = row_to_seq ? row_to_seq[w.t] : w.t;
-    const int total = (w.ctx + kTileTok - 1) / kTileTok;
+    w.r0 = ((it % n_base) / hkv) * R;
     w.tile_begin = w.split * tiles_per_split;
-    w.n_tiles = max(min(w.tile_begin + tiles_per_split, total) - w.tile_begin, 0);
-    w.bt = block_table + (int64_t)seq * bt_stride;
-    w.blk0 = w.n_tiles > 0 ? w.bt[(w.tile_begin * kTileTok) / block_size] : 0;   // first tile's block, fetched early
+    int seq[R];
+    bool same = true;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int row = w.r0 + r;
+      const bool valid = row < n_rows;
+      w.ctx[r] = valid ? ctx_lens[row] : 0;
+      seq[r] = valid ? (row_to_seq ? row_to_seq[row] : row) : -1;
+      if (valid && seq[r] != seq[0]) same = false;
+    }
+    w.nrun = same ? 1 : R;
+    w.total_tiles = 0;
+#pragma unroll
+    for (int u = 0; u < R; ++u) {
+      int cmax = 0, sq = -1;
+      if (same) {
+        if (u == 0) {
+          sq = seq[0];
+#pragma unroll
+          for (int r = 0; r < R; ++r) cmax = max(cmax, w.ctx[r]);
+        }
+      } else {
+        cmax = w.ctx[u];
+        sq = seq[u];
+      }
+      const int total = (cmax + kTileTok - 1) / kTileTok;
+      w.run_ctx[u] = cmax;
+      w.run_tiles[u] = sq < 0 ? 0 : max(min(w.tile_begin + tiles_per_split, total) - w.tile_begin, 0);
+      w.run_bt[u] = block_table + (int64_t)max(sq, 0) * bt_stride;
+      w.total_tiles += w.run_tiles[u];
+    }
     return w;
   };
-  // Every role walks the same item sequence; an item's metadata (context length, block-table row,
-  // first block id: dependent global loads, ~1 us each) is fetched one item AHEAD (`nxt`) so that an
-  // item switch never stalls the TMA stream.
+  // Every role walks the same item sequence; an item's metadata (context lengths, block-table rows:
+  // dependent global loads, ~1 us each) is fetched one item AHEAD (`nxt`) so that an item switch never
+  // stalls the TMA stream.
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -237,24 +273,29 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const Item w = nxt;
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
-        for (int i = 0; i < w.n_tiles; ++i, ++n) {
-          const int st = n % kKvStages;
-          if (n >= kKvStages) mbar_wait(&kv_free[st], ((n / kKvStages) - 1) & 1);
-          const int tok0 = (w.tile_begin + i) * kTileTok;
-          const int blk = i == 0 ? w.blk0 : w.bt[tok0 / block_size];
-          const int row0 = (blk * hkv + w.kvh) * block_size + (tok0 % block_size);
-          unsigned char* sb = kv + st * kStageBytes;
-          mbar_expect_tx(&k_full[st], 2 * kHalfBytes);
-          tma_load_2d(sb, &map_k, 0, row0, &k_full[st]);
-          tma_load_2d(sb + kHalfBytes, &map_k, 64, row0, &k_full[st]);
-          mbar_expect_tx(&v_full[st], 2 * kHalfBytes);
-          tma_load_2d(sb + 2 * kHalfBytes, &map_v, 0, row0, &v_full[st]);
-          tma_load_2d(sb + 3 * kHalfBytes, &map_v, 64, row0, &v_full[st]);
+#pragma unroll
+        for (int u = 0; u < R; ++u) {
+          if (u >= w.nrun) break;
+          for (int i = 0; i < w.run_tiles[u]; ++i, ++n) {
+            const int st = n % kKvStages;
+            if (n >= kKvStages) mbar_wait(&kv_free[st], ((n / kKvStages) - 1) & 1);
+            const int tok0 = (w.tile_begin + i) * kTileTok;
+            const int blk = w.run_bt[u][tok0 / block_size];
+            const int row0 = (blk * hkv + w.kvh) * block_size + (tok0 % block_size);
+            unsigned char* sb = kv + st * kStageBytes;
+            mbar_expect_tx(&k_full[st], 2 * kHalfBytes);
+            tma_load_2d(sb, &map_k, 0, row0, &k_full[st]);
+            tma_load_2d(sb + kHalfBytes, &map_k, 64, row0, &k_full[st]);
+            mbar_expect_tx(&v_full[st], 2 * kHalfBytes);
+            tma_load_2d(sb + 2 * kHalfBytes, &map_v, 0, row0, &v_full[st]);
+            tma_load_2d(sb + 3 * kHalfBytes, &map_v, 64, row0, &v_full[st]);
+          }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread), software pipelined: S(n+1) is issued before waiting for P(n) =====
+    // ===== MMA issuer (one thread), software pipelined: S(n+1) is issued before waiting for P(n).
+    // The tiles of an item (all its runs) form one flat sequence: Q is the same for all of them. =====
     if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc(0);
       constexpr uint32_t idesc_pv = make_idesc(1);
@@ -279,16 +320,17 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const Item w = nxt;
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
-        if (w.n_tiles == 0) continue;
+        const int nt = w.total_tiles;
+        if (nt == 0) continue;
         mbar_wait(&q_ready[active & 1], (active >> 1) & 1);   // this item's Q is in shared memory
         tc_fence_after();
         q_addr = smem_u32(qs + (active & 1) * 2 * kSmallTile);
         issue_s(n);
-        if (w.n_tiles == 1) tc_commit(&q_free[active & 1]);
-        for (int i = 0; i < w.n_tiles; ++i, ++n) {
-          if (i + 1 < w.n_tiles) {
+        if (nt == 1) tc_commit(&q_free[active & 1]);
+        for (int i = 0; i < nt; ++i, ++n) {
+          if (i + 1 < nt) {
             issue_s(n + 1);
-            if (i + 2 == w.n_tiles) tc_commit(&q_free[active & 1]);   // last S of this item issued
+            if (i + 2 == nt) tc_commit(&q_free[active & 1]);   // last S of this item issued
           }
           const int st = n % kKvStages;
           mbar_wait(&v_full[st], (n / kKvStages) & 1);
@@ -311,21 +353,23 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       }
     }
   } else if (warp == 6) {
-    // ===== Q stager: item j's G x 128 query rows -> qs[j & 1] as the swizzled K-major B operand of
-    // S^T = K . Q^T, one item ahead of the MMA warp so that item boundaries cost no bubble =====
+    // ===== Q stager: the group's R*G query heads -> qs[j & 1] as the swizzled K-major B operand of
+    // S^T = K . Q^T (column c = row c / G, head c % G), one item ahead of the MMA warp =====
     int active = 0;
     Item nxt = {};
     if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const Item w = nxt;
       if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
-      if (w.n_tiles == 0) continue;
+      if (w.total_tiles == 0) continue;
       if (active >= 2) mbar_wait(&q_free[active & 1], ((active >> 1) - 1) & 1);
       unsigned char* qb = qs + (active & 1) * 2 * kSmallTile;
-      for (int i = lane; i < G * 16; i += 32) {
-        const int g = i >> 4, ch = i & 15;   // 16-byte chunk ch of head g
-        const uint4 v = *reinterpret_cast<const uint4*>(q + (int64_t)w.t * ldq + (w.kvh * G + g) * kHeadDim + ch * 8);
-        *reinterpret_cast<uint4*>(qb + small_off(g, ch * 8)) = v;
+      for (int i = lane; i < NC * 16; i += 32) {
+        const int c = i >> 4, ch = i & 15;   // 16-byte chunk ch of column c
+        const int row = w.r0 + c / G;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (row < n_rows) v = *reinterpret_cast<const uint4*>(q + (int64_t)row * ldq + (w.kvh * G + c % G) * kHeadDim + ch * 8);
+        *reinterpret_cast<uint4*>(qb + small_off(c, ch * 8)) = v;
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       mbar_arrive(&q_ready[active & 1]);
@@ -344,105 +388,119 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       const Item w = nxt;
       if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
       if (tau == 0) attn_trace(2 + 3 * item_no);
-      float m_run[G], l_run[G], acc[G], alpha_prev[G];
+      float m_run[NC], l_run[NC], acc[NC], alpha_prev[NC];
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
-        m_run[g] = -INFINITY;
-        l_run[g] = 0.f;
-        acc[g] = 0.f;
-        alpha_prev[g] = 0.f;
+      for (int c = 0; c < NC; ++c) {
+        m_run[c] = -INFINITY;
+        l_run[c] = 0.f;
+        acc[c] = 0.f;
+        alpha_prev[c] = 1.f;
       }
-      for (int i = 0; i < w.n_tiles; ++i, ++n) {
-        const int st = n % kKvStages;
-        const int tok0 = (w.tile_begin + i) * kTileTok;
-        const int n_valid = min(kTileTok, w.ctx - tok0);
-        mbar_wait(&s_full[n & 1], (n >> 1) & 1);
-        if (i == 0 && tau == 0) attn_trace(3 + 3 * item_no);
-        tc_fence_after();
-        uint32_t r[16];
-        tmem_ld16(lane_addr + (n & 1) * 16, r);
-        float sc[G];
+      int done = 0;   // tiles of this item already handed to the MMA warp
 #pragma unroll
-        for (int g = 0; g < G; ++g) sc[g] = tau < n_valid ? __uint_as_float(r[g]) * scale : -INFINITY;
-        // tile max per head over the 128 tokens
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-          const float wm = warp_max(sc[g]);
-          if (lane == 0) xmax[wq * 8 + g] = wm;
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        float alpha[G];
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-          const float tm = fmaxf(fmaxf(xmax[g], xmax[8 + g]), fmaxf(xmax[16 + g], xmax[24 + g]));
-          const float m_new = fmaxf(m_run[g], tm);   // finite: token tok0 of an active tile is valid
-          alpha[g] = __expf(m_run[g] - m_new);       // 0 on the first tile
-          m_run[g] = m_new;
-          const float pv = __expf(sc[g] - m_new);    // 0 for masked tokens
-          l_run[g] = l_run[g] * alpha[g] + pv;
-          const float hi = round_bf16(pv);
-          const float lo = pv - hi;
-          const uint32_t off = small_off(g, tau) + (n & 1) * 2 * kSmallTile;
-          *reinterpret_cast<__nv_bfloat16*>(p_hi + off) = __float2bfloat16_rn(hi);
-          *reinterpret_cast<__nv_bfloat16*>(p_lo + off) = __float2bfloat16_rn(lo);
-        }
-        if (n_valid < kTileTok) {
-          // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor
-          // core) — wait for the tile, then zero this thread's row if it is past the end
-          mbar_wait(&v_full[st], (n / kKvStages) & 1);
-          if (tau >= n_valid) {
-            unsigned char* vb = kv + st * kStageBytes + 2 * kHalfBytes;
-#pragma unroll
-            for (int h2 = 0; h2 < 2; ++h2)
-#pragma unroll
-              for (int c = 0; c < 8; ++c)
-                *reinterpret_cast<uint4*>(vb + h2 * kHalfBytes + tau * 128 + c * 16) = make_uint4(0u, 0u, 0u, 0u);
-          }
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
-        tc_fence_before();
-        mbar_arrive(&p_ready[n & 1]);
-        // Fold the PREVIOUS tile's O_tile^T[dim = tau][head] into the running output (O is double
-        // buffered in TMEM): the P.V MMAs of this tile run while the next tile's softmax is computed.
-        if (i > 0) {
-          mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
+      for (int u = 0; u < R; ++u) {
+        if (u >= w.nrun) break;
+        for (int i = 0; i < w.run_tiles[u]; ++i, ++n, ++done) {
+          const int st = n % kKvStages;
+          const int tok0 = (w.tile_begin + i) * kTileTok;
+          const int n_valid = min(kTileTok, w.run_ctx[u] - tok0);
+          mbar_wait(&s_full[n & 1], (n >> 1) & 1);
+          if (done == 0 && tau == 0) attn_trace(3 + 3 * item_no);
           tc_fence_after();
-          tmem_ld16(lane_addr + 32 + ((n - 1) & 1) * 16, r);
+          uint32_t r[16];
+          tmem_ld16(lane_addr + (n & 1) * 16, r);
+          float sc[NC];
 #pragma unroll
-          for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha_prev[g] + __uint_as_float(r[g]);
+          for (int c = 0; c < NC; ++c) {
+            // column c = (row c / G, head c % G): live in this run, and causal: token < that row's context
+            const bool live = (w.nrun == 1 || c / G == u) && (tok0 + tau < w.ctx[c / G]);
+            sc[c] = live ? __uint_as_float(r[c]) * scale : -INFINITY;
+          }
+          // tile max per column over the 128 tokens
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            const float wm = warp_max(sc[c]);
+            if (lane == 0) xmax[wq * 16 + c] = wm;
+          }
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          float alpha[NC];
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            const float tm = fmaxf(fmaxf(xmax[c], xmax[16 + c]), fmaxf(xmax[32 + c], xmax[48 + c]));
+            const float m_new = fmaxf(m_run[c], tm);
+            // a column with nothing seen so far (other run, or causally empty tile) keeps its state
+            const bool seen = m_new > -INFINITY;
+            alpha[c] = seen ? __expf(m_run[c] - m_new) : 1.f;   // exp(-inf) = 0 on the column's first tile
+            m_run[c] = m_new;
+            const float pv = seen ? __expf(sc[c] - m_new) : 0.f;   // 0 for masked tokens
+            l_run[c] = l_run[c] * alpha[c] + pv;
+            const float hi = round_bf16(pv);
+            const float lo = pv - hi;
+            const uint32_t off = small_off(c, tau) + (n & 1) * 2 * kSmallTile;
+            *reinterpret_cast<__nv_bfloat16*>(p_hi + off) = __float2bfloat16_rn(hi);
+            *reinterpret_cast<__nv_bfloat16*>(p_lo + off) = __float2bfloat16_rn(lo);
+          }
+          if (n_valid < kTileTok) {
+            // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor
+            // core) — wait for the tile, then zero this thread's row if it is past the end
+            mbar_wait(&v_full[st], (n / kKvStages) & 1);
+            if (tau >= n_valid) {
+              unsigned char* vb = kv + st * kStageBytes + 2 * kHalfBytes;
+#pragma unroll
+              for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+                for (int cc = 0; cc < 8; ++cc)
+                  *reinterpret_cast<uint4*>(vb + h2 * kHalfBytes + tau * 128 + cc * 16) = make_uint4(0u, 0u, 0u, 0u);
+            }
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
+          tc_fence_before();
+          mbar_arrive(&p_ready[n & 1]);
+          // Fold the PREVIOUS tile's O_tile^T[dim = tau][column] into the running output (O is double
+          // buffered in TMEM): the P.V MMAs of this tile run while the next tile's softmax is computed.
+          if (done > 0) {
+            mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
+            tc_fence_after();
+            tmem_ld16(lane_addr + 32 + ((n - 1) & 1) * 16, r);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[c] = acc[c] * alpha_prev[c] + __uint_as_float(r[c]);
+          }
+#pragma unroll
+          for (int c = 0; c < NC; ++c) alpha_prev[c] = alpha[c];
+          asm volatile("bar.sync 1, 128;" ::: "memory");  // xmax is rewritten by the next tile
         }
-#pragma unroll
-        for (int g = 0; g < G; ++g) alpha_prev[g] = alpha[g];
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // xmax is rewritten by the next tile
       }
-      if (w.n_tiles > 0) {   // the last tile's O
+      if (done > 0) {   // the last tile's O
         uint32_t r[16];
         mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
         tc_fence_after();
         tmem_ld16(lane_addr + 32 + ((n - 1) & 1) * 16, r);
 #pragma unroll
-        for (int g = 0; g < G; ++g) acc[g] = acc[g] * alpha_prev[g] + __uint_as_float(r[g]);
+        for (int c = 0; c < NC; ++c) acc[c] = acc[c] * alpha_prev[c] + __uint_as_float(r[c]);
       }
-      // total l per head: sum the per-token partial sums over the 128 threads
+      // total l per column: sum the per-token partial sums over the 128 threads
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
-        const float ws = warp_sum(l_run[g]);
-        if (lane == 0) xsum[wq * 8 + g] = ws;
+      for (int c = 0; c < NC; ++c) {
+        const float ws = warp_sum(l_run[c]);
+        if (lane == 0) xsum[wq * 16 + c] = ws;
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       const int d = tau;
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
-        const float l = xsum[g] + xsum[8 + g] + xsum[16 + g] + xsum[24 + g];
-        const int head = w.kvh * G + g;
-        if (n_splits == 1) {
-          out[(int64_t)w.t * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? acc[g] / l : 0.f);
-        } else {
-          const int64_t pi = ((int64_t)w.t * hq + head) * n_splits + w.split;
-          part_o[pi * kHeadDim + d] = acc[g];
-          if (d == 0) {
-            part_ml[pi * 2] = m_run[g];
-            part_ml[pi * 2 + 1] = l;
+      for (int c = 0; c < NC; ++c) {
+        const int row = w.r0 + c / G;
+        if (row < n_rows) {
+          const float l = xsum[c] + xsum[16 + c] + xsum[32 + c] + xsum[48 + c];
+          const int head = w.kvh * G + c % G;
+          if (n_splits == 1) {
+            out[(int64_t)row * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? acc[c] / l : 0.f);
+          } else {
+            const int64_t pi = ((int64_t)row * hq + head) * n_splits + w.split;
+            part_o[pi * kHeadDim + d] = acc[c];
+            if (d == 0) {
+              part_ml[pi * 2] = m_run[c];
+              part_ml[pi * 2 + 1] = l;
+            }
           }
         }
       }
@@ -460,21 +518,21 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
 
 constexpr int kAttnTcSmem = kKvStages * kStageBytes + (4 + 8) * kSmallTile + 512 + 1024;
 
-template <int G>
+template <int G, int R>
 int launch_attn_tc(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
                    const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                    __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
                    float* part_o, float* part_ml, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnTcSmem));
+    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnTcSmem));
     attr_set = true;
   }
   static const int trace_on = getenv("B200_ATTN_TRACE") ? atoi(getenv("B200_ATTN_TRACE")) : 0;
   if (trace_on) cudaMemcpyToSymbol(g_attn_trace_on, &trace_on, sizeof(int));
-  const int64_t items = (int64_t)n_splits * hkv * T;
+  const int64_t items = (int64_t)n_splits * hkv * ((T + R - 1) / R);
   const int grid = (int)(items < kNumSMs ? items : kNumSMs);   // persistent: one CTA per SM, items round-robin
-  B200_CUDA(launch(paged_attn_tc_kernel<G>, dim3(grid), dim3(kThreads), (size_t)kAttnTcSmem, s, mk, mv, q, ldq,
+  B200_CUDA(launch(paged_attn_tc_kernel<G, R>, dim3(grid), dim3(kThreads), (size_t)kAttnTcSmem, s, mk, mv, q, ldq,
                    block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, T, scale,
                    part_o, part_ml));
   return B200_OK;
@@ -493,15 +551,20 @@ bool paged_attn_tc_supported(int hq, int hkv, int block_size) {
   return block_size % kTileTok == 0 && (G == 1 || G == 2 || G == 4 || G == 5 || G == 8);
 }
 
+// rows per group when packing query rows of one sequence into the 16 MMA columns
+int attn_tc_pack_rows(int G) { return G <= 4 ? 4 : (G == 5 ? 3 : 2); }
+
 int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
-                  void* ws, int64_t ws_bytes, cudaStream_t s) {
+                  void* ws, int64_t ws_bytes, int pack, cudaStream_t s) {
   B200_REQUIRE(paged_attn_tc_supported(hq, hkv, block_size), B200_ERR_UNSUPPORTED, "attn_tc: unsupported shape");
   B200_REQUIRE(ldq % 8 == 0, B200_ERR_INVALID, "attn_tc: ldq must be a multiple of 8");
   if (T == 0) return B200_OK;
+  const int G = hq / hkv;
+  const int R = pack ? attn_tc_pack_rows(G) : 1;
   int n_splits, tps;
-  attn_split_plan_tc(T, hkv, max_ctx, &n_splits, &tps);
+  attn_split_plan_tc((T + R - 1) / R, hkv, max_ctx, &n_splits, &tps);
   float* part_o = nullptr;
   float* part_ml = nullptr;
   if (n_splits > 1) {
@@ -519,19 +582,27 @@ int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
   if (rc) return rc;
   rc = get_tensor_map_2d(vc, rows, kHeadDim, kHeadDim, kTileTok, &mv);
   if (rc) return rc;
-  const int G = hq / hkv;
-#define B200_ATTN_TC_CASE(g)                                                                                        \
-  case g:                                                                                                           \
-    rc = launch_attn_tc<g>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv, block_size, \
-                           n_splits, tps, scale, part_o, part_ml, s);                                               \
-    break;
-  switch (G) {
-    B200_ATTN_TC_CASE(1)
-    B200_ATTN_TC_CASE(2)
-    B200_ATTN_TC_CASE(4)
-    B200_ATTN_TC_CASE(5)
-    B200_ATTN_TC_CASE(8)
-    default: rc = B200_ERR_UNSUPPORTED;
+#define B200_ATTN_TC_CASE(g, r)                                                                                        \
+  rc = launch_attn_tc<g, r>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv, block_size, \
+                            n_splits, tps, scale, part_o, part_ml, s)
+  if (!pack) {
+    switch (G) {
+      case 1: B200_ATTN_TC_CASE(1, 1); break;
+      case 2: B200_ATTN_TC_CASE(2, 1); break;
+      case 4: B200_ATTN_TC_CASE(4, 1); break;
+      case 5: B200_ATTN_TC_CASE(5, 1); break;
+      case 8: B200_ATTN_TC_CASE(8, 1); break;
+      default: rc = B200_ERR_UNSUPPORTED;
+    }
+  } else {
+    switch (G) {
+      case 1: B200_ATTN_TC_CASE(1, 4); break;
+      case 2: B200_ATTN_TC_CASE(2, 4); break;
+      case 4: B200_ATTN_TC_CASE(4, 4); break;
+      case 5: B200_ATTN_TC_CASE(5, 3); break;
+      case 8: B200_ATTN_TC_CASE(8, 2); break;
+      default: rc = B200_ERR_UNSUPPORTED;
+    }
   }
 #undef B200_ATTN_TC_CASE
   if (rc) return rc;

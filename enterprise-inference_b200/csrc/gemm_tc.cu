@@ -40,10 +40,13 @@ constexpr int kCounterBytes = 64 * 1024;  // slab tickets at the head of the wor
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
 
+#ifndef B200_STAGES16
+#define B200_STAGES16 5
+#endif
 #ifndef B200_STAGES64
 #define B200_STAGES64 4
 #endif
-__host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? 5 : (N <= 32 ? 4 : (N <= 64 ? B200_STAGES64 : (N <= 128 ? 3 : 4))); }
+__host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? B200_STAGES16 : (N <= 32 ? 4 : (N <= 64 ? B200_STAGES64 : (N <= 128 ? 3 : 4))); }
 __host__ __device__ constexpr int stage_bytes(int N) { return kBlockM * kBlockK * 2 + N * kBlockK * 2; }
 __host__ __device__ constexpr int smem_bytes_for(int N) { return stages_for(N) * stage_bytes(N) + 1024 + 256; }
 

@@ -209,6 +209,18 @@ B200_API int b200_paged_attn_decode(const void* q, int64_t ldq, const void* k_ca
                            int32_t block_size, int32_t max_ctx_len, float scale, void* workspace,
                            int64_t workspace_bytes, void* stream);
 
+/* (a6, prefill rows) Same contract and results as b200_paged_attn_decode, for steps dominated by the rows of
+ * a prefill chunk: up to 4 consecutive rows that belong to one sequence (row_to_seq) share ONE pass over that
+ * sequence's K/V cache with a per-row causal mask (their query heads fill the 16 MMA columns); rows of
+ * different sequences inside a group fall back to one pass each.  Chunked prefill in the reference:
+ * xeon-values.yaml:80-83 (--enable_chunked_prefill, --max-num-batched-tokens 2048). */
+B200_API int b200_paged_attn_prefill(const void* q, int64_t ldq, const void* k_cache_layer,
+                            const void* v_cache_layer, const int32_t* block_table, int32_t bt_stride,
+                            const int32_t* row_to_seq, const int32_t* ctx_lens, void* out, int64_t ldo,
+                            int32_t n_tokens, int32_t n_q_heads, int32_t n_kv_heads, int32_t block_size,
+                            int32_t max_ctx_len, float scale, void* workspace, int64_t workspace_bytes,
+                            void* stream);
+
 /* No counterpart in the reference: a variant of b200_paged_attn_decode for callers that cannot
  * allocate device memory after start-up (engines with a fixed memory plan, bindings that cannot call
  * cudaMalloc).  Same inputs, outputs and results, but the split-KV partials live in a 2 MiB array

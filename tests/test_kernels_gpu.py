@@ -327,6 +327,51 @@ def test_paged_attention_vs_oracle(lib, abi, hq, hkv, ctx_lens, bs):
     ulp_close(got, want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
 
 
+@pytest.mark.parametrize("hq,hkv", [(4, 1), (5, 1), (16, 2), (8, 8), (2, 1)])
+def test_paged_attention_prefill_rows_packed(lib, abi, hq, hkv):
+    """b200_paged_attn_prefill: rows of one sequence share a pass over its cache with a per-row causal mask.
+    Mixed step: 3 decode rows of different sequences, a 37-row prefill chunk of sequence 3 starting at
+    position 200 (so groups straddle the decode/prefill boundary and the chunk's ragged end), then one more
+    decode row.  Checked against the oracle row by row and against the row-at-a-time kernel."""
+    g = torch.Generator().manual_seed(hq + 31 * hkv)
+    bs = 128
+    seq_ctx = [150, 1, 300, 237, 64]                    # tokens cached per sequence after this step
+    rows = [(0, 150), (1, 1), (2, 300)] + [(3, 200 + i + 1) for i in range(37)] + [(4, 64)]   # (seq, ctx_len)
+    T = len(rows)
+    K = [torch.randn(n, hkv, 128, generator=g).to(BF) for n in seq_ctx]
+    V = [torch.randn(n, hkv, 128, generator=g).to(BF) for n in seq_ctx]
+    nblk = [(n + bs - 1) // bs for n in seq_ctx]
+    total = sum(nblk) + 2
+    perm = iter(torch.randperm(total, generator=g).tolist())
+    kc = torch.full((total, hkv, bs, 128), float("nan"), dtype=BF)
+    vc = torch.full_like(kc, float("nan"))
+    bt = torch.zeros(len(seq_ctx), max(nblk), dtype=torch.int32)
+    for sq, n in enumerate(seq_ctx):
+        for j in range(nblk[sq]):
+            b = next(perm)
+            bt[sq, j] = b
+            m = min(bs, n - j * bs)
+            kc[b, :, :m] = K[sq][j * bs:j * bs + m].permute(1, 0, 2)
+            vc[b, :, :m] = V[sq][j * bs:j * bs + m].permute(1, 0, 2)
+    q = torch.randn(T, hq, 128, generator=g).to(BF)
+    r2s = torch.tensor([r[0] for r in rows], dtype=torch.int32)
+    cl = torch.tensor([r[1] for r in rows], dtype=torch.int32)
+    max_ctx = int(cl.max())
+    wsb = lib.b200_paged_attn_workspace_bytes(T, hq, max_ctx, bs)
+    ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
+    qd, kcd, vcd, btd, r2sd, cld = dev(q.reshape(T, hq * 128)), dev(kc), dev(vc), dev(bt), dev(r2s), dev(cl)
+    outs = []
+    for fn in (lib.b200_paged_attn_prefill, lib.b200_paged_attn_decode):
+        out = torch.full((T, hq * 128), float("nan"), dtype=BF, device="cuda")
+        sync_check(abi, fn(qd.data_ptr(), hq * 128, kcd.data_ptr(), vcd.data_ptr(), btd.data_ptr(), bt.shape[1], r2sd.data_ptr(),
+                           cld.data_ptr(), out.data_ptr(), hq * 128, T, hq, hkv, bs, max_ctx, 128 ** -0.5, ws.data_ptr(), wsb, None))
+        outs.append(out.cpu().view(T, hq, 128))
+    want = torch.stack([O.attend(q[t], K[sq], V[sq], n, 128 ** -0.5) for t, (sq, n) in enumerate(rows)])
+    assert torch.isfinite(outs[0].float()).all()
+    ulp_close(outs[0], want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
+    ulp_close(outs[0], outs[1], max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
+
+
 def test_paged_attention_split_invariance_long_context(lib, abi):
     """Config-3 scale (ctx 32768, G=4): the split-KV result must not depend on the split plan —
     compare the plan for max_ctx=32768 with a larger hint (different split count) and the oracle."""
