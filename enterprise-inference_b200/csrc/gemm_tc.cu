@@ -150,6 +150,11 @@ struct TcParams {
 };
 
 __device__ __forceinline__ void tc_trace(const TcParams& p, int slot) {
+#ifndef B200_TRACE_BUILD
+  (void)p;
+  (void)slot;
+  return;
+#endif
   if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
