@@ -31,6 +31,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 PKG = "enterprise-inference_b200"
 
+OUT_LEN = {"llama8b-bs64": 256, "llama8b-bs1": 128, "llama8b-ctx32k": 64, "llama70b-tp": 256, "llama70b-tp-bs1": 128,
+           "qwen32b-tp": 256, "tiny": 16}   # generated tokens per request: a finished request is replaced by a new one
+
 WORKLOADS = {
     # name: (model, batch, ctx_start, description)
     "llama8b-bs64": ("llama-3.1-8b", 64, 512,
@@ -232,8 +235,8 @@ def run_b200(args):
     tp = "-tp" in args.workload
     cfg = Cfg.get_config(model)
     K, W = args.steps, args.warmup
-    total_steps = 2 * (K + W) + 8
-    max_len = ctx0 + total_steps + 1
+    out_len = OUT_LEN[args.workload]
+    max_len = ctx0 + out_len + 2          # bounded for any --steps: requests are recycled after out_len tokens
     bs = 128
     blocks_per_seq = (max_len + bs - 1) // bs
     n_blocks = B * blocks_per_seq + 2
@@ -269,9 +272,19 @@ def run_b200(args):
     out = torch.empty(B, dtype=torch.int32, device="cuda")
     stream = r.stream
     step_no = [0]
+    init = [t.clone() for t in (pos, slots, ctxl)]
+    ctx_sum = [0.0, 0]
 
     def dev_step():
-        max_ctx = ctx0 + step_no[0] + 1
+        k = step_no[0] % out_len
+        if k == 0 and step_no[0] > 0:
+            # every request has produced out_len tokens: the batch is replaced by new requests whose prompt
+            # KV is (the same synthetic) cache content — positions/slots/context restart, the model does not
+            for dst, src in zip((pos, slots, ctxl), init):
+                dst.copy_(src)
+        max_ctx = ctx0 + k + 1
+        ctx_sum[0] += max_ctx
+        ctx_sum[1] += 1
         r.step_device(ids, pos, slots, bt, ctxl, max_ctx, out_tokens=out, stream=stream)
         abi.check(lib.b200_advance_decode_rows(ids.data_ptr(), pos.data_ptr(), slots.data_ptr(), ctxl.data_ptr(),
                                                bt.data_ptr(), blocks_per_seq, None, out.data_ptr(), B, bs,
@@ -282,6 +295,7 @@ def run_b200(args):
         for _ in range(W):
             dev_step()
     barrier()
+    ctx_sum[0], ctx_sum[1] = 0.0, 0
     sampler = ClockSampler(local)
     sampler.start()
     time.sleep(0.25)
@@ -300,7 +314,7 @@ def run_b200(args):
     launches_per_step = r.last_step_launches() + 1
     n_eff = 1 if tp else world
     value = n_eff * B * K / total_ms * 1e3
-    mean_ctx = ctx0 + W + K / 2.0
+    mean_ctx = ctx_sum[0] / max(ctx_sum[1], 1)
     step_bytes = (cfg.weight_bytes() + B * mean_ctx * cfg.kv_bytes_per_token()) / (world if tp else 1)
     step_gbs = step_bytes / (total_ms / K) / 1e6
 
@@ -342,17 +356,26 @@ def run_b200(args):
     # ---- (3) end to end through the engine API: host scheduling, pinned H2D, step, D2H ----
     eng = E.LLMEngine(r, max_num_batched_tokens=max(B, 8), max_num_seqs=max(B, 8), max_model_len=blocks_per_seq * bs)
     gp = torch.Generator().manual_seed(1000 + rank)
-    for i in range(B):
-        prompt = torch.randint(0, cfg.vocab, (ctx0,), generator=gp).tolist()
-        req = E.Request(f"r{i}", prompt, max_tokens=K + W + 4, ignore_eos=True)
-        eng.add_prefilled(req, ctx0 - 1)   # prompt KV is the synthetic cache content
-    for _ in range(W):
+    n_req = [0]
+
+    def admit():
+        while len(eng.scheduler.running) < B:
+            prompt = torch.randint(0, cfg.vocab, (ctx0,), generator=gp).tolist()
+            req = E.Request(f"r{n_req[0]}", prompt, max_tokens=out_len, ignore_eos=True)
+            n_req[0] += 1
+            eng.add_prefilled(req, ctx0 - 1)   # prompt KV is the synthetic cache content
+
+    def e2e_step():
+        admit()                                # continuous batching: finished requests are replaced
         eng.step()
+
+    for _ in range(W):
+        e2e_step()
     barrier()
     a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a0.record(stream)
     for _ in range(K):
-        eng.step()
+        e2e_step()
     a1.record(stream)
     barrier()
     e2e_ms = max_over_ranks(a0.elapsed_time(a1))
@@ -391,7 +414,7 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--steps", type=int, default=256)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="llama8b-bs64", choices=sorted(WORKLOADS))
