@@ -242,10 +242,9 @@ __device__ __forceinline__ void finalize4(const TcParams& p, int m_tile, int lan
   }
 }
 
-template <int N, int MODE>
+template <int N, int MODE, int S>
 __global__ void __launch_bounds__(kTcThreads)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, TcParams p) {
-  constexpr int S = stages_for(N);
   constexpr int kStageBytes = stage_bytes(N);
   constexpr int kABytes = kBlockM * kBlockK * 2;
   constexpr int kTmemCols = N < 32 ? 32 : N;
@@ -593,6 +592,7 @@ inline int n_tile_for(int T) { return T <= 16 ? 16 : (T <= 32 ? 32 : (T <= 64 ? 
 
 struct Plan {
   int N, m_tiles, tok_tiles, n_kblocks, splits, n_out_pad;
+  int deep;   // experiment (B200_TC_DEEP=1): at most one CTA per SM, each with a ring that fills the SM's shared memory
 };
 
 Plan make_plan(int T, int n_out, int k) {
@@ -617,20 +617,37 @@ Plan make_plan(int T, int n_out, int k) {
     s = max(1, min(s, 32));
   }
   pl.splits = s;
+  static const int deep_env = getenv("B200_TC_DEEP") ? atoi(getenv("B200_TC_DEEP")) : 0;
+  pl.deep = 0;
+  if (deep_env && pl.N <= 64 && tiles <= kNumSMs) {
+    int sd = kNumSMs / tiles;                              // never more than one CTA per SM
+    sd = max(1, min(min(sd, 8), max(pl.n_kblocks / min_kb, 1)));
+    pl.splits = sd;
+    pl.deep = 1;
+  }
   return pl;
+}
+
+// deep ring: as many stages as fit one CTA per SM (for launches of at most one CTA per SM)
+__host__ __device__ constexpr int deep_stages_for(int N) { return (200 * 1024) / stage_bytes(N); }
+
+template <int N, int MODE, int S>
+int launch_tc3(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
+  static bool attr_set = false;
+  const int smem = S * stage_bytes(N) + 1024 + 256;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N, MODE, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  B200_CUDA(launch_cluster(linear_tc_kernel<N, MODE, S>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads),
+                           (size_t)smem, s, p.cluster ? dim3(1, pl.splits, 1) : dim3(1, 1, 1), mw, mx, p));
+  return B200_OK;
 }
 
 template <int N, int MODE>
 int launch_tc2(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
-  static bool attr_set = false;
-  const int smem = smem_bytes_for(N);
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
-  }
-  B200_CUDA(launch_cluster(linear_tc_kernel<N, MODE>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads),
-                           (size_t)smem, s, p.cluster ? dim3(1, pl.splits, 1) : dim3(1, 1, 1), mw, mx, p));
-  return B200_OK;
+  if (pl.deep) return launch_tc3<N, MODE, deep_stages_for(N)>(mw, mx, p, pl, s);
+  return launch_tc3<N, MODE, stages_for(N)>(mw, mx, p, pl, s);
 }
 
 template <int N>
