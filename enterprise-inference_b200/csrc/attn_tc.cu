@@ -33,9 +33,8 @@ int launch_attn_merge(const float* part_o, const float* part_ml, __nv_bfloat16* 
 namespace {
 
 constexpr int kTileTok = 128;
-constexpr int kKvStages = 3;
 constexpr int kHalfBytes = kTileTok * 64 * 2;     // one [128 tok][64 dim] swizzled sub-tile: 16 KiB
-constexpr int kStageBytes = 4 * kHalfBytes;       // K lo|hi dims, V lo|hi dims: 64 KiB
+constexpr int kSlotBytes = 2 * kHalfBytes;        // one K tile or one V tile (lo|hi dims): 32 KiB
 constexpr int kSmallTile = 16 * 64 * 2;           // one [16 heads][64] swizzled sub-tile: 2 KiB
 constexpr int kThreads = 224;                     // TMA warp, MMA warp, 4 softmax warps, Q-staging warp
 constexpr int kNPad = 16;                         // heads padded to the UMMA N
@@ -141,7 +140,11 @@ struct Smem {
   // followed by the barriers and small exchange areas (see carve-up in the kernel)
 };
 
-template <int G, int R>
+// NSLOT: 32 KiB ring slots, alternately a K tile and a V tile (tile n: K in slot 2n % NSLOT, V in slot
+// (2n+1) % NSLOT).  3 slots (96 KiB) let a CTA share its SM with a CTA of the neighbouring linear kernel,
+// so that under programmatic dependent launch their prologues and first tiles overlap this kernel's tail
+// and vice versa; 6 slots (192 KiB in flight) are used for long contexts where the stream is what matters.
+template <int G, int R, int NSLOT>
 __global__ void __launch_bounds__(kThreads, 1)
 paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
                      const __nv_bfloat16* __restrict__ q, int64_t ldq, const int32_t* __restrict__ block_table,
@@ -152,14 +155,13 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   if (threadIdx.x == 64) attn_trace(0);
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* kv = smem;
-  unsigned char* qs = kv + kKvStages * kStageBytes;
+  unsigned char* qs = kv + NSLOT * kSlotBytes;
   unsigned char* p_hi = qs + 2 * 2 * kSmallTile;          // qs: [2 buffers][2 sub-tiles]; p: [2 buffers][2 sub-tiles]
   unsigned char* p_lo = p_hi + 2 * 2 * kSmallTile;
   uint64_t* bars = reinterpret_cast<uint64_t*>(p_lo + 2 * 2 * kSmallTile);
-  uint64_t* k_full = bars;                   // [kKvStages]
-  uint64_t* v_full = k_full + kKvStages;     // [kKvStages]
-  uint64_t* kv_free = v_full + kKvStages;    // [kKvStages]
-  uint64_t* s_full = kv_free + kKvStages;    // [2]
+  uint64_t* kv_full = bars;                  // [NSLOT] TMA landed
+  uint64_t* kv_free = kv_full + 6;           // [NSLOT] the MMAs that read the slot have completed
+  uint64_t* s_full = kv_free + 6;            // [2]
   uint64_t* p_ready = s_full + 2;            // [2]
   uint64_t* o_full = p_ready + 2;            // [2] one per O buffer
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 6);   // o_full[2..3] q_ready[2], o_full[4..5] q_free[2]
@@ -174,9 +176,8 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   uint64_t* q_free = o_full + 4;    // [2], tcgen05.commit: the S MMAs of item j no longer read qs[j & 1]
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kKvStages; ++s) {
-      mbar_init(&k_full[s], 1);
-      mbar_init(&v_full[s], 1);
+    for (int s = 0; s < NSLOT; ++s) {
+      mbar_init(&kv_full[s], 1);
       mbar_init(&kv_free[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
@@ -283,18 +284,19 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         for (int u = 0; u < R; ++u) {
           if (u >= w.nrun) break;
           for (int i = 0; i < w.run_tiles[u]; ++i, ++n) {
-            const int st = n % kKvStages;
-            if (n >= kKvStages) mbar_wait(&kv_free[st], ((n / kKvStages) - 1) & 1);
+            const int qk = 2 * n, qv = 2 * n + 1;          // ring sequence numbers of this tile's K and V
+            const int sk = qk % NSLOT, sv = qv % NSLOT;
             const int tok0 = (w.tile_begin + i) * kTileTok;
             const int blk = (u == 0 && i == 0) ? w.blk0 : w.run_bt[u][tok0 / block_size];
             const int row0 = (blk * hkv + w.kvh) * block_size + (tok0 % block_size);
-            unsigned char* sb = kv + st * kStageBytes;
-            mbar_expect_tx(&k_full[st], 2 * kHalfBytes);
-            tma_load_2d(sb, &map_k, 0, row0, &k_full[st]);
-            tma_load_2d(sb + kHalfBytes, &map_k, 64, row0, &k_full[st]);
-            mbar_expect_tx(&v_full[st], 2 * kHalfBytes);
-            tma_load_2d(sb + 2 * kHalfBytes, &map_v, 0, row0, &v_full[st]);
-            tma_load_2d(sb + 3 * kHalfBytes, &map_v, 64, row0, &v_full[st]);
+            if (qk >= NSLOT) mbar_wait(&kv_free[sk], ((qk / NSLOT) - 1) & 1);
+            mbar_expect_tx(&kv_full[sk], kSlotBytes);
+            tma_load_2d(kv + sk * kSlotBytes, &map_k, 0, row0, &kv_full[sk]);
+            tma_load_2d(kv + sk * kSlotBytes + kHalfBytes, &map_k, 64, row0, &kv_full[sk]);
+            if (qv >= NSLOT) mbar_wait(&kv_free[sv], ((qv / NSLOT) - 1) & 1);
+            mbar_expect_tx(&kv_full[sv], kSlotBytes);
+            tma_load_2d(kv + sv * kSlotBytes, &map_v, 0, row0, &kv_full[sv]);
+            tma_load_2d(kv + sv * kSlotBytes + kHalfBytes, &map_v, 64, row0, &kv_full[sv]);
           }
         }
       }
@@ -307,10 +309,10 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       constexpr uint32_t idesc_pv = make_idesc(1);
       uint32_t q_addr = smem_u32(qs);
       auto issue_s = [&](int n) {
-        const int st = n % kKvStages;
-        mbar_wait(&k_full[st], (n / kKvStages) & 1);
+        const int qk = 2 * n, sk = qk % NSLOT;
+        mbar_wait(&kv_full[sk], (qk / NSLOT) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(kv + st * kStageBytes);
+        const uint32_t k_addr = smem_u32(kv + sk * kSlotBytes);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
@@ -318,6 +320,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
           tc_mma(tmem_base + (n & 1) * 16, make_desc(k_addr + ao, 16, 1024), make_desc(q_addr + bo, 16, 1024), idesc_qk,
                  j ? 1u : 0u);
         }
+        tc_commit(&kv_free[sk]);   // the K slot is free as soon as these MMAs have read it
         tc_commit(&s_full[n & 1]);
       };
       int n = 0, active = 0;
@@ -338,11 +341,11 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
             issue_s(n + 1);
             if (i + 2 == nt) tc_commit(&q_free[active & 1]);   // last S of this item issued
           }
-          const int st = n % kKvStages;
-          mbar_wait(&v_full[st], (n / kKvStages) & 1);
+          const int qv = 2 * n + 1, sv = qv % NSLOT;
+          mbar_wait(&kv_full[sv], (qv / NSLOT) & 1);
           mbar_wait(&p_ready[n & 1], (n >> 1) & 1);
           tc_fence_after();
-          const uint32_t v_addr = smem_u32(kv + st * kStageBytes + 2 * kHalfBytes);
+          const uint32_t v_addr = smem_u32(kv + sv * kSlotBytes);
           const uint32_t ph = smem_u32(p_hi + (n & 1) * 2 * kSmallTile);
           const uint32_t pl = smem_u32(p_lo + (n & 1) * 2 * kSmallTile);
 #pragma unroll
@@ -352,7 +355,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
             tc_mma(tmem_base + 32 + (n & 1) * 16, da, make_desc(ph + bo, 16, 1024), idesc_pv, j ? 1u : 0u);
             tc_mma(tmem_base + 32 + (n & 1) * 16, da, make_desc(pl + bo, 16, 1024), idesc_pv, 1u);
           }
-          tc_commit(&kv_free[st]);  // K and V of this stage are no longer read
+          tc_commit(&kv_free[sv]);  // the V slot is no longer read
           tc_commit(&o_full[n & 1]);
         }
         ++active;
@@ -407,7 +410,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       for (int u = 0; u < R; ++u) {
         if (u >= w.nrun) break;
         for (int i = 0; i < w.run_tiles[u]; ++i, ++n, ++done) {
-          const int st = n % kKvStages;
+          const int qv = 2 * n + 1, sv = qv % NSLOT;
           const int tok0 = (w.tile_begin + i) * kTileTok;
           const int n_valid = min(kTileTok, w.run_ctx[u] - tok0);
           mbar_wait(&s_full[n & 1], (n >> 1) & 1);
@@ -449,9 +452,9 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
           if (n_valid < kTileTok) {
             // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor
             // core) — wait for the tile, then zero this thread's row if it is past the end
-            mbar_wait(&v_full[st], (n / kKvStages) & 1);
+            mbar_wait(&kv_full[sv], (qv / NSLOT) & 1);
             if (tau >= n_valid) {
-              unsigned char* vb = kv + st * kStageBytes + 2 * kHalfBytes;
+              unsigned char* vb = kv + sv * kSlotBytes;
 #pragma unroll
               for (int h2 = 0; h2 < 2; ++h2)
 #pragma unroll
@@ -522,26 +525,38 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   }
 }
 
-constexpr int kAttnTcSmem = kKvStages * kStageBytes + (4 + 8) * kSmallTile + 512 + 1024;
+constexpr int attn_tc_smem(int nslot) { return nslot * kSlotBytes + (4 + 8) * kSmallTile + 1024 /* barriers, exchange */ + 1024 /* alignment */; }
 
-template <int G, int R>
-int launch_attn_tc(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
+template <int G, int R, int NSLOT>
+int launch_attn_tc2(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
                    const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                    __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
                    float* part_o, float* part_ml, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnTcSmem));
+    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G, R, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tc_smem(NSLOT)));
     attr_set = true;
   }
   static const int trace_on = getenv("B200_ATTN_TRACE") ? atoi(getenv("B200_ATTN_TRACE")) : 0;
   if (trace_on) cudaMemcpyToSymbol(g_attn_trace_on, &trace_on, sizeof(int));
   const int64_t items = (int64_t)n_splits * hkv * ((T + R - 1) / R);
   const int grid = (int)(items < kNumSMs ? items : kNumSMs);   // persistent: one CTA per SM, items round-robin
-  B200_CUDA(launch(paged_attn_tc_kernel<G, R>, dim3(grid), dim3(kThreads), (size_t)kAttnTcSmem, s, mk, mv, q, ldq,
+  B200_CUDA(launch(paged_attn_tc_kernel<G, R, NSLOT>, dim3(grid), dim3(kThreads), (size_t)attn_tc_smem(NSLOT), s, mk, mv, q, ldq,
                    block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, T, scale,
                    part_o, part_ml));
   return B200_OK;
+}
+
+template <int G, int R>
+int launch_attn_tc(int nslot, const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
+                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                   __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
+                   float* part_o, float* part_ml, cudaStream_t s) {
+  if (nslot == 3)
+    return launch_attn_tc2<G, R, 3>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv,
+                                    block_size, n_splits, tps, scale, part_o, part_ml, s);
+  return launch_attn_tc2<G, R, 6>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv,
+                                  block_size, n_splits, tps, scale, part_o, part_ml, s);
 }
 
 }  // namespace
@@ -569,6 +584,12 @@ int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
   if (T == 0) return B200_OK;
   const int G = hq / hkv;
   const int R = pack ? attn_tc_pack_rows(G) : 1;
+  // 6 slots = 192 KiB in flight.  A 3-slot ring (B200_ATTN_SLOTS=3) would let this kernel share an SM with the
+  // neighbouring linear's CTA under PDL, but measured: no gain in the step at 2 tiles per row and 19 % slower
+  // in isolation at 5 tiles per row (64 x 640), so it is not the default.
+  static const int nslot_env = getenv("B200_ATTN_SLOTS") ? atoi(getenv("B200_ATTN_SLOTS")) : 0;
+  const int nslot = nslot_env == 3 ? 3 : 6;
+  (void)max_ctx;
   int n_splits, tps;
   attn_split_plan_tc((T + R - 1) / R, hkv, max_ctx, &n_splits, &tps);
   float* part_o = nullptr;
@@ -589,7 +610,7 @@ int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
   rc = get_tensor_map_2d(vc, rows, kHeadDim, kHeadDim, kTileTok, &mv);
   if (rc) return rc;
 #define B200_ATTN_TC_CASE(g, r)                                                                                        \
-  rc = launch_attn_tc<g, r>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv, block_size, \
+  rc = launch_attn_tc<g, r>(nslot, mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv, block_size, \
                             n_splits, tps, scale, part_o, part_ml, s)
   if (!pack) {
     switch (G) {
