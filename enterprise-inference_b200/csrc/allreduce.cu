@@ -64,11 +64,19 @@ __global__ void __launch_bounds__(256) allreduce_oneshot_kernel(ArParams p) {
   }
   __syncthreads();
   for (long long i = (long long)blockIdx.x * blockDim.x + tid; i < p.n_chunks; i += (long long)gridDim.x * blockDim.x) {
+    // all peer loads are issued before the first use: ONE NVLink round trip per chunk, not one per rank
+    uint4 pv[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+      if (r < p.world) pv[r] = ld_peer(reinterpret_cast<const uint4*>(p.bufs[r]) + i);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int r = 0; r < p.world; ++r) {
-      const uint4 v = ld_peer(reinterpret_cast<const uint4*>(p.bufs[r]) + i);
-      acc[0] += bf16lo(v.x); acc[1] += bf16hi(v.x); acc[2] += bf16lo(v.y); acc[3] += bf16hi(v.y);
-      acc[4] += bf16lo(v.z); acc[5] += bf16hi(v.z); acc[6] += bf16lo(v.w); acc[7] += bf16hi(v.w);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      if (r < p.world) {   // rank order: every rank computes the same bits
+        const uint4 v = pv[r];
+        acc[0] += bf16lo(v.x); acc[1] += bf16hi(v.x); acc[2] += bf16lo(v.y); acc[3] += bf16hi(v.y);
+        acc[4] += bf16lo(v.z); acc[5] += bf16hi(v.z); acc[6] += bf16lo(v.w); acc[7] += bf16hi(v.w);
+      }
     }
     reinterpret_cast<uint4*>(p.out)[i] = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]),
                                                     pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
@@ -85,12 +93,122 @@ __global__ void __launch_bounds__(256) allreduce_oneshot_kernel(ArParams p) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Fused collective + compute: all-reduce of the row-parallel partials, residual add and RMSNorm in ONE
+// kernel (one CTA per token row).  Same flag barrier as above; then every thread pulls its chunks of the
+// row from all ranks over NVLink, sums them in rank order, rounds to bf16 (the all-reduced activation is
+// bf16: identical numerics to all-reduce followed by the add+RMSNorm kernel), adds the residual in fp32
+// and normalises (R1 of the oracle).  Replaces two launches per half-layer (160 per 70B step).
+// ---------------------------------------------------------------------------------------------------
+constexpr int kArNormThreads = 1024;  // one 16-byte chunk per thread at h = 8192: ONE NVLink round trip per row
+constexpr int kArNormMaxChunks = 1;   // hidden <= 8192
+
+__global__ void __launch_bounds__(kArNormThreads)
+allreduce_add_rmsnorm_kernel(ArParams p, __nv_bfloat16* res, const __nv_bfloat16* __restrict__ w, __nv_bfloat16* y,
+                             int hidden, float eps) {
+  __shared__ unsigned int seq_s;
+  __shared__ float red[kArNormThreads / 32];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int tid = threadIdx.x;
+  if (tid == 0) seq_s = *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) + 1u;
+  __syncthreads();
+  const unsigned int seq = seq_s;
+  if (blockIdx.x == 0 && tid < p.world) {
+    __threadfence_system();
+    st_release_sys(p.flags[tid] + (p.buf_idx * 8 + p.rank) * 32, seq);
+  }
+  if (tid < p.world) {
+    const unsigned int* f = p.flags[p.rank] + (p.buf_idx * 8 + tid) * 32;
+    while ((int)(ld_acquire_sys(f) - seq) < 0) __nanosleep(20);
+  }
+  __syncthreads();
+  const int t = blockIdx.x;
+  const int nchunk = hidden >> 3;
+  uint4* rr = reinterpret_cast<uint4*>(res + (int64_t)t * hidden);
+  float v[kArNormMaxChunks][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kArNormMaxChunks; ++i) {
+    const int c = tid + i * kArNormThreads;
+    if (c < nchunk) {
+      uint4 pv[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < p.world) pv[r] = ld_peer(reinterpret_cast<const uint4*>(p.bufs[r] + (int64_t)t * hidden) + c);
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        if (r < p.world) {
+          const uint4 q = pv[r];
+          acc[0] += bf16lo(q.x); acc[1] += bf16hi(q.x); acc[2] += bf16lo(q.y); acc[3] += bf16hi(q.y);
+          acc[4] += bf16lo(q.z); acc[5] += bf16hi(q.z); acc[6] += bf16lo(q.w); acc[7] += bf16hi(q.w);
+        }
+      }
+      const uint4 b = rr[c];
+      const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[i][2 * j] = round_bf16(acc[2 * j]) + bf16lo(bw[j]);         // x = bf16(all-reduce); s = x + res in fp32
+        v[i][2 * j + 1] = round_bf16(acc[2 * j + 1]) + bf16hi(bw[j]);
+        o[j] = pack_bf16(v[i][2 * j], v[i][2 * j + 1]);
+      }
+      rr[c] = make_uint4(o[0], o[1], o[2], o[3]);                     // res' = bf16(s)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss = fmaf(v[i][j], v[i][j], ss);
+    }
+  }
+  ss = warp_sum(ss);
+  if ((tid & 31) == 0) red[tid >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < kArNormThreads / 32; ++i) tot += red[i];
+  const float rinv = 1.0f / sqrtf(tot / (float)hidden + eps);
+  const uint4* wr = reinterpret_cast<const uint4*>(w);
+  uint4* yr = reinterpret_cast<uint4*>(y + (int64_t)t * hidden);
+#pragma unroll
+  for (int i = 0; i < kArNormMaxChunks; ++i) {
+    const int c = tid + i * kArNormThreads;
+    if (c < nchunk) {
+      const uint4 wq = __ldg(wr + c);
+      const uint32_t ww[4] = {wq.x, wq.y, wq.z, wq.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float n0 = round_bf16(v[i][2 * j] * rinv), n1 = round_bf16(v[i][2 * j + 1] * rinv);
+        o[j] = pack_bf16(n0 * bf16lo(ww[j]), n1 * bf16hi(ww[j]));
+      }
+      yr[c] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    const unsigned int tk = atomicAdd(p.state + 2 + p.buf_idx, 1u);
+    if (tk == gridDim.x - 1) {
+      p.state[2 + p.buf_idx] = 0u;
+      *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) = seq;
+    }
+  }
+}
+
 }  // namespace
+
+int allreduce_add_rmsnorm(const ArParams& p, int T, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int hidden,
+                          float eps, cudaStream_t s) {
+  B200_REQUIRE(hidden % 8 == 0 && hidden <= 8 * kArNormThreads * kArNormMaxChunks, B200_ERR_UNSUPPORTED,
+               "allreduce_add_rmsnorm: hidden=%d unsupported", hidden);
+  if (T == 0) return B200_OK;
+  B200_CUDA(launch(allreduce_add_rmsnorm_kernel, dim3(T), dim3(kArNormThreads), 0, s, p, res, w, y, hidden, eps));
+  return B200_OK;
+}
 
 int allreduce_oneshot(const ArParams& p, cudaStream_t s) {
   if (p.n_chunks == 0) return B200_OK;
   long long g = (p.n_chunks + 255) / 256;
-  if (g > 64) g = 64;
+  if (g > 296) g = 296;
   B200_CUDA(launch(allreduce_oneshot_kernel, dim3((unsigned)g), dim3(256), 0, s, p));
   return B200_OK;
 }

@@ -117,6 +117,8 @@ struct ArParams {
   int rank, world, buf_idx;
 };
 int allreduce_oneshot(const ArParams& p, cudaStream_t s);
+int allreduce_add_rmsnorm(const ArParams& p, int T, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int hidden,
+                          float eps, cudaStream_t s);
 }  // namespace b200
 
 using namespace b200;
@@ -595,18 +597,16 @@ extern "C" int b200_advance_decode_rows(int32_t* ids, int32_t* positions, int32_
 
 // Row-parallel linears write into partial_dst(); tp_reduce() turns the partials of all ranks into c->x.
 // The one-shot peer-memory kernel wins where the all-reduce is latency bound (small messages); for large
-// messages NCCL's bandwidth-optimal algorithm is faster (measured at TP8: 1 MiB messages 15.0 vs 20.1 ms
-// per 70B step, 16 KiB messages 8.6 vs 9.7 ms) — switch-over tunable with B200_PEER_AR_MAX_KB.
+// messages NCCL's bandwidth-optimal algorithms take over.  Measured at TP8 (70B): 16 KiB messages 6.9 ms per step
+// one-shot vs 9.7 ms NCCL; 1 MiB messages 11.9 vs 15.0 ms — so the switch-over sits at 2 MiB (B200_PEER_AR_MAX_KB).
 static bool use_peer_ar(const b200_ctx* c, int T) {
-  static const int64_t max_kb = getenv("B200_PEER_AR_MAX_KB") ? atoi(getenv("B200_PEER_AR_MAX_KB")) : 256;
+  static const int64_t max_kb = getenv("B200_PEER_AR_MAX_KB") ? atoi(getenv("B200_PEER_AR_MAX_KB")) : 2048;
   return c->ar_ready && (int64_t)T * c->cfg.hidden * 2 <= max_kb * 1024;
 }
 static __nv_bfloat16* partial_dst(b200_ctx* c, int buf_idx, int T) {
   return use_peer_ar(c, T) ? reinterpret_cast<__nv_bfloat16*>(c->ar_mem + (int64_t)buf_idx * c->ar_buf_bytes) : c->x;
 }
-static int tp_reduce(b200_ctx* c, int buf_idx, int T, cudaStream_t s) {
-  const int64_t count = (int64_t)T * c->cfg.hidden;
-  if (!use_peer_ar(c, T)) return b200_allreduce_bf16(c, c->x, count, s);   // NCCL
+static ArParams ar_params(b200_ctx* c, int buf_idx, int T) {
   ArParams p = {};
   for (int r = 0; r < c->cfg.tp_world; ++r) {
     p.bufs[r] = reinterpret_cast<const __nv_bfloat16*>(c->ar_peer[r] + (int64_t)buf_idx * c->ar_buf_bytes);
@@ -614,11 +614,29 @@ static int tp_reduce(b200_ctx* c, int buf_idx, int T, cudaStream_t s) {
   }
   p.state = reinterpret_cast<unsigned int*>(c->ar_mem + 2 * c->ar_buf_bytes + 2 * 8 * 128);
   p.out = c->x;
-  p.n_chunks = count / 8;
+  p.n_chunks = (int64_t)T * c->cfg.hidden / 8;
   p.rank = c->cfg.tp_rank;
   p.world = c->cfg.tp_world;
   p.buf_idx = buf_idx;
-  return allreduce_oneshot(p, s);
+  return p;
+}
+static int tp_reduce(b200_ctx* c, int buf_idx, int T, cudaStream_t s) {
+  const int64_t count = (int64_t)T * c->cfg.hidden;
+  if (!use_peer_ar(c, T)) return b200_allreduce_bf16(c, c->x, count, s);   // NCCL
+  return allreduce_oneshot(ar_params(c, buf_idx, T), s);
+}
+// all-reduce of buffer buf_idx + residual add + RMSNorm: ONE fused peer-memory kernel for latency-bound
+// messages, else (NCCL or single rank) the all-reduce followed by the add+RMSNorm kernel
+static int tp_reduce_norm(b200_ctx* c, int buf_idx, int T, const __nv_bfloat16* w, cudaStream_t s) {
+  static const int fuse_env = getenv("B200_FUSE_AR_NORM") ? atoi(getenv("B200_FUSE_AR_NORM")) : 0;   // opt-in: correct (TP2 parity test) but not yet faster than the two kernels
+  const b200_model_cfg& m = c->cfg;
+  if (m.tp_world > 1 && fuse_env && use_peer_ar(c, T))
+    return allreduce_add_rmsnorm(ar_params(c, buf_idx, T), T, c->res, w, c->normed, m.hidden, m.rms_eps, s);
+  if (m.tp_world > 1) {
+    int rc = tp_reduce(c, buf_idx, T, s);
+    if (rc) return rc;
+  }
+  return rmsnorm(c->x, c->res, w, c->normed, T, m.hidden, m.rms_eps, s);
 }
 
 // ---- the step --------------------------------------------------------------------------------------
@@ -654,6 +672,9 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   const int qn = c->qkv_w, on = h, ok = c->hq * kHeadDim, gn = 2 * c->inter, dn = h, dk = c->inter;
   // timing experiments only (results are wrong): B200_DEBUG_SKIP bit 0 = skip the per-layer norms, bit 1 = skip attention
   static const int dbg_skip = getenv("B200_DEBUG_SKIP") ? atoi(getenv("B200_DEBUG_SKIP")) : 0;
+  // TP: the all-reduce after the down projection is folded into the norm that consumes it (next layer's ln1 or the
+  // final norm); with a debug tap it runs right after the projection so that the tap sees reduced activations
+  const bool defer_ar = tp && c->tap_layer < 0 && !(dbg_skip & 1);
   // Prefill-heavy steps (many more rows than sequences) pack consecutive rows of a sequence into one pass
   // over its K/V; decode steps keep one row per work item.
   const int attn_pack = a.row_to_seq && (a.n_seqs > 0 ? (T >= 4 * a.n_seqs && T >= 32) : T >= 512);
@@ -663,7 +684,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     if (l == 0)
       STEP(rmsnorm(c->res, nullptr, L.ln1, c->normed, T, h, m.rms_eps, s));
     else if (!(dbg_skip & 1))
-      STEP(rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
+      STEP(defer_ar ? tp_reduce_norm(c, 1, T, L.ln1, s) : rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
     __nv_bfloat16* kcl = c->kc + (int64_t)l * kv_layer_elems;
     __nv_bfloat16* vcl = c->vc + (int64_t)l * kv_layer_elems;
     {  // QKV (+ RoPE + KV append in the epilogue when on the tcgen05 path)
@@ -696,8 +717,11 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       STEP(linear_any(c->attn_out, ok, L.o, nullptr, tp ? partial_dst(c, 0, T) : c->x, h, T, on, ok, 0, c->gemv_max_t,
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
-    if (tp) STEP(tp_reduce(c, 0, T, s));
-    if (!(dbg_skip & 1)) STEP(rmsnorm(c->x, c->res, L.ln2, c->normed, T, h, m.rms_eps, s));
+    if (dbg_skip & 1) {
+      if (tp) STEP(tp_reduce(c, 0, T, s));
+    } else {
+      STEP(tp_reduce_norm(c, 0, T, L.ln2, s));   // (all-reduce +) residual add + RMSNorm
+    }
     {  // gate_up (+ SiLU*mul in the epilogue over interleaved slabs)
       LinearExtra ex;
       const bool tcp = tc_path(T, gn, h, c->gemv_max_t);
@@ -724,13 +748,13 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       STEP(linear_any(c->act, dk, L.down, nullptr, tp ? partial_dst(c, 1, T) : c->x, h, T, dn, dk, 0, c->gemv_max_t,
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
-    if (tp) STEP(tp_reduce(c, 1, T, s));
+    if (tp && !defer_ar) STEP(tp_reduce(c, 1, T, s));   // else: folded into the next norm (ln1 of layer l+1 / final norm)
     if (l == c->tap_layer && c->tap_hidden) {
       B200_CUDA(cudaMemcpyAsync(c->tap_hidden, c->x, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));
       if (c->tap_res) B200_CUDA(cudaMemcpyAsync(c->tap_res, c->res, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));
     }
   }
-  STEP(rmsnorm(c->x, c->res, c->final_norm, c->normed, T, h, m.rms_eps, s));
+  STEP(defer_ar ? tp_reduce_norm(c, 1, T, c->final_norm, s) : rmsnorm(c->x, c->res, c->final_norm, c->normed, T, h, m.rms_eps, s));
   const __nv_bfloat16* lm_in = c->normed;
   if (a.logit_rows) {
     STEP(embed(a.logit_rows, c->normed, c->lm_in, a.R, h, T, s));  // row gather
