@@ -248,23 +248,42 @@ paged_attn_kernel(const __nv_bfloat16* __restrict__ q, int64_t ldq, const __nv_b
 }
 
 // Merge the splits of one (row, head): o = sum_s o_s * exp(m_s - m) / sum_s l_s * exp(m_s - m).
+// The (m, l) pairs are loaded by one thread per split (parallel, not a dependent chain), the weights are
+// shared through smem, and each thread's partial-output loads are issued in batches of 8 before the
+// first dependent FMA — in-order issue would otherwise pay one L2 round trip per split.
 __global__ void __launch_bounds__(kHeadDim)
 attn_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml, __nv_bfloat16* __restrict__ out,
                   int64_t ldo, int hq, int n_splits) {
+  __shared__ float wgt[128];
+  __shared__ float red_m[4], red_l[4];
   pdl_wait();
   pdl_launch_dependents();
   const int head = blockIdx.x, t = blockIdx.y, d = threadIdx.x;
   const int64_t base = ((int64_t)t * hq + head) * n_splits;
-  float m = -INFINITY;
-  for (int s = 0; s < n_splits; ++s) m = fmaxf(m, part_ml[(base + s) * 2]);
-  float o = 0.f, l = 0.f;
-  for (int s = 0; s < n_splits; ++s) {
-    const float ms = part_ml[(base + s) * 2], ls = part_ml[(base + s) * 2 + 1];
-    if (ls > 0.f) {
-      const float w = __expf(ms - m);
-      l = fmaf(ls, w, l);
-      o = fmaf(part_o[(base + s) * kHeadDim + d], w, o);
-    }
+  float ms = -INFINITY, ls = 0.f;
+  if (d < n_splits) {
+    ms = part_ml[(base + d) * 2];
+    ls = part_ml[(base + d) * 2 + 1];
+    if (!(ls > 0.f)) ms = -INFINITY;
+  }
+  const float wm = warp_max(ms);
+  if ((d & 31) == 0) red_m[d >> 5] = wm;
+  __syncthreads();
+  const float m = fmaxf(fmaxf(red_m[0], red_m[1]), fmaxf(red_m[2], red_m[3]));
+  const float w = (d < n_splits && ls > 0.f) ? __expf(ms - m) : 0.f;
+  wgt[d] = w;
+  const float wl = warp_sum(ls * w);
+  if ((d & 31) == 0) red_l[d >> 5] = wl;
+  __syncthreads();
+  const float l = red_l[0] + red_l[1] + red_l[2] + red_l[3];
+  float o = 0.f;
+  for (int s0 = 0; s0 < n_splits; s0 += 8) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (s0 + j < n_splits) ? part_o[(base + s0 + j) * kHeadDim + d] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (s0 + j < n_splits) o = fmaf(v[j], wgt[s0 + j], o);
   }
   out[(int64_t)t * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? o / l : 0.f);
 }
