@@ -540,7 +540,15 @@ int launch_attn_tc2(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfl
   static const int trace_on = getenv("B200_ATTN_TRACE") ? atoi(getenv("B200_ATTN_TRACE")) : 0;
   if (trace_on) cudaMemcpyToSymbol(g_attn_trace_on, &trace_on, sizeof(int));
   const int64_t items = (int64_t)n_splits * hkv * ((T + R - 1) / R);
-  const int grid = (int)(items < kNumSMs ? items : kNumSMs);   // persistent: one CTA per SM, items round-robin
+  // persistent: at most one CTA per SM, items round-robin.  Items cost about the same, so the kernel ends
+  // when the CTAs with ceil(items/grid) items end.  Keep that round count, but spread the items evenly:
+  // 512 items run as 128 CTAs x 4 (each CTA gets a larger share of HBM while all of them stream) rather
+  // than 148 CTAs of which 68 take a fourth round while 80 idle.
+  int grid = (int)(items < kNumSMs ? items : kNumSMs);
+  if (items > kNumSMs) {
+    const int64_t rounds = (items + kNumSMs - 1) / kNumSMs;
+    grid = (int)((items + rounds - 1) / rounds);
+  }
   B200_CUDA(launch(paged_attn_tc_kernel<G, R, NSLOT>, dim3(grid), dim3(kThreads), (size_t)attn_tc_smem(NSLOT), s, mk, mv, q, ldq,
                    block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, T, scale,
                    part_o, part_ml));
