@@ -47,7 +47,15 @@ def _newest_header() -> float:
     return max(t, os.path.getmtime(__file__))
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """trace=True: a second library (lib/libb200decode_trace.so, -DB200_TRACE_BUILD) whose kernels carry
+    %globaltimer stamps for tools/*_trace.py (load it with B200_LIB=...); never the product library."""
+    global OBJ, LIB
+    flags = list(NVCC_FLAGS)
+    if trace:
+        OBJ = os.path.join(HERE, "build_trace")
+        LIB = os.path.join(LIBDIR, "libb200decode_trace.so")
+        flags.append("-DB200_TRACE_BUILD")
     os.makedirs(OBJ, exist_ok=True)
     os.makedirs(LIBDIR, exist_ok=True)
     hdr_t = _newest_header()
@@ -61,7 +69,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(so):
         s, o = so
-        cmd = [nvcc(), *NVCC_FLAGS, "-c", s, "-o", o]
+        cmd = [nvcc(), *flags, "-c", s, "-o", o]
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")
@@ -85,4 +93,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, trace="--trace" in sys.argv))

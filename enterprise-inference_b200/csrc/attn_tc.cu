@@ -165,8 +165,8 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   uint64_t* p_ready = s_full + 2;            // [2]
   uint64_t* o_full = p_ready + 2;            // [2] one per O buffer
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 6);   // o_full[2..3] q_ready[2], o_full[4..5] q_free[2]
-  float* xmax = reinterpret_cast<float*>(tmem_slot + 2);   // [4 warps][16 columns]
-  float* xsum = xmax + 64;                                  // [4 warps][16 columns]
+  float* xmax_all = reinterpret_cast<float*>(tmem_slot + 2);   // [2 (tile parity)][4 warps][16 columns]
+  float* xsum = xmax_all + 128;                                 // [4 warps][16 columns]
 
   constexpr int NC = G * R;   // live columns of the N = 16 MMA
   static_assert(NC <= kNPad, "row group does not fit the MMA N");
@@ -174,37 +174,6 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   const int hq = hkv * G;
   uint64_t* q_ready = o_full + 2;   // [2], 32 arrivals: Q of work item j is staged in qs[j & 1]
   uint64_t* q_free = o_full + 4;    // [2], tcgen05.commit: the S MMAs of item j no longer read qs[j & 1]
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < NSLOT; ++s) {
-      mbar_init(&kv_full[s], 1);
-      mbar_init(&kv_free[s], 1);
-    }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(&s_full[s], 1);
-      mbar_init(&p_ready[s], 128);
-      mbar_init(&o_full[s], 1);
-      mbar_init(&q_ready[s], 32);
-      mbar_init(&q_free[s], 1);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(kTmemCols));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
-  }
-  // zero the small operand tiles (Q, P hi/lo) once: rows >= G must not feed NaNs into the unused columns
-  for (int i = threadIdx.x; i < (4 + 8) * kSmallTile / 16; i += kThreads)
-    reinterpret_cast<uint4*>(qs)[i] = make_uint4(0u, 0u, 0u, 0u);
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-  pdl_wait();               // q and the newest K/V rows come from the previous kernel; the set-up above overlapped its tail
-  pdl_launch_dependents();
-  if (threadIdx.x == 64) attn_trace(1);
 
   // Persistent CTA: work items (row group, kv head, split) are taken round-robin; the K/V ring, the S/P
   // double buffers and all barrier phases run on ONE tile counter across items, so the TMA producer
@@ -265,6 +234,44 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     w.blk0 = w.run_tiles[0] > 0 ? w.run_bt[0][(w.tile_begin * kTileTok) / block_size] : 0;
     return w;
   };
+  // The first item's metadata is requested BEFORE the set-up below and before griddepcontrol.wait: its
+  // dependent global loads (~1 us) overlap the barrier/TMEM set-up.  Safe under programmatic dependent
+  // launch: context lengths and block tables are written at the start of a step, at least two kernels
+  // earlier, and a kernel only launches once its predecessor has passed its own griddepcontrol.wait.
+  Item first = {};
+  if ((int)blockIdx.x < n_items) first = get_item(blockIdx.x);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NSLOT; ++s) {
+      mbar_init(&kv_full[s], 1);
+      mbar_init(&kv_free[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&s_full[s], 1);
+      mbar_init(&p_ready[s], 4);     // one arrival per softmax warp
+      mbar_init(&o_full[s], 1);
+      mbar_init(&q_ready[s], 32);
+      mbar_init(&q_free[s], 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  // zero the small operand tiles (Q, P hi/lo) once: rows >= G must not feed NaNs into the unused columns
+  for (int i = threadIdx.x; i < (4 + 8) * kSmallTile / 16; i += kThreads)
+    reinterpret_cast<uint4*>(qs)[i] = make_uint4(0u, 0u, 0u, 0u);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();               // q and the newest K/V rows come from the previous kernel; the set-up above overlapped its tail
+  pdl_launch_dependents();
+  if (threadIdx.x == 64) attn_trace(1);
+
   // Every role walks the same item sequence; an item's metadata (context lengths, block-table rows:
   // dependent global loads, ~1 us each) is fetched one item AHEAD (`nxt`) so that an item switch never
   // stalls the TMA stream.
@@ -275,8 +282,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
       int n = 0;
-      Item nxt = {};
-      if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
+      Item nxt = first;
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const Item w = nxt;
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
@@ -324,8 +330,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         tc_commit(&s_full[n & 1]);
       };
       int n = 0, active = 0;
-      Item nxt = {};
-      if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
+      Item nxt = first;
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const Item w = nxt;
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
@@ -365,8 +370,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     // ===== Q stager: the group's R*G query heads -> qs[j & 1] as the swizzled K-major B operand of
     // S^T = K . Q^T (column c = row c / G, head c % G), one item ahead of the MMA warp =====
     int active = 0;
-    Item nxt = {};
-    if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
+    Item nxt = first;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const Item w = nxt;
       if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
@@ -391,8 +395,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     const int wq = warp - 2;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
     int n = 0, item_no = 0;
-    Item nxt = {};
-    if ((int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
+    Item nxt = first;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++item_no) {
       const Item w = nxt;
       if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
@@ -415,10 +418,12 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
           const int n_valid = min(kTileTok, w.run_ctx[u] - tok0);
           mbar_wait(&s_full[n & 1], (n >> 1) & 1);
           if (done == 0 && tau == 0) attn_trace(3 + 3 * item_no);
+          if (tau == 0 && n < 10) attn_trace(20 + 4 * n);       // S(n) landed
           tc_fence_after();
           uint32_t r[16];
           tmem_ld16(lane_addr + (n & 1) * 16, r);
           float sc[NC];
+          float* xmax = xmax_all + (n & 1) * 64;   // double buffered: one CTA-wide barrier per tile is enough
 #pragma unroll
           for (int c = 0; c < NC; ++c) {
             // column c = (row c / G, head c % G): live in this run, and causal: token < that row's context
@@ -432,6 +437,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
             if (lane == 0) xmax[wq * 16 + c] = wm;
           }
           asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (tau == 0 && n < 10) attn_trace(21 + 4 * n);       // tile max exchanged
           float alpha[NC];
 #pragma unroll
           for (int c = 0; c < NC; ++c) {
@@ -462,9 +468,12 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
                   *reinterpret_cast<uint4*>(vb + h2 * kHalfBytes + tau * 128 + cc * 16) = make_uint4(0u, 0u, 0u, 0u);
             }
           }
+          if (tau == 0 && n < 10) attn_trace(22 + 4 * n);       // P(n) stored
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
           tc_fence_before();
-          mbar_arrive(&p_ready[n & 1]);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&p_ready[n & 1]);
+          if (tau == 0 && n < 10) attn_trace(23 + 4 * n);       // P(n) handed over
           // Fold the PREVIOUS tile's O_tile^T[dim = tau][column] into the running output (O is double
           // buffered in TMEM): the P.V MMAs of this tile run while the next tile's softmax is computed.
           if (done > 0) {
@@ -476,7 +485,6 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
           }
 #pragma unroll
           for (int c = 0; c < NC; ++c) alpha_prev[c] = alpha[c];
-          asm volatile("bar.sync 1, 128;" ::: "memory");  // xmax is rewritten by the next tile
         }
       }
       if (done > 0) {   // the last tile's O

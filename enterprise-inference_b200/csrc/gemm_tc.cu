@@ -453,6 +453,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // summing the S partials in rank order (deterministic) straight out of its peers' smem (DSMEM).
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (threadIdx.x == 64) tc_trace(p, 10);   // every CTA of the cluster has staged its partial tile
     if (warp >= 2) {
       const int S2 = p.splits, rank = split, wq = warp - 2, r4 = lane * 4;
       const int tok0 = tok_tile * N;
@@ -502,6 +503,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
       }
     }
+    if (threadIdx.x == 64) tc_trace(p, 11);   // this CTA's share finalized
     // nobody may exit (and release its shared memory) while a peer still reads it
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");

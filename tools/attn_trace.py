@@ -1,6 +1,7 @@
 """Item timeline of CTA 0 of the tcgen05 attention (B200_ATTN_TRACE=1)."""
 import ctypes as C, importlib, os, sys
 os.environ["B200_ATTN_TRACE"] = "1"
+os.environ.setdefault("B200_LIB", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "enterprise-inference_b200", "lib", "libb200decode_trace.so"))
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -32,3 +33,6 @@ for (B, ctx, hq, hkv) in ((64, 640, 32, 8), (8, 32768, 32, 8)):
     vals = [(buf[i] - t0) / 1e3 if buf[i] >= t0 else None for i in range(20)]
     print(f"B={B} ctx={ctx}: start->pdl {vals[1]:.2f} us;", "items (start, first S ready, end):",
           [tuple(None if v is None else round(v, 2) for v in vals[2 + 3 * k: 5 + 3 * k]) for k in range(5)])
+    tl = [(buf[i] - t0) / 1e3 if buf[i] >= t0 else None for i in range(20, 60)]
+    print("  tiles (S landed, max exchanged, P stored, P handed over):",
+          [tuple(None if v is None else round(v, 2) for v in tl[4 * k: 4 * k + 4]) for k in range(10)])

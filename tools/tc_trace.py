@@ -1,6 +1,7 @@
 """Phase timeline of CTA 0 of the tcgen05 linear (B200_TC_TRACE=1): where does a short kernel spend its time?"""
 import ctypes as C, importlib, os, sys
 os.environ["B200_TC_TRACE"] = "1"
+os.environ.setdefault("B200_LIB", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "enterprise-inference_b200", "lib", "libb200decode_trace.so"))
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -8,7 +9,7 @@ abi = importlib.import_module("enterprise-inference_b200._abi")
 lib = abi.lib()
 BF = torch.bfloat16
 names = ["cta_start", "W_requested", "pdl_wait_done", "first_stage_landed", "last_mma_issued", "accum_complete",
-         "tile_staged", "before_cluster", "finalize_done", "cta_end"]
+         "tile_staged", "before_cluster", "finalize_done", "cta_end", "cluster_ready", "own_share_done"]
 for (nm, T, n, k) in [("o T=64", 64, 4096, 4096), ("o T=1", 1, 4096, 4096), ("qkv T=64", 64, 6144, 4096), ("down T=64", 64, 4096, 14336),
                       ("gate_up T=64", 64, 28672, 4096)]:
     x = torch.randn(T, k, device="cuda").to(BF)
@@ -28,4 +29,4 @@ for (nm, T, n, k) in [("o T=64", 64, 4096, 4096), ("o T=1", 1, 4096, 4096), ("qk
     buf = (C.c_ulonglong * 16)()
     lib.b200_debug_linear_trace(buf)
     t0 = buf[0]
-    print(nm, f"event {e0.elapsed_time(e1)*1e3:.1f} us |", " ".join(f"{names[i]}={(buf[i]-t0)/1e3:.2f}" for i in range(1, 10)))
+    print(nm, f"event {e0.elapsed_time(e1)*1e3:.1f} us |", " ".join(f"{names[i]}={(buf[i]-t0)/1e3:.2f}" for i in (1, 2, 3, 4, 5, 6, 7, 10, 11, 8, 9)))
