@@ -677,7 +677,10 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   const bool defer_ar = tp && c->tap_layer < 0 && !(dbg_skip & 1);
   // Prefill-heavy steps (many more rows than sequences) pack consecutive rows of a sequence into one pass
   // over its K/V; decode steps keep one row per work item.
-  const int attn_pack = a.row_to_seq && (a.n_seqs > 0 ? (T >= 4 * a.n_seqs && T >= 32) : T >= 512);
+  // Decode-only steps (every row its own sequence: one new token each) are flagged with -1: the attention may
+  // then request the cache tiles older than that token before the QKV kernel has completed.
+  int attn_pack = a.row_to_seq && (a.n_seqs > 0 ? (T >= 4 * a.n_seqs && T >= 32) : T >= 512);
+  if (!attn_pack && (a.row_to_seq == nullptr || a.n_seqs == T)) attn_pack = -1;
   STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
   for (int l = 0; l < m.n_layers; ++l) {
     const LayerW& L = c->layers[l];

@@ -430,7 +430,8 @@ static int paged_attn_cc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat1
 
 
 
-// pack != 0: consecutive query rows of one sequence (a prefill chunk) share one pass over the K/V cache
+// pack > 0: consecutive query rows of one sequence (a prefill chunk) share one pass over the K/V cache;
+// pack < 0: decode-only step (each row its own sequence, only position ctx-1 is new): early cache requests
 int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,

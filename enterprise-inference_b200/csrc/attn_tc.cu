@@ -150,7 +150,8 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
                      const __nv_bfloat16* __restrict__ q, int64_t ldq, const int32_t* __restrict__ block_table,
                      int bt_stride, const int32_t* __restrict__ row_to_seq, const int32_t* __restrict__ ctx_lens,
                      __nv_bfloat16* __restrict__ out, int64_t ldo, int hkv, int block_size, int tiles_per_split,
-                     int n_splits, int n_rows, float scale, float* __restrict__ part_o, float* __restrict__ part_ml) {
+                     int n_splits, int n_rows, float scale, float* __restrict__ part_o, float* __restrict__ part_ml,
+                     int early) {
   extern __shared__ unsigned char smem_raw[];
   if (threadIdx.x == 64) attn_trace(0);
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -241,6 +242,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   Item first = {};
   if ((int)blockIdx.x < n_items) first = get_item(blockIdx.x);
 
+  int pre_tiles = 0;   // tiles of the first item already requested (meaningful in thread 0 = the TMA thread)
   if (threadIdx.x == 0) {
     for (int s = 0; s < NSLOT; ++s) {
       mbar_init(&kv_full[s], 1);
@@ -254,6 +256,30 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       mbar_init(&q_free[s], 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // Decode-only steps (`early`): every row is its own sequence and the previous kernel wrote only
+    // position ctx-1 of it, so the tiles that end before that position are from earlier steps and can be
+    // requested right now -- before the set-up below and before griddepcontrol.wait.
+    if (R == 1 && early && first.total_tiles > 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      const int lim = min(NSLOT / 2, first.run_tiles[0]);
+      int blk[NSLOT / 2];
+#pragma unroll
+      for (int i = 0; i < NSLOT / 2; ++i)
+        blk[i] = (i > 0 && i < lim) ? first.run_bt[0][((first.tile_begin + i) * kTileTok) / block_size] : first.blk0;
+#pragma unroll
+      for (int i = 0; i < NSLOT / 2; ++i) {
+        const int tok0 = (first.tile_begin + i) * kTileTok;
+        if (i >= lim || i != pre_tiles || tok0 + kTileTok > first.run_ctx[0] - 1) continue;
+        const int row0 = (blk[i] * hkv + first.kvh) * block_size + (tok0 % block_size);
+        mbar_expect_tx(&kv_full[2 * i], kSlotBytes);
+        tma_load_2d(kv + (2 * i) * kSlotBytes, &map_k, 0, row0, &kv_full[2 * i]);
+        tma_load_2d(kv + (2 * i) * kSlotBytes + kHalfBytes, &map_k, 64, row0, &kv_full[2 * i]);
+        mbar_expect_tx(&kv_full[2 * i + 1], kSlotBytes);
+        tma_load_2d(kv + (2 * i + 1) * kSlotBytes, &map_v, 0, row0, &kv_full[2 * i + 1]);
+        tma_load_2d(kv + (2 * i + 1) * kSlotBytes + kHalfBytes, &map_v, 64, row0, &kv_full[2 * i + 1]);
+        ++pre_tiles;
+      }
+    }
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
@@ -293,6 +319,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
             const int qk = 2 * n, qv = 2 * n + 1;          // ring sequence numbers of this tile's K and V
             const int sk = qk % NSLOT, sv = qv % NSLOT;
             const int tok0 = (w.tile_begin + i) * kTileTok;
+            if (n < pre_tiles) continue;   // requested before the set-up (decode-only steps)
             const int blk = (u == 0 && i == 0) ? w.blk0 : w.run_bt[u][tok0 / block_size];
             const int row0 = (blk * hkv + w.kvh) * block_size + (tok0 % block_size);
             if (qk >= NSLOT) mbar_wait(&kv_free[sk], ((qk / NSLOT) - 1) & 1);
@@ -539,7 +566,7 @@ template <int G, int R, int NSLOT>
 int launch_attn_tc2(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
                    const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                    __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
-                   float* part_o, float* part_ml, cudaStream_t s) {
+                   float* part_o, float* part_ml, int early, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G, R, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tc_smem(NSLOT)));
@@ -559,7 +586,7 @@ int launch_attn_tc2(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfl
   }
   B200_CUDA(launch(paged_attn_tc_kernel<G, R, NSLOT>, dim3(grid), dim3(kThreads), (size_t)attn_tc_smem(NSLOT), s, mk, mv, q, ldq,
                    block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, T, scale,
-                   part_o, part_ml));
+                   part_o, part_ml, early));
   return B200_OK;
 }
 
@@ -567,12 +594,12 @@ template <int G, int R>
 int launch_attn_tc(int nslot, const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
                    const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                    __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
-                   float* part_o, float* part_ml, cudaStream_t s) {
+                   float* part_o, float* part_ml, int early, cudaStream_t s) {
   if (nslot == 3)
     return launch_attn_tc2<G, R, 3>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv,
-                                    block_size, n_splits, tps, scale, part_o, part_ml, s);
+                                    block_size, n_splits, tps, scale, part_o, part_ml, early, s);
   return launch_attn_tc2<G, R, 6>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv,
-                                  block_size, n_splits, tps, scale, part_o, part_ml, s);
+                                  block_size, n_splits, tps, scale, part_o, part_ml, early, s);
 }
 
 }  // namespace
@@ -599,7 +626,9 @@ int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
   B200_REQUIRE(ldq % 8 == 0, B200_ERR_INVALID, "attn_tc: ldq must be a multiple of 8");
   if (T == 0) return B200_OK;
   const int G = hq / hkv;
-  const int R = pack ? attn_tc_pack_rows(G) : 1;
+  const int R = pack > 0 ? attn_tc_pack_rows(G) : 1;
+  static const int early_env = getenv("B200_ATTN_EARLY") ? atoi(getenv("B200_ATTN_EARLY")) : 1;
+  const int early = (pack < 0 && early_env) ? 1 : 0;   // pack < 0: decode-only step (see the kernel)
   // 6 slots = 192 KiB in flight.  A 3-slot ring (B200_ATTN_SLOTS=3) would let this kernel share an SM with the
   // neighbouring linear's CTA under PDL, but measured: no gain in the step at 2 tiles per row and 19 % slower
   // in isolation at 5 tiles per row (64 x 640), so it is not the default.
@@ -627,8 +656,8 @@ int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
   if (rc) return rc;
 #define B200_ATTN_TC_CASE(g, r)                                                                                        \
   rc = launch_attn_tc<g, r>(nslot, mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv, block_size, \
-                            n_splits, tps, scale, part_o, part_ml, s)
-  if (!pack) {
+                            n_splits, tps, scale, part_o, part_ml, early, s)
+  if (pack <= 0) {
     switch (G) {
       case 1: B200_ATTN_TC_CASE(1, 1); break;
       case 2: B200_ATTN_TC_CASE(2, 1); break;
