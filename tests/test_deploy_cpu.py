@@ -61,3 +61,21 @@ def test_our_values_args_parse_and_validate():
         args, unknown = S.make_arg_parser().parse_known_args(argv)
         assert unknown == []
         S.validate_args(args)
+
+
+def test_playbook_models_exist_in_the_values_file():
+    """Every model the B200 task file can deploy has a modelConfigs entry, and its default TP degree
+    matches the values file (the helm --set only overrides it when the operator asks)."""
+    tasks = load(os.path.join(ROOT, "deploy", "playbooks", "deploy-b200-models.yml"))
+    table = next(t["ansible.builtin.set_fact"]["b200_models"] for t in tasks if "ansible.builtin.set_fact" in t)
+    values = load(os.path.join(ROOT, "deploy", "helm-charts", "vllm", "b200-values.yaml"))
+    assert len(table) >= 3
+    for m in table:
+        assert m["hf"] in values["modelConfigs"], m["hf"]
+        assert int(values["modelConfigs"][m["hf"]]["tensor_parallel_size"]) == int(m["tp"]), m
+        assert m["key"].startswith("b200-") and m["release"].endswith("-b200")
+    tags = {tag for t in tasks for tag in (t.get("tags") if isinstance(t.get("tags"), list) else [])}
+    for m in table:
+        assert f"install-{m['key']}" in tags
+    vars_ = load(os.path.join(ROOT, "deploy", "inventory", "b200-vars.yml"))
+    assert vars_["b200_values_file"].endswith("/vllm/b200-values.yaml")
