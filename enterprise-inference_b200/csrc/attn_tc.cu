@@ -36,7 +36,10 @@ constexpr int kTileTok = 128;
 constexpr int kHalfBytes = kTileTok * 64 * 2;     // one [128 tok][64 dim] swizzled sub-tile: 16 KiB
 constexpr int kSlotBytes = 2 * kHalfBytes;        // one K tile or one V tile (lo|hi dims): 32 KiB
 constexpr int kSmallTile = 16 * 64 * 2;           // one [16 heads][64] swizzled sub-tile: 2 KiB
-constexpr int kThreads = 224;                     // TMA warp, MMA warp, 4 softmax warps, Q-staging warp
+// TMA warp, MMA warp, CG groups of 4 softmax warps, Q-staging warp
+__host__ __device__ constexpr int attn_threads(int cg) { return (3 + 4 * cg) * 32; }
+// column groups for NC live MMA columns: 2 warps per scheduler from 2 columns on, 4 from 8 on
+__host__ __device__ constexpr int attn_col_groups(int nc) { return nc >= 8 ? 4 : (nc >= 2 ? 2 : 1); }
 constexpr int kNPad = 16;                         // heads padded to the UMMA N
 constexpr uint32_t kTmemCols = 64;                // S0 | S1 | O0 | O1, 16 columns each
 
@@ -112,6 +115,27 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
       : "r"(taddr));
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+template <int NL>
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&r)[NL]) {
+  if constexpr (NL == 1) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r[0]) : "r"(taddr));
+  } else if constexpr (NL == 2) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr));
+  } else if constexpr (NL == 4) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr));
+  } else if constexpr (NL == 8) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr));
+  } else {
+    static_assert(NL == 16, "tmem_ld width");
+    tmem_ld16(taddr, r);
+    return;
+  }
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
 // byte offset of element (row r < 16, column c < 128) inside a [16][128] bf16 operand stored as two
 // K-major SWIZZLE_128B sub-tiles of 64 columns (Q and P operands)
 __device__ __forceinline__ uint32_t small_off(int r, int c) {
@@ -144,8 +168,8 @@ struct Smem {
 // (2n+1) % NSLOT).  3 slots (96 KiB) let a CTA share its SM with a CTA of the neighbouring linear kernel,
 // so that under programmatic dependent launch their prologues and first tiles overlap this kernel's tail
 // and vice versa; 6 slots (192 KiB in flight) are used for long contexts where the stream is what matters.
-template <int G, int R, int NSLOT>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int G, int R, int NSLOT, int CG>
+__global__ void __launch_bounds__(attn_threads(CG), 1)
 paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
                      const __nv_bfloat16* __restrict__ q, int64_t ldq, const int32_t* __restrict__ block_table,
                      int bt_stride, const int32_t* __restrict__ row_to_seq, const int32_t* __restrict__ ctx_lens,
@@ -166,8 +190,8 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   uint64_t* p_ready = s_full + 2;            // [2]
   uint64_t* o_full = p_ready + 2;            // [2] one per O buffer
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 6);   // o_full[2..3] q_ready[2], o_full[4..5] q_free[2]
-  float* xmax_all = reinterpret_cast<float*>(tmem_slot + 2);   // [2 (tile parity)][4 warps][16 columns]
-  float* xsum = xmax_all + 128;                                 // [4 warps][16 columns]
+  float* xmax_all = reinterpret_cast<float*>(tmem_slot + 2);   // [CG groups][2 (tile parity)][4 warps][16 columns]
+  float* xsum = xmax_all + 4 * 128;                             // [CG groups][4 warps][16 columns]
 
   constexpr int NC = G * R;   // live columns of the N = 16 MMA
   static_assert(NC <= kNPad, "row group does not fit the MMA N");
@@ -239,8 +263,19 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   // dependent global loads (~1 us) overlap the barrier/TMEM set-up.  Safe under programmatic dependent
   // launch: context lengths and block tables are written at the start of a step, at least two kernels
   // earlier, and a kernel only launches once its predecessor has passed its own griddepcontrol.wait.
+  // (Decode kernels only: with R > 1 the compiler keeps a hoisted Item on the stack, and the stores of
+  // the look-ahead fetch then wait for their loads -- 1.6 us per item; those roles fetch their own.)
   Item first = {};
-  if ((int)blockIdx.x < n_items) first = get_item(blockIdx.x);
+  if (R == 1 && (int)blockIdx.x < n_items) first = get_item(blockIdx.x);
+  auto first_item = [&]() -> Item {
+    if constexpr (R == 1) {
+      return first;
+    } else {
+      Item z = {};
+      if ((int)blockIdx.x < n_items) z = get_item(blockIdx.x);
+      return z;
+    }
+  };
 
   int pre_tiles = 0;   // tiles of the first item already requested (meaningful in thread 0 = the TMA thread)
   if (threadIdx.x == 0) {
@@ -250,7 +285,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&s_full[s], 1);
-      mbar_init(&p_ready[s], 4);     // one arrival per softmax warp
+      mbar_init(&p_ready[s], 4 * CG);   // one arrival per softmax warp
       mbar_init(&o_full[s], 1);
       mbar_init(&q_ready[s], 32);
       mbar_init(&q_free[s], 1);
@@ -287,7 +322,7 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   // zero the small operand tiles (Q, P hi/lo) once: rows >= G must not feed NaNs into the unused columns
-  for (int i = threadIdx.x; i < (4 + 8) * kSmallTile / 16; i += kThreads)
+  for (int i = threadIdx.x; i < (4 + 8) * kSmallTile / 16; i += attn_threads(CG))
     reinterpret_cast<uint4*>(qs)[i] = make_uint4(0u, 0u, 0u, 0u);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   tc_fence_before();
@@ -308,7 +343,8 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
       int n = 0;
-      Item nxt = first;
+      Item nxt = first_item();
+      if (R > 1 && (int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const Item w = nxt;
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
@@ -357,7 +393,8 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         tc_commit(&s_full[n & 1]);
       };
       int n = 0, active = 0;
-      Item nxt = first;
+      Item nxt = first_item();
+      if (R > 1 && (int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const Item w = nxt;
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
@@ -393,11 +430,11 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
         ++active;
       }
     }
-  } else if (warp == 6) {
+  } else if (warp == 2 + 4 * CG) {
     // ===== Q stager: the group's R*G query heads -> qs[j & 1] as the swizzled K-major B operand of
     // S^T = K . Q^T (column c = row c / G, head c % G), one item ahead of the MMA warp =====
     int active = 0;
-    Item nxt = first;
+    Item nxt = first_item();
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const Item w = nxt;
       if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
@@ -416,24 +453,49 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       ++active;
     }
   } else {
-    // ===== softmax / output: 128 threads; thread = token (S lanes) and = head dim (O lanes) =====
+    // ===== softmax / output: CG column groups of 128 threads; thread = token (S lanes) and = head dim
+    // (O lanes).  One warp per scheduler cannot hide its own latencies (the per-tile chain is ~100
+    // dependent instructions per column), so the NC live columns are dealt to CG groups of four warps
+    // (one per TMEM lane quadrant): the groups run the same tile concurrently on different columns and
+    // share nothing but the P hand-over barrier. =====
+    const int grp = (warp - 2) >> 2;
     const int quad = warp & 3;
     const int tau = quad * 32 + lane;   // TMEM lane
-    const int wq = warp - 2;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    constexpr int NCG = (NC + CG - 1) / CG;                                              // columns per group
+    constexpr int NL = NCG <= 1 ? 1 : (NCG <= 2 ? 2 : (NCG <= 4 ? 4 : (NCG <= 8 ? 8 : 16)));   // tcgen05.ld width
+    const int c0 = grp * NCG;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0;
+    float* xmax_grp = xmax_all + grp * 128;   // [2 (tile parity)][4 quads][16]
+    float* xsum_grp = xsum + grp * 64;        // [4 quads][16]
+    const uint32_t bar_id = 1 + grp;
+    const bool lead = tau == 0 && grp == 0;   // trace stamps
+    uint32_t poff[NCG];                       // this thread's element of column c0+j in a P operand tile
+    int col_row[NCG], col_head[NCG];
+#pragma unroll
+    for (int j = 0; j < NCG; ++j) {
+      const int c = min(c0 + j, kNPad - 1);
+      poff[j] = small_off(c, tau);
+      col_row[j] = c / G;
+      col_head[j] = c % G;
+    }
     int n = 0, item_no = 0;
-    Item nxt = first;
+    Item nxt = first_item();
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++item_no) {
       const Item w = nxt;
       if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
-      if (tau == 0) attn_trace(2 + 3 * item_no);
-      float m_run[NC], l_run[NC], acc[NC], alpha_prev[NC];
+      if (lead && item_no < 6) attn_trace(2 + 3 * item_no);
+      float m_run[NCG], l_run[NCG], acc[NCG], alpha_prev[NCG];
+      int col_ctx[NCG];   // context of the column's row; 0 for a dead column (past NC, or row absent)
 #pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        m_run[c] = -INFINITY;
-        l_run[c] = 0.f;
-        acc[c] = 0.f;
-        alpha_prev[c] = 1.f;
+      for (int j = 0; j < NCG; ++j) {
+        m_run[j] = -INFINITY;
+        l_run[j] = 0.f;
+        acc[j] = 0.f;
+        alpha_prev[j] = 1.f;
+        col_ctx[j] = 0;
+        // mask-select (not an indexed read: a dynamic index would push the whole Item onto the stack)
+#pragma unroll
+        for (int r = 0; r < R; ++r) col_ctx[j] |= w.ctx[r] & -(int)(col_row[j] == r && c0 + j < NC);
       }
       int done = 0;   // tiles of this item already handed to the MMA warp
 #pragma unroll
@@ -444,45 +506,48 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
           const int tok0 = (w.tile_begin + i) * kTileTok;
           const int n_valid = min(kTileTok, w.run_ctx[u] - tok0);
           mbar_wait(&s_full[n & 1], (n >> 1) & 1);
-          if (done == 0 && tau == 0) attn_trace(3 + 3 * item_no);
-          if (tau == 0 && n < 10) attn_trace(20 + 4 * n);       // S(n) landed
+          if (done == 0 && lead && item_no < 6) attn_trace(3 + 3 * item_no);
+          if (lead && n < 10) attn_trace(20 + 4 * n);       // S(n) landed
           tc_fence_after();
-          uint32_t r[16];
-          tmem_ld16(lane_addr + (n & 1) * 16, r);
-          float sc[NC];
-          float* xmax = xmax_all + (n & 1) * 64;   // double buffered: one CTA-wide barrier per tile is enough
+          uint32_t r[NL];
+          tmem_ld<NL>(lane_addr + (n & 1) * 16, r);
+          float sc[NCG];
+          float* xmax = xmax_grp + (n & 1) * 64;   // double buffered: one group-wide barrier per tile is enough
 #pragma unroll
-          for (int c = 0; c < NC; ++c) {
-            // column c = (row c / G, head c % G): live in this run, and causal: token < that row's context
-            const bool live = (w.nrun == 1 || c / G == u) && (tok0 + tau < w.ctx[c / G]);
-            sc[c] = live ? __uint_as_float(r[c]) * scale : -INFINITY;
+          for (int j = 0; j < NCG; ++j) {
+            // column (row col_row, head col_head): live in this run, and causal: token < that row's context
+            const bool live = (w.nrun == 1 || col_row[j] == u) && (tok0 + tau < col_ctx[j]);
+            sc[j] = live ? __uint_as_float(r[j]) * scale : -INFINITY;
           }
           // tile max per column over the 128 tokens
 #pragma unroll
-          for (int c = 0; c < NC; ++c) {
-            const float wm = warp_max(sc[c]);
-            if (lane == 0) xmax[wq * 16 + c] = wm;
+          for (int j = 0; j < NCG; ++j) {
+            const float wm = warp_max_redux(sc[j]);
+            if (lane == 0) xmax[quad * 16 + j] = wm;
           }
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (tau == 0 && n < 10) attn_trace(21 + 4 * n);       // tile max exchanged
-          float alpha[NC];
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+          if (lead && n < 10) attn_trace(21 + 4 * n);       // tile max exchanged
+          float alpha[NCG];
+          unsigned char* ph = p_hi + (n & 1) * 2 * kSmallTile;
+          unsigned char* pl = p_lo + (n & 1) * 2 * kSmallTile;
 #pragma unroll
-          for (int c = 0; c < NC; ++c) {
-            const float tm = fmaxf(fmaxf(xmax[c], xmax[16 + c]), fmaxf(xmax[32 + c], xmax[48 + c]));
-            const float m_new = fmaxf(m_run[c], tm);
+          for (int j = 0; j < NCG; ++j) {
+            const float tm = fmaxf(fmaxf(xmax[j], xmax[16 + j]), fmaxf(xmax[32 + j], xmax[48 + j]));
+            const float m_new = fmaxf(m_run[j], tm);
             // a column with nothing seen so far (other run, or causally empty tile) keeps its state
             const bool seen = m_new > -INFINITY;
-            alpha[c] = seen ? __expf(m_run[c] - m_new) : 1.f;   // exp(-inf) = 0 on the column's first tile
-            m_run[c] = m_new;
-            const float pv = seen ? __expf(sc[c] - m_new) : 0.f;   // 0 for masked tokens
-            l_run[c] = l_run[c] * alpha[c] + pv;
+            alpha[j] = seen ? __expf(m_run[j] - m_new) : 1.f;   // exp(-inf) = 0 on the column's first tile
+            m_run[j] = m_new;
+            const float pv = seen ? __expf(sc[j] - m_new) : 0.f;   // 0 for masked tokens
+            l_run[j] = l_run[j] * alpha[j] + pv;
             const float hi = round_bf16(pv);
             const float lo = pv - hi;
-            const uint32_t off = small_off(c, tau) + (n & 1) * 2 * kSmallTile;
-            *reinterpret_cast<__nv_bfloat16*>(p_hi + off) = __float2bfloat16_rn(hi);
-            *reinterpret_cast<__nv_bfloat16*>(p_lo + off) = __float2bfloat16_rn(lo);
+            if (c0 + j < kNPad) {
+              *reinterpret_cast<__nv_bfloat16*>(ph + poff[j]) = __float2bfloat16_rn(hi);
+              *reinterpret_cast<__nv_bfloat16*>(pl + poff[j]) = __float2bfloat16_rn(lo);
+            }
           }
-          if (n_valid < kTileTok) {
+          if (n_valid < kTileTok && grp == 0) {
             // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor
             // core) — wait for the tile, then zero this thread's row if it is past the end
             mbar_wait(&kv_full[sv], (qv / NSLOT) & 1);
@@ -495,61 +560,61 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
                   *reinterpret_cast<uint4*>(vb + h2 * kHalfBytes + tau * 128 + cc * 16) = make_uint4(0u, 0u, 0u, 0u);
             }
           }
-          if (tau == 0 && n < 10) attn_trace(22 + 4 * n);       // P(n) stored
+          if (lead && n < 10) attn_trace(22 + 4 * n);       // P(n) stored
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to the MMA
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&p_ready[n & 1]);
-          if (tau == 0 && n < 10) attn_trace(23 + 4 * n);       // P(n) handed over
+          if (lead && n < 10) attn_trace(23 + 4 * n);       // P(n) handed over
           // Fold the PREVIOUS tile's O_tile^T[dim = tau][column] into the running output (O is double
           // buffered in TMEM): the P.V MMAs of this tile run while the next tile's softmax is computed.
           if (done > 0) {
             mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
             tc_fence_after();
-            tmem_ld16(lane_addr + 32 + ((n - 1) & 1) * 16, r);
+            tmem_ld<NL>(lane_addr + 32 + ((n - 1) & 1) * 16, r);
 #pragma unroll
-            for (int c = 0; c < NC; ++c) acc[c] = acc[c] * alpha_prev[c] + __uint_as_float(r[c]);
+            for (int j = 0; j < NCG; ++j) acc[j] = acc[j] * alpha_prev[j] + __uint_as_float(r[j]);
           }
 #pragma unroll
-          for (int c = 0; c < NC; ++c) alpha_prev[c] = alpha[c];
+          for (int j = 0; j < NCG; ++j) alpha_prev[j] = alpha[j];
         }
       }
       if (done > 0) {   // the last tile's O
-        uint32_t r[16];
+        uint32_t r[NL];
         mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
         tc_fence_after();
-        tmem_ld16(lane_addr + 32 + ((n - 1) & 1) * 16, r);
+        tmem_ld<NL>(lane_addr + 32 + ((n - 1) & 1) * 16, r);
 #pragma unroll
-        for (int c = 0; c < NC; ++c) acc[c] = acc[c] * alpha_prev[c] + __uint_as_float(r[c]);
+        for (int j = 0; j < NCG; ++j) acc[j] = acc[j] * alpha_prev[j] + __uint_as_float(r[j]);
       }
       // total l per column: sum the per-token partial sums over the 128 threads
 #pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        const float ws = warp_sum(l_run[c]);
-        if (lane == 0) xsum[wq * 16 + c] = ws;
+      for (int j = 0; j < NCG; ++j) {
+        const float ws = warp_sum(l_run[j]);
+        if (lane == 0) xsum_grp[quad * 16 + j] = ws;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
       const int d = tau;
 #pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        const int row = w.r0 + c / G;
-        if (row < n_rows) {
-          const float l = xsum[c] + xsum[16 + c] + xsum[32 + c] + xsum[48 + c];
-          const int head = w.kvh * G + c % G;
+      for (int j = 0; j < NCG; ++j) {
+        const int row = w.r0 + col_row[j];
+        if (c0 + j < NC && row < n_rows) {
+          const float l = xsum_grp[j] + xsum_grp[16 + j] + xsum_grp[32 + j] + xsum_grp[48 + j];
+          const int head = w.kvh * G + col_head[j];
           if (n_splits == 1) {
-            out[(int64_t)row * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? acc[c] / l : 0.f);
+            out[(int64_t)row * ldo + head * kHeadDim + d] = __float2bfloat16_rn(l > 0.f ? acc[j] / l : 0.f);
           } else {
             const int64_t pi = ((int64_t)row * hq + head) * n_splits + w.split;
-            part_o[pi * kHeadDim + d] = acc[c];
+            part_o[pi * kHeadDim + d] = acc[j];
             if (d == 0) {
-              part_ml[pi * 2] = m_run[c];
+              part_ml[pi * 2] = m_run[j];
               part_ml[pi * 2 + 1] = l;
             }
           }
         }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // xsum is rewritten by the next item
-      if (tau == 0) attn_trace(4 + 3 * item_no);
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // xsum is rewritten by the next item
+      if (lead && item_no < 6) attn_trace(4 + 3 * item_no);
     }
     tc_fence_before();
   }
@@ -560,16 +625,17 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   }
 }
 
-constexpr int attn_tc_smem(int nslot) { return nslot * kSlotBytes + (4 + 8) * kSmallTile + 1024 /* barriers, exchange */ + 1024 /* alignment */; }
+constexpr int attn_tc_smem(int nslot) { return nslot * kSlotBytes + (4 + 8) * kSmallTile + 4096 /* barriers, exchange */ + 1024 /* alignment */; }
 
-template <int G, int R, int NSLOT>
-int launch_attn_tc2(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
-                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
-                   __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
-                   float* part_o, float* part_ml, int early, cudaStream_t s) {
+template <int G, int R, int NSLOT, int CG>
+int launch_attn_tc3(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
+                    const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                    __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
+                    float* part_o, float* part_ml, int early, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G, R, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tc_smem(NSLOT)));
+    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G, R, NSLOT, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   attn_tc_smem(NSLOT)));
     attr_set = true;
   }
   static const int trace_on = getenv("B200_ATTN_TRACE") ? atoi(getenv("B200_ATTN_TRACE")) : 0;
@@ -584,10 +650,25 @@ int launch_attn_tc2(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfl
     const int64_t rounds = (items + kNumSMs - 1) / kNumSMs;
     grid = (int)((items + rounds - 1) / rounds);
   }
-  B200_CUDA(launch(paged_attn_tc_kernel<G, R, NSLOT>, dim3(grid), dim3(kThreads), (size_t)attn_tc_smem(NSLOT), s, mk, mv, q, ldq,
-                   block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits, T, scale,
-                   part_o, part_ml, early));
+  B200_CUDA(launch(paged_attn_tc_kernel<G, R, NSLOT, CG>, dim3(grid), dim3(attn_threads(CG)), (size_t)attn_tc_smem(NSLOT), s,
+                   mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tps, n_splits,
+                   T, scale, part_o, part_ml, early));
   return B200_OK;
+}
+
+// B200_ATTN_CG=1: one softmax group (A/B against the column groups)
+template <int G, int R, int NSLOT>
+int launch_attn_tc2(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq,
+                    const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                    __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
+                    float* part_o, float* part_ml, int early, cudaStream_t s) {
+  static const int cg_env = getenv("B200_ATTN_CG") ? atoi(getenv("B200_ATTN_CG")) : 0;
+  constexpr int CG = attn_col_groups(G * R);
+  if (cg_env == 1 || CG == 1)
+    return launch_attn_tc3<G, R, NSLOT, 1>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv,
+                                           block_size, n_splits, tps, scale, part_o, part_ml, early, s);
+  return launch_attn_tc3<G, R, NSLOT, CG>(mk, mv, q, ldq, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hkv,
+                                          block_size, n_splits, tps, scale, part_o, part_ml, early, s);
 }
 
 template <int G, int R>

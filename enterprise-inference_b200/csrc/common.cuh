@@ -58,6 +58,15 @@ __device__ __forceinline__ float warp_sum(float v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// Warp max of floats in ONE instruction (redux.sync on an order-preserving integer image of the float)
+// instead of five shuffle + max rounds.  -inf maps through unchanged; NaNs do not occur where it is used
+// (masked scores are -inf before the reduction).
+__device__ __forceinline__ float warp_max_redux(float v) {
+  int i = __float_as_int(v);
+  i = i >= 0 ? i : (i ^ 0x7fffffff);
+  i = __reduce_max_sync(0xffffffffu, i);
+  return __int_as_float(i >= 0 ? i : (i ^ 0x7fffffff));
+}
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));

@@ -188,21 +188,23 @@ __device__ __forceinline__ void finalize4(const TcParams& p, int m_tile, int lan
         if (row + e < p.n_out) dst[e] = __float2bfloat16_rn(v[e]);
     }
   } else if (MODE == kSiluMul) {
-    float u[4];
+    // lanes 0..15 hold 4 gate rows, lanes 16..31 the 4 matching up rows: after the exchange every lane has
+    // both, and each half-warp finalises two of the four features (all 32 lanes busy: the accurate
+    // expf + division of R5 is what this epilogue costs at large T)
+    float x[4];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) u[e] = __shfl_xor_sync(0xffffffffu, v[e], 16);  // lanes 16..31 hold the up rows
-    if (lane < 16) {
-      const int f = m_tile * 64 + r4;                                           // output feature
-      float o[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) o[e] = silu_bf16_dev(v[e]) * u[e];
-      __nv_bfloat16* dst = p.y + (int64_t)tok * p.ldy + f;
-      if ((p.ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 7) == 0)) {
-        *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]));
-      } else {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) dst[e] = __float2bfloat16_rn(o[e]);
-      }
+    for (int e = 0; e < 4; ++e) x[e] = __shfl_xor_sync(0xffffffffu, v[e], 16);
+    const bool lo = lane < 16;
+    const float g0 = lo ? v[0] : x[2], g1 = lo ? v[1] : x[3];
+    const float u0 = lo ? x[0] : v[2], u1 = lo ? x[1] : v[3];
+    const int f = m_tile * 64 + (lane & 15) * 4 + (lo ? 0 : 2);                  // output feature
+    const float o0 = silu_bf16_dev(g0) * u0, o1 = silu_bf16_dev(g1) * u1;
+    __nv_bfloat16* dst = p.y + (int64_t)tok * p.ldy + f;
+    if ((p.ldy % 2 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 3) == 0)) {
+      *reinterpret_cast<uint32_t*>(dst) = pack_bf16(o0, o1);
+    } else {
+      dst[0] = __float2bfloat16_rn(o0);
+      dst[1] = __float2bfloat16_rn(o1);
     }
   } else {  // kRopeKv
     const int head = m_tile;
@@ -398,6 +400,15 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           if (m_tile * kBlockM + r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[m_tile * kBlockM + r4 + e]);
       }
       const int64_t split_stride = (int64_t)gridDim.z * N * p.n_out_pad;
+      if (MODE == kRopeKv && tmax > 16) {
+        // prefill-sized tiles: the cos/sin row of a token is a dependent load (position -> row); request
+        // the rows of all of this warp's tokens now so that the loop below finds them in L1/L2
+        for (int t = wq + 4 * lane; t < tmax; t += 128) {
+          const char* row = reinterpret_cast<const char*>(p.cos_sin + (int64_t)p.positions[tok0 + t] * kHeadDim);
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(row));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 128));
+        }
+      }
       for (int t = wq; t < tmax; t += 16) {
         float4 acc[4];
         if (p.splits == 1) {

@@ -36,3 +36,34 @@ for (B, ctx, hq, hkv) in ((64, 640, 32, 8), (8, 32768, 32, 8)):
     tl = [(buf[i] - t0) / 1e3 if buf[i] >= t0 else None for i in range(20, 60)]
     print("  tiles (S landed, max exchanged, P stored, P handed over):",
           [tuple(None if v is None else round(v, 2) for v in tl[4 * k: 4 * k + 4]) for k in range(10)])
+
+# ---- prefill rows: one sequence, T rows with context 1..T (row groups of 4 rows share a pass) ----
+for T in (2048,):
+    bs, hq, hkv = 128, 32, 8
+    nb = T // bs
+    kc = torch.randn(nb, hkv, bs, 128, device="cuda", dtype=BF)
+    vc = torch.randn(nb, hkv, bs, 128, device="cuda", dtype=BF)
+    bt = torch.arange(nb, device="cuda", dtype=torch.int32).view(1, nb).contiguous()
+    q = torch.randn(T, hq * 128, device="cuda", dtype=BF)
+    out = torch.empty_like(q)
+    cl = torch.arange(1, T + 1, dtype=torch.int32, device="cuda")
+    r2s = torch.zeros(T, dtype=torch.int32, device="cuda")
+    wsb = lib.b200_paged_attn_workspace_bytes(T, hq, T, bs)
+    ws = torch.empty(max(wsb, 16), dtype=torch.uint8, device="cuda")
+    for rep in range(3):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        lib.b200_paged_attn_prefill(q.data_ptr(), hq * 128, kc.data_ptr(), vc.data_ptr(), bt.data_ptr(), nb, r2s.data_ptr(),
+                                    cl.data_ptr(), out.data_ptr(), hq * 128, T, hq, hkv, bs, T, 128 ** -0.5, ws.data_ptr(), wsb, None)
+        e1.record()
+        torch.cuda.synchronize()
+    buf = (C.c_ulonglong * 64)()
+    lib.b200_debug_attn_trace(buf)
+    t0 = buf[0]
+    vals = [(buf[i] - t0) / 1e3 if buf[i] >= t0 else None for i in range(20)]
+    print(f"prefill T={T}: event {e0.elapsed_time(e1) * 1e3:.1f} us; items (start, first S ready, end):",
+          [tuple(None if v is None else round(v, 2) for v in vals[2 + 3 * k: 5 + 3 * k]) for k in range(5)])
+    tl = [(buf[i] - t0) / 1e3 if buf[i] >= t0 else None for i in range(20, 60)]
+    print("  tiles (S landed, max exchanged, P stored, P handed over):",
+          [tuple(None if v is None else round(v, 2) for v in tl[4 * k: 4 * k + 4]) for k in range(10)])

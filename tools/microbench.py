@@ -62,7 +62,8 @@ def bench_linear(impls=(1,), Ts=(1, 2, 4)):
                     continue
                 gbs = n * k * 2 / ms / 1e6
                 print(json.dumps({"kernel": "linear", "shape": name, "n": n, "k": k, "T": T, "impl": impl,
-                                  "us": round(ms * 1e3, 2), "GBps": round(gbs, 1), "frac_of_measured": round(gbs / PEAK, 3)}))
+                                  "us": round(ms * 1e3, 2), "GBps": round(gbs, 1), "frac_of_measured": round(gbs / PEAK, 3),
+                                  "TFLOPs": round(2.0 * n * k * T / ms / 1e9, 1)}))
         del ws
         torch.cuda.empty_cache()
 
@@ -134,6 +135,8 @@ if __name__ == "__main__":
         bench_linear()
     if "linear_tc" in what:
         bench_linear(impls=(1, 2), Ts=(1, 4, 16, 64, 128))
+    if "linear_big" in what:
+        bench_linear(impls=(2,), Ts=(256, 512, 2048))
     if "attn" in what:
         bench_attn()
     if "step" in what:
