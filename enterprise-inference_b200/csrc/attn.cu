@@ -327,6 +327,12 @@ int launch_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, co
 
 // ---- tcgen05 variant (attn_tc.cu) -----------------------------------------------------------
 bool paged_attn_tc_supported(int hq, int hkv, int block_size);
+int64_t paged_attn_prefill_plan_bytes(int T);
+bool paged_attn_prefill_fa_supported(int hq, int hkv, int block_size);
+int paged_attn_prefill_fa(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
+                          const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
+                          __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, float scale, void* ws,
+                          int64_t ws_bytes, cudaStream_t s);
 int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
@@ -380,7 +386,8 @@ int64_t paged_attn_workspace_bytes(int T, int hq, int max_ctx, int block_size) {
     attn_split_plan_tc((T + r - 1) / r, 1, max_ctx, &ns2, &tps);
     ns = max(ns, ns2);
   }
-  return (int64_t)T * hq * ns * (kHeadDim + 2) * sizeof(float) + 256;
+  // + the work plan of the prefill kernel (attn_prefill.cu), which uses no split partials
+  return (int64_t)T * hq * ns * (kHeadDim + 2) * sizeof(float) + paged_attn_prefill_plan_bytes(T) + 256;
 }
 
 static int paged_attn_cc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
@@ -449,6 +456,13 @@ int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
                   void* ws, int64_t ws_bytes, int pack, cudaStream_t s) {
+  // prefill-dominated steps: query rows on the MMA M dimension (attn_prefill.cu); B200_ATTN_FA=0: the row
+  // groups of attn_tc.cu instead
+  static const int fa_env = getenv("B200_ATTN_FA") ? atoi(getenv("B200_ATTN_FA")) : 1;
+  if (pack > 0 && fa_env && use_tc_attn(hq, hkv, block_size) && paged_attn_prefill_fa_supported(hq, hkv, block_size) &&
+      ws && ws_bytes >= paged_attn_prefill_plan_bytes(T))
+    return paged_attn_prefill_fa(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv,
+                                 block_size, scale, ws, ws_bytes, s);
   if (use_tc_attn(hq, hkv, block_size))
     return paged_attn_tc(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv, block_size,
                          max_ctx, scale, ws, ws_bytes, pack, s);
