@@ -475,7 +475,12 @@ static int linear_any(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* 
   return linear_tc(x, ldx, w, bias, y, ldy, T, n_out, k, ws, ws_bytes, ex, s);
 }
 
-namespace b200 { int linear_tc_read_trace(unsigned long long* host16); int attn_tc_read_trace(unsigned long long* host64); }
+namespace b200 { int linear_tc_read_trace(unsigned long long* host16); int attn_tc_read_trace(unsigned long long* host64);
+                 int attn_prefill_read_trace(unsigned long long* host256); }
+// debug helper (not in the public header): tile timeline of CTA 0 of the last prefill attention (trace builds)
+extern "C" __attribute__((visibility("default"))) int b200_debug_prefill_trace(unsigned long long* host256) {
+  return b200::attn_prefill_read_trace(host256);
+}
 extern "C" __attribute__((visibility("default"))) int b200_debug_attn_trace(unsigned long long* host64) {
   return b200::attn_tc_read_trace(host64);
 }

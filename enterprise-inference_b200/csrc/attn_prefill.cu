@@ -34,9 +34,10 @@ constexpr int kTileTok = 128;
 constexpr int kHalfBytes = 128 * 64 * 2;          // one [128 rows][64 cols] bf16 SWIZZLE_128B sub-tile: 16 KiB
 constexpr int kTileBytes = 2 * kHalfBytes;        // a [128][128] bf16 operand tile: 32 KiB
 constexpr int kSlots = 4;                         // K/V ring: K, V, K, V (two tiles in flight)
-constexpr int kFaThreads = 224;                   // TMA warp, MMA warp, 4 softmax warps, Q-staging warp
+constexpr int kFaThreads = 352;                   // TMA warp, MMA warp, 8 softmax warps, Q-staging warp
 constexpr uint32_t kFaTmemCols = 512;             // S0 | S1 | O0 | O1, 128 columns each
-constexpr int kFaSmem = (1 /*Q*/ + 2 /*P hi, lo*/ + kSlots) * kTileBytes + 512 /* barriers */ + 1024 /* alignment */;
+constexpr int kFaNeed = (1 /*Q*/ + 2 /*P hi, lo*/ + kSlots) * kTileBytes + 128 /* barriers */ + 2048 /* row max exchange */;
+constexpr int kFaSmem = 232448;   // all of the SM's 227 KiB: leaves 896 B for aligning the base to 1024 (checked in the kernel)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -125,6 +126,20 @@ __device__ __forceinline__ float fast_exp2(float x) {   // x <= 0 or -inf here
   return y;
 }
 
+// debug (trace builds, -DB200_TRACE_BUILD): %globaltimer stamps of CTA 0's first softmax thread
+__device__ unsigned long long g_fa_trace[256];
+__device__ __forceinline__ void fa_trace(int slot) {
+#ifdef B200_TRACE_BUILD
+  if (blockIdx.x == 0 && slot < 256) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_fa_trace[slot] = t;
+  }
+#else
+  (void)slot;
+#endif
+}
+
 struct PlanItem {
   int row0, nrows, seq, ctx_max;
 };
@@ -190,6 +205,7 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
                         int hkv, int block_size, float scale, const PlanItem* __restrict__ plan) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  if ((int)(smem - smem_raw) + kFaNeed > kFaSmem) __trap();   // dynamic smem base less aligned than assumed
   unsigned char* qs = smem;                       // Q   [128 m][128 dim]
   unsigned char* p_hi = qs + kTileBytes;          // P   [128 m][128 tok], high bf16 term
   unsigned char* p_lo = p_hi + kTileBytes;        //                        low bf16 term
@@ -198,10 +214,11 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
   uint64_t* kv_free = kv_full + kSlots;
   uint64_t* s_full = kv_free + kSlots;            // [2]
   uint64_t* o_full = s_full + 2;                  // [2]
-  uint64_t* p_ready = o_full + 2;                 // P(n) is in shared memory (4 arrivals: one per softmax warp)
+  uint64_t* p_ready = o_full + 2;                 // P(n) is in shared memory (8 arrivals: one per softmax warp)
   uint64_t* q_ready = p_ready + 1;                // Q of the current item is staged (32 arrivals)
   uint64_t* q_free = q_ready + 1;                 // the S MMAs of the current item no longer read Q
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_free + 1);
+  float* xmax = reinterpret_cast<float*>(kv_full + 16);   // [2 (tile parity)][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -213,7 +230,7 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
       mbar_init(&s_full[s], 1);
       mbar_init(&o_full[s], 1);
     }
-    mbar_init(p_ready, 4);
+    mbar_init(p_ready, 8);
     mbar_init(q_ready, 32);
     mbar_init(q_free, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -323,7 +340,7 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
         ++active;
       }
     }
-  } else if (warp == 6) {
+  } else if (warp == 10) {
     // ===== Q stager: rows (row0 + m / G, head kvh * G + m % G) -> the swizzled K-major A operand =====
     int active = 0;
     for (int it = blockIdx.x; it < n_work; it += gridDim.x) {
@@ -346,12 +363,18 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
       ++active;
     }
   } else {
-    // ===== softmax / output: 128 threads, thread = query row m (TMEM lane) =====
+    // ===== softmax / output: 256 threads; a PAIR of threads (warps w and w + 4, same TMEM lane) owns query
+    // row m: thread `half` takes tokens [64 half, 64 half + 64) of S/P and head dims [64 half, +64) of O.
+    // Two warps per scheduler hide each other's latencies; the pair meets once per tile to combine its
+    // two partial row maxima (shared memory + one 256-thread barrier, double buffered by tile parity). =====
+    const int half = (warp - 2) >> 2;
     const int quad = warp & 3;
     const int m = quad * 32 + lane;
     const int r = m / G, g = m % G;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 64);
     const float sc2 = scale * 1.4426950408889634f;   // scores in the log2 domain: p = exp2(s * sc2 - m2)
+    const bool lead = m == 0 && half == 0;
+    if (lead) fa_trace(0);
     int n = 0;
     for (int it = blockIdx.x; it < n_work; it += gridDim.x) {
       PlanItem w;
@@ -362,66 +385,86 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
       const bool alive = r < w.nrows;
       const int ctx_m = alive ? ctx_lens[w.row0 + r] : 0;
       float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;
-      float acc[128];
+      float acc[64];
 #pragma unroll
-      for (int d = 0; d < 128; ++d) acc[d] = 0.f;
+      for (int d = 0; d < 64; ++d) acc[d] = 0.f;
       for (int i = 0; i < nt; ++i, ++n) {
-        const int tok0 = i * kTileTok;
-        const int n_live = min(max(ctx_m - tok0, 0), kTileTok);   // causal: tokens [tok0, tok0 + n_live) count
-        const int n_valid = min(kTileTok, w.ctx_max - tok0);       // tokens of the tile that exist at all
+        const int tok0 = i * kTileTok + half * 64;                 // first token of this thread's 64 columns
+        const int n_live = min(max(ctx_m - tok0, 0), 64);          // causal: columns [0, n_live) count
+        const int n_valid = min(kTileTok, w.ctx_max - i * kTileTok);   // tokens of the tile that exist at all
         // tcgen05.ld is warp-collective: which 32-column chunks are read is decided per warp
         const int n_live_w = __reduce_max_sync(0xffffffffu, n_live);
+        const bool full = __reduce_min_sync(0xffffffffu, n_live) == 64;   // no masking needed in this warp
+        if (lead && n < 40) fa_trace(8 + 6 * n);        // tile begins (waiting for S)
         mbar_wait(&s_full[n & 1], (n >> 1) & 1);
+        if (lead && n < 40) fa_trace(9 + 6 * n);        // S landed
         tc_fence_after();
         const uint32_t s_addr = lane_addr + (n & 1) * 128;
-        // pass 1: row max (in-thread: the row lives in this thread's TMEM lane)
+        // pass 1: row max over this thread's columns, then over the pair
         float mx = -INFINITY;
-        {
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            if (c * 32 < n_live_w) {
-              uint32_t s[32];
-              tmem_ld32(s_addr + c * 32, s);
+        for (int c = 0; c < 2; ++c) {
+          if (c * 32 < n_live_w) {
+            uint32_t s[32];
+            tmem_ld32(s_addr + c * 32, s);
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(s[j]));
+            } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
                 if (c * 32 + j < n_live) mx = fmaxf(mx, __uint_as_float(s[j]));
             }
           }
         }
+        float* xm = xmax + (n & 1) * 256;
+        xm[half * 128 + m] = mx;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        mx = fmaxf(mx, xm[(half ^ 1) * 128 + m]);
         const float m_new = fmaxf(m_run, mx * sc2);
         const bool seen = m_new > -INFINITY;
         const float alpha = seen ? fast_exp2(m_run - m_new) : 1.f;   // exp2(-inf) = 0 on the row's first live tile
         m_run = m_new;
         // fold the previous tile's O_t into the running output; this also proves that the P.V MMAs of the
         // previous tile have finished reading P, which pass 2 overwrites
+        if (lead && n < 40) fa_trace(10 + 6 * n);       // pass 1 + pair exchange done
         if (i > 0) {
           mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
+          if (lead && n < 40) fa_trace(11 + 6 * n);     // previous P.V complete
           tc_fence_after();
           const uint32_t o_addr = lane_addr + 256 + ((n - 1) & 1) * 128;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
+          for (int c = 0; c < 2; ++c) {
             uint32_t o[32];
             tmem_ld32(o_addr + c * 32, o);
 #pragma unroll
             for (int j = 0; j < 32; ++j) acc[c * 32 + j] = acc[c * 32 + j] * alpha_prev + __uint_as_float(o[j]);
           }
         }
-        // pass 2: P = exp2(s * sc2 - m) as hi + lo bf16, this row of the A operand of P.V
+        if (lead && n < 40) fa_trace(12 + 6 * n);       // fold done
+        // pass 2: P = exp2(s * sc2 - m) as hi + lo bf16, this thread's 64 columns of row m of the A operand
         float lsum = 0.f;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           uint32_t hi[16], lo[16];
           if (c * 32 < n_live_w) {
             uint32_t s[32];
             tmem_ld32(s_addr + c * 32, s);
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
-              const float p0 = (c * 32 + j < n_live) ? fast_exp2(__uint_as_float(s[j]) * sc2 - m_new) : 0.f;
-              const float p1 = (c * 32 + j + 1 < n_live) ? fast_exp2(__uint_as_float(s[j + 1]) * sc2 - m_new) : 0.f;
+              float p0 = fast_exp2(__uint_as_float(s[j]) * sc2 - m_new);
+              float p1 = fast_exp2(__uint_as_float(s[j + 1]) * sc2 - m_new);
+              if (!full) {
+                p0 = (c * 32 + j < n_live) ? p0 : 0.f;
+                p1 = (c * 32 + j + 1 < n_live) ? p1 : 0.f;
+              }
               lsum += p0 + p1;
-              const float h0 = round_bf16(p0), h1 = round_bf16(p1);
-              hi[j >> 1] = pack_bf16(h0, h1);
-              lo[j >> 1] = pack_bf16(p0 - h0, p1 - h1);
+              // hi = p rounded to bf16 (nearest even, integer arithmetic: conversions share the MUFU pipe)
+              const uint32_t b0 = __float_as_uint(p0), b1 = __float_as_uint(p1);
+              const uint32_t h0 = (b0 + 0x7fffu + ((b0 >> 16) & 1u)) & 0xffff0000u;
+              const uint32_t h1 = (b1 + 0x7fffu + ((b1 >> 16) & 1u)) & 0xffff0000u;
+              hi[j >> 1] = __byte_perm(h0, h1, 0x7632);
+              lo[j >> 1] = pack_bf16(p0 - __uint_as_float(h0), p1 - __uint_as_float(h1));
             }
           } else {
 #pragma unroll
@@ -429,13 +472,13 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
           }
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const uint32_t off = tile_chunk_off(m, c * 4 + k);
+            const uint32_t off = tile_chunk_off(m, half * 8 + c * 4 + k);
             *reinterpret_cast<uint4*>(p_hi + off) = make_uint4(hi[4 * k], hi[4 * k + 1], hi[4 * k + 2], hi[4 * k + 3]);
             *reinterpret_cast<uint4*>(p_lo + off) = make_uint4(lo[4 * k], lo[4 * k + 1], lo[4 * k + 2], lo[4 * k + 3]);
           }
         }
         l_run = l_run * alpha + lsum;
-        if (n_valid < kTileTok) {
+        if (n_valid < kTileTok && half == 0) {
           // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor core):
           // wait for the tile, then zero this thread's token row if it is past the end
           const int qv = 2 * n + 1, sv = qv % kSlots;
@@ -453,17 +496,22 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(p_ready);
+        if (lead && n < 40) fa_trace(13 + 6 * n);       // P handed over
         alpha_prev = alpha;
       }
-      // the last tile's O_t, then normalise and store this row: 128 dims = 256 contiguous bytes
+      // the pair's row sum, the last tile's O_t, then normalise and store 64 dims = 128 contiguous bytes
       {
+        float* xl = xmax + (n & 1) * 256;   // the buffer the next tile would use: free until the barrier below
+        xl[half * 128 + m] = l_run;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float l_tot = l_run + xl[(half ^ 1) * 128 + m];
         mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
         tc_fence_after();
         const uint32_t o_addr = lane_addr + 256 + ((n - 1) & 1) * 128;
-        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-        __nv_bfloat16* dst = out + (int64_t)(w.row0 + r) * ldo + (kvh * G + g) * kHeadDim;
+        const float inv = l_tot > 0.f ? 1.f / l_tot : 0.f;
+        __nv_bfloat16* dst = out + (int64_t)(w.row0 + r) * ldo + (kvh * G + g) * kHeadDim + half * 64;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           uint32_t o[32];
           tmem_ld32(o_addr + c * 32, o);
           if (alive) {
@@ -481,6 +529,7 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
             }
           }
         }
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // xl is rewritten by the next item
       }
     }
     tc_fence_before();
@@ -509,6 +558,11 @@ int launch_fa(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16*
 }
 
 }  // namespace
+
+int attn_prefill_read_trace(unsigned long long* host256) {
+  B200_CUDA(cudaMemcpyFromSymbol(host256, g_fa_trace, 256 * sizeof(unsigned long long)));
+  return B200_OK;
+}
 
 int64_t paged_attn_prefill_plan_bytes(int T) { return (int64_t)(T + 1) * (int64_t)sizeof(PlanItem); }
 

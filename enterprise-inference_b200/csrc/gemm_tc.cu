@@ -39,6 +39,7 @@ constexpr int kTcThreads = 192;
 constexpr int kCounterBytes = 64 * 1024;  // slab tickets at the head of the workspace (16384 slabs x token tiles)
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
+constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 
 #ifndef B200_STAGES16
 #define B200_STAGES16 5
@@ -46,7 +47,12 @@ constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
 #ifndef B200_STAGES64
 #define B200_STAGES64 4
 #endif
-__host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? B200_STAGES16 : (N <= 32 ? 4 : (N <= 64 ? B200_STAGES64 : (N <= 128 ? 3 : 4))); }
+// N = 256 (prefill-sized token tiles): 2 stages of 48 KiB so that TWO CTAs share an SM (2 x 256 TMEM columns):
+// one CTA's epilogue then overlaps the other's main loop; 4 stages are in flight per SM as before.
+#ifndef B200_STAGES256
+#define B200_STAGES256 2
+#endif
+__host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? B200_STAGES16 : (N <= 32 ? 4 : (N <= 64 ? B200_STAGES64 : (N <= 128 ? 3 : B200_STAGES256))); }
 __host__ __device__ constexpr int stage_bytes(int N) { return kBlockM * kBlockK * 2 + N * kBlockK * 2; }
 __host__ __device__ constexpr int smem_bytes_for(int N) { return stages_for(N) * stage_bytes(N) + 1024 + 256; }
 
@@ -259,7 +265,12 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   int* ticket_slot = reinterpret_cast<int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_tile = blockIdx.x, split = blockIdx.y, tok_tile = blockIdx.z;
+  // Several token tiles (prefill): the token tile is the FAST index, so that the CTAs that share a weight slab
+  // run in the same wave (the slab comes from HBM once, then from L2; x stays in L2 throughout).
+  const int lin = blockIdx.x + gridDim.x * blockIdx.z;
+  const int m_tile = gridDim.z > 1 ? lin / (int)gridDim.z : (int)blockIdx.x, split = blockIdx.y;
+  const int tok_tile = gridDim.z > 1 ? lin % (int)gridDim.z : 0;
+  const uint64_t w_policy = gridDim.z > 1 ? kEvictNormal : kEvictFirst;   // a slab read once is evicted first
   if (threadIdx.x == 0) tc_trace(p, 0);   // CTA start
   // K range of this split (balanced: the first `rem` splits get one more block)
   const int base = p.n_kblocks / p.splits, rem = p.n_kblocks % p.splits;
@@ -293,7 +304,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       // weights first: they do not depend on the producer of x
       for (int i = 0; i < pre; ++i) {
         mbar_expect_tx(&full[i], kStageBytes);
-        tma_load_2d(smem + i * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[i], kEvictFirst);
+        tma_load_2d(smem + i * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[i], w_policy);
       }
       tc_trace(p, 1);   // W of the first stages requested
       // While the previous kernel drains (its epilogue, then the small kernels that produce x), HBM would
@@ -309,7 +320,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         const int st = i % S;
         mbar_wait(&empty[st], ((i / S) - 1) & 1);
         mbar_expect_tx(&full[st], kStageBytes);
-        tma_load_2d(smem + st * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[st], kEvictFirst);
+        tma_load_2d(smem + st * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[st], w_policy);
         tma_load_2d(smem + st * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[st], kEvictLast);
       }
     } else {
@@ -355,6 +366,51 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // All MMAs have completed (tmem_full), so the pipeline stages are free: stage the fp32 tile
     // [token][128 rows] there for the direct case, or spill it to the split-K workspace.
     float* stg = reinterpret_cast<float*>(smem);
+    constexpr bool kChunked = S * kStageBytes < N * kBlockM * 4;   // N = 256 with 2 stages: 128 tokens at a time
+    if constexpr (kChunked) {
+      // (host side: this instantiation is only launched with splits == 1 and no cluster)
+      constexpr int kEpiTok = 128;
+      static_assert(kEpiTok * kBlockM * 4 <= S * kStageBytes, "staging area");
+      const int r4 = lane * 4;
+      float bb[4] = {0.f, 0.f, 0.f, 0.f};
+      if (p.bias) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (m_tile * kBlockM + r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[m_tile * kBlockM + r4 + e]);
+      }
+      for (int cb = 0; cb < N && tok0 + cb < p.T; cb += kEpiTok) {
+#pragma unroll
+        for (int c = 0; c < kEpiTok; c += 16) {
+          uint32_t r[16];
+          if (nkb > 0) {
+            tmem_ld16(taddr + cb + c, r);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) r[j] = 0u;
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) stg[(c + j) * kBlockM + srow] = __uint_as_float(r[j]);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int tmax = min(kEpiTok, p.T - tok0 - cb);
+        if (MODE == kRopeKv) {
+          for (int t = wq + 4 * lane; t < tmax; t += 128) {
+            const char* row = reinterpret_cast<const char*>(p.cos_sin + (int64_t)p.positions[tok0 + cb + t] * kHeadDim);
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(row));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(row + 128));
+          }
+        }
+        for (int t = wq; t < tmax; t += 16) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int tt = t + 4 * u;
+            if (tt < tmax)   // warp-uniform: the shuffles inside finalize4 stay convergent
+              finalize4<MODE>(p, m_tile, lane, tok0 + cb + tt, *reinterpret_cast<const float4*>(stg + tt * kBlockM + r4), bb);
+          }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // the staging area is reused by the next 128 tokens
+      }
+    } else {
 #pragma unroll
     for (int c = 0; c < N; c += 16) {
       uint32_t r[16];
@@ -443,6 +499,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       if (p.splits > 1 && warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
     }
+    }   // !kChunked
     // This CTA is done streaming: pull (a prefix of) the NEXT linear's weights towards L2 so that HBM
     // keeps working through this kernel's tail and the small kernels that follow (fire and forget).
     if (p.pf_bytes > 0) {
@@ -660,6 +717,12 @@ int launch_tc3(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, 
 template <int N, int MODE>
 int launch_tc2(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
   if (pl.deep) return launch_tc3<N, MODE, deep_stages_for(N)>(mw, mx, p, pl, s);
+  if constexpr (N == 256) {
+    // the 2-stage kernel (two CTAs per SM, chunked epilogue) has no room for a whole fp32 tile: split-K
+    // launches of a single token tile keep 4 stages
+    static const int two_env = getenv("B200_TC_N256_STAGES") ? atoi(getenv("B200_TC_N256_STAGES")) : 2;
+    if (pl.splits > 1 || p.cluster || two_env == 4) return launch_tc3<N, MODE, 4>(mw, mx, p, pl, s);
+  }
   return launch_tc3<N, MODE, stages_for(N)>(mw, mx, p, pl, s);
 }
 
