@@ -218,6 +218,7 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
   uint64_t* q_ready = p_ready + 1;                // Q of the current item is staged (32 arrivals)
   uint64_t* q_free = q_ready + 1;                 // the S MMAs of the current item no longer read Q
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_free + 1);
+  int* pv_fresh = reinterpret_cast<int*>(tmem_slot + 1);   // 1: P.V of this tile starts a new O_t, 0: accumulates
   float* xmax = reinterpret_cast<float*>(kv_full + 16);   // [2 (tile parity)][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -326,13 +327,14 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
           mbar_wait(&kv_full[sv], (qv / kSlots) & 1);
           mbar_wait(p_ready, n & 1);
           tc_fence_after();
+          const bool fresh = *reinterpret_cast<volatile int*>(pv_fresh) != 0;   // written before the P hand-over
           const uint32_t v_addr = smem_u32(kv + sv * kTileBytes);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {   // 16 tokens per step
             const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
             const uint64_t db = make_desc(v_addr + j * 2048, kHalfBytes, 1024);   // MN-major: two 8-token groups
-            tc_mma(tmem_base + 256 + (n & 1) * 128, make_desc(ph_addr + ao, 16, 1024), db, idesc_pv, j ? 1u : 0u);
-            tc_mma(tmem_base + 256 + (n & 1) * 128, make_desc(pl_addr + ao, 16, 1024), db, idesc_pv, 1u);
+            tc_mma(tmem_base + 256, make_desc(ph_addr + ao, 16, 1024), db, idesc_pv, (j || !fresh) ? 1u : 0u);
+            tc_mma(tmem_base + 256, make_desc(pl_addr + ao, 16, 1024), db, idesc_pv, 1u);
           }
           tc_commit(&kv_free[sv]);
           tc_commit(&o_full[n & 1]);
@@ -365,14 +367,17 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
   } else {
     // ===== softmax / output: 256 threads; a PAIR of threads (warps w and w + 4, same TMEM lane) owns query
     // row m: thread `half` takes tokens [64 half, 64 half + 64) of S/P and head dims [64 half, +64) of O.
-    // Two warps per scheduler hide each other's latencies; the pair meets once per tile to combine its
-    // two partial row maxima (shared memory + one 256-thread barrier, double buffered by tile parity). =====
+    // TMEM reads are the scarce resource (64 B/clk: a full 128 x 128 fp32 tile costs 1024 cycles), so S is
+    // read ONCE per tile (kept in registers between the max and the exp) and O_t is NOT read per tile: the
+    // P.V products accumulate in TMEM for as long as every row's reference max m_used is good enough
+    // (tile max <= m_used + 8 in the log2 domain, i.e. p <= 256: exact, only the scaling is stale); a tile
+    // where some row jumps further folds O_t into the registers, rescales and starts a new O_t. =====
     const int half = (warp - 2) >> 2;
     const int quad = warp & 3;
     const int m = quad * 32 + lane;
     const int r = m / G, g = m % G;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 64);
-    const float sc2 = scale * 1.4426950408889634f;   // scores in the log2 domain: p = exp2(s * sc2 - m2)
+    const float sc2 = scale * 1.4426950408889634f;   // scores in the log2 domain: p = exp2(s * sc2 - m_used)
     const bool lead = m == 0 && half == 0;
     if (lead) fa_trace(0);
     int n = 0;
@@ -384,7 +389,7 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
       if (nt == 0) continue;
       const bool alive = r < w.nrows;
       const int ctx_m = alive ? ctx_lens[w.row0 + r] : 0;
-      float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;
+      float m_used = -INFINITY, l_run = 0.f;
       float acc[64];
 #pragma unroll
       for (int d = 0; d < 64; ++d) acc[d] = 0.f;
@@ -400,75 +405,91 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
         if (lead && n < 40) fa_trace(9 + 6 * n);        // S landed
         tc_fence_after();
         const uint32_t s_addr = lane_addr + (n & 1) * 128;
-        // pass 1: row max over this thread's columns, then over the pair
-        float mx = -INFINITY;
+        // S row (this thread's 64 columns), masked columns = -inf
+        float sv[64];
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           if (c * 32 < n_live_w) {
-            uint32_t s[32];
-            tmem_ld32(s_addr + c * 32, s);
+            uint32_t t32[32];
+            tmem_ld32(s_addr + c * 32, t32);
             if (full) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(s[j]));
+              for (int j = 0; j < 32; ++j) sv[c * 32 + j] = __uint_as_float(t32[j]);
             } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (c * 32 + j < n_live) mx = fmaxf(mx, __uint_as_float(s[j]));
+              for (int j = 0; j < 32; ++j) sv[c * 32 + j] = (c * 32 + j < n_live) ? __uint_as_float(t32[j]) : -INFINITY;
             }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) sv[c * 32 + j] = -INFINITY;
           }
         }
+        float mx = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 64; ++j) mx = fmaxf(mx, sv[j]);
+        // the pair's row max through shared memory; the same barrier ORs "some row must rescale"
         float* xm = xmax + (n & 1) * 256;
         xm[half * 128 + m] = mx;
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const int jump = (i == 0) || (mx * sc2 > m_used + 8.f);
+        int any_jump;
+        asm volatile(
+            "{\n"
+            ".reg .pred pi, po;\n"
+            "setp.ne.b32 pi, %1, 0;\n"
+            "bar.red.or.pred po, 1, 256, pi;\n"
+            "selp.b32 %0, 1, 0, po;\n"
+            "}\n"
+            : "=r"(any_jump)
+            : "r"(jump)
+            : "memory");
         mx = fmaxf(mx, xm[(half ^ 1) * 128 + m]);
-        const float m_new = fmaxf(m_run, mx * sc2);
-        const bool seen = m_new > -INFINITY;
-        const float alpha = seen ? fast_exp2(m_run - m_new) : 1.f;   // exp2(-inf) = 0 on the row's first live tile
-        m_run = m_new;
-        // fold the previous tile's O_t into the running output; this also proves that the P.V MMAs of the
-        // previous tile have finished reading P, which pass 2 overwrites
-        if (lead && n < 40) fa_trace(10 + 6 * n);       // pass 1 + pair exchange done
+        if (lead && n < 40) fa_trace(10 + 6 * n);       // max + pair exchange done
+        // the previous tile's P.V MMAs must have finished reading P before it is overwritten below
         if (i > 0) {
           mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
-          if (lead && n < 40) fa_trace(11 + 6 * n);     // previous P.V complete
           tc_fence_after();
-          const uint32_t o_addr = lane_addr + 256 + ((n - 1) & 1) * 128;
+        }
+        if (lead && n < 40) fa_trace(11 + 6 * n);       // previous P.V complete
+        if (any_jump) {   // CTA-uniform
+          // fold what has accumulated in TMEM since the last fold (same reference max as acc), then move
+          // every row to its true running max
+          if (i > 0) {
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            uint32_t o[32];
-            tmem_ld32(o_addr + c * 32, o);
+            for (int c = 0; c < 2; ++c) {
+              uint32_t o[32];
+              tmem_ld32(lane_addr + 256 + c * 32, o);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) acc[c * 32 + j] = acc[c * 32 + j] * alpha_prev + __uint_as_float(o[j]);
+              for (int j = 0; j < 32; ++j) acc[c * 32 + j] += __uint_as_float(o[j]);
+            }
           }
+          const float m_new = fmaxf(m_used, mx * sc2);
+          const float alpha = (m_new > -INFINITY && m_used > -INFINITY) ? fast_exp2(m_used - m_new) : 1.f;
+          if (i > 0) {
+#pragma unroll
+            for (int d = 0; d < 64; ++d) acc[d] *= alpha;
+          }
+          l_run *= alpha;
+          m_used = m_new;
+          if (lead) *reinterpret_cast<volatile int*>(pv_fresh) = 1;
+        } else if (lead) {
+          *reinterpret_cast<volatile int*>(pv_fresh) = 0;
         }
         if (lead && n < 40) fa_trace(12 + 6 * n);       // fold done
-        // pass 2: P = exp2(s * sc2 - m) as hi + lo bf16, this thread's 64 columns of row m of the A operand
+        // P = exp2(s * sc2 - m_used) as hi + lo bf16 (hi = p truncated to bf16, lo = the exact rest rounded):
+        // this thread's 64 columns of row m of the A operand of P.V
+        const float mref = m_used > -INFINITY ? m_used : 0.f;   // a row that has seen nothing: every s is -inf
         float lsum = 0.f;
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t hi[16], lo[16];
-          if (c * 32 < n_live_w) {
-            uint32_t s[32];
-            tmem_ld32(s_addr + c * 32, s);
 #pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              float p0 = fast_exp2(__uint_as_float(s[j]) * sc2 - m_new);
-              float p1 = fast_exp2(__uint_as_float(s[j + 1]) * sc2 - m_new);
-              if (!full) {
-                p0 = (c * 32 + j < n_live) ? p0 : 0.f;
-                p1 = (c * 32 + j + 1 < n_live) ? p1 : 0.f;
-              }
-              lsum += p0 + p1;
-              // hi = p rounded to bf16 (nearest even, integer arithmetic: conversions share the MUFU pipe)
-              const uint32_t b0 = __float_as_uint(p0), b1 = __float_as_uint(p1);
-              const uint32_t h0 = (b0 + 0x7fffu + ((b0 >> 16) & 1u)) & 0xffff0000u;
-              const uint32_t h1 = (b1 + 0x7fffu + ((b1 >> 16) & 1u)) & 0xffff0000u;
-              hi[j >> 1] = __byte_perm(h0, h1, 0x7632);
-              lo[j >> 1] = pack_bf16(p0 - __uint_as_float(h0), p1 - __uint_as_float(h1));
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) hi[j] = lo[j] = 0u;
+          for (int j = 0; j < 32; j += 2) {
+            const float p0 = fast_exp2(sv[c * 32 + j] * sc2 - mref);       // exp2(-inf) = 0 for masked columns
+            const float p1 = fast_exp2(sv[c * 32 + j + 1] * sc2 - mref);
+            lsum += p0 + p1;
+            const uint32_t h0 = __float_as_uint(p0) & 0xffff0000u, h1 = __float_as_uint(p1) & 0xffff0000u;
+            hi[j >> 1] = __byte_perm(h0, h1, 0x7632);
+            lo[j >> 1] = pack_bf16(p0 - __uint_as_float(h0), p1 - __uint_as_float(h1));
           }
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
@@ -477,14 +498,14 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
             *reinterpret_cast<uint4*>(p_lo + off) = make_uint4(lo[4 * k], lo[4 * k + 1], lo[4 * k + 2], lo[4 * k + 3]);
           }
         }
-        l_run = l_run * alpha + lsum;
+        l_run += lsum;
         if (n_valid < kTileTok && half == 0) {
           // partial last tile: V rows past the context may hold anything (0 * NaN = NaN on the tensor core):
           // wait for the tile, then zero this thread's token row if it is past the end
-          const int qv = 2 * n + 1, sv = qv % kSlots;
-          mbar_wait(&kv_full[sv], (qv / kSlots) & 1);
+          const int qv = 2 * n + 1, sv_slot = qv % kSlots;
+          mbar_wait(&kv_full[sv_slot], (qv / kSlots) & 1);
           if (m >= n_valid) {
-            unsigned char* vb = kv + sv * kTileBytes;
+            unsigned char* vb = kv + sv_slot * kTileBytes;
 #pragma unroll
             for (int h2 = 0; h2 < 2; ++h2)
 #pragma unroll
@@ -497,9 +518,8 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
         __syncwarp();
         if (lane == 0) mbar_arrive(p_ready);
         if (lead && n < 40) fa_trace(13 + 6 * n);       // P handed over
-        alpha_prev = alpha;
       }
-      // the pair's row sum, the last tile's O_t, then normalise and store 64 dims = 128 contiguous bytes
+      // the pair's row sum, what is still in TMEM, then normalise and store 64 dims = 128 contiguous bytes
       {
         float* xl = xmax + (n & 1) * 256;   // the buffer the next tile would use: free until the barrier below
         xl[half * 128 + m] = l_run;
@@ -507,13 +527,12 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
         const float l_tot = l_run + xl[(half ^ 1) * 128 + m];
         mbar_wait(&o_full[(n - 1) & 1], ((n - 1) >> 1) & 1);
         tc_fence_after();
-        const uint32_t o_addr = lane_addr + 256 + ((n - 1) & 1) * 128;
         const float inv = l_tot > 0.f ? 1.f / l_tot : 0.f;
         __nv_bfloat16* dst = out + (int64_t)(w.row0 + r) * ldo + (kvh * G + g) * kHeadDim + half * 64;
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t o[32];
-          tmem_ld32(o_addr + c * 32, o);
+          tmem_ld32(lane_addr + 256 + c * 32, o);
           if (alive) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -521,15 +540,16 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 const int d = c * 32 + k * 8 + e * 2;
-                const float v0 = (acc[d] * alpha_prev + __uint_as_float(o[k * 8 + e * 2])) * inv;
-                const float v1 = (acc[d + 1] * alpha_prev + __uint_as_float(o[k * 8 + e * 2 + 1])) * inv;
+                const float v0 = (acc[d] + __uint_as_float(o[k * 8 + e * 2])) * inv;
+                const float v1 = (acc[d + 1] + __uint_as_float(o[k * 8 + e * 2 + 1])) * inv;
                 pk[e] = pack_bf16(v0, v1);
               }
               *reinterpret_cast<uint4*>(dst + c * 32 + k * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             }
           }
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // xl is rewritten by the next item
+        tc_fence_before();
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // xl is rewritten by the next item; O_t has been read by all
       }
     }
     tc_fence_before();
