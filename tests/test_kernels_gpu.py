@@ -372,6 +372,52 @@ def test_paged_attention_prefill_rows_packed(lib, abi, hq, hkv):
     ulp_close(outs[0], outs[1], max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
 
 
+@pytest.mark.parametrize("hq,hkv", [(8, 2), (5, 1), (8, 1)])
+def test_prefill_attention_chunk_with_max_jumps(lib, abi, hq, hkv):
+    """attn_prefill.cu on a 200-row chunk of one sequence that starts at position 600 (items of 128/G rows,
+    ragged last item, contexts crossing tile boundaries), between two decode rows.  The keys of tokens
+    >= 384 are 6x larger, so row maxima jump by far more than 2^8 in the middle of a pass: the lazy
+    rescale (fold O_t, rescale, fresh accumulation) must give the oracle's result, not just the
+    common no-jump path."""
+    g = torch.Generator().manual_seed(7 * hq + hkv)
+    bs, start, nrows = 128, 600, 200
+    seq_ctx = [90, start + nrows, 513]
+    rows = [(0, 90)] + [(1, start + i + 1) for i in range(nrows)] + [(2, 513)]
+    T = len(rows)
+    K = [torch.randn(n, hkv, 128, generator=g) for n in seq_ctx]
+    K[1][384:] *= 6.0
+    K = [k.to(BF) for k in K]
+    V = [torch.randn(n, hkv, 128, generator=g).to(BF) for n in seq_ctx]
+    nblk = [(n + bs - 1) // bs for n in seq_ctx]
+    total = sum(nblk) + 1
+    perm = iter(torch.randperm(total, generator=g).tolist())
+    kc = torch.full((total, hkv, bs, 128), float("nan"), dtype=BF)
+    vc = torch.full_like(kc, float("nan"))
+    bt = torch.zeros(len(seq_ctx), max(nblk), dtype=torch.int32)
+    for sq, n in enumerate(seq_ctx):
+        for j in range(nblk[sq]):
+            b = next(perm)
+            bt[sq, j] = b
+            m = min(bs, n - j * bs)
+            kc[b, :, :m] = K[sq][j * bs:j * bs + m].permute(1, 0, 2)
+            vc[b, :, :m] = V[sq][j * bs:j * bs + m].permute(1, 0, 2)
+    q = torch.randn(T, hq, 128, generator=g).to(BF)
+    r2s = torch.tensor([r[0] for r in rows], dtype=torch.int32)
+    cl = torch.tensor([r[1] for r in rows], dtype=torch.int32)
+    max_ctx = int(cl.max())
+    wsb = lib.b200_paged_attn_workspace_bytes(T, hq, max_ctx, bs)
+    ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
+    out = torch.full((T, hq * 128), float("nan"), dtype=BF, device="cuda")
+    sync_check(abi, lib.b200_paged_attn_prefill(dev(q.reshape(T, hq * 128)).data_ptr(), hq * 128, dev(kc).data_ptr(),
+                                                dev(vc).data_ptr(), dev(bt).data_ptr(), bt.shape[1], dev(r2s).data_ptr(),
+                                                dev(cl).data_ptr(), out.data_ptr(), hq * 128, T, hq, hkv, bs, max_ctx,
+                                                128 ** -0.5, ws.data_ptr(), wsb, None))
+    got = out.cpu().view(T, hq, 128)
+    want = torch.stack([O.attend(q[t], K[sq], V[sq], n, 128 ** -0.5) for t, (sq, n) in enumerate(rows)])
+    assert torch.isfinite(got.float()).all()
+    ulp_close(got, want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
+
+
 def test_paged_attention_split_invariance_long_context(lib, abi):
     """Config-3 scale (ctx 32768, G=4): the split-KV result must not depend on the split plan —
     compare the plan for max_ctx=32768 with a larger hint (different split count) and the oracle."""
