@@ -686,6 +686,13 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   // then request the cache tiles older than that token before the QKV kernel has completed.
   int attn_pack = a.row_to_seq && (a.n_seqs > 0 ? (T >= 4 * a.n_seqs && T >= 32) : T >= 512);
   if (!attn_pack && (a.row_to_seq == nullptr || a.n_seqs == T)) attn_pack = -1;
+  if (attn_pack > 0) {
+    // the prefill attention's row plan depends on the step, not on the layer: build it once
+    const int built = paged_attn_prefill_plan_step(a.row_to_seq, a.ctx_lens, T, c->hq, c->hkv, m.block_size, c->attn_ws,
+                                                   c->attn_ws_bytes, s);
+    if (built < 0) return built;
+    if (built == 1) attn_pack = 2;
+  }
   STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
   for (int l = 0; l < m.n_layers; ++l) {
     const LayerW& L = c->layers[l];

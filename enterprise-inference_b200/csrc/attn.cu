@@ -329,10 +329,12 @@ int launch_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, co
 bool paged_attn_tc_supported(int hq, int hkv, int block_size);
 int64_t paged_attn_prefill_plan_bytes(int T);
 bool paged_attn_prefill_fa_supported(int hq, int hkv, int block_size);
+int paged_attn_prefill_plan(const int32_t* row_to_seq, const int32_t* ctx_lens, int T, int hq, int hkv, void* ws,
+                            int64_t ws_bytes, cudaStream_t s);
 int paged_attn_prefill_fa(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                           const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                           __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, float scale, void* ws,
-                          int64_t ws_bytes, cudaStream_t s);
+                          int64_t ws_bytes, bool plan_ready, cudaStream_t s);
 int paged_attn_tc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
@@ -437,12 +439,25 @@ static int paged_attn_cc(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat1
 
 
 
-// pack > 0: consecutive query rows of one sequence (a prefill chunk) share one pass over the K/V cache;
+// pack > 0: consecutive query rows of one sequence (a prefill chunk) share one pass over the K/V cache
+//           (pack == 2: the caller already built the row plan in `ws` with paged_attn_prefill_plan_step);
 // pack < 0: decode-only step (each row its own sequence, only position ctx-1 is new): early cache requests
 int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx, float scale,
                   void* ws, int64_t ws_bytes, int pack, cudaStream_t s);
+
+// Once per step, before the layer loop: builds the prefill kernel's row plan in `ws` when that kernel will
+// serve the step (pack > 0).  Returns < 0 on error, 1 if the plan was built (pass pack = 2 to the layers), 0 if not.
+int paged_attn_prefill_plan_step(const int32_t* row_to_seq, const int32_t* ctx_lens, int T, int hq, int hkv, int block_size,
+                                 void* ws, int64_t ws_bytes, cudaStream_t s) {
+  static const int fa_env = getenv("B200_ATTN_FA") ? atoi(getenv("B200_ATTN_FA")) : 1;
+  if (!(fa_env && use_tc_attn(hq, hkv, block_size) && paged_attn_prefill_fa_supported(hq, hkv, block_size) && ws &&
+        ws_bytes >= paged_attn_prefill_plan_bytes(T)))
+    return 0;
+  const int rc = paged_attn_prefill_plan(row_to_seq, ctx_lens, T, hq, hkv, ws, ws_bytes, s);
+  return rc ? rc : 1;
+}
 
 int paged_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
@@ -462,7 +477,7 @@ int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
   if (pack > 0 && fa_env && use_tc_attn(hq, hkv, block_size) && paged_attn_prefill_fa_supported(hq, hkv, block_size) &&
       ws && ws_bytes >= paged_attn_prefill_plan_bytes(T))
     return paged_attn_prefill_fa(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv,
-                                 block_size, scale, ws, ws_bytes, s);
+                                 block_size, scale, ws, ws_bytes, /*plan_ready=*/pack == 2, s);
   if (use_tc_attn(hq, hkv, block_size))
     return paged_attn_tc(q, ldq, kc, vc, block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, T, hq, hkv, block_size,
                          max_ctx, scale, ws, ws_bytes, pack, s);

@@ -156,7 +156,8 @@ __global__ void __launch_bounds__(256) attn_prefill_plan_kernel(const int32_t* _
   const int lane = threadIdx.x & 31;
   if (threadIdx.x < 32) {
     int count = 0, seg_carry = 0;
-    for (int base = 0; base < n_rows; base += 32) {
+#pragma unroll 4
+    for (int base = 0; base < n_rows; base += 32) {   // the loads do not depend on the carried state: 4 rounds in flight
       const int r = base + lane;
       const bool valid = r < n_rows;
       const int seq = valid ? (row_to_seq ? row_to_seq[r] : r) : -1;
@@ -593,10 +594,24 @@ bool paged_attn_prefill_fa_supported(int hq, int hkv, int block_size) {
 }
 
 // Same contract as paged_attn (attn.cu); `ws` holds the plan (paged_attn_prefill_plan_bytes(T)).
+// The plan depends on the step's rows only, not on the layer: a caller that runs many layers over the same
+// rows builds it once (this function) and passes plan_ready = true to paged_attn_prefill_fa.
+int paged_attn_prefill_plan(const int32_t* row_to_seq, const int32_t* ctx_lens, int T, int hq, int hkv, void* ws,
+                            int64_t ws_bytes, cudaStream_t s) {
+  B200_REQUIRE(hkv > 0 && hq % hkv == 0, B200_ERR_INVALID, "attn_prefill: hq=%d not a multiple of hkv=%d", hq, hkv);
+  if (T == 0) return B200_OK;
+  B200_REQUIRE(ws && ws_bytes >= paged_attn_prefill_plan_bytes(T), B200_ERR_INVALID,
+               "attn_prefill: workspace too small (%lld < %lld)", (long long)ws_bytes,
+               (long long)paged_attn_prefill_plan_bytes(T));
+  B200_CUDA(launch(attn_prefill_plan_kernel, dim3(1), dim3(256), (size_t)0, s, row_to_seq, ctx_lens, T, 128 / (hq / hkv),
+                   static_cast<PlanItem*>(ws)));
+  return B200_OK;
+}
+
 int paged_attn_prefill_fa(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, const __nv_bfloat16* vc,
                           const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                           __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, float scale, void* ws,
-                          int64_t ws_bytes, cudaStream_t s) {
+                          int64_t ws_bytes, bool plan_ready, cudaStream_t s) {
   B200_REQUIRE(paged_attn_prefill_fa_supported(hq, hkv, block_size), B200_ERR_UNSUPPORTED, "attn_prefill: unsupported shape");
   B200_REQUIRE(ldq % 8 == 0 && ldo % 8 == 0, B200_ERR_INVALID, "attn_prefill: ldq/ldo must be multiples of 8");
   B200_REQUIRE(((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(out)) & 15) == 0, B200_ERR_INVALID,
@@ -608,7 +623,10 @@ int paged_attn_prefill_fa(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat
                (long long)paged_attn_prefill_plan_bytes(T));
   const int G = hq / hkv;
   PlanItem* plan = static_cast<PlanItem*>(ws);
-  B200_CUDA(launch(attn_prefill_plan_kernel, dim3(1), dim3(256), (size_t)0, s, row_to_seq, ctx_lens, T, 128 / G, plan));
+  if (!plan_ready) {
+    const int rc0 = paged_attn_prefill_plan(row_to_seq, ctx_lens, T, hq, hkv, ws, ws_bytes, s);
+    if (rc0) return rc0;
+  }
   CUtensorMap mk, mv;
   const uint64_t rows = 1ull << 31;   // upper limit for TMA's bounds logic; rows touched come from the block table
   int rc = get_tensor_map_2d(kc, rows, kHeadDim, kHeadDim, kTileTok, &mk);

@@ -173,6 +173,9 @@ int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
                   const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                   __nv_bfloat16* out, int64_t ldo, int T, int hq, int hkv, int block_size, int max_ctx,
                   float scale, void* ws, int64_t ws_bytes, int pack, cudaStream_t s);
+// once per step when pack > 0: builds the prefill attention's row plan in ws; 1 = built (use pack = 2), 0 = not used
+int paged_attn_prefill_plan_step(const int32_t* row_to_seq, const int32_t* ctx_lens, int T, int hq, int hkv, int block_size,
+                                 void* ws, int64_t ws_bytes, cudaStream_t s);
 int advance_rows(int32_t* ids, int32_t* positions, int32_t* slots, int32_t* ctx_lens, const int32_t* block_table,
                  int bt_stride, const int32_t* row_to_seq, const int32_t* sampled, int n, int block_size,
                  cudaStream_t s);
