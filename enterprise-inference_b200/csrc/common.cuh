@@ -58,6 +58,12 @@ __device__ __forceinline__ float warp_sum(float v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// (a8, R5) bf16(silu(g)) for a bf16-valued g: accurate expf, the division as a correctly rounded reciprocal
+// times g (<= 1 fp32 ulp from g / d, i.e. the bf16 result differs once in ~2^15 elements; an IEEE division
+// costs three times as much and this sits in the gate_up epilogue).  One definition for the fused epilogue
+// and the stand-alone kernel: they stay bit-identical.
+__device__ __forceinline__ float silu_to_bf16(float g) { return round_bf16(g * __frcp_rn(1.0f + expf(-g))); }
+
 // Warp max of floats in ONE instruction (redux.sync on an order-preserving integer image of the float)
 // instead of five shuffle + max rounds.  -inf maps through unchanged; NaNs do not occur where it is used
 // (masked scores are -inf before the reduction).

@@ -144,7 +144,6 @@ rope_kv_kernel(__nv_bfloat16* qkv, const int32_t* __restrict__ positions, const 
 // ---------------------------------------------------------------------------------------
 // (a8) SiLU*mul: a = bf16(bf16(silu(g)) * u)             [V22] activation.py:137-141
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ float silu_bf16(float g) { return round_bf16(g / (1.0f + expf(-g))); }
 
 __global__ void __launch_bounds__(256)
 silu_mul_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ out, int inter, int64_t total_chunks) {
@@ -161,7 +160,7 @@ silu_mul_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict_
     uint32_t o[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-      o[j] = pack_bf16(silu_bf16(bf16lo(gw[j])) * bf16lo(uw[j]), silu_bf16(bf16hi(gw[j])) * bf16hi(uw[j]));
+      o[j] = pack_bf16(silu_to_bf16(bf16lo(gw[j])) * bf16lo(uw[j]), silu_to_bf16(bf16hi(gw[j])) * bf16hi(uw[j]));
     *reinterpret_cast<uint4*>(out + t * inter + c * 8) = make_uint4(o[0], o[1], o[2], o[3]);
   }
 }

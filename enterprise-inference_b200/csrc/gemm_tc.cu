@@ -176,7 +176,6 @@ __device__ __forceinline__ void tc_trace(const TcParams& p, int slot) {
 //            and k heads, q rows to y, k/v rows straight into the paged cache at slots[t]
 enum { kPlain = 0, kSiluMul = 1, kRopeKv = 2 };
 
-__device__ __forceinline__ float silu_bf16_dev(float g) { return round_bf16(g / (1.0f + expf(-g))); }
 
 // One thread finalises 4 consecutive slab rows (r4..r4+3, lane = r4/4) of one token.
 template <int MODE>
@@ -204,7 +203,7 @@ __device__ __forceinline__ void finalize4(const TcParams& p, int m_tile, int lan
     const float g0 = lo ? v[0] : x[2], g1 = lo ? v[1] : x[3];
     const float u0 = lo ? x[0] : v[2], u1 = lo ? x[1] : v[3];
     const int f = m_tile * 64 + (lane & 15) * 4 + (lo ? 0 : 2);                  // output feature
-    const float o0 = silu_bf16_dev(g0) * u0, o1 = silu_bf16_dev(g1) * u1;
+    const float o0 = silu_to_bf16(g0) * u0, o1 = silu_to_bf16(g1) * u1;
     __nv_bfloat16* dst = p.y + (int64_t)tok * p.ldy + f;
     if ((p.ldy % 2 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 3) == 0)) {
       *reinterpret_cast<uint32_t*>(dst) = pack_bf16(o0, o1);
