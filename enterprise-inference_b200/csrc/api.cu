@@ -161,6 +161,8 @@ struct b200_ctx {
   float* d_max;
   float* d_pairs;     // [rows][2] local (max, idx)
   float* d_gathered;  // [world][rows][2]
+  void* d_sample;     // sampling parameters of the rows, packed (b200_ctx_sample_last)
+  __nv_bfloat16* logits_full;  // TP only: [world][rows][vocab_local], gathered for the sampler
   // graphs
   bool graphs = true;
   std::unordered_map<GraphKey, cudaGraphExec_t, GraphKeyHash> graph_cache;
@@ -267,6 +269,8 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
       {(void**)&c->d_max, R * 4},
       {(void**)&c->d_pairs, R * 8},
       {(void**)&c->d_gathered, R * 8 * W},
+      {(void**)&c->d_sample, R * 40},
+      {(void**)&c->logits_full, W > 1 ? R * (int64_t)c->vocab_local * 2 * W : 16},
   };
   int64_t total = 0;
   for (auto& it : items) total += align_up(std::max<int64_t>(it.bytes, 16), 1024);
@@ -875,6 +879,50 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   }
   launch_opts().pdl = pdl_prev;
   B200_CUDA(cudaGraphLaunch(it->second, s));
+  return B200_OK;
+}
+
+// (a10, widened) sampling ---------------------------------------------------------------------------------
+extern "C" int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const float* temperature,
+                           const int32_t* top_k, const float* top_p, const uint64_t* seeds, const uint64_t* draws,
+                           int32_t* out_ids, void* stream) {
+  B200_REQUIRE(n_rows >= 0 && vocab > 0 && ld >= vocab, B200_ERR_INVALID, "sample: bad sizes (rows=%d vocab=%d ld=%lld)",
+               n_rows, vocab, (long long)ld);
+  return sample_rows((const __nv_bfloat16*)logits, ld, n_rows, vocab, vocab, 0, temperature, top_k, top_p, seeds, draws,
+                     out_ids, (cudaStream_t)stream);
+}
+
+// The rows are the logit rows of the LAST step of this ctx (its logits are still in the ctx's buffer).
+// host_params: n_rows x {float temperature; int32 top_k; float top_p; uint32 pad; uint64 seed; uint64 draw} as
+// five arrays back to back: temperature[n] | top_k[n] | top_p[n] | pad[n] | seed[n] | draw[n]  (32 n bytes).
+extern "C" int b200_ctx_sample_last(b200_ctx* c, int32_t n_rows, const void* host_params, int32_t* host_out_ids,
+                                    void* stream) {
+  B200_REQUIRE(c && host_params && host_out_ids, B200_ERR_INVALID, "sample_last: null argument");
+  B200_REQUIRE(n_rows > 0 && n_rows <= c->max_logit_rows, B200_ERR_INVALID, "sample_last: n_rows=%d outside (0,%d]", n_rows,
+               c->max_logit_rows);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t n = n_rows;
+  B200_CUDA(cudaMemcpyAsync(c->d_sample, host_params, (size_t)n * 32, cudaMemcpyHostToDevice, s));
+  const char* base = static_cast<const char*>(c->d_sample);
+  const float* temperature = reinterpret_cast<const float*>(base);
+  const int32_t* top_k = reinterpret_cast<const int32_t*>(base + 4 * n);
+  const float* top_p = reinterpret_cast<const float*>(base + 8 * n);
+  const uint64_t* seeds = reinterpret_cast<const uint64_t*>(base + 16 * n);
+  const uint64_t* draws = reinterpret_cast<const uint64_t*>(base + 24 * n);
+  const int W = c->cfg.tp_world;
+  int rc;
+  if (W > 1) {
+    // vocab-parallel logits: gather the shards rank-major; every rank then draws the same token (the kernel
+    // is deterministic given the seed)
+    B200_NCCL(nccl().AllGather(c->logits, c->logits_full, (size_t)n * c->vocab_local, ncclBfloat16, c->comm, s));
+    rc = sample_rows(c->logits_full, c->vocab_local, n_rows, c->vocab_local * W, c->vocab_local, n * c->vocab_local,
+                     temperature, top_k, top_p, seeds, draws, c->d_tokens, s);
+  } else {
+    rc = sample_rows(c->logits, c->vocab_local, n_rows, c->vocab_local, c->vocab_local, 0, temperature, top_k, top_p, seeds,
+                     draws, c->d_tokens, s);
+  }
+  if (rc) return rc;
+  B200_CUDA(cudaMemcpyAsync(host_out_ids, c->d_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
   return B200_OK;
 }
 

@@ -9,6 +9,7 @@ Pure host logic: unit-tested on CPU with a fake runner.
 """
 from __future__ import annotations
 
+import os
 import time
 from collections import deque
 from dataclasses import dataclass, field
@@ -61,6 +62,12 @@ class Request:
     eos_token_ids: tuple = ()
     stop_token_ids: tuple = ()
     min_tokens: int = 0
+    # sampling (docs/api-spec.yaml: temperature, top_p, seed; top_k is vLLM's extension).  temperature 0 =
+    # greedy = the device's argmax; anything else goes through b200_ctx_sample_last after the step.
+    temperature: float = 0.0
+    top_k: int = 0
+    top_p: float = 1.0
+    seed: Optional[int] = None          # None: drawn once when the request is added
     arrival: float = field(default_factory=time.monotonic)
     # state
     output_ids: List[int] = field(default_factory=list)
@@ -252,6 +259,8 @@ class LLMEngine:
         self.steps = 0
 
     def add_request(self, req: Request) -> None:
+        if req.temperature > 0.0 and req.seed is None:
+            req.seed = int.from_bytes(os.urandom(8), "little")
         self.scheduler.add(req)
         self.requests[req.request_id] = req
 
@@ -279,7 +288,15 @@ class LLMEngine:
             self.runner.step(batch)
             sampled = []
         self.steps += 1
-        done = self.scheduler.commit(sched, list(sampled))
+        sampled = list(sampled)
+        if sampled and any(s.samples and s.req.temperature > 0.0 for s in sched):
+            # some rows do not want the argmax: one more kernel over the logits the step left on the device
+            # (greedy rows get their argmax back).  Draw number = tokens generated so far: a seed replays.
+            rows = [s.req for s in sched if s.samples]
+            sampled = list(self.runner.sample_last([r.temperature for r in rows], [r.top_k for r in rows],
+                                                   [r.top_p for r in rows], [r.seed or 0 for r in rows],
+                                                   [len(r.output_ids) for r in rows]))
+        done = self.scheduler.commit(sched, sampled)
         for r in done:
             self.requests.pop(r.request_id, None)
         return done

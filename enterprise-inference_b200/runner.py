@@ -96,6 +96,9 @@ class ModelRunner:
         self._h_out_np = self._h_out.numpy()
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
+        self.max_logit_rows = min(max_tokens, 512)
+        self._h_sample = torch.zeros(self.max_logit_rows * 32, dtype=torch.uint8).pin_memory()
+        self._h_sample_np = self._h_sample.numpy()
 
     # ---- weights ---------------------------------------------------------------------------
     def _set(self, layer: int, kind: int, t: torch.Tensor):
@@ -220,6 +223,33 @@ class ModelRunner:
             block_table.stride(0), _abi.ptr(row_to_seq), ctx_lens.data_ptr(), T, int(max_ctx),
             _abi.ptr(logit_rows), R, out_tokens.data_ptr(), _abi.ptr(out_logits), s))
         return out_tokens
+
+    def pack_sampling(self, temperature, top_k, top_p, seeds, draws) -> int:
+        """Per-row sampling parameters of the last step's logit rows into the pinned buffer
+        (layout of b200_ctx_sample_last); returns the row count."""
+        n = len(temperature)
+        if not 0 < n <= self.max_logit_rows:
+            raise ValueError(f"sample_last: {n} rows outside (0, {self.max_logit_rows}]")
+        a = self._h_sample_np
+        a[0:4 * n].view(np.float32)[:] = temperature
+        a[4 * n:8 * n].view(np.int32)[:] = top_k
+        a[8 * n:12 * n].view(np.float32)[:] = top_p
+        a[12 * n:16 * n] = 0
+        a[16 * n:24 * n].view(np.uint64)[:] = np.asarray(seeds, dtype=np.uint64)
+        a[24 * n:32 * n].view(np.uint64)[:] = np.asarray(draws, dtype=np.uint64)
+        return n
+
+    def sample_packed(self, n: int, sync: bool = True) -> np.ndarray:
+        _abi.check(self.lib.b200_ctx_sample_last(self.ctx, n, self._h_sample.data_ptr(), self._h_out.data_ptr(),
+                                                 self.stream.cuda_stream))
+        if sync:
+            self.stream.synchronize()
+        return self._h_out_np[:n]
+
+    def sample_last(self, temperature, top_k, top_p, seeds, draws, sync: bool = True) -> np.ndarray:
+        """Tokens for the logit rows of the LAST step under per-row (temperature, top_k, top_p, seed, draw);
+        temperature 0 rows return the step's greedy token.  The greedy hot path never calls this."""
+        return self.sample_packed(self.pack_sampling(temperature, top_k, top_p, seeds, draws), sync)
 
     def last_step_launches(self) -> int:
         return int(self.lib.b200_ctx_last_step_launches(self.ctx))

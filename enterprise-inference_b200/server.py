@@ -8,8 +8,10 @@ and templates/deployment.yaml:66-87.  HTTP surface: /root/reference/docs/api-spe
 /v1/completions, /v1/chat/completions; 422 on a bad body, additionalProperties: false), GET /health
 (values.yaml:135-141), GET /metrics with the vllm:* series the Grafana dashboard queries
 (observability/xeon-exporter/grafana-xeon-dashboard.json), GET /v1/models (docs/getting-started-example.md:79-81).
-Sampling on the device is greedy (the reference's clients send "temperature": 0); other sampling
-parameters are accepted and ignored.  /v1/embeddings is served by TEI in the reference, not here.
+"temperature": 0 (what the reference's clients send) is the device's argmax; temperature / top_p / top_k /
+seed sample on the device (csrc/sample.cu) with vLLM's semantics and defaults (the model's generation_config.json,
+else temperature 1); penalties, logit_bias, min_p, logprobs, n > 1 and guided decoding are accepted and ignored
+or rejected (n, best_of, beam search).  /v1/embeddings is served by TEI in the reference, not here.
 """
 from __future__ import annotations
 
@@ -129,9 +131,9 @@ class _Sampling(BaseModel):
     model_config = ConfigDict(extra="forbid")
     model: str
     max_tokens: Optional[int] = 16
-    temperature: Optional[float] = 0.0
-    top_p: Optional[float] = 1.0
-    top_k: Optional[int] = -1
+    temperature: Optional[float] = None      # None: the model's generation_config.json, else 1.0 (vLLM's default)
+    top_p: Optional[float] = None
+    top_k: Optional[int] = None
     min_p: Optional[float] = 0.0
     n: Optional[int] = 1
     best_of: Optional[int] = None
@@ -296,7 +298,8 @@ class EngineLoop:
 # ------------------------------------------------------------------------------------------------
 # app
 # ------------------------------------------------------------------------------------------------
-def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_len: int, tool_parser=None) -> FastAPI:
+def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_len: int, tool_parser=None,
+               default_sampling: Optional[Dict[str, Any]] = None) -> FastAPI:
     metrics = Metrics(served_model_name)
     loop_ = EngineLoop(engine, metrics)
 
@@ -344,9 +347,15 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
         if body.truncate_prompt_tokens:
             prompt_ids = prompt_ids[-body.truncate_prompt_tokens:]
         max_tokens = body.max_tokens if body.max_tokens is not None else max(max_model_len - len(prompt_ids), 1)
+        d = default_sampling or {}
+        temperature = body.temperature if body.temperature is not None else float(d.get("temperature", 1.0))
+        top_p = body.top_p if body.top_p is not None else float(d.get("top_p", 1.0))
+        top_k = body.top_k if body.top_k is not None else int(d.get("top_k", 0))
         return Request(request_id="cmpl-" + uuid.uuid4().hex, prompt_ids=prompt_ids, max_tokens=max_tokens,
                        ignore_eos=bool(body.ignore_eos), eos_token_ids=eos_ids,
-                       stop_token_ids=tuple(body.stop_token_ids or ()), min_tokens=body.min_tokens or 0)
+                       stop_token_ids=tuple(body.stop_token_ids or ()), min_tokens=body.min_tokens or 0,
+                       temperature=max(float(temperature), 0.0), top_k=max(int(top_k), 0),
+                       top_p=min(max(float(top_p), 0.0), 1.0), seed=body.seed)
 
     class Detok:
         """Incremental detokenisation + stop strings."""
@@ -559,6 +568,25 @@ def build_engine(args):
     return engine, tok, workers
 
 
+def load_default_sampling(model_path: Optional[str]) -> Dict[str, Any]:
+    """Default sampling parameters as vLLM takes them (`--generation-config auto`): the model's
+    generation_config.json next to its weights, when there is one."""
+    if not model_path:
+        return {}
+    f = os.path.join(model_path, "generation_config.json")
+    if not os.path.isfile(f):
+        return {}
+    try:
+        with open(f) as fh:
+            g = json.load(fh)
+    except (OSError, ValueError):
+        return {}
+    out = {k: g[k] for k in ("temperature", "top_p", "top_k") if isinstance(g.get(k), (int, float))}
+    if g.get("do_sample") is False:
+        out["temperature"] = 0.0
+    return out
+
+
 def main(argv=None):
     args, unknown = make_arg_parser().parse_known_args(argv)
     if unknown:
@@ -568,7 +596,8 @@ def main(argv=None):
     engine, tok, workers = build_engine(args)
     from .tool_parsers import get_parser
     parser = get_parser(args.tool_call_parser) if args.enable_auto_tool_choice else None
-    app = create_app(engine, tok, args.served_model_name or args.model, args.max_model_len, tool_parser=parser)
+    app = create_app(engine, tok, args.served_model_name or args.model, args.max_model_len, tool_parser=parser,
+                     default_sampling=load_default_sampling(_RunnerFactory(args).resolve()[0]))
     signal.signal(signal.SIGTERM, lambda *_: (_ for _ in ()).throw(KeyboardInterrupt()))
     try:
         uvicorn.run(app, host=args.host, port=args.port, log_level="warning" if args.disable_log_requests else "info")

@@ -16,7 +16,7 @@ import torch
 import torch.distributed as dist
 
 HEADER = 8   # T, R, S, bt_stride, max_ctx, n_ints, opcode, reserved
-OP_STEP, OP_STOP = 1, 2
+OP_STEP, OP_STOP, OP_SAMPLE = 1, 2, 3
 
 
 class TPLeader:
@@ -36,6 +36,15 @@ class TPLeader:
         dist.broadcast(r._h_meta[:n_ints], src=0, group=self.group)
         return r.step_packed(T, R, S, bt_stride, batch.max_ctx, n_ints)
 
+    def sample_last(self, temperature, top_k, top_p, seeds, draws):
+        """Sampling over the last step's logits on every rank (the vocab shards are all-gathered on the device)."""
+        r = self.runner
+        n = r.pack_sampling(temperature, top_k, top_p, seeds, draws)
+        self._hdr[:7] = torch.tensor([n, 0, 0, 0, 0, 0, OP_SAMPLE], dtype=torch.int32)
+        dist.broadcast(self._hdr, src=0, group=self.group)
+        dist.broadcast(r._h_sample[:32 * n], src=0, group=self.group)
+        return r.sample_packed(n)
+
     def stop(self):
         self._hdr[6] = OP_STOP
         dist.broadcast(self._hdr, src=0, group=self.group)
@@ -53,6 +62,10 @@ def worker_loop(runner, group=None) -> None:
         T, R, S, bt_stride, max_ctx, n_ints, op = (int(v) for v in hdr[:7])
         if op == OP_STOP:
             return
+        if op == OP_SAMPLE:
+            dist.broadcast(runner._h_sample[:32 * T], src=0, group=group)
+            runner.sample_packed(T)
+            continue
         dist.broadcast(runner._h_meta[:n_ints], src=0, group=group)
         runner.step_packed(T, R, S, bt_stride, max_ctx, n_ints)
 

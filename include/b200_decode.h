@@ -244,6 +244,25 @@ B200_API int b200_silu_mul(const void* gu, void* out, int32_t n_tokens, int32_t 
 B200_API int b200_argmax(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, int32_t index_offset,
                 int32_t* out_ids, float* out_max, void* stream);
 
+/* (a10, widened) stochastic sampling for requests that do not ask for greedy decoding: per row
+ * logits / temperature, top-k mask (values below the k-th largest dropped, ties at it kept), top-p on the
+ * renormalised rest (the smallest-probability tokens with cumulative mass <= 1 - p dropped), one draw
+ * ([V22] vllm/v1/sample/sampler.py:90-91,235-256, ops/topk_topp_sampler.py; fields of docs/api-spec.yaml).
+ * temperature[r] <= 0 -> the argmax of b200_argmax.  top_k[r] <= 0 and top_p[r] >= 1 disable the filters.
+ * The draw is a function of (seeds[r], draws[r], logits row): same inputs, same token.  All arrays are device
+ * pointers of n_rows elements; temperature/top_k/top_p/seeds/draws may be NULL (0, off, off, 0, 0). */
+B200_API int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const float* temperature,
+                const int32_t* top_k, const float* top_p, const uint64_t* seeds, const uint64_t* draws,
+                int32_t* out_ids, void* stream);
+
+/* Sampling over the logit rows of the LAST b200_decode_step[_host] of this ctx (they are still in the ctx's
+ * buffer; with tensor parallelism the vocab shards are all-gathered first: a collective, call it on every rank
+ * with the same arguments).  host_params = five host arrays back to back,
+ *   float temperature[n] | int32 top_k[n] | float top_p[n] | uint32 pad[n] | uint64 seed[n] | uint64 draw[n],
+ * 32 n bytes; host_out_ids receives n token ids (asynchronously: synchronise the stream before reading). */
+B200_API int b200_ctx_sample_last(b200_ctx* ctx, int32_t n_rows, const void* host_params, int32_t* host_out_ids,
+                         void* stream);
+
 /* (a0) device-side scheduler advance for pure-decode rows: ids[t]=sampled[t], positions[t]+=1,
  * ctx_lens[t]=positions[t]+1, slot_mapping[t] from the block table.  The image's scheduler does this
  * on the host every iteration ([V22] vllm/v1/attention/backends/cpu_attn.py:107-117 metadata build);

@@ -270,6 +270,31 @@ def greedy(logits_bf16: torch.Tensor) -> torch.Tensor:
     return logits_bf16.float().argmax(dim=-1)
 
 
+def sampling_probs(logits_bf16: torch.Tensor, temperature: float, top_k: int = 0, top_p: float = 1.0) -> torch.Tensor:
+    """The distribution vLLM's sampler draws from for one logits row [V] (temperature > 0): logits / T, top-k
+    mask, top-p mask on the renormalised rest, softmax -- a restatement of
+    [V22] vllm/v1/sample/sampler.py:235-256 (temperature, then the top-k/top-p sampler) and
+    vllm/v1/sample/ops/topk_topp_sampler.py:328-370 (apply_top_k_top_p_pytorch: ascending sort, values below the
+    k-th largest -> -inf, cumulative probability <= 1 - p -> -inf, the largest always kept).
+    Returns fp32 probabilities [V] (0 for dropped tokens).  Pinned against the vLLM function itself by
+    tests/golden/sampling_masks.npz (tools/make_sampling_golden.py)."""
+    x = logits_bf16.float() / float(temperature)
+    xs, idx = x.sort(descending=False)
+    V = x.numel()
+    if top_k and 0 < top_k < V:
+        kth = xs[V - top_k]
+        xs = xs.masked_fill(xs < kth, float("-inf"))
+    if top_p < 1.0:
+        ps = xs.softmax(dim=-1)
+        cum = torch.cumsum(ps, dim=-1)
+        mask = cum <= 1.0 - top_p
+        mask[-1] = False
+        xs = xs.masked_fill(mask, float("-inf"))
+    out = torch.empty_like(x)
+    out[idx] = xs
+    return out.softmax(dim=-1)
+
+
 # --------------------------------------------------------------------------------------
 # the model
 # --------------------------------------------------------------------------------------

@@ -281,6 +281,84 @@ def test_argmax_exact_with_ties(lib, abi):
 
 
 # ---------------------------------------------------------------------------------------------
+def run_sample(lib, abi, logits, temperature, top_k, top_p, seeds, draws):
+    R, V = logits.shape
+    out = torch.empty(R, dtype=torch.int32, device="cuda")
+    t = dev(torch.tensor(temperature, dtype=torch.float32))
+    k = dev(torch.tensor(top_k, dtype=torch.int32))
+    p = dev(torch.tensor(top_p, dtype=torch.float32))
+    sd = dev(torch.tensor(seeds, dtype=torch.int64))
+    dr = dev(torch.tensor(draws, dtype=torch.int64))
+    sync_check(abi, lib.b200_sample(dev(logits).data_ptr(), V, R, V, t.data_ptr(), k.data_ptr(), p.data_ptr(), sd.data_ptr(),
+                                    dr.data_ptr(), out.data_ptr(), None))
+    return out.cpu()
+
+
+def test_sample_greedy_rows_and_top_k_1_are_argmax(lib, abi):
+    g = torch.Generator().manual_seed(3)
+    V = 5003
+    lg = torch.randn(6, V, generator=g).to(BF)
+    lg[1, 77] = lg[1, 4000] = lg[1].float().max() + 1      # tie: lowest index wins
+    got = run_sample(lib, abi, lg, [0.0, 0.0, 1.0, 0.8, 0.0, 2.0], [0, 0, 1, 1, 50, 1], [1.0, 0.5, 1.0, 0.3, 0.9, 1.0],
+                     [1, 2, 3, 4, 5, 6], [0, 0, 0, 9, 0, 1])
+    assert got.tolist() == O.greedy(lg).tolist()
+    assert got[1] == 77
+
+
+def test_sample_is_a_function_of_seed_and_draw(lib, abi):
+    g = torch.Generator().manual_seed(4)
+    V, R = 32000, 16
+    lg = (torch.randn(1, V, generator=g) * 2).to(BF).expand(R, V).contiguous()
+    a = run_sample(lib, abi, lg, [1.0] * R, [0] * R, [1.0] * R, [42] * R, list(range(R)))
+    b = run_sample(lib, abi, lg, [1.0] * R, [0] * R, [1.0] * R, [42] * R, list(range(R)))
+    c = run_sample(lib, abi, lg, [1.0] * R, [0] * R, [1.0] * R, [43] * R, list(range(R)))
+    assert a.tolist() == b.tolist()                         # same (seed, draw) -> same token
+    assert len(set(a.tolist())) > R // 2                    # different draws differ
+    assert a.tolist() != c.tolist()                         # another seed, another stream
+
+
+@pytest.mark.parametrize("T,k,p", [(1.0, 0, 0.9), (0.7, 20, 1.0), (1.3, 40, 0.8), (0.5, 0, 0.3)])
+def test_sample_support_and_frequencies_match_the_oracle(lib, abi, T, k, p):
+    """4096 draws from one row: every token drawn is one the oracle keeps (ties at the cut value may add
+    tokens of exactly that value), and the empirical frequencies follow the oracle's probabilities."""
+    g = torch.Generator().manual_seed(int(T * 10) + k)
+    V, R = 300, 4096
+    row = (torch.randn(V, generator=g) * 2.5).to(BF)
+    probs = O.sampling_probs(row, T, k, p)
+    got = run_sample(lib, abi, row[None].expand(R, V).contiguous(), [T] * R, [k] * R, [p] * R, [7] * R, list(range(R)))
+    kept = probs > 0
+    cut = row.float()[kept].min()
+    allowed = kept | (row.float() == cut)
+    assert bool(allowed[got.long()].all()), "a dropped token was sampled"
+    # renormalise over what the kernel keeps (identical to the oracle unless there is a tie at the cut)
+    ref = (row.float() / T).masked_fill(~allowed, float("-inf")).softmax(-1)
+    freq = torch.bincount(got.long(), minlength=V).float() / R
+    sigma = (ref * (1 - ref) / R).sqrt()
+    assert bool(((freq - ref).abs() <= 4.5 * sigma + 2e-3).all()), float(((freq - ref).abs() - 4.5 * sigma).max())
+
+
+def test_ctx_sample_last_follows_the_step(lib, abi):
+    """b200_ctx_sample_last over the logits of the last step: temperature 0 reproduces the step's greedy tokens."""
+    import numpy as np
+    R_ = pkg("runner")
+    cfg = pkg("config").get_config("tiny")
+    r = R_.ModelRunner(cfg, max_tokens=16, max_model_len=256, kv_cache_gib=0.05)
+    r.init_random_weights()
+    T = 4
+    ids = torch.tensor([5, 9, 11, 3], dtype=torch.int32, device="cuda")
+    pos = torch.zeros(T, dtype=torch.int32, device="cuda")
+    slots = torch.arange(T, dtype=torch.int32, device="cuda") * r.block_size
+    bt = torch.arange(T, dtype=torch.int32, device="cuda").view(T, 1)
+    greedy = r.step_device(ids, pos, slots, bt, pos + 1, 1).cpu().tolist()
+    torch.cuda.synchronize()
+    same = r.sample_last([0.0] * T, [0] * T, [1.0] * T, [1] * T, [0] * T)
+    assert same.tolist() == greedy
+    hot = r.sample_last([5.0] * T, [0] * T, [1.0] * T, [1, 2, 3, 4], [0] * T)
+    assert all(0 <= t < cfg.vocab for t in hot.tolist())
+    r.close()
+
+
+# ---------------------------------------------------------------------------------------------
 def run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv, max_ctx_hint=None, seed=0, bs=128):
     """q [T,hq,128]; K,V per row: list of [n,hkv,128] -> scatter into a shuffled paged cache.
     bs=128 takes the tcgen05 kernel, bs=64 the CUDA-core kernel."""

@@ -1,6 +1,7 @@
 """CPU: the oracle against its frozen golden vectors (and through them the HF stand-in), the
 product-side config/rope restatement against the oracle's, and size-independent properties."""
 import ast
+import os
 
 import numpy as np
 import pytest
@@ -91,3 +92,22 @@ def test_batched_step_matches_per_sequence_forward():
         import copy
         got = om.step_batch(copy.deepcopy(sts), [p[-1] for p in prompts], fast_linear=fast)
         assert (torch.softmax(got.float(), -1) - torch.softmax(torch.stack(ref).float(), -1)).abs().max() <= 1e-3
+
+
+def test_sampling_probs_match_vllm_masks():
+    """oracle.sampling_probs against keep-masks produced by vLLM's own apply_top_k_top_p_pytorch
+    (tools/make_sampling_golden.py): the same tokens survive top-k / top-p, probabilities sum to 1."""
+    import numpy as np
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "sampling_masks.npz"))
+    seeds = sorted(int(k.split("_")[1]) for k in z.files if k.startswith("logits_"))
+    assert len(seeds) >= 8
+    for sd in seeds:
+        logits = torch.from_numpy(z[f"logits_{sd}"].copy()).view(torch.bfloat16)
+        T, k, p = z[f"params_{sd}"]
+        probs = O.sampling_probs(logits, float(T), int(k), float(p))
+        keep = torch.from_numpy(z[f"keep_{sd}"])
+        assert torch.equal(probs > 0, keep), f"case {sd}: kept sets differ"
+        assert abs(float(probs.sum()) - 1.0) < 1e-5
+        # the kept probabilities are the softmax of logits / T restricted to the kept set
+        ref = (logits.float() / float(T)).masked_fill(~keep, float("-inf")).softmax(-1)
+        assert torch.allclose(probs, ref, atol=1e-6)

@@ -28,7 +28,14 @@ class FakeRunner:
         for r in b.logit_rows:
             bt = b.block_tables[int(b.row_to_seq[r])]
             out.append(sum(self.kv[int(bt[p // 16]) * 16 + p % 16] for p in range(int(b.ctx_lens[r]))) % 251)
-        return np.array(out, dtype=np.int32)
+        self.last = np.array(out, dtype=np.int32)
+        return self.last
+
+    def sample_last(self, temperature, top_k, top_p, seeds, draws):
+        """Records the call; a 'sampled' token = greedy token + 1 for rows with temperature > 0."""
+        self.sample_calls = getattr(self, "sample_calls", []) + [dict(temperature=list(temperature), top_k=list(top_k),
+                                                                         top_p=list(top_p), seeds=list(seeds), draws=list(draws))]
+        return np.array([t + 1 if temperature[i] > 0 else t for i, t in enumerate(self.last)], dtype=np.int32)
 
 
 def expect_ids(prompt_ids, n):
@@ -77,12 +84,12 @@ def test_completion_matches_engine_and_usage(client):
     assert r["choices"][0]["finish_reason"] == "length"
     assert r["usage"] == {"prompt_tokens": len(ids), "completion_tokens": 25, "total_tokens": len(ids) + 25}
     # token-id prompt + echo
-    r2 = client.post("/v1/completions", json={"model": MODEL, "prompt": ids, "max_tokens": 25}).json()
+    r2 = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": ids, "max_tokens": 25}).json()
     assert r2["choices"][0]["text"] == want
 
 
 def test_streaming_sse_with_usage(client):
-    with client.stream("POST", "/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 8, "stream": True,
+    with client.stream("POST", "/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "abc", "max_tokens": 8, "stream": True,
                                                         "stream_options": {"include_usage": True}}) as r:
         assert r.status_code == 200
         lines = [l for l in r.iter_lines() if l.startswith("data: ")]
@@ -108,21 +115,21 @@ def test_chat_completion_and_stream(client):
 
 def test_validation_and_errors(client):
     assert client.post("/v1/completions", json={"model": MODEL}).status_code == 422                     # prompt missing
-    assert client.post("/v1/completions", json={"model": MODEL, "prompt": "x", "bogus_field": 1}).status_code == 422
-    assert client.post("/v1/chat/completions", json={"model": MODEL, "messages": []}).status_code == 422
+    assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "bogus_field": 1}).status_code == 422
+    assert client.post("/v1/chat/completions", json={"model": MODEL, "temperature": 0, "messages": []}).status_code == 422
     r = client.post("/v1/completions", json={"model": "other", "prompt": "x"})
     assert r.status_code == 404 and r.json()["object"] == "error"
-    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "x" * 300, "max_tokens": 10})
+    r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x" * 300, "max_tokens": 10})
     assert r.status_code == 400 and "maximum context length" in r.json()["message"]
-    assert client.post("/v1/completions", json={"model": MODEL, "prompt": "x", "n": 2}).status_code == 400
+    assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "n": 2}).status_code == 400
 
 
 def test_stop_and_ignore_eos(client):
     ids = client.tok.encode("hello")
     first = expect_ids(ids, 1)[0]
-    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "hello", "max_tokens": 9, "stop_token_ids": [first]}).json()
+    r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "hello", "max_tokens": 9, "stop_token_ids": [first]}).json()
     assert r["usage"]["completion_tokens"] == 1 and r["choices"][0]["finish_reason"] == "stop"
-    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "hello", "max_tokens": 9, "ignore_eos": True}).json()
+    r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "hello", "max_tokens": 9, "ignore_eos": True}).json()
     assert r["usage"]["completion_tokens"] == 9
 
 
@@ -148,7 +155,7 @@ def test_health_goes_red_when_the_engine_dies(client):
     def boom(_):
         raise RuntimeError("device lost")
     loop.engine.runner.step = boom
-    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "x", "max_tokens": 2})
+    r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "max_tokens": 2})
     assert r.status_code == 500
     assert client.get("/health").status_code == 503
 
@@ -190,7 +197,33 @@ def test_chat_tool_calls_through_the_server():
     fr.prompt_len = len(tok.encode(tok.apply_chat_template(msgs), add_special_tokens=False))
     tools = [{"type": "function", "function": {"name": "get_weather", "parameters": {"type": "object"}}}]
     with TestClient(app) as c:
-        r = c.post("/v1/chat/completions", json={"model": MODEL, "messages": msgs, "tools": tools, "max_tokens": 80}).json()
+        r = c.post("/v1/chat/completions", json={"model": MODEL, "temperature": 0, "messages": msgs, "tools": tools, "max_tokens": 80}).json()
     ch = r["choices"][0]
     assert ch["finish_reason"] == "tool_calls" and ch["message"]["content"] is None
     assert ch["message"]["tool_calls"][0]["function"]["name"] == "get_weather"
+
+
+def test_sampling_fields_reach_the_device_sampler():
+    """temperature / top_p / top_k / seed of the OpenAI body (docs/api-spec.yaml) travel to the runner's
+    sampler with the draw number = tokens generated so far; temperature 0 never calls it; an omitted
+    temperature takes the server default (vLLM: generation_config.json, else 1.0)."""
+    runner = FakeRunner()
+    engine = E.LLMEngine(runner, max_num_batched_tokens=64, max_num_seqs=8, max_model_len=256)
+    app = S.create_app(engine, S.ByteTokenizer(512), MODEL, 256, default_sampling={"temperature": 0.6, "top_p": 0.9})
+    with TestClient(app) as client:
+        r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 3, "temperature": 0})
+        assert r.status_code == 200 and not getattr(runner, "sample_calls", [])
+        r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 3, "temperature": 0.8,
+                                                 "top_p": 0.5, "top_k": 7, "seed": 1234})
+        assert r.status_code == 200
+        calls = runner.sample_calls
+        assert len(calls) == 3
+        assert [c["draws"] for c in calls] == [[0], [1], [2]]
+        assert all(c["seeds"] == [1234] and c["top_k"] == [7] for c in calls)
+        assert all(abs(c["temperature"][0] - 0.8) < 1e-6 and abs(c["top_p"][0] - 0.5) < 1e-6 for c in calls)
+        runner.sample_calls = []
+        r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 2})
+        assert r.status_code == 200
+        c = runner.sample_calls[0]
+        assert abs(c["temperature"][0] - 0.6) < 1e-6 and abs(c["top_p"][0] - 0.9) < 1e-6 and c["top_k"] == [0]
+        assert c["seeds"][0] != 0          # no seed in the body: one is drawn per request

@@ -121,3 +121,75 @@ def test_shards_partition_the_weights():
     assert torch.equal(torch.cat([parts[r][(0, W.LM_HEAD)] for r in range(2)], 0), full[(0, W.LM_HEAD)])
     with pytest.raises(ValueError):
         list(W.shard_weights(w, cfg, 0, 3))
+
+
+class _ProtoRunner:
+    """Stand-in for a ModelRunner on the CPU: enough of its buffers for tp_exec's broadcast protocol."""
+    def __init__(self, log):
+        self.n_blocks, self.block_size, self.max_tokens, self.max_model_len, self.cfg = 8, 16, 32, 64, None
+        self._h_meta = torch.zeros(4096, dtype=torch.int32)
+        self._h_sample = torch.zeros(64 * 32, dtype=torch.uint8)
+        self.log = log
+        self.h2d_bytes_last = 0
+
+    def pack(self, batch):
+        self._h_meta[:5] = torch.tensor(batch, dtype=torch.int32)
+        return 1, 1, 1, 1, 5
+
+    def step_packed(self, T, R, S, bt_stride, max_ctx, n_ints, sync=True):
+        self.log.append(("step", self._h_meta[:n_ints].tolist(), max_ctx))
+        return [0]
+
+    def pack_sampling(self, temperature, top_k, top_p, seeds, draws):
+        n = len(temperature)
+        a = self._h_sample.numpy()
+        a[:32 * n] = 0
+        a[0:4 * n].view("float32")[:] = temperature
+        a[16 * n:24 * n].view("uint64")[:] = seeds
+        return n
+
+    def sample_packed(self, n, sync=True):
+        a = self._h_sample.numpy()
+        self.log.append(("sample", a[0:4 * n].view("float32").tolist(), a[16 * n:24 * n].view("uint64").tolist()))
+        return [0] * n
+
+
+def _proto_rank(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    X = pkg("tp_exec")
+    log = []
+    r = _ProtoRunner(log)
+    if rank == 0:
+        lead = X.TPLeader(r)
+        batch = type("B", (), {"max_ctx": 33})()
+        r.pack = lambda b: (r._h_meta.__setitem__(slice(0, 5), torch.tensor([1, 2, 3, 4, 5], dtype=torch.int32)), (1, 1, 1, 1, 5))[1]
+        lead.step(batch)
+        lead.sample_last([0.5, 0.0], [0, 0], [1.0, 1.0], [77, 78], [0, 0])
+        lead.step(batch)
+        lead.stop()
+    else:
+        X.worker_loop(r)
+    q.put((rank, log))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_leader_worker_protocol_carries_steps_and_sampling():
+    """world_size 2 over gloo: every step and every sampling call of rank 0 reaches the worker with the same
+    payload (the device-side collectives need both ranks to make the same calls in the same order)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() + 7) % 2000
+    procs = [ctx.Process(target=_proto_rank, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    logs = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert logs[0] == logs[1]
+    kinds = [e[0] for e in logs[1]]
+    assert kinds == ["step", "sample", "step"]
+    assert logs[1][0][1] == [1, 2, 3, 4, 5] and logs[1][0][2] == 33
+    assert logs[1][1][1] == [0.5, 0.0] and logs[1][1][2] == [77, 78]
