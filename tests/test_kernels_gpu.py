@@ -349,8 +349,9 @@ def test_ctx_sample_last_follows_the_step(lib, abi):
     pos = torch.zeros(T, dtype=torch.int32, device="cuda")
     slots = torch.arange(T, dtype=torch.int32, device="cuda") * r.block_size
     bt = torch.arange(T, dtype=torch.int32, device="cuda").view(T, 1)
-    greedy = r.step_device(ids, pos, slots, bt, pos + 1, 1).cpu().tolist()
+    out = r.step_device(ids, pos, slots, bt, pos + 1, 1)   # runs on the runner's stream
     torch.cuda.synchronize()
+    greedy = out.cpu().tolist()
     same = r.sample_last([0.0] * T, [0] * T, [1.0] * T, [1] * T, [0] * T)
     assert same.tolist() == greedy
     hot = r.sample_last([5.0] * T, [0] * T, [1.0] * T, [1, 2, 3, 4], [0] * T)

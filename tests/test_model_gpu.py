@@ -237,7 +237,8 @@ def test_openai_server_end_to_end_on_the_gpu():
         import concurrent.futures as cf
         with cf.ThreadPoolExecutor(4) as ex:
             res = list(ex.map(lambda i: c.post("/v1/completions", json={"model": "tiny", "prompt": ids, "max_tokens": 8,
-                                                                         "ignore_eos": True}).json(), range(4)))
+                                                                         "temperature": 0, "ignore_eos": True}).json(),
+                           range(4)))
         assert all(x["choices"][0]["text"] == res[0]["choices"][0]["text"] for x in res)
         assert "vllm:generation_tokens_total" in c.get("/metrics").text
     got_text = out["choices"][0]["text"]
