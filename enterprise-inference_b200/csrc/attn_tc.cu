@@ -8,13 +8,16 @@
 //   S^T[128 tok][16]  = K_tile[128 tok x 128 dim] . Q^T          (A = K, K-major;  B = Q padded to 16 heads)
 //   O^T[128 dim][16]  = V_tile^T[128 dim x 128 tok] . P^T        (A = V, MN-major; B = P, 16 heads x 128 tok)
 // K and V tiles arrive by TMA (cp.async.bulk.tensor, SWIZZLE_128B, two 64-dim halves each) straight
-// from the paged cache — a (block, kv head) tile is one box — into a 3-stage ring (64 KiB per stage).
-// 128 softmax threads own one token (TMEM lane) each for S and one head-dim each for O: scores are
-// read with tcgen05.ld, scaled, masked and exponentiated in fp32 (online softmax, running max per
-// head shared through smem), P is written back to smem as TWO bf16 terms (hi + lo, so that P keeps
-// ~16 mantissa bits: R4 of the oracle keeps P in fp32) and the running output is rescaled in
-// registers, so TMEM never needs a read-modify-write.  GQA: the G query heads of the kv head share
-// every K/V byte.  Split-KV + LSE merge as in attn.cu (same workspace layout, same merge kernel).
+// from the paged cache — a (block, kv head) tile is one box — into a ring of 32 KiB slots (K, V, K, V, ...:
+// three tiles in flight with six slots).  The softmax threads own one token (TMEM lane) each for S and
+// one head-dim each for O: scores are read with tcgen05.ld, scaled, masked and exponentiated in fp32
+// (online softmax, tile max per column by redux.sync + one exchange through smem), P is written back to
+// smem as TWO bf16 terms (hi + lo, so that P keeps ~16 mantissa bits: R4 of the oracle keeps P in fp32)
+// and the running output is rescaled in registers, so TMEM never needs a read-modify-write.  The live MMA
+// columns are dealt to CG groups of four softmax warps (2 for decode, 4 for packed prefill rows) so that
+// every scheduler has 2-4 warps to interleave.  GQA: the G query heads of the kv head share every K/V
+// byte.  Split-KV + LSE merge as in attn.cu (same workspace layout, same merge kernel).  Prefill-dominated
+// steps go to attn_prefill.cu (query rows on the MMA M) unless B200_ATTN_FA=0.
 //
 // Replaces: paged_attention_v1/v2 CPU kernels of the vLLM-CPU image
 // ([V22] vllm/v1/attention/backends/cpu_attn.py:377-396).
