@@ -11,7 +11,7 @@ and templates/deployment.yaml:66-87.  HTTP surface: /root/reference/docs/api-spe
 "temperature": 0 (what the reference's clients send) is the device's argmax; temperature / top_p / top_k /
 seed sample on the device (csrc/sample.cu) with vLLM's semantics and defaults (the model's generation_config.json,
 else temperature 1); penalties, logit_bias, min_p, logprobs, n > 1 and guided decoding are accepted and ignored
-or rejected (n, best_of, beam search).  /v1/embeddings is served by TEI in the reference, not here.
+or rejected (best_of != n, beam search); n parallel samples run as n engine requests.  /v1/embeddings is served by TEI in the reference, not here.
 """
 from __future__ import annotations
 
@@ -121,6 +121,19 @@ def load_tokenizer(kind: str, model_path: Optional[str], vocab: int):
 # ------------------------------------------------------------------------------------------------
 # request / response schema (docs/api-spec.yaml; extra fields are rejected with 422)
 # ------------------------------------------------------------------------------------------------
+class TokenizeRequest(BaseModel):
+    model_config = ConfigDict(extra="ignore")
+    model: Optional[str] = None
+    prompt: str
+    add_special_tokens: Optional[bool] = True
+
+
+class DetokenizeRequest(BaseModel):
+    model_config = ConfigDict(extra="ignore")
+    model: Optional[str] = None
+    tokens: List[int]
+
+
 class StreamOptions(BaseModel):
     model_config = ConfigDict(extra="forbid")
     include_usage: Optional[bool] = True
@@ -325,6 +338,25 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
             return PlainTextResponse(loop_.error or "engine thread stopped", status_code=503)
         return PlainTextResponse("", status_code=200)
 
+    # the small utility routes of the image's server (health probes of other stacks, tokenizer access)
+    @app.get("/ping")
+    @app.post("/ping")
+    async def ping():
+        return await health()
+
+    @app.get("/version")
+    async def version():
+        return {"version": "b200-decode 0.1 (vLLM-compatible API surface of the v0.10.2 image)"}
+
+    @app.post("/tokenize")
+    async def tokenize(body: TokenizeRequest):
+        ids = tokenizer.encode(body.prompt, add_special_tokens=body.add_special_tokens is not False)
+        return {"count": len(ids), "max_model_len": max_model_len, "tokens": ids}
+
+    @app.post("/detokenize")
+    async def detokenize(body: DetokenizeRequest):
+        return {"prompt": tokenizer.decode(list(body.tokens), skip_special_tokens=False)}
+
     @app.get("/metrics")
     async def metrics_ep():
         return PlainTextResponse(generate_latest(metrics.registry).decode(), media_type="text/plain; version=0.0.4")
@@ -380,28 +412,48 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
             delta, self.sent = text[self.sent:], max(len(text), self.sent)
             return delta
 
+        def flush(self) -> str:
+            """At the end of the request: whatever was held back as a possibly incomplete UTF-8 sequence."""
+            if self.stopped:
+                return ""
+            text = tokenizer.decode(self.ids, skip_special_tokens=self.skip_special)
+            delta, self.sent = text[self.sent:], max(len(text), self.sent)
+            return delta
+
     async def run(body: _Sampling, prompt_ids: List[int], chat: bool, prompt_text: str = ""):
         if len(prompt_ids) == 0:
             return error(400, "the prompt is empty")
-        if body.n not in (None, 1) or (body.best_of not in (None, 1)) or body.use_beam_search:
-            return error(400, "n > 1, best_of > 1 and beam search are not supported by this backend")
-        req = make_request(body, prompt_ids)
-        if len(prompt_ids) + req.max_tokens > max_model_len:
+        n = body.n or 1
+        if (body.best_of not in (None, n)) or body.use_beam_search:
+            return error(400, "best_of != n and beam search are not supported by this backend")
+        if not 1 <= n <= 16:
+            return error(400, "n must be between 1 and 16")
+        # n parallel samples = n engine requests over the same prompt (vLLM: child i samples with seed + i)
+        reqs = []
+        for i in range(n):
+            r_ = make_request(body, prompt_ids)
+            if body.seed is not None:
+                r_.seed = body.seed + i
+            reqs.append(r_)
+        req0 = reqs[0]
+        if len(prompt_ids) + req0.max_tokens > max_model_len:
             return error(400, f"This model's maximum context length is {max_model_len} tokens. However, you requested "
-                              f"{len(prompt_ids) + req.max_tokens} tokens ({len(prompt_ids)} in the prompt, {req.max_tokens} "
+                              f"{len(prompt_ids) + req0.max_tokens} tokens ({len(prompt_ids)} in the prompt, {req0.max_tokens} "
                               "in the completion).")
-        q: asyncio.Queue = asyncio.Queue()
-        loop_.submit(req, asyncio.get_running_loop(), q)
+        queues = [asyncio.Queue() for _ in reqs]
+        for r_, q_ in zip(reqs, queues):
+            loop_.submit(r_, asyncio.get_running_loop(), q_)
         created = int(time.time())
-        rid = req.request_id if not chat else "chat" + req.request_id
+        rid = req0.request_id if not chat else "chat" + req0.request_id
         obj = "chat.completion" if chat else "text_completion"
-        detok = Detok(body)
+        detoks = [Detok(body) for _ in reqs]
 
         def usage():
-            return {"prompt_tokens": len(prompt_ids), "completion_tokens": len(req.output_ids),
-                    "total_tokens": len(prompt_ids) + len(req.output_ids)}
+            done = sum(len(r_.output_ids) for r_ in reqs)
+            return {"prompt_tokens": len(prompt_ids), "completion_tokens": done, "total_tokens": len(prompt_ids) + done}
 
-        async def events():
+        async def events(i: int):
+            q, detok, req = queues[i], detoks[i], reqs[i]
             while True:
                 kind, val = await q.get()
                 if kind == "tokens":
@@ -413,6 +465,9 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                         yield "done", "stop"
                         return
                 elif kind == "done":
+                    rest = detok.flush()
+                    if rest:
+                        yield "delta", rest
                     yield "done", val
                     return
                 else:
@@ -421,56 +476,75 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
 
         if body.stream:
             async def sse():
-                first = True
                 include_usage = bool(body.stream_options and body.stream_options.include_usage)
                 cont = bool(body.stream_options and body.stream_options.continuous_usage_stats)
-                async for kind, val in events():
-                    if kind == "error":
-                        yield f"data: {json.dumps({'error': {'message': val, 'type': 'InternalServerError', 'code': 500}})}\n\n"
-                        break
-                    finish = val if kind == "done" else None
-                    text = val if kind == "delta" else ""
-                    if kind == "delta" and not text and not first:
-                        continue
-                    if chat:
-                        delta = {"content": text}
-                        if first:
-                            delta["role"] = "assistant"
-                        choice = {"index": 0, "delta": delta if kind == "delta" else {}, "logprobs": None, "finish_reason": finish}
-                        chunk = {"id": rid, "object": "chat.completion.chunk", "created": created, "model": served_model_name,
-                                 "choices": [choice]}
-                    else:
-                        chunk = {"id": rid, "object": "text_completion", "created": created, "model": served_model_name,
-                                 "choices": [{"index": 0, "text": text, "logprobs": None, "finish_reason": finish, "stop_reason": None}]}
-                    if include_usage:
-                        chunk["usage"] = usage() if cont else None
-                    first = False
-                    yield f"data: {json.dumps(chunk)}\n\n"
+                merged: asyncio.Queue = asyncio.Queue()
+
+                async def pump(i: int):
+                    async for kind, val in events(i):
+                        await merged.put((i, kind, val))
+
+                tasks = [asyncio.ensure_future(pump(i)) for i in range(n)]
+                first = [True] * n
+                live = n
+                try:
+                    while live:
+                        i, kind, val = await merged.get()
+                        if kind == "error":
+                            yield f"data: {json.dumps({'error': {'message': val, 'type': 'InternalServerError', 'code': 500}})}\n\n"
+                            break
+                        finish = val if kind == "done" else None
+                        if kind == "done":
+                            live -= 1
+                        text = val if kind == "delta" else ""
+                        if kind == "delta" and not text and not first[i]:
+                            continue
+                        if chat:
+                            delta = {"content": text}
+                            if first[i]:
+                                delta["role"] = "assistant"
+                            choice = {"index": i, "delta": delta if kind == "delta" else {}, "logprobs": None,
+                                      "finish_reason": finish}
+                            chunk = {"id": rid, "object": "chat.completion.chunk", "created": created,
+                                     "model": served_model_name, "choices": [choice]}
+                        else:
+                            chunk = {"id": rid, "object": "text_completion", "created": created, "model": served_model_name,
+                                     "choices": [{"index": i, "text": text, "logprobs": None, "finish_reason": finish,
+                                                  "stop_reason": None}]}
+                        if include_usage:
+                            chunk["usage"] = usage() if cont else None
+                        first[i] = False
+                        yield f"data: {json.dumps(chunk)}\n\n"
+                finally:
+                    for t in tasks:
+                        t.cancel()
                 if include_usage:
                     yield f"data: {json.dumps({'id': rid, 'object': 'chat.completion.chunk' if chat else 'text_completion', 'created': created, 'model': served_model_name, 'choices': [], 'usage': usage()})}\n\n"
                 yield "data: [DONE]\n\n"
             return StreamingResponse(sse(), media_type="text/event-stream")
 
-        text, finish = "", None
-        async for kind, val in events():
-            if kind == "delta":
-                text += val
-            elif kind == "done":
-                finish = val
+        choices = []
+        for i in range(n):
+            text, finish = "", None
+            async for kind, val in events(i):
+                if kind == "delta":
+                    text += val
+                elif kind == "done":
+                    finish = val
+                else:
+                    return error(500, val, "InternalServerError")
+            if chat:
+                content, tool_calls = text, []
+                if tool_parser is not None and getattr(body, "tools", None) and body.tool_choice != "none":
+                    content, tool_calls = tool_parser(text, body.tools)
+                    if tool_calls:
+                        finish = "tool_calls"
+                choices.append({"index": i, "message": {"role": "assistant", "content": content, "tool_calls": tool_calls},
+                                "logprobs": None, "finish_reason": finish, "stop_reason": None})
             else:
-                return error(500, val, "InternalServerError")
-        if chat:
-            content, tool_calls = text, []
-            if tool_parser is not None and getattr(body, "tools", None) and body.tool_choice != "none":
-                content, tool_calls = tool_parser(text, body.tools)
-                if tool_calls:
-                    finish = "tool_calls"
-            choice = {"index": 0, "message": {"role": "assistant", "content": content, "tool_calls": tool_calls},
-                      "logprobs": None, "finish_reason": finish, "stop_reason": None}
-        else:
-            choice = {"index": 0, "text": (prompt_text + text) if body.echo else text, "logprobs": None,
-                      "finish_reason": finish, "stop_reason": None}
-        return {"id": rid, "object": obj, "created": created, "model": served_model_name, "choices": [choice], "usage": usage()}
+                choices.append({"index": i, "text": (prompt_text + text) if body.echo else text, "logprobs": None,
+                                "finish_reason": finish, "stop_reason": None})
+        return {"id": rid, "object": obj, "created": created, "model": served_model_name, "choices": choices, "usage": usage()}
 
     @app.post("/v1/completions")
     async def completions(body: CompletionRequest):

@@ -121,7 +121,9 @@ def test_validation_and_errors(client):
     assert r.status_code == 404 and r.json()["object"] == "error"
     r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x" * 300, "max_tokens": 10})
     assert r.status_code == 400 and "maximum context length" in r.json()["message"]
-    assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "n": 2}).status_code == 400
+    assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "n": 64}).status_code == 400
+    assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "n": 2, "best_of": 4}).status_code == 400
+    assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "use_beam_search": True}).status_code == 400
 
 
 def test_stop_and_ignore_eos(client):
@@ -227,3 +229,35 @@ def test_sampling_fields_reach_the_device_sampler():
         c = runner.sample_calls[0]
         assert abs(c["temperature"][0] - 0.6) < 1e-6 and abs(c["top_p"][0] - 0.9) < 1e-6 and c["top_k"] == [0]
         assert c["seeds"][0] != 0          # no seed in the body: one is drawn per request
+
+
+def test_n_parallel_samples(client):
+    """`n` (docs/api-spec.yaml): n choices with indices 0..n-1 from n engine requests over the same prompt;
+    usage counts all of them; a body seed gives child i the seed + i; streaming interleaves the choices."""
+    ids = client.tok.encode("abc")
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 5, "temperature": 0, "n": 3}).json()
+    assert [c["index"] for c in r["choices"]] == [0, 1, 2]
+    want = client.tok.decode(expect_ids(ids, 5))
+    assert all(c["text"] == want and c["finish_reason"] == "length" for c in r["choices"])      # greedy: identical
+    assert r["usage"] == {"prompt_tokens": len(ids), "completion_tokens": 15, "total_tokens": len(ids) + 15}
+    r = client.post("/v1/chat/completions", json={"model": MODEL, "messages": [{"role": "user", "content": "hi"}],
+                                                  "max_tokens": 4, "temperature": 0, "n": 2}).json()
+    assert [c["index"] for c in r["choices"]] == [0, 1] and r["choices"][0]["message"] == r["choices"][1]["message"]
+    with client.stream("POST", "/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 4, "temperature": 0,
+                                                        "n": 2, "stream": True}) as resp:
+        lines = [l for l in resp.iter_lines() if l.startswith("data: ")]
+    assert lines[-1] == "data: [DONE]"
+    chunks = [json.loads(l[6:]) for l in lines[:-1]]
+    for i in (0, 1):
+        text = "".join(c["choices"][0]["text"] for c in chunks if c["choices"] and c["choices"][0]["index"] == i)
+        assert text == client.tok.decode(expect_ids(ids, 4))
+        assert [c["choices"][0]["finish_reason"] for c in chunks if c["choices"] and c["choices"][0]["index"] == i][-1] == "length"
+
+
+def test_utility_routes(client):
+    assert client.get("/ping").status_code == 200 and client.post("/ping").status_code == 200
+    assert "version" in client.get("/version").json()
+    t = client.post("/tokenize", json={"model": MODEL, "prompt": "What is Deep Learning?"}).json()
+    assert t["count"] == len(t["tokens"]) > 0 and t["tokens"] == client.tok.encode("What is Deep Learning?")
+    d = client.post("/detokenize", json={"model": MODEL, "tokens": t["tokens"]}).json()
+    assert d["prompt"].endswith("What is Deep Learning?")
