@@ -162,6 +162,7 @@ struct b200_ctx {
   float* d_pairs;     // [rows][2] local (max, idx)
   float* d_gathered;  // [world][rows][2]
   void* d_sample;     // sampling parameters of the rows, packed (b200_ctx_sample_last)
+  void* d_logprob;    // [rows] chosen ids | [rows] logprob | [rows][32] top ids | [rows][32] top logprobs
   __nv_bfloat16* logits_full;  // TP only: [world][rows][vocab_local], gathered for the sampler
   // graphs
   bool graphs = true;
@@ -270,6 +271,7 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
       {(void**)&c->d_pairs, R * 8},
       {(void**)&c->d_gathered, R * 8 * W},
       {(void**)&c->d_sample, R * 40},
+      {(void**)&c->d_logprob, R * (8 + 32 * 8)},
       {(void**)&c->logits_full, W > 1 ? R * (int64_t)c->vocab_local * 2 * W : 16},
   };
   int64_t total = 0;
@@ -923,6 +925,43 @@ extern "C" int b200_ctx_sample_last(b200_ctx* c, int32_t n_rows, const void* hos
   }
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(host_out_ids, c->d_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+  return B200_OK;
+}
+
+extern "C" int b200_logprobs(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const int32_t* token_ids,
+                             int32_t n_top, float* out_logprob, int32_t* out_top_ids, float* out_top_logprobs, void* stream) {
+  B200_REQUIRE(n_rows >= 0 && vocab > 0 && ld >= vocab, B200_ERR_INVALID, "logprobs: bad sizes (rows=%d vocab=%d ld=%lld)",
+               n_rows, vocab, (long long)ld);
+  return logprob_rows((const __nv_bfloat16*)logits, ld, n_rows, vocab, vocab, 0, token_ids, n_top, out_logprob, out_top_ids,
+                      out_top_logprobs, (cudaStream_t)stream);
+}
+
+// Log-probabilities over the logit rows of the LAST step (see b200_ctx_sample_last for the TP gather).
+// host_out: float logprob[n] | int32 top_ids[n][n_top] | float top_logprobs[n][n_top], contiguous.
+extern "C" int b200_ctx_logprobs_last(b200_ctx* c, int32_t n_rows, const int32_t* host_token_ids, int32_t n_top,
+                                      void* host_out, void* stream) {
+  B200_REQUIRE(c && host_token_ids && host_out, B200_ERR_INVALID, "logprobs_last: null argument");
+  B200_REQUIRE(n_rows > 0 && n_rows <= c->max_logit_rows && n_top >= 0 && n_top <= 32, B200_ERR_INVALID,
+               "logprobs_last: n_rows=%d outside (0,%d] or n_top=%d outside [0,32]", n_rows, c->max_logit_rows, n_top);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t n = n_rows;
+  char* base = static_cast<char*>(c->d_logprob);
+  int32_t* d_tok = reinterpret_cast<int32_t*>(base);
+  float* d_lp = reinterpret_cast<float*>(base + 4 * n);
+  int32_t* d_ids = reinterpret_cast<int32_t*>(base + 8 * n);
+  float* d_tlp = reinterpret_cast<float*>(base + 8 * n + 4 * n * n_top);
+  B200_CUDA(cudaMemcpyAsync(d_tok, host_token_ids, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+  const int W = c->cfg.tp_world;
+  int rc;
+  if (W > 1) {
+    B200_NCCL(nccl().AllGather(c->logits, c->logits_full, (size_t)n * c->vocab_local, ncclBfloat16, c->comm, s));
+    rc = logprob_rows(c->logits_full, c->vocab_local, n_rows, c->vocab_local * W, c->vocab_local, n * c->vocab_local, d_tok,
+                      n_top, d_lp, d_ids, d_tlp, s);
+  } else {
+    rc = logprob_rows(c->logits, c->vocab_local, n_rows, c->vocab_local, c->vocab_local, 0, d_tok, n_top, d_lp, d_ids, d_tlp, s);
+  }
+  if (rc) return rc;
+  B200_CUDA(cudaMemcpyAsync(host_out, d_lp, (size_t)n * 4 * (1 + 2 * n_top), cudaMemcpyDeviceToHost, s));
   return B200_OK;
 }
 

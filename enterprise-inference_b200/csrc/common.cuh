@@ -182,6 +182,8 @@ int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
 int sample_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
                 const float* temperature, const int32_t* top_k, const float* top_p, const uint64_t* seeds,
                 const uint64_t* draws, int32_t* out, cudaStream_t s);
+int logprob_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
+                 const int32_t* tok, int n_top, float* out_lp, int32_t* top_ids, float* top_lp, cudaStream_t s);
 // once per step when pack > 0: builds the prefill attention's row plan in ws; 1 = built (use pack = 2), 0 = not used
 int paged_attn_prefill_plan_step(const int32_t* row_to_seq, const int32_t* ctx_lens, int T, int hq, int hkv, int block_size,
                                  void* ws, int64_t ws_bytes, cudaStream_t s);

@@ -225,7 +225,161 @@ sample_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, i
   if (tid == 0) out[row] = s.i < vocab ? s.i : b.i;
 }
 
+// ---- log-probabilities of chosen tokens + the top-N alternatives (OpenAI `logprobs` / `top_logprobs`) ----------
+// log softmax over the RAW logits (vLLM's default logprobs_mode; [V22] vllm/v1/sample/sampler.py:90-118): for row r
+//   out_lp[r] = l[tok[r]] - logsumexp(l),  top_ids/top_lp[r][0..n_top) = the n_top largest, value descending, ties by
+// lowest index.  One CTA per row; the N-th largest value by the same two-level radix select as top-k.
+constexpr int kTopCap = 96;   // candidates collected in shared memory (n_top <= 32 plus ties at the cut value)
+
+__global__ void __launch_bounds__(kSampleThreads)
+logprob_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, int seg_len, int64_t seg_stride,
+               const int32_t* __restrict__ tok, int n_top, float* __restrict__ out_lp, int32_t* __restrict__ top_ids,
+               float* __restrict__ top_lp) {
+  __shared__ Best sh_best[32];
+  __shared__ float sh_sum[32];
+  __shared__ unsigned int hist[256];
+  __shared__ unsigned int sel[2];
+  __shared__ int cand_i[kTopCap];
+  __shared__ float cand_v[kTopCap];
+  __shared__ int n_cand, n_ties;
+  pdl_wait();
+  pdl_launch_dependents();
+  const int row = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const RowView lv{logits + (int64_t)row * ld, seg_len, seg_stride};
+  Best b{-INFINITY, 0x7fffffff};
+  for (int i = tid; i < vocab; i += kSampleThreads) b = better(b, Best{__bfloat162float(lv.at(i)), i});
+  b = block_best(b, sh_best);
+  const float vmax = b.v;
+  // sum of exp in a fixed order: per thread, then warp tree, then the 32 warp sums by one warp
+  float se = 0.f;
+  for (int i = tid; i < vocab; i += kSampleThreads) se += expf(__bfloat162float(lv.at(i)) - vmax);
+  se = warp_sum(se);
+  if (lane == 0) sh_sum[warp] = se;
+  __syncthreads();
+  if (warp == 0) {
+    float t = warp_sum(sh_sum[lane]);
+    if (lane == 0) sh_sum[0] = t;
+  }
+  __syncthreads();
+  const float lse = vmax + logf(sh_sum[0]);
+  if (tid == 0) {
+    const int t = tok ? tok[row] : -1;
+    out_lp[row] = (t >= 0 && t < vocab) ? __bfloat162float(lv.at(t)) - lse : -INFINITY;
+  }
+  if (n_top <= 0) return;
+  // key of the n_top-th largest value
+  uint32_t thr = 0;
+  {
+    uint32_t prefix = 0, above = 0;
+    for (int level = 0; level < 2; ++level) {
+      for (int j = tid; j < 256; j += kSampleThreads) hist[j] = 0u;
+      __syncthreads();
+      for (int i = tid; i < vocab; i += kSampleThreads) {
+        const uint32_t key = key16(lv.at(i));
+        if (level == 0)
+          atomicAdd(&hist[key >> 8], 1u);
+        else if ((key >> 8) == prefix)
+          atomicAdd(&hist[key & 255u], 1u);
+      }
+      __syncthreads();
+      if (tid == 0) {
+        uint32_t cum = above;
+        int bin = 255;
+        for (; bin > 0; --bin) {
+          if (cum + hist[bin] >= (uint32_t)n_top) break;
+          cum += hist[bin];
+        }
+        sel[0] = (uint32_t)bin;
+        sel[1] = cum;
+      }
+      __syncthreads();
+      if (level == 0) {
+        prefix = sel[0];
+        above = sel[1];
+      } else {
+        thr = (prefix << 8) | sel[0];
+      }
+      __syncthreads();
+    }
+  }
+  // candidates: everything above the cut (fewer than n_top), then the ties at the cut
+  if (tid == 0) {
+    n_cand = 0;
+    n_ties = 0;
+  }
+  __syncthreads();
+  for (int i = tid; i < vocab; i += kSampleThreads) {
+    const __nv_bfloat16 v = lv.at(i);
+    const uint32_t key = key16(v);
+    if (key > thr) {
+      const int at = atomicAdd(&n_cand, 1);
+      if (at < kTopCap) {
+        cand_i[at] = i;
+        cand_v[at] = __bfloat162float(v);
+      }
+    }
+  }
+  __syncthreads();
+  const int n_above = min(n_cand, kTopCap);
+  for (int i = tid; i < vocab; i += kSampleThreads) {
+    const __nv_bfloat16 v = lv.at(i);
+    if (key16(v) == thr) {
+      const int at = n_above + atomicAdd(&n_ties, 1);
+      if (at < kTopCap) {
+        cand_i[at] = i;
+        cand_v[at] = __bfloat162float(v);
+      }
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int n = min(n_above + n_ties, kTopCap);
+    if (n_above + n_ties > kTopCap) {
+      // more ties at the cut value than the buffer holds (degenerate logits): take the lowest indices by a scan
+      n = n_above;
+      for (int i = 0; i < vocab && n < kTopCap; ++i) {
+        const __nv_bfloat16 v = lv.at(i);
+        if (key16(v) == thr) {
+          cand_i[n] = i;
+          cand_v[n] = __bfloat162float(v);
+          ++n;
+        }
+      }
+    }
+    // insertion sort: value descending, index ascending (n <= 96)
+    for (int a = 1; a < n; ++a) {
+      const int ci = cand_i[a];
+      const float cv = cand_v[a];
+      int p = a - 1;
+      while (p >= 0 && (cand_v[p] < cv || (cand_v[p] == cv && cand_i[p] > ci))) {
+        cand_i[p + 1] = cand_i[p];
+        cand_v[p + 1] = cand_v[p];
+        --p;
+      }
+      cand_i[p + 1] = ci;
+      cand_v[p + 1] = cv;
+    }
+    for (int j = 0; j < n_top; ++j) {
+      top_ids[(int64_t)row * n_top + j] = j < n ? cand_i[j] : -1;
+      top_lp[(int64_t)row * n_top + j] = j < n ? cand_v[j] - lse : -INFINITY;
+    }
+  }
+}
+
 }  // namespace
+
+int logprob_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
+                 const int32_t* tok, int n_top, float* out_lp, int32_t* top_ids, float* top_lp, cudaStream_t s) {
+  B200_REQUIRE(logits && out_lp, B200_ERR_INVALID, "logprobs: null argument");
+  B200_REQUIRE(n_top >= 0 && n_top <= 32 && (n_top == 0 || (top_ids && top_lp)), B200_ERR_INVALID,
+               "logprobs: n_top=%d outside [0,32] or no output for it", n_top);
+  B200_REQUIRE(vocab > 0 && seg_len > 0 && vocab % seg_len == 0, B200_ERR_INVALID, "logprobs: vocab=%d seg_len=%d", vocab,
+               seg_len);
+  if (n_rows == 0) return B200_OK;
+  B200_CUDA(launch(logprob_kernel, dim3(n_rows), dim3(kSampleThreads), (size_t)0, s, logits, ld, vocab, seg_len, seg_stride,
+                   tok, n_top, out_lp, top_ids, top_lp));
+  return B200_OK;
+}
 
 int sample_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
                 const float* temperature, const int32_t* top_k, const float* top_p, const uint64_t* seeds,

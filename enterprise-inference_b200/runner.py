@@ -99,6 +99,8 @@ class ModelRunner:
         self.max_logit_rows = min(max_tokens, 512)
         self._h_sample = torch.zeros(self.max_logit_rows * 32, dtype=torch.uint8).pin_memory()
         self._h_sample_np = self._h_sample.numpy()
+        self._h_lp_tok = torch.zeros(self.max_logit_rows, dtype=torch.int32).pin_memory()
+        self._h_lp_out = torch.zeros(self.max_logit_rows * (1 + 2 * 32), dtype=torch.float32).pin_memory()
 
     # ---- weights ---------------------------------------------------------------------------
     def _set(self, layer: int, kind: int, t: torch.Tensor):
@@ -250,6 +252,22 @@ class ModelRunner:
         """Tokens for the logit rows of the LAST step under per-row (temperature, top_k, top_p, seed, draw);
         temperature 0 rows return the step's greedy token.  The greedy hot path never calls this."""
         return self.sample_packed(self.pack_sampling(temperature, top_k, top_p, seeds, draws), sync)
+
+    def logprobs_last(self, token_ids, n_top: int = 0):
+        """Log-probabilities (log softmax of the raw logits) of `token_ids` under the LAST step's logit rows, plus
+        the n_top most likely tokens per row: (logprob[n], top_ids[n, n_top], top_logprobs[n, n_top])."""
+        n = len(token_ids)
+        if not 0 < n <= self.max_logit_rows or not 0 <= n_top <= 32:
+            raise ValueError(f"logprobs_last: {n} rows / n_top {n_top} out of range")
+        self._h_lp_tok.numpy()[:n] = token_ids
+        _abi.check(self.lib.b200_ctx_logprobs_last(self.ctx, n, self._h_lp_tok.data_ptr(), n_top, self._h_lp_out.data_ptr(),
+                                                   self.stream.cuda_stream))
+        self.stream.synchronize()
+        out = self._h_lp_out.numpy()
+        lp = out[:n].copy()
+        ids = out[n:n + n * n_top].view(np.int32).reshape(n, n_top).copy()
+        tlp = out[n + n * n_top:n + 2 * n * n_top].reshape(n, n_top).copy()
+        return lp, ids, tlp
 
     def last_step_launches(self) -> int:
         return int(self.lib.b200_ctx_last_step_launches(self.ctx))

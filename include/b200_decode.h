@@ -263,6 +263,19 @@ B200_API int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32_t
 B200_API int b200_ctx_sample_last(b200_ctx* ctx, int32_t n_rows, const void* host_params, int32_t* host_out_ids,
                          void* stream);
 
+/* (a10, widened) OpenAI `logprobs` / `top_logprobs`: log softmax over the raw logits (vLLM's default logprobs mode,
+ * [V22] vllm/v1/sample/sampler.py:90-118).  out_logprob[r] = l[token_ids[r]] - logsumexp(l); out_top_ids /
+ * out_top_logprobs [r][n_top] = the n_top (<= 32) most likely tokens, value descending, ties by lowest index
+ * (may be NULL when n_top == 0).  Device pointers. */
+B200_API int b200_logprobs(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const int32_t* token_ids,
+                  int32_t n_top, float* out_logprob, int32_t* out_top_ids, float* out_top_logprobs, void* stream);
+
+/* The same over the logit rows of the LAST step of this ctx (a collective under tensor parallelism, like
+ * b200_ctx_sample_last).  host_out receives float logprob[n] | int32 top_ids[n][n_top] | float top_logprobs[n][n_top]
+ * (4 n (1 + 2 n_top) bytes), asynchronously. */
+B200_API int b200_ctx_logprobs_last(b200_ctx* ctx, int32_t n_rows, const int32_t* host_token_ids, int32_t n_top,
+                           void* host_out, void* stream);
+
 /* (a0) device-side scheduler advance for pure-decode rows: ids[t]=sampled[t], positions[t]+=1,
  * ctx_lens[t]=positions[t]+1, slot_mapping[t] from the block table.  The image's scheduler does this
  * on the host every iteration ([V22] vllm/v1/attention/backends/cpu_attn.py:107-117 metadata build);

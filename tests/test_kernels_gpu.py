@@ -337,6 +337,31 @@ def test_sample_support_and_frequencies_match_the_oracle(lib, abi, T, k, p):
     assert bool(((freq - ref).abs() <= 4.5 * sigma + 2e-3).all()), float(((freq - ref).abs() - 4.5 * sigma).max())
 
 
+@pytest.mark.parametrize("V,n_top", [(5003, 5), (32000, 20), (300, 0), (64, 32)])
+def test_logprobs_match_log_softmax(lib, abi, V, n_top):
+    """b200_logprobs: log softmax of the raw logits for the chosen token and the n_top most likely tokens (value
+    descending, ties by lowest index) against torch.log_softmax in fp32."""
+    g = torch.Generator().manual_seed(V + n_top)
+    R = 7
+    lg = (torch.randn(R, V, generator=g) * 3).to(BF)
+    lg[2, 10] = lg[2, 3] = lg[2].float().max() + 2            # a tie at the top
+    lg[3] = 0.5                                               # fully degenerate row: every token ties
+    tok = torch.randint(0, V, (R,), generator=g, dtype=torch.int32)
+    out_lp = torch.empty(R, dtype=torch.float32, device="cuda")
+    out_ids = torch.empty(R, max(n_top, 1), dtype=torch.int32, device="cuda")
+    out_tlp = torch.empty(R, max(n_top, 1), dtype=torch.float32, device="cuda")
+    sync_check(abi, lib.b200_logprobs(dev(lg).data_ptr(), V, R, V, dev(tok).data_ptr(), n_top, out_lp.data_ptr(),
+                                      out_ids.data_ptr() if n_top else None, out_tlp.data_ptr() if n_top else None, None))
+    ref = torch.log_softmax(lg.float(), dim=-1)
+    assert torch.allclose(out_lp.cpu(), ref[torch.arange(R), tok.long()], atol=2e-5, rtol=1e-5)
+    if n_top:
+        k = min(n_top, V)
+        # expected order: value descending, index ascending among equals
+        order = torch.stack([torch.tensor(sorted(range(V), key=lambda i: (-float(lg[r, i]), i))[:k]) for r in range(R)])
+        assert torch.equal(out_ids.cpu()[:, :k].long(), order)
+        assert torch.allclose(out_tlp.cpu()[:, :k], torch.gather(ref, 1, order), atol=2e-5, rtol=1e-5)
+
+
 def test_ctx_sample_last_follows_the_step(lib, abi):
     """b200_ctx_sample_last over the logits of the last step: temperature 0 reproduces the step's greedy tokens."""
     import numpy as np
@@ -356,6 +381,9 @@ def test_ctx_sample_last_follows_the_step(lib, abi):
     assert same.tolist() == greedy
     hot = r.sample_last([5.0] * T, [0] * T, [1.0] * T, [1, 2, 3, 4], [0] * T)
     assert all(0 <= t < cfg.vocab for t in hot.tolist())
+    lp, ids, tlp = r.logprobs_last(greedy, 3)
+    assert ids[:, 0].tolist() == greedy                       # the greedy token is the most likely one
+    assert np.allclose(lp, tlp[:, 0]) and (tlp[:, 0] >= tlp[:, 1]).all() and (lp <= 0).all()
     r.close()
 
 
