@@ -68,6 +68,7 @@ class Request:
     top_k: int = 0
     top_p: float = 1.0
     seed: Optional[int] = None          # None: drawn once when the request is added
+    logprobs: Optional[int] = None      # None: off; N >= 0: logprob of each emitted token + the N most likely
     arrival: float = field(default_factory=time.monotonic)
     # state
     output_ids: List[int] = field(default_factory=list)
@@ -79,6 +80,7 @@ class Request:
     first_token_time: Optional[float] = None
     finish_time: Optional[float] = None
     token_times: List[float] = field(default_factory=list)
+    logprob_data: List[tuple] = field(default_factory=list)   # per emitted token: (logprob, [(id, logprob), ...])
 
     @property
     def all_ids(self) -> List[int]:
@@ -296,6 +298,15 @@ class LLMEngine:
             sampled = list(self.runner.sample_last([r.temperature for r in rows], [r.top_k for r in rows],
                                                    [r.top_p for r in rows], [r.seed or 0 for r in rows],
                                                    [len(r.output_ids) for r in rows]))
+        if sampled and any(s.samples and s.req.logprobs is not None for s in sched):
+            # log softmax of the raw logits for the tokens just chosen (+ the N most likely), same logits buffer
+            rows = [s.req for s in sched if s.samples]
+            n_top = min(max((r.logprobs or 0) for r in rows), 32)
+            lp, ids, tlp = self.runner.logprobs_last([int(t) for t in sampled], n_top)
+            for i, r in enumerate(rows):
+                if r.logprobs is not None:
+                    k = min(r.logprobs, n_top)
+                    r.logprob_data.append((float(lp[i]), [(int(ids[i, j]), float(tlp[i, j])) for j in range(k)]))
         done = self.scheduler.commit(sched, sampled)
         for r in done:
             self.requests.pop(r.request_id, None)

@@ -10,7 +10,8 @@ and templates/deployment.yaml:66-87.  HTTP surface: /root/reference/docs/api-spe
 (observability/xeon-exporter/grafana-xeon-dashboard.json), GET /v1/models (docs/getting-started-example.md:79-81).
 "temperature": 0 (what the reference's clients send) is the device's argmax; temperature / top_p / top_k /
 seed sample on the device (csrc/sample.cu) with vLLM's semantics and defaults (the model's generation_config.json,
-else temperature 1); penalties, logit_bias, min_p, logprobs, n > 1 and guided decoding are accepted and ignored
+else temperature 1), `logprobs` / `top_logprobs` come from a log-softmax kernel over the same logits; penalties,
+logit_bias, min_p and guided decoding are accepted and ignored
 or rejected (best_of != n, beam search); n parallel samples run as n engine requests.  /v1/embeddings is served by TEI in the reference, not here.
 """
 from __future__ import annotations
@@ -387,7 +388,42 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                        ignore_eos=bool(body.ignore_eos), eos_token_ids=eos_ids,
                        stop_token_ids=tuple(body.stop_token_ids or ()), min_tokens=body.min_tokens or 0,
                        temperature=max(float(temperature), 0.0), top_k=max(int(top_k), 0),
-                       top_p=min(max(float(top_p), 0.0), 1.0), seed=body.seed)
+                       top_p=min(max(float(top_p), 0.0), 1.0), seed=body.seed, logprobs=want_logprobs(body))
+
+    def want_logprobs(body: _Sampling) -> Optional[int]:
+        """None: off.  Completions: `logprobs: N`; chat: `logprobs: true` + `top_logprobs: N`."""
+        lp = body.logprobs
+        if lp is None or lp is False:
+            return None
+        if lp is True:
+            return int(getattr(body, "top_logprobs", None) or 0)
+        return int(lp)
+
+    def tok_str(t: int) -> str:
+        return tokenizer.decode([int(t)], skip_special_tokens=False)
+
+    def format_logprobs(entries, token_ids, chat: bool, offset0: int = 0):
+        """OpenAI shapes (docs/api-spec.yaml): completions = parallel arrays, chat = one object per token."""
+        if chat:
+            content = []
+            for tid, (lp, top) in zip(token_ids, entries):
+                ts = tok_str(tid)
+                content.append({"token": ts, "logprob": lp, "bytes": list(ts.encode("utf-8")),
+                                "top_logprobs": [{"token": tok_str(a), "logprob": b, "bytes": list(tok_str(a).encode("utf-8"))}
+                                                 for a, b in top]})
+            return {"content": content}
+        out = {"text_offset": [], "token_logprobs": [], "tokens": [], "top_logprobs": []}
+        off = offset0
+        for tid, (lp, top) in zip(token_ids, entries):
+            ts = tok_str(tid)
+            out["text_offset"].append(off)
+            off += len(ts)
+            out["tokens"].append(ts)
+            out["token_logprobs"].append(lp)
+            alts = {tok_str(a): b for a, b in top}
+            alts.setdefault(ts, lp)      # the chosen token is always listed (vLLM does the same)
+            out["top_logprobs"].append(alts)
+        return out
 
     class Detok:
         """Incremental detokenisation + stop strings."""
@@ -428,6 +464,9 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
             return error(400, "best_of != n and beam search are not supported by this backend")
         if not 1 <= n <= 16:
             return error(400, "n must be between 1 and 16")
+        nlp = want_logprobs(body)
+        if nlp is not None and not 0 <= nlp <= 20:
+            return error(400, "logprobs / top_logprobs must be between 0 and 20")
         # n parallel samples = n engine requests over the same prompt (vLLM: child i samples with seed + i)
         reqs = []
         for i in range(n):
@@ -447,6 +486,17 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
         rid = req0.request_id if not chat else "chat" + req0.request_id
         obj = "chat.completion" if chat else "text_completion"
         detoks = [Detok(body) for _ in reqs]
+        lp_seen = [0] * n
+
+        def pending_logprobs(i: int):
+            """Log-probabilities of request i's tokens not yet sent (None when the request did not ask)."""
+            r_ = reqs[i]
+            if r_.logprobs is None:
+                return None
+            a, b_ = lp_seen[i], min(len(r_.logprob_data), len(r_.output_ids))   # the engine thread appends both
+            lp_seen[i] = b_
+            off = sum(len(tok_str(t)) for t in r_.output_ids[:a]) if not chat else 0
+            return format_logprobs(r_.logprob_data[a:b_], r_.output_ids[a:b_], chat, off)
 
         def usage():
             done = sum(len(r_.output_ids) for r_ in reqs)
@@ -503,14 +553,14 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                             delta = {"content": text}
                             if first[i]:
                                 delta["role"] = "assistant"
-                            choice = {"index": i, "delta": delta if kind == "delta" else {}, "logprobs": None,
+                            choice = {"index": i, "delta": delta if kind == "delta" else {}, "logprobs": pending_logprobs(i),
                                       "finish_reason": finish}
                             chunk = {"id": rid, "object": "chat.completion.chunk", "created": created,
                                      "model": served_model_name, "choices": [choice]}
                         else:
                             chunk = {"id": rid, "object": "text_completion", "created": created, "model": served_model_name,
-                                     "choices": [{"index": i, "text": text, "logprobs": None, "finish_reason": finish,
-                                                  "stop_reason": None}]}
+                                     "choices": [{"index": i, "text": text, "logprobs": pending_logprobs(i),
+                                                  "finish_reason": finish, "stop_reason": None}]}
                         if include_usage:
                             chunk["usage"] = usage() if cont else None
                         first[i] = False
@@ -540,9 +590,9 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                     if tool_calls:
                         finish = "tool_calls"
                 choices.append({"index": i, "message": {"role": "assistant", "content": content, "tool_calls": tool_calls},
-                                "logprobs": None, "finish_reason": finish, "stop_reason": None})
+                                "logprobs": pending_logprobs(i), "finish_reason": finish, "stop_reason": None})
             else:
-                choices.append({"index": i, "text": (prompt_text + text) if body.echo else text, "logprobs": None,
+                choices.append({"index": i, "text": (prompt_text + text) if body.echo else text, "logprobs": pending_logprobs(i),
                                 "finish_reason": finish, "stop_reason": None})
         return {"id": rid, "object": obj, "created": created, "model": served_model_name, "choices": choices, "usage": usage()}
 

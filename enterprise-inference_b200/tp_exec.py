@@ -16,7 +16,7 @@ import torch
 import torch.distributed as dist
 
 HEADER = 8   # T, R, S, bt_stride, max_ctx, n_ints, opcode, reserved
-OP_STEP, OP_STOP, OP_SAMPLE = 1, 2, 3
+OP_STEP, OP_STOP, OP_SAMPLE, OP_LOGPROBS = 1, 2, 3, 4
 
 
 class TPLeader:
@@ -45,6 +45,16 @@ class TPLeader:
         dist.broadcast(r._h_sample[:32 * n], src=0, group=self.group)
         return r.sample_packed(n)
 
+    def logprobs_last(self, token_ids, n_top: int = 0):
+        """Log-probabilities over the last step's logits: a collective like sample_last (rank 0 returns the result)."""
+        r = self.runner
+        n = len(token_ids)
+        self._hdr[:7] = torch.tensor([n, n_top, 0, 0, 0, 0, OP_LOGPROBS], dtype=torch.int32)
+        dist.broadcast(self._hdr, src=0, group=self.group)
+        toks = torch.tensor([int(t) for t in token_ids], dtype=torch.int32)
+        dist.broadcast(toks, src=0, group=self.group)
+        return r.logprobs_last(toks.tolist(), n_top)
+
     def stop(self):
         self._hdr[6] = OP_STOP
         dist.broadcast(self._hdr, src=0, group=self.group)
@@ -62,6 +72,11 @@ def worker_loop(runner, group=None) -> None:
         T, R, S, bt_stride, max_ctx, n_ints, op = (int(v) for v in hdr[:7])
         if op == OP_STOP:
             return
+        if op == OP_LOGPROBS:
+            toks = torch.zeros(T, dtype=torch.int32)
+            dist.broadcast(toks, src=0, group=group)
+            runner.logprobs_last(toks.tolist(), R)
+            continue
         if op == OP_SAMPLE:
             dist.broadcast(runner._h_sample[:32 * T], src=0, group=group)
             runner.sample_packed(T)

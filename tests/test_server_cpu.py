@@ -38,6 +38,15 @@ class FakeRunner:
         return np.array([t + 1 if temperature[i] > 0 else t for i, t in enumerate(self.last)], dtype=np.int32)
 
 
+    def logprobs_last(self, token_ids, n_top=0):
+        """logprob of the chosen token = -0.25; alternatives = the next token ids with -1, -2, ..."""
+        n = len(token_ids)
+        lp = np.full(n, -0.25, dtype=np.float32)
+        ids = np.array([[(int(t) + j) % 251 for j in range(n_top)] for t in token_ids], dtype=np.int32).reshape(n, n_top)
+        tlp = np.array([[-0.25 - j for j in range(n_top)] for _ in token_ids], dtype=np.float32).reshape(n, n_top)
+        return lp, ids, tlp
+
+
 def expect_ids(prompt_ids, n):
     ids = list(prompt_ids)
     for _ in range(n):
@@ -261,3 +270,26 @@ def test_utility_routes(client):
     assert t["count"] == len(t["tokens"]) > 0 and t["tokens"] == client.tok.encode("What is Deep Learning?")
     d = client.post("/detokenize", json={"model": MODEL, "tokens": t["tokens"]}).json()
     assert d["prompt"].endswith("What is Deep Learning?")
+
+
+def test_logprobs_shapes(client):
+    """`logprobs` (completions: N) and `logprobs` + `top_logprobs` (chat) in the OpenAI shapes of docs/api-spec.yaml."""
+    ids = client.tok.encode("abc")
+    toks = expect_ids(ids, 4)
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 4, "temperature": 0, "logprobs": 2}).json()
+    lp = r["choices"][0]["logprobs"]
+    assert lp["tokens"] == [client.tok.decode([t], skip_special_tokens=False) for t in toks]
+    assert lp["token_logprobs"] == [-0.25] * 4 and len(lp["top_logprobs"]) == 4 and lp["text_offset"][0] == 0
+    assert all(len(d) in (1, 2) and min(d.values()) >= -1.25 for d in lp["top_logprobs"])
+    r = client.post("/v1/chat/completions", json={"model": MODEL, "messages": [{"role": "user", "content": "hi"}], "max_tokens": 3,
+                                                  "temperature": 0, "logprobs": True, "top_logprobs": 3}).json()
+    content = r["choices"][0]["logprobs"]["content"]
+    assert len(content) == 3 and all(len(c["top_logprobs"]) == 3 and c["logprob"] == -0.25 and "bytes" in c for c in content)
+    r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 2, "temperature": 0}).json()
+    assert r["choices"][0]["logprobs"] is None
+    assert client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "temperature": 0, "logprobs": 50}).status_code == 400
+    with client.stream("POST", "/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 4, "temperature": 0,
+                                                        "logprobs": 1, "stream": True}) as resp:
+        chunks = [json.loads(l[6:]) for l in resp.iter_lines() if l.startswith("data: ") and l != "data: [DONE]"]
+    got = [t for c in chunks if c["choices"] and c["choices"][0]["logprobs"] for t in c["choices"][0]["logprobs"]["tokens"]]
+    assert got == lp["tokens"]
