@@ -139,6 +139,15 @@ def test_engine_sampling_is_seeded_and_mixes_with_greedy(golden_dir):
     assert a[0] == b[0]                               # same seed, same tokens (whatever else is in the batch)
     assert a[0] != a[2] and a[0] != greedy[0]         # another seed / not the argmax path
     assert all(0 <= t < cfg.vocab for o in a for t in o)
+    # logprobs of a greedy request: the chosen token is the most likely one, values are log-probabilities
+    eng = E.LLMEngine(r, max_num_batched_tokens=64, max_num_seqs=8, max_model_len=1024)
+    q = E.Request("lp", list(prompt), max_tokens=6, ignore_eos=True, logprobs=3)
+    eng.add_request(q)
+    while eng.has_work():
+        eng.step()
+    assert len(q.logprob_data) == 6
+    for tok, (lp, top) in zip(q.output_ids, q.logprob_data):
+        assert top[0][0] == tok and abs(top[0][1] - lp) < 1e-6 and lp <= 0 and top[0][1] >= top[1][1] >= top[2][1]
     r.close()
 
 
