@@ -92,6 +92,30 @@ def test_tp2_serving_executor_generates_oracle_tokens():
                 if a != b:
                     assert float(O.top2_margin(logits[i])) < 0.08
                     break
+        # sampling and logprobs are collectives over the vocab shards: seeded draws replay, top_k = 1 and the
+        # top-1 logprob agree with the greedy token
+        def run(specs):
+            eng2 = E.LLMEngine(leader, max_num_batched_tokens=64, max_num_seqs=4, max_model_len=512)
+            reqs = [E.Request(f"s{i}", list(prompts[0]), max_tokens=8, ignore_eos=True, **kw) for i, kw in enumerate(specs)]
+            for q in reqs:
+                eng2.add_request(q)
+            while eng2.has_work():
+                eng2.step()
+            return reqs
+        a = run([dict(temperature=1.2, seed=5), dict(temperature=0.9, top_k=1, seed=9), dict(logprobs=2)])
+        b = run([dict(temperature=1.2, seed=5), dict(temperature=1.2, seed=6), dict()])
+        assert a[0].output_ids == b[0].output_ids, "a seeded request must replay its tokens"
+        assert a[0].output_ids != b[1].output_ids, "another seed, another stream"
+        assert a[2].output_ids == b[2].output_ids, "greedy rows do not depend on their neighbours' sampling"
+        # top_k = 1 is the argmax unless the two best bf16 logits tie (both are then kept, as in vLLM)
+        for i, (x, y) in enumerate(zip(a[1].output_ids, a[2].output_ids)):
+            if x != y:
+                top = a[2].logprob_data[i][1]
+                assert top[0][1] == top[1][1], f"top_k=1 left the argmax at step {i} without a tie"
+                break
+        assert all(0 <= t < cfg.vocab for t in a[0].output_ids)
+        for tok, (lp, top) in zip(a[2].output_ids, a[2].logprob_data):
+            assert top[0][0] == tok and abs(top[0][1] - lp) < 1e-6 and lp <= 0
     finally:
         TP.shutdown(leader, procs)
     assert all(p.exitcode == 0 for p in procs)
