@@ -1,6 +1,9 @@
 """CPU oracle for the decode hot path (TEST INFRASTRUCTURE — never the product path).
 
-PARITY UNPINNED.  The reference (psurabh/Enterprise-Inference v1.3.0) holds no source
+PARITY UNPINNED end to end; operators pinned.  (R1-R3 and R5 below equal vLLM's own native-path operators bit
+for bit, and the sampler's top-k/top-p masks equal vLLM's: tests/golden/vllm_native_ops.npz and
+sampling_masks.npz, captured from the `vllm` package by tools/make_vllm_op_golden.py / make_sampling_golden.py.
+No output of the v0.10.2 CPU image itself is available, so whole-model parity stays unpinned.)  The reference (psurabh/Enterprise-Inference v1.3.0) holds no source
 for this path: its chart only names the third-party image
 ``public.ecr.aws/q9t5s3a7/vllm-cpu-release-repo:v0.10.2``
 (/root/reference/core/helm-charts/vllm/values.yaml:23-28,

@@ -111,3 +111,32 @@ def test_sampling_probs_match_vllm_masks():
         # the kept probabilities are the softmax of logits / T restricted to the kept set
         ref = (logits.float() / float(T)).masked_fill(~keep, float("-inf")).softmax(-1)
         assert torch.allclose(probs, ref, atol=1e-6)
+
+
+def _bf(a):
+    import numpy as np
+    return torch.from_numpy(np.ascontiguousarray(a)).view(torch.bfloat16)
+
+
+def test_oracle_ops_equal_vllm_native_ops_bit_for_bit():
+    """The oracle's rounding points against vLLM's OWN native-path operators (RMSNorm / fused add+RMSNorm,
+    SiluAndMul, Llama3 and plain rotary embedding: cache and application), outputs captured from the `vllm`
+    package by tools/make_vllm_op_golden.py.  Bit equality pins R1-R3 and R5 at the operator level."""
+    import numpy as np
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "vllm_native_ops.npz"))
+    for h in (256, 4096):
+        x, res, w = _bf(z[f"rms_x_{h}"]), _bf(z[f"rms_res_{h}"]), _bf(z[f"rms_w_{h}"])
+        assert torch.equal(O.rms_norm(x, w, 1e-5), _bf(z[f"rms_y_{h}"]))
+        y, r = O.add_rms_norm(x, res, w, 1e-5)
+        assert torch.equal(y, _bf(z[f"addrms_y_{h}"])) and torch.equal(r, _bf(z[f"addrms_res_{h}"]))
+    assert torch.equal(O.silu_mul(_bf(z["silu_gu"])), _bf(z["silu_y"]))
+    pos = torch.from_numpy(z["rope_pos"])
+    rows = torch.from_numpy(z["rope_cache_rows"])
+    q, k = _bf(z["rope_q"]), _bf(z["rope_k"])
+    for name, cfg in (("llama3", O.CONFIGS["llama-3.1-8b"]), ("plain", O.CONFIGS["qwen2-32b"])):
+        cache = O.cos_sin_cache(cfg, 8192)
+        assert torch.equal(cache[rows], _bf(z[f"rope_cache_{name}"])), f"{name}: cos/sin cache differs"
+        cs = cache[pos]
+        q2 = O.rope_apply(q.view(len(pos), 4, 128), cs[:, :64], cs[:, 64:]).reshape(len(pos), -1)
+        k2 = O.rope_apply(k.view(len(pos), 2, 128), cs[:, :64], cs[:, 64:]).reshape(len(pos), -1)
+        assert torch.equal(q2, _bf(z[f"rope_q_{name}"])) and torch.equal(k2, _bf(z[f"rope_k_{name}"]))
