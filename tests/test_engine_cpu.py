@@ -90,3 +90,43 @@ def test_stop_conditions_and_limits():
         eng.add_request(E.Request("c", [], max_tokens=1))
     with pytest.raises(ValueError):
         eng.add_request(E.Request("d", [1] * 60, max_tokens=10))
+
+
+from hypothesis import given, settings, strategies as st, HealthCheck
+
+
+@settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(
+    prompts=st.lists(st.lists(st.integers(0, 96), min_size=1, max_size=20), min_size=1, max_size=7),
+    max_new=st.lists(st.integers(1, 9), min_size=7, max_size=7),
+    arrivals=st.lists(st.integers(0, 6), min_size=7, max_size=7),
+    n_blocks=st.integers(8, 24), budget=st.sampled_from([4, 8, 16]), max_seqs=st.integers(1, 5),
+)
+def test_scheduler_property_any_arrival_pattern_matches_sequential(prompts, max_new, arrivals, n_blocks, budget, max_seqs):
+    """Whatever the arrival pattern, token budget, sequence cap and cache size (preemptions included): every
+    request gets exactly the tokens a sequential run would give it, a step never exceeds the budget or the
+    sequence cap, no cache block is shared by two running requests, and every block comes back."""
+    bs = 4
+    need = max((len(p) + max_new[i] + bs - 1) // bs for i, p in enumerate(prompts))
+    if need > n_blocks:          # a single sequence must fit (the engine raises OutOfBlocks otherwise, tested elsewhere)
+        n_blocks = need
+    fr = FakeRunner(n_blocks=n_blocks, block_size=bs, max_tokens=budget, max_model_len=64)
+    eng = E.LLMEngine(fr, max_num_batched_tokens=budget, max_num_seqs=max_seqs, max_model_len=64)
+    reqs = [E.Request(f"r{i}", list(p), max_tokens=max_new[i], ignore_eos=True) for i, p in enumerate(prompts)]
+    pending = sorted(range(len(reqs)), key=lambda i: arrivals[i])
+    step = 0
+    while pending or eng.has_work():
+        while pending and arrivals[pending[0]] <= step:
+            eng.add_request(reqs[pending.pop(0)])
+        if eng.has_work():
+            n_before = len(fr.batches)
+            eng.step()
+            for b in fr.batches[n_before:]:
+                assert b.n_tokens <= budget and len(b.block_tables) <= max_seqs
+            used = [blk for r in eng.scheduler.running for blk in r.block_table]
+            assert len(used) == len(set(used)), "a cache block is owned by two running requests"
+        step += 1
+        assert step < 2000
+    for r, p, n in zip(reqs, prompts, max_new):
+        assert r.finished and r.output_ids == expect(p, n)
+    assert len(eng.blocks.free) == n_blocks
