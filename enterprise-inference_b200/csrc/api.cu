@@ -890,13 +890,13 @@ extern "C" int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32
                            int32_t* out_ids, void* stream) {
   B200_REQUIRE(n_rows >= 0 && vocab > 0 && ld >= vocab, B200_ERR_INVALID, "sample: bad sizes (rows=%d vocab=%d ld=%lld)",
                n_rows, vocab, (long long)ld);
-  return sample_rows((const __nv_bfloat16*)logits, ld, n_rows, vocab, vocab, 0, temperature, top_k, top_p, seeds, draws,
-                     out_ids, (cudaStream_t)stream);
+  return sample_rows((const __nv_bfloat16*)logits, ld, n_rows, vocab, vocab, 0, temperature, top_k, top_p, nullptr, seeds,
+                     draws, out_ids, (cudaStream_t)stream);
 }
 
 // The rows are the logit rows of the LAST step of this ctx (its logits are still in the ctx's buffer).
 // host_params: n_rows x {float temperature; int32 top_k; float top_p; uint32 pad; uint64 seed; uint64 draw} as
-// five arrays back to back: temperature[n] | top_k[n] | top_p[n] | pad[n] | seed[n] | draw[n]  (32 n bytes).
+// six arrays back to back: temperature[n] | top_k[n] | top_p[n] | min_p[n] | seed[n] | draw[n]  (32 n bytes).
 extern "C" int b200_ctx_sample_last(b200_ctx* c, int32_t n_rows, const void* host_params, int32_t* host_out_ids,
                                     void* stream) {
   B200_REQUIRE(c && host_params && host_out_ids, B200_ERR_INVALID, "sample_last: null argument");
@@ -909,6 +909,7 @@ extern "C" int b200_ctx_sample_last(b200_ctx* c, int32_t n_rows, const void* hos
   const float* temperature = reinterpret_cast<const float*>(base);
   const int32_t* top_k = reinterpret_cast<const int32_t*>(base + 4 * n);
   const float* top_p = reinterpret_cast<const float*>(base + 8 * n);
+  const float* min_p = reinterpret_cast<const float*>(base + 12 * n);   // 0 = off
   const uint64_t* seeds = reinterpret_cast<const uint64_t*>(base + 16 * n);
   const uint64_t* draws = reinterpret_cast<const uint64_t*>(base + 24 * n);
   const int W = c->cfg.tp_world;
@@ -918,10 +919,10 @@ extern "C" int b200_ctx_sample_last(b200_ctx* c, int32_t n_rows, const void* hos
     // is deterministic given the seed)
     B200_NCCL(nccl().AllGather(c->logits, c->logits_full, (size_t)n * c->vocab_local, ncclBfloat16, c->comm, s));
     rc = sample_rows(c->logits_full, c->vocab_local, n_rows, c->vocab_local * W, c->vocab_local, n * c->vocab_local,
-                     temperature, top_k, top_p, seeds, draws, c->d_tokens, s);
+                     temperature, top_k, top_p, min_p, seeds, draws, c->d_tokens, s);
   } else {
-    rc = sample_rows(c->logits, c->vocab_local, n_rows, c->vocab_local, c->vocab_local, 0, temperature, top_k, top_p, seeds,
-                     draws, c->d_tokens, s);
+    rc = sample_rows(c->logits, c->vocab_local, n_rows, c->vocab_local, c->vocab_local, 0, temperature, top_k, top_p, min_p,
+                     seeds, draws, c->d_tokens, s);
   }
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(host_out_ids, c->d_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost, s));

@@ -101,7 +101,8 @@ struct RowView {
 __global__ void __launch_bounds__(kSampleThreads)
 sample_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, int seg_len, int64_t seg_stride,
               const float* __restrict__ temperature, const int32_t* __restrict__ top_k, const float* __restrict__ top_p,
-              const uint64_t* __restrict__ seeds, const uint64_t* __restrict__ draws, int32_t* __restrict__ out) {
+              const float* __restrict__ min_p, const uint64_t* __restrict__ seeds, const uint64_t* __restrict__ draws,
+              int32_t* __restrict__ out) {
   __shared__ Best sh_best[32];
   __shared__ unsigned int hist[256];
   __shared__ unsigned long long mass[256];
@@ -125,6 +126,11 @@ sample_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, i
   const int k = top_k ? top_k[row] : 0;
   const float p = top_p ? top_p[row] : 1.0f;
   uint32_t thr = 0;   // keep tokens with key16 >= thr
+  // min_p ([V22] vllm/v1/sample/logits_processor: after the temperature, before top-k/top-p): keep tokens whose
+  // probability is >= min_p x the largest one, i.e. (l - max) / T >= log(min_p).  The tokens it drops are the
+  // lowest ones, so the k-th largest value of top-k is unaffected; top-p's mass is taken over what it leaves.
+  const float mp = min_p ? min_p[row] : 0.f;
+  const float min_logit = (mp > 0.f && mp <= 1.f) ? vmax + T * logf(mp) : -INFINITY;
 
   // ---- top-k: key of the k-th largest value (two-level radix select on the 16-bit key)
   if (k > 0 && k < vocab) {
@@ -172,7 +178,7 @@ sample_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, i
       for (int i = tid; i < vocab; i += kSampleThreads) {
         const __nv_bfloat16 v = lv.at(i);
         const uint32_t key = key16(v);
-        if (key < thr) continue;
+        if (key < thr || __bfloat162float(v) < min_logit) continue;
         if (level == 1 && (key >> 8) != prefix) continue;
         const float e = __expf((__bfloat162float(v) - vmax) * inv_t);                    // in (0, 1]
         const unsigned long long fx = (unsigned long long)(e * 4294967296.0f);           // 2^-32 fixed point
@@ -216,7 +222,7 @@ sample_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, i
   Best s{-INFINITY, 0x7fffffff};
   for (int i = tid; i < vocab; i += kSampleThreads) {
     const __nv_bfloat16 v = lv.at(i);
-    if (key16(v) < thr) continue;
+    if (key16(v) < thr || __bfloat162float(v) < min_logit) continue;
     const float u = philox_uniform(seed, draw, (uint32_t)i);
     const float g = -logf(-logf(u));
     s = better(s, Best{(__bfloat162float(v) - vmax) * inv_t + g, i});
@@ -382,14 +388,45 @@ int logprob_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab,
 }
 
 int sample_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
-                const float* temperature, const int32_t* top_k, const float* top_p, const uint64_t* seeds,
-                const uint64_t* draws, int32_t* out, cudaStream_t s) {
+                const float* temperature, const int32_t* top_k, const float* top_p, const float* min_p,
+                const uint64_t* seeds, const uint64_t* draws, int32_t* out, cudaStream_t s) {
   B200_REQUIRE(logits && out, B200_ERR_INVALID, "sample: null argument");
   B200_REQUIRE(vocab > 0 && seg_len > 0 && vocab % seg_len == 0, B200_ERR_INVALID, "sample: vocab=%d seg_len=%d", vocab,
                seg_len);
   if (n_rows == 0) return B200_OK;
   B200_CUDA(launch(sample_kernel, dim3(n_rows), dim3(kSampleThreads), (size_t)0, s, logits, ld, vocab, seg_len, seg_stride,
-                   temperature, top_k, top_p, seeds, draws, out));
+                   temperature, top_k, top_p, min_p, seeds, draws, out));
+  return B200_OK;
+}
+
+// ---- sparse logit adjustments before sampling: repetition / presence / frequency penalties and logit_bias -------
+// ([V22] vllm/v1/sample/ops/penalties.py, logits_processor/builtin.py).  entry = {row, token, rep, add}:
+//   l = logits[row][token];  l = l > 0 ? l / rep : l * rep;  l += add      (rep = 1 and add = 0 leave it alone)
+// `add` carries logit_bias - presence_penalty - frequency_penalty * count, worked out by the host, which knows the
+// token counts.  The logits are bf16 (R6), so the adjusted value is rounded back to bf16.  With vocab-parallel
+// logits every rank applies the entries of its own shard: tokens outside [tok0, tok0 + vocab_local) are skipped.
+__global__ void adjust_logits_kernel(__nv_bfloat16* __restrict__ logits, int64_t ld, int n_rows, int tok0, int vocab_local,
+                                     const int4* __restrict__ entries, int n) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int4 e = entries[i];
+  const int row = e.x, tok = e.y - tok0;
+  if (row < 0 || row >= n_rows || tok < 0 || tok >= vocab_local) return;
+  const float rep = __int_as_float(e.z), add = __int_as_float(e.w);
+  __nv_bfloat16* p = logits + (int64_t)row * ld + tok;
+  float l = __bfloat162float(*p);
+  if (rep > 0.f && rep != 1.f) l = l > 0.f ? l / rep : l * rep;
+  *p = __float2bfloat16_rn(l + add);
+}
+
+int adjust_logits(__nv_bfloat16* logits, int64_t ld, int n_rows, int tok0, int vocab_local, const void* entries, int n,
+                  cudaStream_t s) {
+  B200_REQUIRE(logits && (entries || n == 0), B200_ERR_INVALID, "adjust_logits: null argument");
+  if (n <= 0) return B200_OK;
+  B200_CUDA(launch(adjust_logits_kernel, dim3((n + 255) / 256), dim3(256), (size_t)0, s, logits, ld, n_rows, tok0, vocab_local,
+                   static_cast<const int4*>(entries), n));
   return B200_OK;
 }
 

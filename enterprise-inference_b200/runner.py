@@ -226,7 +226,7 @@ class ModelRunner:
             _abi.ptr(logit_rows), R, out_tokens.data_ptr(), _abi.ptr(out_logits), s))
         return out_tokens
 
-    def pack_sampling(self, temperature, top_k, top_p, seeds, draws) -> int:
+    def pack_sampling(self, temperature, top_k, top_p, seeds, draws, min_p=None) -> int:
         """Per-row sampling parameters of the last step's logit rows into the pinned buffer
         (layout of b200_ctx_sample_last); returns the row count."""
         n = len(temperature)
@@ -236,7 +236,7 @@ class ModelRunner:
         a[0:4 * n].view(np.float32)[:] = temperature
         a[4 * n:8 * n].view(np.int32)[:] = top_k
         a[8 * n:12 * n].view(np.float32)[:] = top_p
-        a[12 * n:16 * n] = 0
+        a[12 * n:16 * n].view(np.float32)[:] = 0.0 if min_p is None else min_p
         a[16 * n:24 * n].view(np.uint64)[:] = np.asarray(seeds, dtype=np.uint64)
         a[24 * n:32 * n].view(np.uint64)[:] = np.asarray(draws, dtype=np.uint64)
         return n
@@ -248,10 +248,10 @@ class ModelRunner:
             self.stream.synchronize()
         return self._h_out_np[:n]
 
-    def sample_last(self, temperature, top_k, top_p, seeds, draws, sync: bool = True) -> np.ndarray:
+    def sample_last(self, temperature, top_k, top_p, seeds, draws, sync: bool = True, min_p=None) -> np.ndarray:
         """Tokens for the logit rows of the LAST step under per-row (temperature, top_k, top_p, seed, draw);
         temperature 0 rows return the step's greedy token.  The greedy hot path never calls this."""
-        return self.sample_packed(self.pack_sampling(temperature, top_k, top_p, seeds, draws), sync)
+        return self.sample_packed(self.pack_sampling(temperature, top_k, top_p, seeds, draws, min_p), sync)
 
     def logprobs_last(self, token_ids, n_top: int = 0):
         """Log-probabilities (log softmax of the raw logits) of `token_ids` under the LAST step's logit rows, plus

@@ -258,7 +258,7 @@ B200_API int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32_t
 /* Sampling over the logit rows of the LAST b200_decode_step[_host] of this ctx (they are still in the ctx's
  * buffer; with tensor parallelism the vocab shards are all-gathered first: a collective, call it on every rank
  * with the same arguments).  host_params = five host arrays back to back,
- *   float temperature[n] | int32 top_k[n] | float top_p[n] | uint32 pad[n] | uint64 seed[n] | uint64 draw[n],
+ *   float temperature[n] | int32 top_k[n] | float top_p[n] | float min_p[n] (0: off) | uint64 seed[n] | uint64 draw[n],
  * 32 n bytes; host_out_ids receives n token ids (asynchronously: synchronise the stream before reading). */
 B200_API int b200_ctx_sample_last(b200_ctx* ctx, int32_t n_rows, const void* host_params, int32_t* host_out_ids,
                          void* stream);
