@@ -273,15 +273,22 @@ def greedy(logits_bf16: torch.Tensor) -> torch.Tensor:
     return logits_bf16.float().argmax(dim=-1)
 
 
-def sampling_probs(logits_bf16: torch.Tensor, temperature: float, top_k: int = 0, top_p: float = 1.0) -> torch.Tensor:
+def sampling_probs(logits_bf16: torch.Tensor, temperature: float, top_k: int = 0, top_p: float = 1.0,
+                   min_p: float = 0.0) -> torch.Tensor:
     """The distribution vLLM's sampler draws from for one logits row [V] (temperature > 0): logits / T, top-k
     mask, top-p mask on the renormalised rest, softmax -- a restatement of
     [V22] vllm/v1/sample/sampler.py:235-256 (temperature, then the top-k/top-p sampler) and
     vllm/v1/sample/ops/topk_topp_sampler.py:328-370 (apply_top_k_top_p_pytorch: ascending sort, values below the
     k-th largest -> -inf, cumulative probability <= 1 - p -> -inf, the largest always kept).
-    Returns fp32 probabilities [V] (0 for dropped tokens).  Pinned against the vLLM function itself by
-    tests/golden/sampling_masks.npz (tools/make_sampling_golden.py)."""
+    Returns fp32 probabilities [V] (0 for dropped tokens).  Pinned against the vLLM functions themselves
+    (apply_top_k_top_p_pytorch, MinPLogitsProcessor.apply) by tests/golden/sampling_masks.npz
+    (tools/make_sampling_golden.py)."""
     x = logits_bf16.float() / float(temperature)
+    if min_p and min_p > 0.0:
+        # [V22] vllm/v1/sample/logits_processor/builtin.py:101 (MinPLogitsProcessor.apply), run by Sampler.sample after
+        # the temperature and before top-k/top-p: in PROBABILITY space, strict "<" (a token exactly at the cut stays)
+        pr = torch.nn.functional.softmax(x, dim=-1)
+        x = x.masked_fill(pr < torch.amax(pr, dim=-1, keepdim=True) * torch.tensor(min_p, dtype=torch.float32), float("-inf"))
     xs, idx = x.sort(descending=False)
     V = x.numel()
     if top_k and 0 < top_k < V:

@@ -140,3 +140,19 @@ def test_oracle_ops_equal_vllm_native_ops_bit_for_bit():
         q2 = O.rope_apply(q.view(len(pos), 4, 128), cs[:, :64], cs[:, 64:]).reshape(len(pos), -1)
         k2 = O.rope_apply(k.view(len(pos), 2, 128), cs[:, :64], cs[:, 64:]).reshape(len(pos), -1)
         assert torch.equal(q2, _bf(z[f"rope_q_{name}"])) and torch.equal(k2, _bf(z[f"rope_k_{name}"]))
+
+
+def test_sampling_probs_min_p_matches_vllm_masks():
+    """min_p: oracle.sampling_probs against the keep-masks of vLLM's own MinPLogitsProcessor.apply followed by its
+    top-k/top-p function (captured by tools/make_sampling_golden.py in Sampler.sample's order)."""
+    import numpy as np
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "sampling_masks.npz"))
+    seeds = sorted(int(k.split("_")[2]) for k in z.files if k.startswith("mp_logits_"))
+    assert len(seeds) >= 7
+    for sd in seeds:
+        logits = torch.from_numpy(z[f"mp_logits_{sd}"].copy()).view(torch.bfloat16)
+        T, mp, k, p = z[f"mp_params_{sd}"]
+        probs = O.sampling_probs(logits, float(T), int(k), float(p), min_p=float(mp))
+        keep = torch.from_numpy(z[f"mp_keep_{sd}"])
+        assert torch.equal(probs > 0, keep), f"min_p case {sd}: kept sets differ ({int((probs > 0).sum())} vs {int(keep.sum())})"
+        assert abs(float(probs.sum()) - 1.0) < 1e-5
