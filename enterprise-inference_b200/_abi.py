@@ -65,7 +65,7 @@ SIGNATURES = {
                                                 _i32, _i32, _f32, _vp]),
     "b200_silu_mul": (C.c_int, [_vp, _vp, _i32, _i32, _vp]),
     "b200_argmax": (C.c_int, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp]),
-    "b200_sample": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200_sample": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200_ctx_sample_last": (C.c_int, [_vp, _i32, _vp, _vp, _vp]),
     "b200_logprobs": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "b200_ctx_logprobs_last": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp]),

@@ -886,11 +886,11 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
 
 // (a10, widened) sampling ---------------------------------------------------------------------------------
 extern "C" int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const float* temperature,
-                           const int32_t* top_k, const float* top_p, const uint64_t* seeds, const uint64_t* draws,
-                           int32_t* out_ids, void* stream) {
+                           const int32_t* top_k, const float* top_p, const float* min_p, const uint64_t* seeds,
+                           const uint64_t* draws, int32_t* out_ids, void* stream) {
   B200_REQUIRE(n_rows >= 0 && vocab > 0 && ld >= vocab, B200_ERR_INVALID, "sample: bad sizes (rows=%d vocab=%d ld=%lld)",
                n_rows, vocab, (long long)ld);
-  return sample_rows((const __nv_bfloat16*)logits, ld, n_rows, vocab, vocab, 0, temperature, top_k, top_p, nullptr, seeds,
+  return sample_rows((const __nv_bfloat16*)logits, ld, n_rows, vocab, vocab, 0, temperature, top_k, top_p, min_p, seeds,
                      draws, out_ids, (cudaStream_t)stream);
 }
 

@@ -250,10 +250,13 @@ B200_API int b200_argmax(const void* logits, int64_t ld, int32_t n_rows, int32_t
  * ([V22] vllm/v1/sample/sampler.py:90-91,235-256, ops/topk_topp_sampler.py; fields of docs/api-spec.yaml).
  * temperature[r] <= 0 -> the argmax of b200_argmax.  top_k[r] <= 0 and top_p[r] >= 1 disable the filters.
  * The draw is a function of (seeds[r], draws[r], logits row): same inputs, same token.  All arrays are device
- * pointers of n_rows elements; temperature/top_k/top_p/seeds/draws may be NULL (0, off, off, 0, 0). */
+ * pointers of n_rows elements; temperature/top_k/top_p/min_p/seeds/draws may be NULL (0, off, off, off, 0, 0).
+ * min_p[r] in (0, 1]: tokens whose probability is below min_p x the largest one are dropped before top-k/top-p
+ * ([V22] vllm/v1/sample/logits_processor/builtin.py:101).  vLLM compares in probability space; this kernel compares
+ * the logit with max + T log(min_p), the same cut up to fp32 rounding of a token that sits exactly on it. */
 B200_API int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const float* temperature,
-                const int32_t* top_k, const float* top_p, const uint64_t* seeds, const uint64_t* draws,
-                int32_t* out_ids, void* stream);
+                const int32_t* top_k, const float* top_p, const float* min_p, const uint64_t* seeds,
+                const uint64_t* draws, int32_t* out_ids, void* stream);
 
 /* Sampling over the logit rows of the LAST b200_decode_step[_host] of this ctx (they are still in the ctx's
  * buffer; with tensor parallelism the vocab shards are all-gathered first: a collective, call it on every rank

@@ -3,6 +3,8 @@ Tolerances: bit-exact for integer/index/copy work (embed, KV append, argmax) and
 elementwise arithmetic of RoPE; for fp32-accumulated ops the only freedom is summation order, so
 the bar is <= 1 bf16 ulp on a small fraction of elements (stated per test)."""
 import numpy as np
+import os
+
 import pytest
 import torch
 
@@ -281,16 +283,18 @@ def test_argmax_exact_with_ties(lib, abi):
 
 
 # ---------------------------------------------------------------------------------------------
-def run_sample(lib, abi, logits, temperature, top_k, top_p, seeds, draws):
+def run_sample(lib, abi, logits, temperature, top_k, top_p, seeds, draws, min_p=None):
     R, V = logits.shape
     out = torch.empty(R, dtype=torch.int32, device="cuda")
     t = dev(torch.tensor(temperature, dtype=torch.float32))
     k = dev(torch.tensor(top_k, dtype=torch.int32))
     p = dev(torch.tensor(top_p, dtype=torch.float32))
+    mp = dev(torch.tensor(min_p, dtype=torch.float32)) if min_p is not None else None
     sd = dev(torch.tensor(seeds, dtype=torch.int64))
     dr = dev(torch.tensor(draws, dtype=torch.int64))
-    sync_check(abi, lib.b200_sample(dev(logits).data_ptr(), V, R, V, t.data_ptr(), k.data_ptr(), p.data_ptr(), sd.data_ptr(),
-                                    dr.data_ptr(), out.data_ptr(), None))
+    sync_check(abi, lib.b200_sample(dev(logits).data_ptr(), V, R, V, t.data_ptr(), k.data_ptr(), p.data_ptr(),
+                                    mp.data_ptr() if mp is not None else None, sd.data_ptr(), dr.data_ptr(),
+                                    out.data_ptr(), None))
     return out.cpu()
 
 
@@ -335,6 +339,40 @@ def test_sample_support_and_frequencies_match_the_oracle(lib, abi, T, k, p):
     freq = torch.bincount(got.long(), minlength=V).float() / R
     sigma = (ref * (1 - ref) / R).sqrt()
     assert bool(((freq - ref).abs() <= 4.5 * sigma + 2e-3).all()), float(((freq - ref).abs() - 4.5 * sigma).max())
+
+
+@pytest.mark.parametrize("seed", [21, 22, 23, 24, 25, 26, 27])
+def test_sample_min_p_against_vllm_masks(lib, abi, seed):
+    """min_p on the cases whose keep-masks were captured from vLLM's own MinPLogitsProcessor (+ its top-k/top-p).
+    vLLM cuts in probability space (p_i < min_p * p_max), the kernel in logit space (l_i < max + T log min_p): the same
+    cut except for a token whose p_i / p_max is within 1e-4 (relative) of min_p -- that BAND, and ties at the final cut
+    value, are the only tokens allowed to differ, and how many there are is part of the assertion message."""
+    import numpy as np
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "sampling_masks.npz"))
+    row = torch.from_numpy(z[f"mp_logits_{seed}"].copy()).view(BF)
+    T, mp, k, p = (float(v) for v in z[f"mp_params_{seed}"])
+    k = int(k)
+    keep = torch.from_numpy(z[f"mp_keep_{seed}"])
+    ratio = torch.from_numpy(z[f"mp_ratio_{seed}"])
+    probs = O.sampling_probs(row, T, k, p, min_p=mp)
+    assert torch.equal(probs > 0, keep)                       # the reference used below IS vLLM's kept set
+    band = (ratio / mp - 1).abs() < 1e-4
+    ties = row.float() == row.float()[keep].min()
+    allowed = keep | band | ties
+    V, R = row.numel(), 4096
+    got = run_sample(lib, abi, row[None].expand(R, V).contiguous(), [T] * R, [k] * R, [p] * R, [11] * R, list(range(R)),
+                     min_p=[mp] * R)
+    n_amb = int((band | ties).sum() - (keep & ties & ~band).sum())      # tokens the two formulations may treat differently
+    assert bool(allowed[got.long()].all()), f"a token vLLM drops was sampled (band+tie tokens: {n_amb})"
+    freq = torch.bincount(got.long(), minlength=V).float() / R
+    sigma = (probs * (1 - probs) / R).sqrt()
+    exact = ~(band | (ties & ~keep))                           # where the reference probability is unambiguous
+    if n_amb == 0:
+        exact = torch.ones_like(exact)
+    dev_ = ((freq - probs).abs() - (4.5 * sigma + 2e-3))[exact]
+    assert bool((dev_ <= 0).all()), f"frequency off by {float(dev_.max()):.4f} beyond 4.5 sigma (band+tie tokens: {n_amb})"
+    if mp >= 1.0:
+        assert set(got.tolist()) <= set(torch.nonzero(row.float() == row.float().max()).flatten().tolist())
 
 
 @pytest.mark.parametrize("V,n_top", [(5003, 5), (32000, 20), (300, 0), (64, 32)])
