@@ -399,35 +399,4 @@ int sample_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, 
   return B200_OK;
 }
 
-// ---- sparse logit adjustments before sampling: repetition / presence / frequency penalties and logit_bias -------
-// ([V22] vllm/v1/sample/ops/penalties.py, logits_processor/builtin.py).  entry = {row, token, rep, add}:
-//   l = logits[row][token];  l = l > 0 ? l / rep : l * rep;  l += add      (rep = 1 and add = 0 leave it alone)
-// `add` carries logit_bias - presence_penalty - frequency_penalty * count, worked out by the host, which knows the
-// token counts.  The logits are bf16 (R6), so the adjusted value is rounded back to bf16.  With vocab-parallel
-// logits every rank applies the entries of its own shard: tokens outside [tok0, tok0 + vocab_local) are skipped.
-__global__ void adjust_logits_kernel(__nv_bfloat16* __restrict__ logits, int64_t ld, int n_rows, int tok0, int vocab_local,
-                                     const int4* __restrict__ entries, int n) {
-  pdl_wait();
-  pdl_launch_dependents();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int4 e = entries[i];
-  const int row = e.x, tok = e.y - tok0;
-  if (row < 0 || row >= n_rows || tok < 0 || tok >= vocab_local) return;
-  const float rep = __int_as_float(e.z), add = __int_as_float(e.w);
-  __nv_bfloat16* p = logits + (int64_t)row * ld + tok;
-  float l = __bfloat162float(*p);
-  if (rep > 0.f && rep != 1.f) l = l > 0.f ? l / rep : l * rep;
-  *p = __float2bfloat16_rn(l + add);
-}
-
-int adjust_logits(__nv_bfloat16* logits, int64_t ld, int n_rows, int tok0, int vocab_local, const void* entries, int n,
-                  cudaStream_t s) {
-  B200_REQUIRE(logits && (entries || n == 0), B200_ERR_INVALID, "adjust_logits: null argument");
-  if (n <= 0) return B200_OK;
-  B200_CUDA(launch(adjust_logits_kernel, dim3((n + 255) / 256), dim3(256), (size_t)0, s, logits, ld, n_rows, tok0, vocab_local,
-                   static_cast<const int4*>(entries), n));
-  return B200_OK;
-}
-
 }  // namespace b200

@@ -67,6 +67,7 @@ class Request:
     temperature: float = 0.0
     top_k: int = 0
     top_p: float = 1.0
+    min_p: float = 0.0                  # 0: off
     seed: Optional[int] = None          # None: drawn once when the request is added
     logprobs: Optional[int] = None      # None: off; N >= 0: logprob of each emitted token + the N most likely
     arrival: float = field(default_factory=time.monotonic)
@@ -297,7 +298,8 @@ class LLMEngine:
             rows = [s.req for s in sched if s.samples]
             sampled = list(self.runner.sample_last([r.temperature for r in rows], [r.top_k for r in rows],
                                                    [r.top_p for r in rows], [r.seed or 0 for r in rows],
-                                                   [len(r.output_ids) for r in rows]))
+                                                   [len(r.output_ids) for r in rows],
+                                                   min_p=[r.min_p for r in rows]))
         if sampled and any(s.samples and s.req.logprobs is not None for s in sched):
             # log softmax of the raw logits for the tokens just chosen (+ the N most likely), same logits buffer
             rows = [s.req for s in sched if s.samples]

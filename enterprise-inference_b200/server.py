@@ -9,9 +9,9 @@ and templates/deployment.yaml:66-87.  HTTP surface: /root/reference/docs/api-spe
 (values.yaml:135-141), GET /metrics with the vllm:* series the Grafana dashboard queries
 (observability/xeon-exporter/grafana-xeon-dashboard.json), GET /v1/models (docs/getting-started-example.md:79-81).
 "temperature": 0 (what the reference's clients send) is the device's argmax; temperature / top_p / top_k /
-seed sample on the device (csrc/sample.cu) with vLLM's semantics and defaults (the model's generation_config.json,
-else temperature 1), `logprobs` / `top_logprobs` come from a log-softmax kernel over the same logits; penalties,
-logit_bias, min_p and guided decoding are accepted and ignored
+min_p / seed sample on the device (csrc/sample.cu) with vLLM's semantics and defaults (the model's generation_config.json,
+else temperature 1), `logprobs` / `top_logprobs` come from a log-softmax kernel over the same logits; frequency_penalty,
+presence_penalty, repetition_penalty, logit_bias and guided decoding are NOT implemented: accepted and ignored
 or rejected (best_of != n, beam search); n parallel samples run as n engine requests.  /v1/embeddings is served by TEI in the reference, not here.
 """
 from __future__ import annotations
@@ -388,7 +388,8 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                        ignore_eos=bool(body.ignore_eos), eos_token_ids=eos_ids,
                        stop_token_ids=tuple(body.stop_token_ids or ()), min_tokens=body.min_tokens or 0,
                        temperature=max(float(temperature), 0.0), top_k=max(int(top_k), 0),
-                       top_p=min(max(float(top_p), 0.0), 1.0), seed=body.seed, logprobs=want_logprobs(body))
+                       top_p=min(max(float(top_p), 0.0), 1.0), min_p=min(max(float(body.min_p or 0.0), 0.0), 1.0),
+                       seed=body.seed, logprobs=want_logprobs(body))
 
     def want_logprobs(body: _Sampling) -> Optional[int]:
         """None: off.  Completions: `logprobs: N`; chat: `logprobs: true` + `top_logprobs: N`."""

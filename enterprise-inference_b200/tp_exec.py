@@ -36,10 +36,10 @@ class TPLeader:
         dist.broadcast(r._h_meta[:n_ints], src=0, group=self.group)
         return r.step_packed(T, R, S, bt_stride, batch.max_ctx, n_ints)
 
-    def sample_last(self, temperature, top_k, top_p, seeds, draws):
+    def sample_last(self, temperature, top_k, top_p, seeds, draws, min_p=None):
         """Sampling over the last step's logits on every rank (the vocab shards are all-gathered on the device)."""
         r = self.runner
-        n = r.pack_sampling(temperature, top_k, top_p, seeds, draws)
+        n = r.pack_sampling(temperature, top_k, top_p, seeds, draws, min_p)   # min_p rides in the same buffer
         self._hdr[:7] = torch.tensor([n, 0, 0, 0, 0, 0, OP_SAMPLE], dtype=torch.int32)
         dist.broadcast(self._hdr, src=0, group=self.group)
         dist.broadcast(r._h_sample[:32 * n], src=0, group=self.group)

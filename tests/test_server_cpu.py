@@ -31,10 +31,11 @@ class FakeRunner:
         self.last = np.array(out, dtype=np.int32)
         return self.last
 
-    def sample_last(self, temperature, top_k, top_p, seeds, draws):
+    def sample_last(self, temperature, top_k, top_p, seeds, draws, min_p=None):
         """Records the call; a 'sampled' token = greedy token + 1 for rows with temperature > 0."""
         self.sample_calls = getattr(self, "sample_calls", []) + [dict(temperature=list(temperature), top_k=list(top_k),
-                                                                         top_p=list(top_p), seeds=list(seeds), draws=list(draws))]
+                                                                         top_p=list(top_p), seeds=list(seeds), draws=list(draws),
+                                                                         min_p=list(min_p) if min_p is not None else None)]
         return np.array([t + 1 if temperature[i] > 0 else t for i, t in enumerate(self.last)], dtype=np.int32)
 
 
@@ -225,10 +226,11 @@ def test_sampling_fields_reach_the_device_sampler():
         r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 3, "temperature": 0})
         assert r.status_code == 200 and not getattr(runner, "sample_calls", [])
         r = client.post("/v1/completions", json={"model": MODEL, "prompt": "abc", "max_tokens": 3, "temperature": 0.8,
-                                                 "top_p": 0.5, "top_k": 7, "seed": 1234})
+                                                 "top_p": 0.5, "top_k": 7, "seed": 1234, "min_p": 0.05})
         assert r.status_code == 200
         calls = runner.sample_calls
         assert len(calls) == 3
+        assert all(abs(c["min_p"][0] - 0.05) < 1e-6 for c in calls)
         assert [c["draws"] for c in calls] == [[0], [1], [2]]
         assert all(c["seeds"] == [1234] and c["top_k"] == [7] for c in calls)
         assert all(abs(c["temperature"][0] - 0.8) < 1e-6 and abs(c["top_p"][0] - 0.5) < 1e-6 for c in calls)

@@ -140,7 +140,7 @@ class _ProtoRunner:
         self.log.append(("step", self._h_meta[:n_ints].tolist(), max_ctx))
         return [0]
 
-    def pack_sampling(self, temperature, top_k, top_p, seeds, draws):
+    def pack_sampling(self, temperature, top_k, top_p, seeds, draws, min_p=None):
         n = len(temperature)
         a = self._h_sample.numpy()
         a[:32 * n] = 0
