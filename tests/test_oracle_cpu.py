@@ -21,8 +21,33 @@ def test_oracle_reproduces_golden(name, golden_dir):
     om = O.OracleModel(cfg, w, capacity=256)
     prompt = g["prompt"].tolist()
     toks, logits = om.generate(prompt, len(g["tokens"]), keep_logits=True)
-    assert toks == g["tokens"].tolist()
-    np.testing.assert_array_equal(logits.numpy(), g["gen_logits"])
+    # Not bit-equal across hosts: R2 leaves the fp32 summation order free, the host BLAS picks it by ISA
+    # (AVX2 / AVX-512 / AMX boxes differ), and one bf16 that rounds the other way in a K/V row moves every
+    # later row by an ulp.  So: the free-running tokens agree up to the first near-tie, and the logits up to
+    # there (same inputs) agree to bf16-ulp level; the teacher-forced logits (same inputs on every row) too.
+    want = g["tokens"].tolist()
+    gl = torch.from_numpy(g["gen_logits"]).float()
+    n = len(want)
+    for i, (a, b) in enumerate(zip(toks, want)):
+        if a != b:
+            m = float(O.top2_margin(gl[i]))
+            assert m < 0.08, f"{name}: greedy token {i} differs from the fixture at an oracle margin of {m:.3f}"
+            n = i + 1
+            break
+    assert_logits_close(logits[:n].float(), gl[:n], name)
+    st = om.new_seq()
+    tf = om.forward(st, prompt + want[:-1]).float()
+    assert_logits_close(tf, torch.from_numpy(g["tf_logits"]).float(), name)
+
+
+def assert_logits_close(a, b, what):
+    """<= 2 bf16 ulp of the row's largest logit per element (an ulp of a small logit is far below the noise of its
+    own sum), softmax max-abs error <= 1e-3 (north_star bar: 2e-2)."""
+    ulp = b.abs().amax(-1, keepdim=True) * 2.0 ** -7
+    worst = ((a - b).abs() / ulp).max().item()
+    assert worst <= 2.0, f"{what}: logits differ from the fixture by {worst:.2f} bf16 ulp of the row maximum"
+    err = (torch.softmax(a, -1) - torch.softmax(b, -1)).abs().max().item()
+    assert err <= 1e-3, f"{what}: softmax differs from the fixture by {err:.2e}"
 
 
 @pytest.mark.parametrize("name", ["tiny", "tiny-qwen", "tiny-g8"])
