@@ -52,6 +52,11 @@ SIGNATURES = {
     "b200_linear_bf16": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _i64, _vp]),
     "b200_linear_fused_bf16": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
                                          _i32, _i32, _i32, _vp, _i64, _vp]),
+    "b200_embed_stream": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp]),
+    "b200_linear_residual_bf16": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _i64, _vp]),
+    "b200_linear_normed_bf16": (C.c_int, [_vp, _vp, _vp, _f32, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp,
+                                          _vp, _vp, _i32, _i32, _i32, _vp, _i64, _vp]),
+    "b200_rmsnorm_stream": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _f32, _vp]),
     "b200_rmsnorm": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _f32, _vp]),
     "b200_embed": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
     "b200_rope_kv_append": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),

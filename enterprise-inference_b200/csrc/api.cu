@@ -131,11 +131,15 @@ struct LayerW {
 };
 
 struct GraphKey {
-  uint64_t h;
-  bool operator==(const GraphKey& o) const { return h == o.h; }
+  uint64_t parts[16];   // every pointer and size the captured graph baked in
+  bool operator==(const GraphKey& o) const { return memcmp(parts, o.parts, sizeof(parts)) == 0; }
 };
 struct GraphKeyHash {
-  size_t operator()(const GraphKey& k) const { return (size_t)k.h; }
+  size_t operator()(const GraphKey& k) const {
+    uint64_t h = 0x1234;
+    for (uint64_t v : k.parts) h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+    return (size_t)h;
+  }
 };
 
 struct b200_ctx {
@@ -151,6 +155,7 @@ struct b200_ctx {
   void* pool = nullptr;
   int64_t pool_bytes = 0;
   __nv_bfloat16 *x, *res, *normed, *qkv_buf, *attn_out, *gu_buf, *act, *lm_in, *logits;
+  float *sres, *ssq;   // fp32 residual stream [T][h] and its per-slab sums of squares [T][h/128] (norm folded into the linears)
   void* attn_ws;
   int64_t attn_ws_bytes;
   void* lin_ws;
@@ -182,7 +187,10 @@ struct b200_ctx {
   int gemv_max_t = 0;  // rows <= this use the CUDA-core GEMV; 0: the tcgen05 path serves every T (measured faster)
   bool pdl = true;
   bool fuse = true;                    // epilogue fusion (RoPE+KV, SiLU*mul) on the tcgen05 path
-  int64_t prefetch_cap = 0;   // bytes of the NEXT linear's weights pulled into L2 per linear (0: off)
+  // Steps of at most this many rows fold the RMSNorms into the linears (0: off).  Measured on 8B: batch 1 3.05 -> 3.00
+  // ms/step; at 64 rows every CTA of a consumer re-normalises 1 MiB of fp32 rows out of L2 and the step slows from 4.6
+  // to 6.3 ms, so the fold stops at the 16-row tile.
+  int fuse_norm_max_t = 16;
 };
 
 static int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
@@ -229,7 +237,7 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
   if (const char* e = getenv("B200_GRAPHS")) c->graphs = atoi(e) != 0;
   if (const char* e = getenv("B200_PDL")) c->pdl = atoi(e) != 0;
   if (const char* e = getenv("B200_FUSE")) c->fuse = atoi(e) != 0;
-  if (const char* e = getenv("B200_PREFETCH_MB")) c->prefetch_cap = (int64_t)atoi(e) << 20;
+  if (const char* e = getenv("B200_FUSE_NORM_MAX_T")) c->fuse_norm_max_t = atoi(e);
 
   const int64_t T = cfg->max_tokens, h = cfg->hidden, R = c->max_logit_rows;
   const int max_ctx = cfg->max_blocks_per_seq * cfg->block_size;
@@ -257,6 +265,8 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
       {(void**)&c->x, T * h * 2},
       {(void**)&c->res, T * h * 2},
       {(void**)&c->normed, T * h * 2},
+      {(void**)&c->sres, std::min<int64_t>(T, 64) * h * 4},
+      {(void**)&c->ssq, std::min<int64_t>(T, 64) * (h / 128 + 1) * 4},
       {(void**)&c->qkv_buf, T * c->qkv_w * 2},
       {(void**)&c->attn_out, T * c->hq * kHeadDim * 2},
       {(void**)&c->gu_buf, T * 2 * c->inter * 2},
@@ -433,16 +443,6 @@ extern "C" int b200_allreduce_bf16(b200_ctx* c, void* buf, int64_t count, void* 
   return B200_OK;
 }
 
-static thread_local const void* g_pf_hint_ptr = nullptr;
-static thread_local int64_t g_pf_hint_bytes = 0;
-// experiment hook (not in the public header): the next b200_linear_bf16 on this thread also pulls
-// [ptr, ptr+bytes) towards L2 when its CTAs finish streaming
-extern "C" __attribute__((visibility("default"))) int b200_debug_prefetch_hint(const void* ptr, int64_t bytes) {
-  g_pf_hint_ptr = ptr;
-  g_pf_hint_bytes = bytes;
-  return B200_OK;
-}
-
 extern "C" int b200_set_launch_pdl(int32_t enabled) {
   launch_opts().pdl = enabled != 0;
   return B200_OK;
@@ -473,7 +473,7 @@ static int linear_any(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* 
   if (T == 0) return B200_OK;
   if (impl == 0) impl = tc_path(T, n_out, k, gemv_max_t) ? 2 : 1;
   if (impl == 1) {
-    B200_REQUIRE(!ex || ex->mode == 0, B200_ERR_UNSUPPORTED, "linear: fused epilogues need the tcgen05 path");
+    B200_REQUIRE(!ex || (ex->mode == 0 && !ex->norm_in), B200_ERR_UNSUPPORTED, "linear: fused epilogues need the tcgen05 path");
     return linear_gemv(x, ldx, w, bias, y, ldy, T, n_out, k, s);
   }
   B200_REQUIRE(linear_tc_supported(T, n_out, k), B200_ERR_UNSUPPORTED,
@@ -505,14 +505,8 @@ extern "C" int b200_linear_bf16(const void* x, int64_t ldx, const void* w, const
   B200_REQUIRE(x && w && y && T >= 0 && n_out > 0 && k > 0, B200_ERR_INVALID, "linear: bad argument");
   int gm = 0;
   if (const char* e = getenv("B200_GEMV_MAX_T")) gm = atoi(e);
-  LinearExtra ex;
-  ex.pf_ptr = g_pf_hint_ptr;
-  ex.pf_bytes = g_pf_hint_bytes;
-  g_pf_hint_ptr = nullptr;
-  g_pf_hint_bytes = 0;
   return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias,
-                    (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, (impl == 1 || !ex.pf_ptr) ? nullptr : &ex,
-                    (cudaStream_t)stream);
+                    (__nv_bfloat16*)y, ldy, T, n_out, k, impl, gm, ws, ws_bytes, nullptr, (cudaStream_t)stream);
 }
 
 extern "C" int b200_linear_fused_bf16(const void* x, int64_t ldx, const void* w, const void* bias, void* y, int64_t ldy,
@@ -534,6 +528,56 @@ extern "C" int b200_linear_fused_bf16(const void* x, int64_t ldx, const void* w,
   ex.block_size = block_size;
   return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias,
                     (__nv_bfloat16*)y, ldy, T, n_out, k, 2, 0, ws, ws_bytes, &ex, (cudaStream_t)stream);
+}
+
+extern "C" int b200_linear_residual_bf16(const void* x, int64_t ldx, const void* w, const void* bias, float* sres, float* ssq,
+                                         int32_t T, int32_t n_out, int32_t k, void* ws, int64_t ws_bytes, void* stream) {
+  B200_REQUIRE(x && w && sres && ssq && T >= 0 && n_out > 0 && k > 0, B200_ERR_INVALID, "linear_residual: bad argument");
+  LinearExtra ex;
+  ex.mode = 3;
+  ex.sres = sres;
+  ex.ssq = ssq;
+  return linear_any((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias, nullptr, n_out, T,
+                    n_out, k, 2, 0, ws, ws_bytes, &ex, (cudaStream_t)stream);
+}
+
+extern "C" int b200_linear_normed_bf16(const float* sres, const float* ssq, const void* norm_w, float eps, const int32_t* rows,
+                                       const void* w, const void* bias, void* y, int64_t ldy, int32_t T, int32_t n_out,
+                                       int32_t k, int32_t mode, const int32_t* positions, const int32_t* slot_mapping,
+                                       const void* cos_sin, void* k_cache_layer, void* v_cache_layer, int32_t n_q_heads,
+                                       int32_t n_kv_heads, int32_t block_size, void* ws, int64_t ws_bytes, void* stream) {
+  B200_REQUIRE(sres && ssq && norm_w && w && y && T >= 0 && n_out > 0 && k > 0, B200_ERR_INVALID, "linear_normed: bad argument");
+  B200_REQUIRE(mode >= 0 && mode <= 2, B200_ERR_INVALID, "linear_normed: mode must be 0 (plain), 1 (silu*mul) or 2 (rope+kv)");
+  LinearExtra ex;
+  ex.mode = mode;
+  ex.norm_in = true;
+  ex.sres = const_cast<float*>(sres);
+  ex.ssq = const_cast<float*>(ssq);
+  ex.norm_w = (const __nv_bfloat16*)norm_w;
+  ex.rows = rows;
+  ex.eps = eps;
+  ex.positions = positions;
+  ex.slots = slot_mapping;
+  ex.cos_sin = (const __nv_bfloat16*)cos_sin;
+  ex.kc = (__nv_bfloat16*)k_cache_layer;
+  ex.vc = (__nv_bfloat16*)v_cache_layer;
+  ex.hq = n_q_heads;
+  ex.hkv = n_kv_heads;
+  ex.block_size = block_size;
+  return linear_any(nullptr, k, (const __nv_bfloat16*)w, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, ldy, T, n_out, k, 2, 0,
+                    ws, ws_bytes, &ex, (cudaStream_t)stream);
+}
+
+extern "C" int b200_embed_stream(const int32_t* ids, const void* table, float* sres, float* ssq, int32_t T, int32_t hidden,
+                                 int32_t vocab, void* stream) {
+  B200_REQUIRE(ids && table && sres && ssq, B200_ERR_INVALID, "embed_stream: null");
+  return embed_stream(ids, (const __nv_bfloat16*)table, sres, ssq, T, hidden, vocab, (cudaStream_t)stream);
+}
+
+extern "C" int b200_rmsnorm_stream(const float* sres, const float* ssq, const int32_t* rows, const void* w, void* y,
+                                   int32_t n_rows, int32_t hidden, float eps, void* stream) {
+  B200_REQUIRE(sres && ssq && w && y, B200_ERR_INVALID, "rmsnorm_stream: null");
+  return rmsnorm_stream(sres, ssq, rows, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, n_rows, hidden, eps, (cudaStream_t)stream);
 }
 
 extern "C" int b200_rmsnorm(const void* x, void* res, const void* w, void* y, int32_t T, int32_t hidden, float eps,
@@ -672,20 +716,25 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     if (rc) return rc;    \
   } while (0)
 
-  // Each tcgen05 linear pulls (a prefix of) the NEXT linear's weights into L2 so that HBM keeps
-  // streaming while the small dependent kernels between two linears run.
-  auto pf = [&](LinearExtra& ex, const void* next, int64_t elems) {
-    if (c->prefetch_cap > 0 && next) {
-      ex.pf_ptr = next;
-      ex.pf_bytes = std::min<int64_t>(elems * 2, c->prefetch_cap);
-    }
-  };
   const int qn = c->qkv_w, on = h, ok = c->hq * kHeadDim, gn = 2 * c->inter, dn = h, dk = c->inter;
-  // timing experiments only (results are wrong): B200_DEBUG_SKIP bit 0 = skip the per-layer norms, bit 1 = skip attention
-  static const int dbg_skip = getenv("B200_DEBUG_SKIP") ? atoi(getenv("B200_DEBUG_SKIP")) : 0;
   // TP: the all-reduce after the down projection is folded into the norm that consumes it (next layer's ln1 or the
   // final norm); with a debug tap it runs right after the projection so that the tap sees reduced activations
-  const bool defer_ar = tp && c->tap_layer < 0 && !(dbg_skip & 1);
+  const bool defer_ar = tp && c->tap_layer < 0;
+  // Decode-sized steps on one GPU keep the residual stream in fp32 and fold every RMSNorm into its neighbours: the O
+  // and down projections add their output into the stream and leave per-slab sums of squares, the QKV, gate_up and
+  // lm_head linears normalise their input rows on the fly (same rounding points as the norm kernel, R1, and the same
+  // summation order: bit-identical to the unfused step).  Two launches fewer per layer.
+  const bool fnorm = !tp && c->fuse && c->tap_layer < 0 && T <= std::min(c->fuse_norm_max_t, 64) && h % 128 == 0 &&
+                     tc_path(T, qn, h, c->gemv_max_t) && tc_path(T, on, ok, c->gemv_max_t) &&
+                     tc_path(T, gn, h, c->gemv_max_t) && tc_path(T, dn, dk, c->gemv_max_t) &&
+                     tc_path(a.R, c->vocab_local, h, c->gemv_max_t);
+  auto norm_in = [&](LinearExtra& ex, const __nv_bfloat16* w) {
+    ex.norm_in = true;
+    ex.sres = c->sres;
+    ex.ssq = c->ssq;
+    ex.norm_w = w;
+    ex.eps = m.rms_eps;
+  };
   // Prefill-heavy steps (many more rows than sequences) pack consecutive rows of a sequence into one pass
   // over its K/V; decode steps keep one row per work item.
   // Decode-only steps (every row its own sequence: one new token each) are flagged with -1: the attention may
@@ -699,19 +748,23 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     if (built < 0) return built;
     if (built == 1) attn_pack = 2;
   }
-  STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
+  if (fnorm)
+    STEP(embed_stream(a.ids, c->embed, c->sres, c->ssq, T, h, m.vocab, s));
+  else
+    STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
   for (int l = 0; l < m.n_layers; ++l) {
     const LayerW& L = c->layers[l];
-    if (l == 0)
-      STEP(rmsnorm(c->res, nullptr, L.ln1, c->normed, T, h, m.rms_eps, s));
-    else if (!(dbg_skip & 1))
-      STEP(defer_ar ? tp_reduce_norm(c, 1, T, L.ln1, s) : rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
+    if (!fnorm) {
+      if (l == 0)
+        STEP(rmsnorm(c->res, nullptr, L.ln1, c->normed, T, h, m.rms_eps, s));
+      else
+        STEP(defer_ar ? tp_reduce_norm(c, 1, T, L.ln1, s) : rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
+    }
     __nv_bfloat16* kcl = c->kc + (int64_t)l * kv_layer_elems;
     __nv_bfloat16* vcl = c->vc + (int64_t)l * kv_layer_elems;
     {  // QKV (+ RoPE + KV append in the epilogue when on the tcgen05 path)
       LinearExtra ex;
       const bool tcp = tc_path(T, qn, h, c->gemv_max_t);
-      if (tcp) pf(ex, L.o, (int64_t)on * ok);
       if (tcp && c->fuse) {
         ex.mode = 2;
         ex.positions = a.positions;
@@ -723,30 +776,30 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
         ex.hkv = c->hkv;
         ex.block_size = m.block_size;
       }
+      if (fnorm) norm_in(ex, L.ln1);
       STEP(linear_any(c->normed, h, L.qkv, L.qkv_b, c->qkv_buf, qn, T, qn, h, 0, c->gemv_max_t, c->lin_ws,
                       c->lin_ws_bytes, &ex, s));
       if (ex.mode != 2)
         STEP(rope_kv_append(c->qkv_buf, a.positions, a.slots, c->cos_sin, kcl, vcl, T, c->hq, c->hkv, m.block_size, s));
     }
-    if (!(dbg_skip & 2))
     STEP(paged_attn_ex(c->qkv_buf, c->qkv_w, kcl, vcl, a.block_table, a.bt_stride, a.row_to_seq, a.ctx_lens, c->attn_out,
                        c->hq * kHeadDim, T, c->hq, c->hkv, m.block_size, a.max_ctx, scale, c->attn_ws, c->attn_ws_bytes,
                        attn_pack, s));
     {  // O
       LinearExtra ex;
-      if (tc_path(T, on, ok, c->gemv_max_t)) pf(ex, L.gu, (int64_t)gn * h);
+      if (fnorm) {
+        ex.mode = 3;
+        ex.sres = c->sres;
+        ex.ssq = c->ssq;
+      }
       STEP(linear_any(c->attn_out, ok, L.o, nullptr, tp ? partial_dst(c, 0, T) : c->x, h, T, on, ok, 0, c->gemv_max_t,
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
-    if (dbg_skip & 1) {
-      if (tp) STEP(tp_reduce(c, 0, T, s));
-    } else {
-      STEP(tp_reduce_norm(c, 0, T, L.ln2, s));   // (all-reduce +) residual add + RMSNorm
-    }
+    if (!fnorm) STEP(tp_reduce_norm(c, 0, T, L.ln2, s));   // (all-reduce +) residual add + RMSNorm
     {  // gate_up (+ SiLU*mul in the epilogue over interleaved slabs)
       LinearExtra ex;
       const bool tcp = tc_path(T, gn, h, c->gemv_max_t);
-      if (tcp) pf(ex, L.down, (int64_t)dn * dk);
+      if (fnorm) norm_in(ex, L.ln2);
       if (L.gu_interleaved) {
         B200_REQUIRE(tcp, B200_ERR_UNSUPPORTED, "interleaved gate_up weights need the tcgen05 path");
         ex.mode = 1;
@@ -760,11 +813,10 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     }
     {  // down
       LinearExtra ex;
-      if (tc_path(T, dn, dk, c->gemv_max_t)) {
-        if (l + 1 < m.n_layers)
-          pf(ex, c->layers[l + 1].qkv, (int64_t)qn * h);
-        else
-          pf(ex, c->lm_head, (int64_t)c->vocab_local * h);
+      if (fnorm) {
+        ex.mode = 3;
+        ex.sres = c->sres;
+        ex.ssq = c->ssq;
       }
       STEP(linear_any(c->act, dk, L.down, nullptr, tp ? partial_dst(c, 1, T) : c->x, h, T, dn, dk, 0, c->gemv_max_t,
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
@@ -775,14 +827,29 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       if (c->tap_res) B200_CUDA(cudaMemcpyAsync(c->tap_res, c->res, (size_t)T * h * 2, cudaMemcpyDeviceToDevice, s));
     }
   }
-  STEP(defer_ar ? tp_reduce_norm(c, 1, T, c->final_norm, s) : rmsnorm(c->x, c->res, c->final_norm, c->normed, T, h, m.rms_eps, s));
-  const __nv_bfloat16* lm_in = c->normed;
-  if (a.logit_rows) {
-    STEP(embed(a.logit_rows, c->normed, c->lm_in, a.R, h, T, s));  // row gather
-    lm_in = c->lm_in;
+  if (fnorm) {
+    // lm_head normalises its own rows (through the logit-row indirection) while the rows are few; with many logit
+    // rows a thousand slabs would each redo the same rows, so the norm runs once as a kernel of its own
+    LinearExtra ex;
+    const __nv_bfloat16* lm_in = c->lm_in;
+    if (a.R <= 16) {
+      norm_in(ex, c->final_norm);
+      ex.rows = a.logit_rows;
+    } else {
+      STEP(rmsnorm_stream(c->sres, c->ssq, a.logit_rows, c->final_norm, c->lm_in, a.R, h, m.rms_eps, s));
+    }
+    STEP(linear_any(lm_in, h, c->lm_head, nullptr, c->logits, c->vocab_local, a.R, c->vocab_local, h, 0, c->gemv_max_t,
+                    c->lin_ws, c->lin_ws_bytes, &ex, s));
+  } else {
+    STEP(defer_ar ? tp_reduce_norm(c, 1, T, c->final_norm, s) : rmsnorm(c->x, c->res, c->final_norm, c->normed, T, h, m.rms_eps, s));
+    const __nv_bfloat16* lm_in = c->normed;
+    if (a.logit_rows) {
+      STEP(embed(a.logit_rows, c->normed, c->lm_in, a.R, h, T, s));  // row gather
+      lm_in = c->lm_in;
+    }
+    STEP(linear_any(lm_in, h, c->lm_head, nullptr, c->logits, c->vocab_local, a.R, c->vocab_local, h, 0, c->gemv_max_t,
+                    c->lin_ws, c->lin_ws_bytes, nullptr, s));
   }
-  STEP(linear_any(lm_in, h, c->lm_head, nullptr, c->logits, c->vocab_local, a.R, c->vocab_local, h, 0, c->gemv_max_t,
-                  c->lin_ws, c->lin_ws_bytes, nullptr, s));
   if (!tp) {
     STEP(argmax_rows(c->logits, c->vocab_local, a.R, c->vocab_local, 0, a.out_tokens, nullptr, s));
     if (a.out_logits)
@@ -804,11 +871,6 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   }
 #undef STEP
   return B200_OK;
-}
-
-static uint64_t mix(uint64_t h, uint64_t v) {
-  h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
-  return h;
 }
 
 static int pow2_bucket(int v) {
@@ -844,14 +906,11 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     launch_opts().pdl = pdl_prev;
     return rc;
   }
-  uint64_t hsh = 0x1234;
-  const uint64_t parts[] = {(uint64_t)a.ids,        (uint64_t)a.positions,  (uint64_t)a.slots,
-                            (uint64_t)a.block_table, (uint64_t)a.row_to_seq, (uint64_t)a.ctx_lens,
-                            (uint64_t)a.logit_rows,  (uint64_t)a.out_tokens, (uint64_t)a.out_logits,
-                            (uint64_t)a.bt_stride,   (uint64_t)a.T,          (uint64_t)pow2_bucket(a.max_ctx),
-                            (uint64_t)a.R,           (uint64_t)launch_opts().pdl, (uint64_t)a.n_seqs};
-  for (uint64_t p : parts) hsh = mix(hsh, p);
-  GraphKey key{hsh};
+  const GraphKey key{{(uint64_t)a.ids,        (uint64_t)a.positions,  (uint64_t)a.slots,
+                      (uint64_t)a.block_table, (uint64_t)a.row_to_seq, (uint64_t)a.ctx_lens,
+                      (uint64_t)a.logit_rows,  (uint64_t)a.out_tokens, (uint64_t)a.out_logits,
+                      (uint64_t)a.bt_stride,   (uint64_t)a.T,          (uint64_t)pow2_bucket(a.max_ctx),
+                      (uint64_t)a.R,           (uint64_t)launch_opts().pdl, (uint64_t)a.n_seqs, 0ull}};
   auto it = c->graph_cache.find(key);
   if (it == c->graph_cache.end()) {
     StepArgs b = a;

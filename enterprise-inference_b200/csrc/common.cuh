@@ -147,12 +147,18 @@ int linear_gemv(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, con
                 __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, cudaStream_t s);
 bool linear_tc_supported(int T, int n_out, int k);
 int64_t linear_tc_workspace_bytes(int T, int n_out, int k);
-// Optional epilogue fusion / prefetch of the tcgen05 linear (modes: 0 plain, 1 silu*mul over an
-// interleaved gate|up slab, 2 RoPE + KV append over a fused qkv projection).
+// Optional fusions of the tcgen05 linear.  Epilogue modes: 0 plain, 1 silu*mul over an interleaved gate|up slab,
+// 2 RoPE + KV append over a fused qkv projection, 3 add into the fp32 residual stream (sres/ssq, no y).
+// norm_in: the input rows are not read from x but normalised on the fly from the fp32 residual stream
+// (RMSNorm folded into the consumer: sres, ssq, norm_w, eps, optional row indirection `rows`).
 struct LinearExtra {
   int mode = 0;
-  const void* pf_ptr = nullptr;  // next weights to pull into L2
-  int64_t pf_bytes = 0;
+  bool norm_in = false;
+  float* sres = nullptr;         // [T][hidden] fp32: x + residual, unrounded
+  float* ssq = nullptr;          // [T][hidden/128] fp32: per-slab sums of squares of sres
+  const __nv_bfloat16* norm_w = nullptr;
+  const int32_t* rows = nullptr;
+  float eps = 0.f;
   const int32_t* positions = nullptr;
   const int32_t* slots = nullptr;
   const __nv_bfloat16* cos_sin = nullptr;
@@ -165,6 +171,11 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
               const LinearExtra* ex, cudaStream_t s);
 int rmsnorm(const __nv_bfloat16* x, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int T,
             int hidden, float eps, cudaStream_t s);
+// fp32 residual stream (RMSNorm folded into the linears): embedding rows -> sres/ssq; stream rows -> normed bf16
+int embed_stream(const int32_t* ids, const __nv_bfloat16* table, float* sres, float* ssq, int T, int hidden, int vocab,
+                 cudaStream_t s);
+int rmsnorm_stream(const float* sres, const float* ssq, const int32_t* rows, const __nv_bfloat16* w, __nv_bfloat16* y,
+                   int R, int hidden, float eps, cudaStream_t s);
 int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, int T, int hidden, int vocab,
           cudaStream_t s);
 int rope_kv_append(__nv_bfloat16* qkv, const int32_t* positions, const int32_t* slots,

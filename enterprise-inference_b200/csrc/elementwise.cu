@@ -29,73 +29,117 @@ embed_kernel(const int32_t* __restrict__ ids, const __nv_bfloat16* __restrict__ 
 //   s = x (+ res) in fp32; res' = bf16(s); var over UNROUNDED s; n = bf16(s / sqrt(var+eps));
 //   y = bf16(n * w)                                   [V22] vllm/ir/ops/layernorm.py:10-21,40-58
 // ---------------------------------------------------------------------------------------
+// The sum of squares is taken in a fixed order that the linears' fused-norm path reproduces exactly (gemm_tc.cu,
+// finalize4<kResidual> / norm_b_tiles): per 128-wide slab, lane l squares its 4 values 4l..4l+3 in order (fma chain),
+// the warp tree (xor 16, 8, 4, 2, 1) adds the lanes, and the slab sums are added in ascending slab order.
 constexpr int kNormThreads = 256;
-constexpr int kNormMaxChunks = 4;  // hidden <= 8192
+constexpr int kNormWarps = kNormThreads / 32;
+constexpr int kNormMaxSlabs = 8;  // per warp: hidden <= 8 * 8 * 128 = 8192
 
 template <bool HAS_RES>
 __global__ void __launch_bounds__(kNormThreads)
 rmsnorm_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* res, const __nv_bfloat16* __restrict__ w,
                __nv_bfloat16* y, int hidden, float eps) {
-  __shared__ float red[kNormThreads / 32];
+  __shared__ float part[kNormWarps * kNormMaxSlabs];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int t = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nslab = hidden >> 7;
+  const uint2* xr = reinterpret_cast<const uint2*>(x + (int64_t)t * hidden);
+  uint2* rr = HAS_RES ? reinterpret_cast<uint2*>(res + (int64_t)t * hidden) : nullptr;
+  float v[kNormMaxSlabs][4];
+#pragma unroll
+  for (int i = 0; i < kNormMaxSlabs; ++i) {
+    const int slab = warp + i * kNormWarps;
+    if (slab < nslab) {
+      const int c = slab * 32 + lane;   // 8-byte chunk index
+      const uint2 a = xr[c];
+      if (HAS_RES) {
+        const uint2 b = rr[c];
+        v[i][0] = bf16lo(a.x) + bf16lo(b.x);
+        v[i][1] = bf16hi(a.x) + bf16hi(b.x);
+        v[i][2] = bf16lo(a.y) + bf16lo(b.y);
+        v[i][3] = bf16hi(a.y) + bf16hi(b.y);
+        rr[c] = make_uint2(pack_bf16(v[i][0], v[i][1]), pack_bf16(v[i][2], v[i][3]));
+      } else {
+        v[i][0] = bf16lo(a.x);
+        v[i][1] = bf16hi(a.x);
+        v[i][2] = bf16lo(a.y);
+        v[i][3] = bf16hi(a.y);
+      }
+      float ss = fmaf(v[i][0], v[i][0], 0.f);
+      ss = fmaf(v[i][1], v[i][1], ss);
+      ss = fmaf(v[i][2], v[i][2], ss);
+      ss = fmaf(v[i][3], v[i][3], ss);
+      ss = warp_sum(ss);
+      if (lane == 0) part[slab] = ss;
+    }
+  }
+  __syncthreads();
+  float tot = 0.f;
+  for (int i = 0; i < nslab; ++i) tot += part[i];
+  const float r = 1.0f / sqrtf(tot / (float)hidden + eps);
+  const uint2* wr = reinterpret_cast<const uint2*>(w);
+  uint2* yr = reinterpret_cast<uint2*>(y + (int64_t)t * hidden);
+#pragma unroll
+  for (int i = 0; i < kNormMaxSlabs; ++i) {
+    const int slab = warp + i * kNormWarps;
+    if (slab < nslab) {
+      const int c = slab * 32 + lane;
+      const uint2 wq = __ldg(wr + c);
+      const float n0 = round_bf16(v[i][0] * r), n1 = round_bf16(v[i][1] * r);
+      const float n2 = round_bf16(v[i][2] * r), n3 = round_bf16(v[i][3] * r);
+      yr[c] = make_uint2(pack_bf16(n0 * bf16lo(wq.x), n1 * bf16hi(wq.x)), pack_bf16(n2 * bf16lo(wq.y), n3 * bf16hi(wq.y)));
+    }
+  }
+}
+
+// Embedding rows into the fp32 residual stream: sres[t] = float(table[ids[t]]), ssq[t][slab] in the order above.
+__global__ void __launch_bounds__(kNormThreads)
+embed_stream_kernel(const int32_t* __restrict__ ids, const __nv_bfloat16* __restrict__ table, float* __restrict__ sres,
+                    float* __restrict__ ssq, int hidden, int vocab) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int t = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nslab = hidden >> 7;
+  int id = ids[t];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const uint2* src = reinterpret_cast<const uint2*>(table + (int64_t)id * hidden);
+  float4* dst = reinterpret_cast<float4*>(sres + (int64_t)t * hidden);
+  for (int slab = warp; slab < nslab; slab += kNormWarps) {
+    const uint2 a = __ldg(src + slab * 32 + lane);
+    const float4 f = make_float4(bf16lo(a.x), bf16hi(a.x), bf16lo(a.y), bf16hi(a.y));
+    dst[slab * 32 + lane] = f;
+    float ss = fmaf(f.x, f.x, 0.f);
+    ss = fmaf(f.y, f.y, ss);
+    ss = fmaf(f.z, f.z, ss);
+    ss = fmaf(f.w, f.w, ss);
+    ss = warp_sum(ss);
+    if (lane == 0) ssq[(int64_t)t * nslab + slab] = ss;
+  }
+}
+
+// Stream rows -> normalised bf16 rows (the consumer side of the folded norm as a kernel of its own, for consumers
+// that would re-normalise the same rows in too many CTAs: lm_head over many logit rows).
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_stream_kernel(const float* __restrict__ sres, const float* __restrict__ ssq, const int32_t* __restrict__ rows,
+                      const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ y, int hidden, float eps) {
   pdl_wait();
   pdl_launch_dependents();
   const int t = blockIdx.x;
-  const int nchunk = hidden >> 3;
-  const uint4* xr = reinterpret_cast<const uint4*>(x + (int64_t)t * hidden);
-  uint4* rr = HAS_RES ? reinterpret_cast<uint4*>(res + (int64_t)t * hidden) : nullptr;
-  float v[kNormMaxChunks][8];
-  float ss = 0.f;
-#pragma unroll
-  for (int i = 0; i < kNormMaxChunks; ++i) {
-    const int c = threadIdx.x + i * kNormThreads;
-    if (c < nchunk) {
-      const uint4 a = xr[c];
-      const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-      if (HAS_RES) {
-        const uint4 b = rr[c];
-        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
-        uint32_t o[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          v[i][2 * j] = bf16lo(aw[j]) + bf16lo(bw[j]);
-          v[i][2 * j + 1] = bf16hi(aw[j]) + bf16hi(bw[j]);
-          o[j] = pack_bf16(v[i][2 * j], v[i][2 * j + 1]);
-        }
-        rr[c] = make_uint4(o[0], o[1], o[2], o[3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          v[i][2 * j] = bf16lo(aw[j]);
-          v[i][2 * j + 1] = bf16hi(aw[j]);
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) ss = fmaf(v[i][j], v[i][j], ss);
-    }
-  }
-  ss = warp_sum(ss);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
-  __syncthreads();
+  const int row = rows ? rows[t] : t;
+  const int nslab = hidden >> 7;
   float tot = 0.f;
-#pragma unroll
-  for (int i = 0; i < kNormThreads / 32; ++i) tot += red[i];
+  for (int i = 0; i < nslab; ++i) tot += __ldcg(ssq + (int64_t)row * nslab + i);
   const float r = 1.0f / sqrtf(tot / (float)hidden + eps);
-  const uint4* wr = reinterpret_cast<const uint4*>(w);
-  uint4* yr = reinterpret_cast<uint4*>(y + (int64_t)t * hidden);
-#pragma unroll
-  for (int i = 0; i < kNormMaxChunks; ++i) {
-    const int c = threadIdx.x + i * kNormThreads;
-    if (c < nchunk) {
-      const uint4 wq = __ldg(wr + c);
-      const uint32_t ww[4] = {wq.x, wq.y, wq.z, wq.w};
-      uint32_t o[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float n0 = round_bf16(v[i][2 * j] * r), n1 = round_bf16(v[i][2 * j + 1] * r);
-        o[j] = pack_bf16(n0 * bf16lo(ww[j]), n1 * bf16hi(ww[j]));
-      }
-      yr[c] = make_uint4(o[0], o[1], o[2], o[3]);
-    }
+  const float4* sr = reinterpret_cast<const float4*>(sres + (int64_t)row * hidden);
+  const uint2* wr = reinterpret_cast<const uint2*>(w);
+  uint2* yr = reinterpret_cast<uint2*>(y + (int64_t)t * hidden);
+  for (int c = threadIdx.x; c < hidden / 4; c += kNormThreads) {
+    const float4 s4 = __ldcg(sr + c);
+    const uint2 wq = __ldg(wr + c);
+    const float n0 = round_bf16(s4.x * r), n1 = round_bf16(s4.y * r), n2 = round_bf16(s4.z * r), n3 = round_bf16(s4.w * r);
+    yr[c] = make_uint2(pack_bf16(n0 * bf16lo(wq.x), n1 * bf16hi(wq.x)), pack_bf16(n2 * bf16lo(wq.y), n3 * bf16hi(wq.y)));
   }
 }
 
@@ -267,13 +311,29 @@ int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, in
 
 int rmsnorm(const __nv_bfloat16* x, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int T,
             int hidden, float eps, cudaStream_t s) {
-  B200_REQUIRE(hidden % 8 == 0 && hidden <= 8 * kNormThreads * kNormMaxChunks, B200_ERR_UNSUPPORTED,
-               "rmsnorm: hidden=%d unsupported (multiple of 8, <= %d)", hidden, 8 * kNormThreads * kNormMaxChunks);
+  B200_REQUIRE(hidden % 128 == 0 && hidden <= 128 * kNormWarps * kNormMaxSlabs, B200_ERR_UNSUPPORTED,
+               "rmsnorm: hidden=%d unsupported (multiple of 128, <= %d)", hidden, 128 * kNormWarps * kNormMaxSlabs);
   if (T == 0) return B200_OK;
   if (res)
     B200_CUDA(launch(rmsnorm_kernel<true>, dim3(T), dim3(kNormThreads), 0, s, x, res, w, y, hidden, eps));
   else
     B200_CUDA(launch(rmsnorm_kernel<false>, dim3(T), dim3(kNormThreads), 0, s, x, res, w, y, hidden, eps));
+  return B200_OK;
+}
+
+int embed_stream(const int32_t* ids, const __nv_bfloat16* table, float* sres, float* ssq, int T, int hidden, int vocab,
+                 cudaStream_t s) {
+  B200_REQUIRE(hidden % 128 == 0, B200_ERR_UNSUPPORTED, "embed_stream: hidden %% 128 != 0");
+  if (T == 0) return B200_OK;
+  B200_CUDA(launch(embed_stream_kernel, dim3(T), dim3(kNormThreads), 0, s, ids, table, sres, ssq, hidden, vocab));
+  return B200_OK;
+}
+
+int rmsnorm_stream(const float* sres, const float* ssq, const int32_t* rows, const __nv_bfloat16* w, __nv_bfloat16* y,
+                   int R, int hidden, float eps, cudaStream_t s) {
+  B200_REQUIRE(hidden % 128 == 0, B200_ERR_UNSUPPORTED, "rmsnorm_stream: hidden %% 128 != 0");
+  if (R == 0) return B200_OK;
+  B200_CUDA(launch(rmsnorm_stream_kernel, dim3(R), dim3(kNormThreads), 0, s, sres, ssq, rows, w, y, hidden, eps));
   return B200_OK;
 }
 

@@ -54,7 +54,8 @@ constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 #endif
 __host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? B200_STAGES16 : (N <= 32 ? 4 : (N <= 64 ? B200_STAGES64 : (N <= 128 ? 3 : B200_STAGES256))); }
 __host__ __device__ constexpr int stage_bytes(int N) { return kBlockM * kBlockK * 2 + N * kBlockK * 2; }
-__host__ __device__ constexpr int smem_bytes_for(int N) { return stages_for(N) * stage_bytes(N) + 1024 + 256; }
+constexpr int kTailBytes = 1024;   // barriers, TMEM slot, ticket | per-token 1/rms [64] | source rows [64] (fused-norm consumer)
+__host__ __device__ constexpr int smem_bytes_for(int N) { return stages_for(N) * stage_bytes(N) + 1024 + kTailBytes; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -83,10 +84,6 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
       : "memory");
-}
-// TMA prefetch of one tile into L2 (no shared-memory destination, no completion to wait for)
-__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int c0, int c1) {
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -140,11 +137,7 @@ struct TcParams {
   float* partials;      // [splits][tok_tiles*N][n_out_pad] fp32
   unsigned int* tickets;  // [m_tiles * tok_tiles], zero on entry, zero on exit
   int n_out_pad;
-  int l2_ahead; // weight tiles (16 KiB each) a CTA prefetches into L2 before griddepcontrol.wait
   int cluster;  // 1: the `splits` CTAs of a slab form a thread-block cluster and reduce through DSMEM
-  // next weights to pull into L2 while this kernel (and the small kernels after it) run
-  const char* pf_ptr;
-  long long pf_bytes;
   // MODE_ROPE_KV (slab == one 128-wide head of the fused qkv projection)
   const int32_t* positions;
   const int32_t* slots;
@@ -153,6 +146,17 @@ struct TcParams {
   __nv_bfloat16* vc;
   int hq, hkv, block_size;
   unsigned long long* trace;  // debug (B200_TC_TRACE=1): %globaltimer stamps of CTA 0, else null
+  // Residual stream in fp32 (RMSNorm folded into the linears, T <= 64):
+  //   producer (MODE kResidual, O / down projection): s = bf16(acc) + bf16(sres) in fp32 -> sres, and the sum of
+  //     squares of the slab's 128 values of s -> ssq[tok][m_tile]              (n_out = hidden)
+  //   consumer (NI, QKV / gate_up / lm_head): the B operand is bf16(bf16(s * rinv) * norm_w) built in shared memory
+  //     from sres, rinv = 1/sqrt(sum_slabs ssq / hidden + eps)                  (k = hidden)
+  float* sres;
+  float* ssq;
+  const __nv_bfloat16* norm_w;
+  const int32_t* rows;   // consumer: token t of the launch reads stream row rows[t] (lm_head's logit rows), or null
+  int nslab;             // hidden / 128
+  float eps;
 };
 
 __device__ __forceinline__ void tc_trace(const TcParams& p, int slot) {
@@ -174,7 +178,8 @@ __device__ __forceinline__ void tc_trace(const TcParams& p, int slot) {
 //            y[t][m_tile*64 + i] = bf16(bf16(silu(bf16(g_i))) * bf16(u_i))          (R5)
 //  kRopeKv   the slab is one head of the fused qkv projection: NeoX RoPE in bf16 arithmetic (R3) on q
 //            and k heads, q rows to y, k/v rows straight into the paged cache at slots[t]
-enum { kPlain = 0, kSiluMul = 1, kRopeKv = 2 };
+//  kResidual the linear's output is added to the fp32 residual stream (see TcParams::sres): no y is written
+enum { kPlain = 0, kSiluMul = 1, kRopeKv = 2, kResidual = 3 };
 
 
 // One thread finalises 4 consecutive slab rows (r4..r4+3, lane = r4/4) of one token.
@@ -211,6 +216,21 @@ __device__ __forceinline__ void finalize4(const TcParams& p, int m_tile, int lan
       dst[0] = __float2bfloat16_rn(o0);
       dst[1] = __float2bfloat16_rn(o1);
     }
+  } else if (MODE == kResidual) {
+    // x = bf16(acc + bias); s = x + bf16(s_old) in fp32 (R1: the residual is kept in bf16, the sum is not rounded
+    // before the variance and the normalisation); sum of squares in a fixed order: lane's 4 rows, then the warp tree
+    const int row = m_tile * kBlockM + r4;
+    float4* sp = reinterpret_cast<float4*>(p.sres + (int64_t)tok * p.n_out + row);
+    const float4 so = *sp;
+    const float4 sn = make_float4(v[0] + round_bf16(so.x), v[1] + round_bf16(so.y), v[2] + round_bf16(so.z),
+                                  v[3] + round_bf16(so.w));
+    *sp = sn;
+    float ss = fmaf(sn.x, sn.x, 0.f);
+    ss = fmaf(sn.y, sn.y, ss);
+    ss = fmaf(sn.z, sn.z, ss);
+    ss = fmaf(sn.w, sn.w, ss);
+    ss = warp_sum(ss);
+    if (lane == 0) p.ssq[(int64_t)tok * p.nslab + m_tile] = ss;
   } else {  // kRopeKv
     const int head = m_tile;
     float o[4];
@@ -249,10 +269,89 @@ __device__ __forceinline__ void finalize4(const TcParams& p, int m_tile, int lan
   }
 }
 
-template <int N, int MODE, int S>
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Fused-norm consumer: the four epilogue warps build the B operand (the normalised token rows) in the ring while the
+// TMA warp streams W.  Warp wq owns the K blocks i = wq (mod 4): it reads the fp32 stream rows (L2), applies R1
+//   n = bf16(s * rinv), y = bf16(n * w),   rinv = 1/sqrt(sum over slabs of ssq / hidden + eps) (slabs in ascending order)
+// and stores the bf16 row chunks where a SWIZZLE_128B TMA box would have put them (16-byte chunk c of row t at
+// t*128 + ((c ^ (t & 7)) << 4)); rows >= T keep whatever the ring held (their accumulator columns are never read).
+template <int N, int S>
+__device__ __forceinline__ void norm_b_tiles(const TcParams& p, unsigned char* smem, uint64_t* full, uint64_t* empty,
+                                             float* rinv_s, int* row_s, int tok0, int kb0, int nkb, int wq, int lane) {
+  constexpr int kStageBytes = stage_bytes(N);
+  constexpr int kABytes = kBlockM * kBlockK * 2;
+  constexpr int U = 4;
+  const int te = wq * 32 + lane;
+  const int tmax = min(N, p.T - tok0);
+  const int hidden = p.nslab * kBlockM;
+  if (te < tmax) {
+    const int row = p.rows ? p.rows[tok0 + te] : tok0 + te;
+    const float* q = p.ssq + (int64_t)row * p.nslab;
+    float tot = 0.f;
+#pragma unroll 8
+    for (int i = 0; i < p.nslab; ++i) tot += __ldcg(q + i);
+    rinv_s[te] = 1.0f / sqrtf(tot / (float)hidden + p.eps);
+    row_s[te] = row;
+  }
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  const int ntask = tmax * 8;   // (token row, 16-byte chunk of the 64-wide K block)
+  for (int i = wq; i < nkb; i += 4) {
+    const int st = i % S;
+    const int kcol = (kb0 + i) * kBlockK;
+    const uint32_t bbase = smem_u32(smem + st * kStageBytes + kABytes);
+    bool need_wait = i >= S;
+    for (int task0 = lane; task0 < ntask; task0 += 32 * U) {
+      float4 a[U][2];
+      uint4 wv[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int task = task0 + 32 * u;
+        if (task < ntask) {
+          const int t = task >> 3, c = task & 7;
+          const float4* src = reinterpret_cast<const float4*>(p.sres + (int64_t)row_s[t] * hidden + kcol + c * 8);
+          a[u][0] = __ldcg(src);
+          a[u][1] = __ldcg(src + 1);
+          wv[u] = __ldg(reinterpret_cast<const uint4*>(p.norm_w + kcol + c * 8));
+        }
+      }
+      if (need_wait) {   // the MMAs that read this stage's previous tile have completed
+        mbar_wait(&empty[st], ((i / S) - 1) & 1);
+        need_wait = false;
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int task = task0 + 32 * u;
+        if (task < ntask) {
+          const int t = task >> 3, c = task & 7;
+          const float r = rinv_s[t];
+          const float sv[8] = {a[u][0].x, a[u][0].y, a[u][0].z, a[u][0].w, a[u][1].x, a[u][1].y, a[u][1].z, a[u][1].w};
+          const uint32_t ww[4] = {wv[u].x, wv[u].y, wv[u].z, wv[u].w};
+          uint32_t o[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float n0 = round_bf16(sv[2 * j] * r), n1 = round_bf16(sv[2 * j + 1] * r);
+            o[j] = pack_bf16(n0 * bf16lo(ww[j]), n1 * bf16hi(ww[j]));
+          }
+          const uint32_t dst = bbase + (uint32_t)t * 128u + (uint32_t)((c ^ (t & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+        }
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to tcgen05.mma
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&full[st]);
+  }
+}
+
+template <int N, int MODE, int S, bool NI>
 __global__ void __launch_bounds__(kTcThreads)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, TcParams p) {
+  static_assert(!NI || N <= 64, "the fused-norm consumer serves decode-sized token tiles");
   constexpr int kStageBytes = stage_bytes(N);
+  constexpr uint32_t kTmaBytes = NI ? kBlockM * kBlockK * 2 : kStageBytes;   // NI: only W arrives by TMA
   constexpr int kABytes = kBlockM * kBlockK * 2;
   constexpr int kTmemCols = N < 32 ? 32 : N;
   extern __shared__ unsigned char smem_raw[];
@@ -262,6 +361,8 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   uint64_t* tmem_full = empty + S;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
   int* ticket_slot = reinterpret_cast<int*>(tmem_slot + 1);
+  float* rinv_s = reinterpret_cast<float*>(smem + S * kStageBytes + 256);   // [64]
+  int* row_s = reinterpret_cast<int*>(rinv_s + 64);                         // [64]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // Several token tiles (prefill): the token tile is the FAST index, so that the CTAs that share a weight slab
@@ -278,7 +379,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], NI ? 2 : 1);   // NI: the TMA producer and the warp that wrote the stage's B tile
       mbar_init(&empty[s], 1);
     }
     mbar_init(tmem_full, 1);
@@ -302,25 +403,24 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const int pre = min(S, nkb);
       // weights first: they do not depend on the producer of x
       for (int i = 0; i < pre; ++i) {
-        mbar_expect_tx(&full[i], kStageBytes);
+        mbar_expect_tx(&full[i], kTmaBytes);
         tma_load_2d(smem + i * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[i], w_policy);
       }
       tc_trace(p, 1);   // W of the first stages requested
-      // While the previous kernel drains (its epilogue, then the small kernels that produce x), HBM would
-      // idle: pull this CTA's NEXT weight tiles into L2 now, so that the loads issued after the wait hit L2.
-      for (int i = pre; i < min(nkb, pre + p.l2_ahead); ++i)
-        tma_prefetch_2d(&map_w, (kb0 + i) * kBlockK, m_tile * kBlockM);
       pdl_wait();
       tc_trace(p, 2);   // previous kernel complete
       pdl_launch_dependents();
-      for (int i = 0; i < pre; ++i)
-        tma_load_2d(smem + i * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[i], kEvictLast);
+      if constexpr (!NI) {
+        for (int i = 0; i < pre; ++i)
+          tma_load_2d(smem + i * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[i], kEvictLast);
+      }
       for (int i = pre; i < nkb; ++i) {
         const int st = i % S;
         mbar_wait(&empty[st], ((i / S) - 1) & 1);
-        mbar_expect_tx(&full[st], kStageBytes);
+        mbar_expect_tx(&full[st], kTmaBytes);
         tma_load_2d(smem + st * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[st], w_policy);
-        tma_load_2d(smem + st * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[st], kEvictLast);
+        if constexpr (!NI)
+          tma_load_2d(smem + st * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[st], kEvictLast);
       }
     } else {
       pdl_wait();
@@ -355,6 +455,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     const int tok0 = tok_tile * N;
     const int wq = warp - 2;
     pdl_wait();
+    if constexpr (NI) norm_b_tiles<N, S>(p, smem, full, empty, rinv_s, row_s, tok0, kb0, nkb, wq, lane);
     if (nkb > 0) {
       mbar_wait(tmem_full, 0);
       tc_fence_after();
@@ -499,18 +600,6 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       if (p.splits > 1 && warp == 2 && lane == 0) p.tickets[tile_id] = 0u;  // leave the tickets zero for the next launch
     }
     }   // !kChunked
-    // This CTA is done streaming: pull (a prefix of) the NEXT linear's weights towards L2 so that HBM
-    // keeps working through this kernel's tail and the small kernels that follow (fire and forget).
-    if (p.pf_bytes > 0) {
-      const long long n_ctas = (long long)gridDim.x * gridDim.y * gridDim.z;
-      const long long cta = blockIdx.x + (long long)gridDim.x * (blockIdx.y + (long long)gridDim.y * blockIdx.z);
-      const long long per = ((p.pf_bytes + n_ctas - 1) / n_ctas + 4095) & ~4095ll;
-      const long long lo = cta * per, hi = min(lo + per, p.pf_bytes);
-      for (long long off = lo + (long long)(wq * 32 + lane) * 4096; off < hi; off += 128ll * 4096) {
-        const uint32_t bytes = (uint32_t)min(4096ll, hi - off) & ~15u;
-        if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.pf_ptr + off), "r"(bytes) : "memory");
-      }
-    }
     tc_fence_before();
   }
   if (threadIdx.x == 64) tc_trace(p, 7);   // before the cluster phase
@@ -661,7 +750,6 @@ inline int n_tile_for(int T) { return T <= 16 ? 16 : (T <= 32 ? 32 : (T <= 64 ? 
 
 struct Plan {
   int N, m_tiles, tok_tiles, n_kblocks, splits, n_out_pad;
-  int deep;   // experiment (B200_TC_DEEP=1): at most one CTA per SM, each with a ring that fills the SM's shared memory
 };
 
 Plan make_plan(int T, int n_out, int k) {
@@ -673,11 +761,9 @@ Plan make_plan(int T, int n_out, int k) {
   pl.n_out_pad = pl.m_tiles * kBlockM;
   // Split K until about one CTA per SM exists (two kernels of the step can then be co-resident
   // under programmatic dependent launch: the next one prefetches its first weight stages while
-  // this one drains).  Tunable for experiments: B200_TC_SLOTS, B200_TC_MIN_KB.
-  static const int slots_env = getenv("B200_TC_SLOTS") ? atoi(getenv("B200_TC_SLOTS")) : 0;
-  static const int minkb_env = getenv("B200_TC_MIN_KB") ? atoi(getenv("B200_TC_MIN_KB")) : 0;
-  const int slots = slots_env > 0 ? slots_env : kNumSMs;
-  const int min_kb = minkb_env > 0 ? minkb_env : 4;
+  // this one drains).
+  const int slots = kNumSMs;
+  const int min_kb = 4;
   const int tiles = pl.m_tiles * pl.tok_tiles;
   int s = 1;
   if (tiles < slots) {
@@ -686,51 +772,52 @@ Plan make_plan(int T, int n_out, int k) {
     s = max(1, min(s, 32));
   }
   pl.splits = s;
-  static const int deep_env = getenv("B200_TC_DEEP") ? atoi(getenv("B200_TC_DEEP")) : 0;
-  pl.deep = 0;
-  if (deep_env && pl.N <= 64 && tiles <= kNumSMs) {
-    int sd = kNumSMs / tiles;                              // never more than one CTA per SM
-    sd = max(1, min(min(sd, 8), max(pl.n_kblocks / min_kb, 1)));
-    pl.splits = sd;
-    pl.deep = 1;
-  }
   return pl;
 }
 
-// deep ring: as many stages as fit one CTA per SM (for launches of at most one CTA per SM)
-__host__ __device__ constexpr int deep_stages_for(int N) { return (200 * 1024) / stage_bytes(N); }
-
-template <int N, int MODE, int S>
+template <int N, int MODE, int S, bool NI>
 int launch_tc3(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
-  static bool attr_set = false;
-  const int smem = S * stage_bytes(N) + 1024 + 256;
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N, MODE, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
+  static bool attr_set[64] = {};   // per device: a process may drive several GPUs
+  const int smem = S * stage_bytes(N) + 1024 + kTailBytes;
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N, MODE, S, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  B200_CUDA(launch_cluster(linear_tc_kernel<N, MODE, S>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads),
+  B200_CUDA(launch_cluster(linear_tc_kernel<N, MODE, S, NI>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads),
                            (size_t)smem, s, p.cluster ? dim3(1, pl.splits, 1) : dim3(1, 1, 1), mw, mx, p));
   return B200_OK;
 }
 
-template <int N, int MODE>
+template <int N, int MODE, bool NI>
 int launch_tc2(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
-  if (pl.deep) return launch_tc3<N, MODE, deep_stages_for(N)>(mw, mx, p, pl, s);
   if constexpr (N == 256) {
     // the 2-stage kernel (two CTAs per SM, chunked epilogue) has no room for a whole fp32 tile: split-K
     // launches of a single token tile keep 4 stages
-    static const int two_env = getenv("B200_TC_N256_STAGES") ? atoi(getenv("B200_TC_N256_STAGES")) : 2;
-    if (pl.splits > 1 || p.cluster || two_env == 4) return launch_tc3<N, MODE, 4>(mw, mx, p, pl, s);
+    if (pl.splits > 1 || p.cluster) return launch_tc3<N, MODE, 4, NI>(mw, mx, p, pl, s);
   }
-  return launch_tc3<N, MODE, stages_for(N)>(mw, mx, p, pl, s);
+  return launch_tc3<N, MODE, stages_for(N), NI>(mw, mx, p, pl, s);
 }
 
 template <int N>
-int launch_tc(int mode, const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
+int launch_tc(int mode, bool ni, const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl,
+              cudaStream_t s) {
+  if constexpr (N <= 64) {   // the fp32 residual stream serves decode-sized steps only
+    if (mode == kResidual) return launch_tc2<N, kResidual, false>(mw, mx, p, pl, s);
+    if (ni) {
+      switch (mode) {
+        case kSiluMul: return launch_tc2<N, kSiluMul, true>(mw, mx, p, pl, s);
+        case kRopeKv: return launch_tc2<N, kRopeKv, true>(mw, mx, p, pl, s);
+        default: return launch_tc2<N, kPlain, true>(mw, mx, p, pl, s);
+      }
+    }
+  }
+  B200_REQUIRE(mode != kResidual && !ni, B200_ERR_UNSUPPORTED, "linear_tc: the fused-norm modes need T <= 64 (T tile %d)", N);
   switch (mode) {
-    case kSiluMul: return launch_tc2<N, kSiluMul>(mw, mx, p, pl, s);
-    case kRopeKv: return launch_tc2<N, kRopeKv>(mw, mx, p, pl, s);
-    default: return launch_tc2<N, kPlain>(mw, mx, p, pl, s);
+    case kSiluMul: return launch_tc2<N, kSiluMul, false>(mw, mx, p, pl, s);
+    case kRopeKv: return launch_tc2<N, kRopeKv, false>(mw, mx, p, pl, s);
+    default: return launch_tc2<N, kPlain, false>(mw, mx, p, pl, s);
   }
 }
 
@@ -765,9 +852,8 @@ int64_t linear_tc_workspace_bytes(int T, int n_out, int k) {
 int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const __nv_bfloat16* bias,
               __nv_bfloat16* y, int64_t ldy, int T, int n_out, int k, void* ws, int64_t ws_bytes,
               const LinearExtra* ex, cudaStream_t s) {
-  B200_REQUIRE(k % 8 == 0 && ldx % 8 == 0, B200_ERR_UNSUPPORTED, "linear_tc: k and ldx must be multiples of 8");
-  B200_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) % 16 == 0, B200_ERR_INVALID,
-               "linear_tc: x and w must be 16-byte aligned");
+  B200_REQUIRE(k % 8 == 0, B200_ERR_UNSUPPORTED, "linear_tc: k must be a multiple of 8");
+  B200_REQUIRE(reinterpret_cast<uintptr_t>(w) % 16 == 0, B200_ERR_INVALID, "linear_tc: w must be 16-byte aligned");
   const Plan pl = make_plan(T, n_out, k);
   const int64_t need = linear_tc_workspace_bytes(T, n_out, k);
   static const int cluster_env = getenv("B200_TC_CLUSTER") ? atoi(getenv("B200_TC_CLUSTER")) : 1;
@@ -777,8 +863,6 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
   const int mode = ex ? ex->mode : 0;
   TcParams p = {};
   p.cluster = use_cluster ? 1 : 0;
-  static const int l2_ahead_env = getenv("B200_TC_L2_AHEAD") ? atoi(getenv("B200_TC_L2_AHEAD")) : 0;   // measured: every depth > 0 is slower (the predecessor is still streaming)
-  p.l2_ahead = launch_opts().pdl ? l2_ahead_env : 0;   // only useful when this kernel starts before its predecessor ends
   p.trace = trace_buffer();
   if (mode == kSiluMul) {
     B200_REQUIRE(n_out % kBlockM == 0, B200_ERR_UNSUPPORTED, "linear_tc(silu_mul): n_out=%d must be a multiple of 128", n_out);
@@ -796,18 +880,36 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
     p.hq = ex->hq;
     p.hkv = ex->hkv;
     p.block_size = ex->block_size;
+  } else if (mode == kResidual) {
+    B200_REQUIRE(ex->sres && ex->ssq && n_out % kBlockM == 0 && pl.N <= 64, B200_ERR_INVALID,
+                 "linear_tc(residual): needs the fp32 stream, n_out %% 128 == 0 and T <= 64 (n_out=%d T=%d)", n_out, T);
+    p.sres = ex->sres;
+    p.ssq = ex->ssq;
+    p.nslab = n_out / kBlockM;
   } else {
     B200_REQUIRE(mode == kPlain, B200_ERR_INVALID, "linear_tc: unknown epilogue mode %d", mode);
   }
-  if (ex && ex->pf_ptr && ex->pf_bytes > 0) {
-    p.pf_ptr = static_cast<const char*>(ex->pf_ptr);
-    p.pf_bytes = ex->pf_bytes & ~15ll;
+  const bool ni = ex && ex->norm_in;
+  if (ni) {
+    B200_REQUIRE(mode != kResidual && ex->sres && ex->ssq && ex->norm_w && k % 128 == 0 && pl.N <= 64 && pl.tok_tiles == 1,
+                 B200_ERR_INVALID, "linear_tc(norm_in): needs the fp32 stream, k %% 128 == 0 and T <= 64 (k=%d T=%d)", k, T);
+    p.sres = ex->sres;
+    p.ssq = ex->ssq;
+    p.norm_w = ex->norm_w;
+    p.rows = ex->rows;
+    p.nslab = k / kBlockM;
+    p.eps = ex->eps;
   }
   CUtensorMap mw, mx;
   int rc = get_map(w, (uint64_t)n_out, (uint64_t)k, (uint64_t)k, kBlockM, &mw);
   if (rc) return rc;
-  rc = get_map(x, (uint64_t)T, (uint64_t)k, (uint64_t)ldx, (uint32_t)pl.N, &mx);
-  if (rc) return rc;
+  if (ni) {
+    mx = mw;   // unused: the B operand is built in shared memory
+  } else {
+    B200_REQUIRE(x && reinterpret_cast<uintptr_t>(x) % 16 == 0 && ldx % 8 == 0, B200_ERR_INVALID, "linear_tc: bad x");
+    rc = get_map(x, (uint64_t)T, (uint64_t)k, (uint64_t)ldx, (uint32_t)pl.N, &mx);
+    if (rc) return rc;
+  }
   p.bias = bias;
   p.y = y;
   p.ldy = ldy;
@@ -819,11 +921,11 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
   p.partials = ws ? reinterpret_cast<float*>(static_cast<char*>(ws) + kCounterBytes) : nullptr;
   p.n_out_pad = pl.n_out_pad;
   switch (pl.N) {
-    case 16: return launch_tc<16>(mode, mw, mx, p, pl, s);
-    case 32: return launch_tc<32>(mode, mw, mx, p, pl, s);
-    case 64: return launch_tc<64>(mode, mw, mx, p, pl, s);
-    case 128: return launch_tc<128>(mode, mw, mx, p, pl, s);
-    default: return launch_tc<256>(mode, mw, mx, p, pl, s);
+    case 16: return launch_tc<16>(mode, ni, mw, mx, p, pl, s);
+    case 32: return launch_tc<32>(mode, ni, mw, mx, p, pl, s);
+    case 64: return launch_tc<64>(mode, ni, mw, mx, p, pl, s);
+    case 128: return launch_tc<128>(mode, ni, mw, mx, p, pl, s);
+    default: return launch_tc<256>(mode, ni, mw, mx, p, pl, s);
   }
 }
 

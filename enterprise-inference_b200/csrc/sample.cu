@@ -39,6 +39,12 @@ __device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint
   c[2] = n2;
   c[3] = lo0;
 }
+// 32 random bits -> uniform strictly inside (0, 1): the top 23 bits plus one half, exact in fp32 (24 significant
+// bits), so that neither -log(u) nor -log(-log(u)) can be infinite.  (24 bits + 0.5 would round to 1.0 for the
+// largest draw: that token would win the Gumbel-max whatever its logit.)
+__host__ __device__ __forceinline__ float uniform_from_bits(uint32_t bits) {
+  return ((float)(bits >> 9) + 0.5f) * (1.0f / 8388608.0f);
+}
 // uniform in (0, 1) for (seed, draw number, token index)
 __device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t draw, uint32_t index) {
   uint32_t c[4] = {index, (uint32_t)draw, (uint32_t)(draw >> 32), 0x5a17u};
@@ -49,7 +55,7 @@ __device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t draw, ui
     k0 += 0x9E3779B9u;
     k1 += 0xBB67AE85u;
   }
-  return ((float)(c[0] >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  return uniform_from_bits(c[0]);
 }
 
 struct Best {
@@ -400,3 +406,9 @@ int sample_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, 
 }
 
 }  // namespace b200
+
+// debug helper (not in the public header): the bits -> uniform mapping of the sampler, callable on the host so that a
+// CPU test can pin its end points (0 < u < 1 for every 32-bit draw)
+extern "C" __attribute__((visibility("default"))) float b200_debug_uniform_from_bits(uint32_t bits) {
+  return b200::uniform_from_bits(bits);
+}

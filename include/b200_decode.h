@@ -181,6 +181,33 @@ B200_API int b200_linear_fused_bf16(const void* x, int64_t ldx, const void* w, c
                            void* k_cache_layer, void* v_cache_layer, int32_t n_q_heads, int32_t n_kv_heads,
                            int32_t block_size, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* (a2 folded into a3/a7/a8/a9) RMSNorm without a kernel of its own, for steps of at most 64 rows.  The residual
+ * stream lives in fp32: sres[T][hidden] holds s = x + res UNROUNDED (what [V22] vllm/ir/ops/layernorm.py:40-58
+ * takes the variance of and normalises; the bf16 residual of the next layer is bf16(s), recomputed on read) and
+ * ssq[T][hidden/128] the sums of squares of s per 128-wide slab.
+ *  - b200_embed_stream: (a1) sres[t] = float(table[ids[t]]) and its ssq;
+ *  - b200_linear_residual_bf16: (a7, a8-down) x = bf16(x_in . w^T + bias); sres = x + bf16(sres); ssq rewritten
+ *    (n_out = hidden, a multiple of 128; no y is written);
+ *  - b200_linear_normed_bf16: (a3, a8-gate_up, a9) the linear over y_in[t] = bf16(bf16(s * rinv) * norm_w),
+ *    rinv = 1/sqrt(sum(ssq[row]) / k + eps), s = sres[rows ? rows[t] : t] (k = hidden); the rows are normalised
+ *    inside the kernel while the weights stream.  mode / trailing arguments as b200_linear_fused_bf16 (0 = plain);
+ *  - b200_rmsnorm_stream: the same normalised rows written out as bf16 [n_rows][hidden].
+ * The summation order of the variance is the one b200_rmsnorm uses, so a step through these entry points is
+ * bit-identical to embed -> rmsnorm -> linear -> ... with bf16 activations. */
+B200_API int b200_embed_stream(const int32_t* ids, const void* table, float* sres, float* ssq, int32_t n_tokens,
+                      int32_t hidden, int32_t vocab, void* stream);
+B200_API int b200_linear_residual_bf16(const void* x, int64_t ldx, const void* w, const void* bias, float* sres,
+                              float* ssq, int32_t n_tokens, int32_t n_out, int32_t k, void* workspace,
+                              int64_t workspace_bytes, void* stream);
+B200_API int b200_linear_normed_bf16(const float* sres, const float* ssq, const void* norm_w, float eps,
+                            const int32_t* rows, const void* w, const void* bias, void* y, int64_t ldy,
+                            int32_t n_tokens, int32_t n_out, int32_t k, int32_t mode, const int32_t* positions,
+                            const int32_t* slot_mapping, const void* cos_sin, void* k_cache_layer,
+                            void* v_cache_layer, int32_t n_q_heads, int32_t n_kv_heads, int32_t block_size,
+                            void* workspace, int64_t workspace_bytes, void* stream);
+B200_API int b200_rmsnorm_stream(const float* sres, const float* ssq, const int32_t* rows, const void* w, void* y,
+                        int32_t n_rows, int32_t hidden, float eps, void* stream);
+
 /* (a2) y = rmsnorm(x)*w, or with res != NULL: s=x+res; res=bf16(s); y=rmsnorm(s)*w
  * ([V22] vllm/ir/ops/layernorm.py:10-21,40-58). y may alias x. */
 B200_API int b200_rmsnorm(const void* x, void* res, const void* w, void* y, int32_t n_tokens,

@@ -51,3 +51,21 @@ def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setattr(abi, "LIB_PATH", "/nonexistent/libb200decode.so")
     with pytest.raises(ImportError, match="no CPU fallback"):
         abi.lib()
+
+
+def test_sampler_uniform_is_strictly_inside_the_unit_interval():
+    """The sampler draws by Gumbel-max: g = -log(-log(u)).  u == 1 would make g = +inf and that token would win
+    whatever its logit (one draw in 2^24 per kept token: several garbage tokens per reply over a 128k vocabulary).
+    The mapping from the 32 Philox bits must stay strictly inside (0, 1) at both end points and in between."""
+    import math
+    import numpy as np
+    lib = pkg("_abi").lib()
+    f = lib.b200_debug_uniform_from_bits
+    f.restype, f.argtypes = C.c_float, [C.c_uint32]
+    rng = np.random.default_rng(0)
+    for bits in [0, 1, 0x1FF, 0x200, 0x7FFFFFFF, 0x80000000, 0xFFFFFE00, 0xFFFFFFFF] + rng.integers(0, 2 ** 32, 64).tolist():
+        u = float(f(int(bits)))
+        assert 0.0 < u < 1.0, f"bits {bits:#x} -> u = {u!r}"
+        g = -math.log(-math.log(u))
+        assert math.isfinite(g)
+    assert f(0) == np.float32(2.0 ** -24) and f(0xFFFFFFFF) == np.float32(1.0 - 2.0 ** -24)

@@ -177,6 +177,108 @@ def test_linear_fused_rope_kv_is_bit_identical_to_unfused(lib, abi, T, hq, hkv, 
     assert out[True][1].any() and out[True][2].any()
 
 
+@pytest.mark.parametrize("T,h,k", [(1, 4096, 4096), (5, 512, 1024), (16, 4096, 14336), (33, 640, 1536), (64, 4096, 4096),
+                                   (64, 1024, 2048)])
+def test_folded_norm_producer_is_bit_identical_to_linear_then_add_norm(lib, abi, T, h, k):
+    """O / down projection that adds into the fp32 residual stream (b200_linear_residual_bf16) followed by
+    b200_rmsnorm_stream == tcgen05 linear followed by the add+RMSNorm kernel: normed rows and residual bit for bit,
+    twice in a row (the stream is updated in place)."""
+    g = torch.Generator().manual_seed(T + h + k)
+    V = 97
+    table = dev(torch.randn(V, h, generator=g).to(BF))
+    ids = dev(torch.randint(0, V, (T,), generator=g).to(torch.int32))
+    w = dev((0.05 * torch.randn(h, k, generator=g)).to(BF))
+    nw = dev((1 + 0.1 * torch.randn(h, generator=g)).to(BF))
+    wsb = lib.b200_linear_workspace_bytes(T, h, k)
+    ws = torch.zeros(wsb, dtype=torch.uint8, device="cuda")
+    sres = torch.full((T, h), float("nan"), dtype=torch.float32, device="cuda")
+    ssq = torch.full((T, h // 128), float("nan"), dtype=torch.float32, device="cuda")
+    res = torch.empty(T, h, dtype=BF, device="cuda")
+    sync_check(abi, lib.b200_embed_stream(ids.data_ptr(), table.data_ptr(), sres.data_ptr(), ssq.data_ptr(), T, h, V, None))
+    sync_check(abi, lib.b200_embed(ids.data_ptr(), table.data_ptr(), res.data_ptr(), T, h, V, None))
+    assert torch.equal(sres, res.float())
+    for it in range(2):
+        x = dev(torch.randn(T, k, generator=g).to(BF))
+        y = torch.empty(T, h, dtype=BF, device="cuda")
+        want = torch.empty(T, h, dtype=BF, device="cuda")
+        got = torch.full((T, h), float("nan"), dtype=BF, device="cuda")
+        sync_check(abi, lib.b200_linear_bf16(x.data_ptr(), k, w.data_ptr(), None, y.data_ptr(), h, T, h, k, 2, ws.data_ptr(), wsb, None))
+        sync_check(abi, lib.b200_rmsnorm(y.data_ptr(), res.data_ptr(), nw.data_ptr(), want.data_ptr(), T, h, 1e-5, None))
+        sync_check(abi, lib.b200_linear_residual_bf16(x.data_ptr(), k, w.data_ptr(), None, sres.data_ptr(), ssq.data_ptr(), T, h, k,
+                                                      ws.data_ptr(), wsb, None))
+        sync_check(abi, lib.b200_rmsnorm_stream(sres.data_ptr(), ssq.data_ptr(), None, nw.data_ptr(), got.data_ptr(), T, h, 1e-5, None))
+        assert torch.equal(sres.to(BF), res), f"residual differs (pass {it})"
+        assert torch.equal(got, want), f"normed rows differ (pass {it})"
+    assert not ws[:65536].any()
+
+
+@pytest.mark.parametrize("T,h,n_out,mode", [(1, 4096, 6144, 2), (1, 4096, 28672, 1), (3, 512, 1024, 0), (16, 4096, 6144, 2),
+                                            (17, 640, 3072, 1), (40, 1024, 2560, 2), (64, 4096, 28672, 1), (64, 4096, 6144, 2),
+                                            (9, 4096, 128256 // 4, 0)])
+def test_folded_norm_consumer_is_bit_identical_to_norm_then_linear(lib, abi, T, h, n_out, mode):
+    """QKV / gate_up / lm_head linears that normalise their input rows from the fp32 stream inside the kernel
+    (b200_linear_normed_bf16; plain, SiLU*mul and RoPE+KV epilogues) == b200_rmsnorm_stream followed by the same
+    linear over the bf16 rows: outputs and cache bit for bit.  Mode 0 also goes through the row indirection."""
+    g = torch.Generator().manual_seed(T + h + n_out + mode)
+    V = 211
+    table = dev(torch.randn(V, h, generator=g).to(BF))
+    ids = dev(torch.randint(0, V, (T,), generator=g).to(torch.int32))
+    w = dev((0.05 * torch.randn(n_out, h, generator=g)).to(BF))
+    nw = dev((1 + 0.1 * torch.randn(h, generator=g)).to(BF))
+    sres = torch.empty(T, h, dtype=torch.float32, device="cuda")
+    ssq = torch.empty(T, h // 128, dtype=torch.float32, device="cuda")
+    sync_check(abi, lib.b200_embed_stream(ids.data_ptr(), table.data_ptr(), sres.data_ptr(), ssq.data_ptr(), T, h, V, None))
+    sres.mul_(1.37)            # not exactly bf16 any more: s * rinv must be taken on the fp32 value
+    ssq.mul_(1.37 * 1.37)
+    wsb = lib.b200_linear_workspace_bytes(T, n_out, h)
+    ws = torch.zeros(wsb, dtype=torch.uint8, device="cuda")
+    rows = None
+    R = T
+    if mode == 0 and T > 1:
+        rows = dev(torch.randperm(T, generator=g)[: max(T // 2, 1)].to(torch.int32))
+        R = rows.numel()
+    normed = torch.empty(R, h, dtype=BF, device="cuda")
+    sync_check(abi, lib.b200_rmsnorm_stream(sres.data_ptr(), ssq.data_ptr(), abi.ptr(rows), nw.data_ptr(), normed.data_ptr(), R, h, 1e-5, None))
+    hq, hkv, bs, nb = 0, 0, 128, 4
+    pos = slots = cs = None
+    ldy = n_out
+    if mode == 1:
+        ldy = n_out // 2
+    if mode == 2:
+        hkv = {48: 8, 20: 2}.get(n_out // 128, 1)
+        hq = n_out // 128 - 2 * hkv
+        pos = dev(torch.randint(0, 700, (T,), generator=g).to(torch.int32))
+        sl = torch.randperm(nb * bs, generator=g)[:T].to(torch.int32)
+        if T > 2:
+            sl[T // 2] = -1
+        slots = dev(sl)
+        cs = dev(O.cos_sin_cache(O.CONFIGS["tiny"], 1024))
+    out = {}
+    for fused in (False, True):
+        y = torch.full((R, ldy), float("nan"), dtype=BF, device="cuda")
+        kc = torch.zeros(nb, max(hkv, 1), bs, 128, dtype=BF, device="cuda")
+        vc = torch.zeros_like(kc)
+        tail = (abi.ptr(pos), abi.ptr(slots), abi.ptr(cs), kc.data_ptr(), vc.data_ptr(), hq, hkv, bs, ws.data_ptr(), wsb, None)
+        if fused:
+            sync_check(abi, lib.b200_linear_normed_bf16(sres.data_ptr(), ssq.data_ptr(), nw.data_ptr(), 1e-5, abi.ptr(rows),
+                                                        w.data_ptr(), None, y.data_ptr(), ldy, R, n_out, h, mode, *tail))
+        elif mode == 0:
+            sync_check(abi, lib.b200_linear_bf16(normed.data_ptr(), h, w.data_ptr(), None, y.data_ptr(), ldy, R, n_out, h, 2,
+                                                 ws.data_ptr(), wsb, None))
+        else:
+            sync_check(abi, lib.b200_linear_fused_bf16(normed.data_ptr(), h, w.data_ptr(), None, y.data_ptr(), ldy, R, n_out, h,
+                                                       mode, *tail))
+        out[fused] = (y[:, :hq * 128].clone() if mode == 2 else y, kc, vc)
+    for a, bb in zip(out[True], out[False]):
+        assert torch.equal(a, bb)
+    assert not ws[:65536].any()
+    # and the normalised rows themselves against the oracle's R1 on the same fp32 stream
+    src = sres.cpu() if rows is None else sres.cpu()[rows.cpu().long()]
+    var = src.pow(2).mean(-1, keepdim=True)
+    want = ((src * torch.rsqrt(var + 1e-5)).to(BF).float() * nw.cpu().float()).to(BF)
+    ulp_close(normed, want, max_ulp=2, max_frac=0.01)
+
+
 def test_linear_is_linear_at_full_width(lib, abi):
     """Size-independent property at the 8B down-proj shape: W(a*x) == a*W(x) for a power of two
     (exact in bf16/fp32), and column-sliced leading dimension works."""

@@ -81,6 +81,31 @@ def test_teacher_forced_logits_vs_golden(name, graphs, golden_dir):
     r.close()
 
 
+@pytest.mark.parametrize("name", ["tiny", "tiny-qwen", "tiny-g8"])
+def test_folded_norm_step_is_bit_identical_to_the_unfused_step(name, golden_dir, monkeypatch):
+    """Steps of <= 64 rows keep the residual stream in fp32 and fold every RMSNorm into the neighbouring linears
+    (B200_FUSE_NORM_MAX_T=0 switches that off): same rounding points, same summation order -> the logits of chunked
+    prefill steps (5 and 33 rows) and of single-row decode steps are equal bit for bit, with and without CUDA graphs."""
+    g = np.load(f"{golden_dir}/{name}.npz")
+    cfg = O.CONFIGS[name]
+    w = O.make_weights(cfg, seed=int(g["seed"]), norm_jitter=float(g["norm_jitter"]))
+    ids = g["prompt"].tolist() + g["tokens"].tolist()[:-1]
+    out = {}
+    for fold in (0, 64):
+        monkeypatch.setenv("B200_FUSE_NORM_MAX_T", str(fold))
+        for graphs in (False, True):
+            r = make_runner(cfg, w, graphs=graphs)
+            out[(fold, graphs)] = [teacher_forced_logits(r, ids, chunk=c) for c in (33, 5, 1)]
+            if fold:
+                n = r.last_step_launches()
+                assert n <= 5 * cfg.n_layers + 4 + 2, f"{n} launches in a folded single-row step"
+            r.close()
+    for graphs in (False, True):
+        for a, b in zip(out[(0, graphs)], out[(64, graphs)]):
+            assert torch.equal(a, b)
+    assert_logits_close(out[(64, True)][2], torch.from_numpy(g["tf_logits"]))
+
+
 @pytest.mark.parametrize("name", ["tiny", "tiny-g8"])
 def test_engine_greedy_generation_vs_oracle(name, golden_dir):
     """Free-running greedy through the serving engine (scheduler, block manager, host-buffer step):
