@@ -76,6 +76,7 @@ SIGNATURES = {
     "b200_ctx_logprobs_last": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp]),
     "b200_advance_decode_rows": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _vp]),
     "b200_allreduce_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
+    "b200_tp_allreduce": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
 }
 
 _lib = None

@@ -29,6 +29,11 @@ class ModelConfig:
     rope_llama3: bool = True
     rms_eps: float = 1e-5
     max_pos: int = 32768
+    # llama3 rope scaling (config.json rope_scaling): Llama-3.1 = 8 / 1 / 4 / 8192, Llama-3.2 uses factor 32
+    rope_factor: float = 8.0
+    rope_low_freq: float = 1.0
+    rope_high_freq: float = 4.0
+    rope_orig_max_pos: int = 8192
 
     def to_dict(self):
         return asdict(self)
@@ -54,6 +59,9 @@ class ModelConfig:
 
 MODELS: Dict[str, ModelConfig] = {
     "tiny": ModelConfig(),
+    # the 70B head ratio (G = 8) over 8 kv heads on a small body: shards over 2, 4 and 8 tensor-parallel ranks
+    "tiny-g8x8": ModelConfig(name="tiny-g8x8", hidden=1024, n_layers=2, n_q_heads=64, n_kv_heads=8, intermediate=4096,
+                             vocab=4096),
     "meta-llama/Llama-3.1-8B-Instruct": ModelConfig(
         name="meta-llama/Llama-3.1-8B-Instruct", hidden=4096, n_layers=32, n_q_heads=32, n_kv_heads=8,
         intermediate=14336, vocab=128256, max_pos=131072),
@@ -78,14 +86,31 @@ def from_hf_config(path: str) -> ModelConfig:
     with open(os.path.join(path, "config.json")) as f:
         c = json.load(f)
     rs = c.get("rope_scaling") or c.get("rope_parameters") or {}
-    return ModelConfig(
+    # what the kernels implement, and nothing else: a config outside it must fail here, not produce wrong logits
+    mt = c.get("model_type", "llama")
+    if mt not in ("llama", "qwen2"):
+        raise ValueError(f"unsupported model_type {mt!r} (llama and qwen2 decoder stacks only)")
+    rope_type = rs.get("rope_type", rs.get("type")) or "default"
+    if rope_type not in ("default", "llama3"):
+        raise ValueError(f"unsupported rope scaling type {rope_type!r} (plain and llama3 RoPE only)")
+    if c.get("use_sliding_window") and c.get("sliding_window"):
+        raise ValueError("sliding-window attention is not supported")
+    head_dim = c.get("head_dim") or c["hidden_size"] // c["num_attention_heads"]
+    if head_dim != 128:
+        raise ValueError(f"head_dim {head_dim} is not supported (the attention kernels are built for 128)")
+    extra = {}
+    if rope_type == "llama3":
+        extra = dict(rope_factor=float(rs.get("factor", 8.0)), rope_low_freq=float(rs.get("low_freq_factor", 1.0)),
+                     rope_high_freq=float(rs.get("high_freq_factor", 4.0)),
+                     rope_orig_max_pos=int(rs.get("original_max_position_embeddings", 8192)))
+    return ModelConfig(**extra, 
         name=c.get("_name_or_path", path), hidden=c["hidden_size"], n_layers=c["num_hidden_layers"],
         n_q_heads=c["num_attention_heads"], n_kv_heads=c.get("num_key_value_heads", c["num_attention_heads"]),
-        head_dim=c.get("head_dim") or c["hidden_size"] // c["num_attention_heads"],
+        head_dim=head_dim,
         intermediate=c["intermediate_size"], vocab=c["vocab_size"],
         qkv_bias=bool(c.get("attention_bias", False)) or c.get("model_type") == "qwen2",
         rope_theta=float(c.get("rope_theta", rs.get("rope_theta", 10000.0))),
-        rope_llama3=(rs.get("rope_type", rs.get("type")) == "llama3"),
+        rope_llama3=(rope_type == "llama3"),
         rms_eps=float(c.get("rms_norm_eps", 1e-5)), max_pos=int(c.get("max_position_embeddings", 8192)))
 
 
@@ -96,7 +121,7 @@ def rope_cos_sin(cfg: ModelConfig, max_pos: Optional[int] = None) -> torch.Tenso
     d = cfg.head_dim
     inv = 1.0 / (cfg.rope_theta ** (torch.arange(0, d, 2, dtype=torch.float32) / d))
     if cfg.rope_llama3:
-        factor, low, high, orig = 8.0, 1.0, 4.0, 8192
+        factor, low, high, orig = cfg.rope_factor, cfg.rope_low_freq, cfg.rope_high_freq, cfg.rope_orig_max_pos
         wavelen = 2 * math.pi / inv
         smooth = (orig / wavelen - low) / (high - low)
         mid = (1 - smooth) * inv / factor + smooth * inv

@@ -694,6 +694,34 @@ static int tp_reduce_norm(b200_ctx* c, int buf_idx, int T, const __nv_bfloat16* 
   return rmsnorm(c->x, c->res, w, c->normed, T, m.hidden, m.rms_eps, s);
 }
 
+// Per-kernel entry to the step's tensor-parallel collective (tests, timing): `partial` ([T][hidden] bf16, this rank's
+// row-parallel partial sums) is copied into the exchange buffer the O (buf_idx 0) / down (1) projection writes, then the
+// same code path as inside b200_decode_step runs: with norm_w the all-reduce + residual add + RMSNorm (res updated in
+// place, y = normed rows), without it the plain all-reduce into y.
+extern "C" int b200_tp_allreduce(b200_ctx* c, int32_t buf_idx, const void* partial, int32_t T, void* res, const void* norm_w,
+                                 void* y, void* stream) {
+  B200_REQUIRE(c && y && T > 0 && T <= c->cfg.max_tokens && (buf_idx == 0 || buf_idx == 1), B200_ERR_INVALID,
+               "tp_allreduce: bad argument");
+  B200_REQUIRE(c->cfg.tp_world > 1 && c->comm, B200_ERR_STATE, "tp_allreduce: needs tp_world > 1 and b200_nccl_init");
+  B200_REQUIRE(!norm_w || res, B200_ERR_INVALID, "tp_allreduce: the fused norm needs the residual");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t bytes = (size_t)T * c->cfg.hidden * 2;
+  if (partial) B200_CUDA(cudaMemcpyAsync(partial_dst(c, buf_idx, T), partial, bytes, cudaMemcpyDeviceToDevice, s));
+  int rc;
+  if (norm_w) {
+    B200_CUDA(cudaMemcpyAsync(c->res, res, bytes, cudaMemcpyDeviceToDevice, s));
+    rc = tp_reduce_norm(c, buf_idx, T, (const __nv_bfloat16*)norm_w, s);
+    if (rc) return rc;
+    B200_CUDA(cudaMemcpyAsync(res, c->res, bytes, cudaMemcpyDeviceToDevice, s));
+    B200_CUDA(cudaMemcpyAsync(y, c->normed, bytes, cudaMemcpyDeviceToDevice, s));
+  } else {
+    rc = tp_reduce(c, buf_idx, T, s);
+    if (rc) return rc;
+    B200_CUDA(cudaMemcpyAsync(y, c->x, bytes, cudaMemcpyDeviceToDevice, s));
+  }
+  return B200_OK;
+}
+
 // ---- the step --------------------------------------------------------------------------------------
 struct StepArgs {
   const int32_t *ids, *positions, *slots, *block_table, *row_to_seq, *ctx_lens, *logit_rows;

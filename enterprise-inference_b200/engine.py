@@ -82,6 +82,7 @@ class Request:
     finish_time: Optional[float] = None
     token_times: List[float] = field(default_factory=list)
     logprob_data: List[tuple] = field(default_factory=list)   # per emitted token: (logprob, [(id, logprob), ...])
+    error: Optional[str] = None         # set when the engine failed this request (finish_reason "error")
 
     @property
     def all_ids(self) -> List[int]:
@@ -117,6 +118,7 @@ class Scheduler:
         self.max_blocks = blocks.blocks_needed(max_model_len) + 1
         self.bt_np = np.zeros((self.max_seqs + 1, self.max_blocks), dtype=np.int32)
         self.free_rows: List[int] = list(range(self.max_seqs, -1, -1))
+        self.failed: List[Request] = []      # requests the scheduler gave up on; LLMEngine.step reports them as done
 
     def _grow(self, req: Request, n_tokens: int) -> None:
         old = len(req.block_table)
@@ -140,7 +142,34 @@ class Scheduler:
         if len(req.prompt_ids) + req.max_tokens > self.max_model_len:
             raise ValueError(f"prompt ({len(req.prompt_ids)}) + max_tokens ({req.max_tokens}) exceeds "
                              f"max-model-len {self.max_model_len}")
+        if self.blocks.blocks_needed(len(req.prompt_ids) + req.max_tokens) > self.blocks.n_blocks:
+            raise ValueError(f"prompt ({len(req.prompt_ids)}) + max_tokens ({req.max_tokens}) does not fit the KV cache "
+                             f"({self.blocks.n_blocks} blocks of {self.blocks.block_size} tokens)")
         self.waiting.append(req)
+
+    def _fail(self, req: Request, why: str) -> None:
+        """Give up on ONE request (its blocks and row are returned); the engine and every other request go on."""
+        if req in self.running:
+            self.running.remove(req)
+        if req in self.waiting:
+            self.waiting.remove(req)
+        self._release(req)
+        req.finished, req.finish_reason, req.error, req.finish_time = True, "error", why, time.monotonic()
+        self.failed.append(req)
+
+    def abort(self, req: Request) -> bool:
+        """Client went away / stop string hit: drop the request wherever it is (vLLM aborts on disconnect)."""
+        if req.finished:
+            return False
+        if req in self.running:
+            self.running.remove(req)
+        elif req in self.waiting:
+            self.waiting.remove(req)
+        else:
+            return False
+        self._release(req)
+        req.finished, req.finish_reason, req.finish_time = True, "abort", time.monotonic()
+        return True
 
     def has_work(self) -> bool:
         return bool(self.waiting or self.running)
@@ -162,7 +191,8 @@ class Scheduler:
                 # preempt the youngest running request (recompute later), vLLM's default policy
                 victim = self.running[-1]
                 if victim is req and len(self.running) == 1:
-                    raise OutOfBlocks("a single sequence does not fit the KV cache")
+                    self._fail(req, "the sequence no longer fits the KV cache")   # add() bounds this; belt and braces
+                    continue
                 self._preempt(victim)
                 if victim is req:
                     continue
@@ -176,6 +206,10 @@ class Scheduler:
             req = self.waiting[0]
             n_new = min(req.n_total - req.n_computed, budget)
             if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
+                if not self.running:
+                    # nothing is running, so no block will ever come back: waiting would spin forever
+                    self._fail(req, f"a chunk of {n_new} tokens does not fit the KV cache ({len(self.blocks.free)} blocks free)")
+                    continue
                 break
             self.waiting.popleft()
             self._grow(req, req.n_computed + n_new)
@@ -264,8 +298,18 @@ class LLMEngine:
     def add_request(self, req: Request) -> None:
         if req.temperature > 0.0 and req.seed is None:
             req.seed = int.from_bytes(os.urandom(8), "little")
+        if req.seed is not None:
+            req.seed = int(req.seed) & (2 ** 64 - 1)      # any Python int (vLLM takes int64 seeds, negatives too): 64 bits of key
+        req.top_k = min(max(int(req.top_k), 0), self.runner.cfg.vocab) if hasattr(self.runner, "cfg") else max(int(req.top_k), 0)
         self.scheduler.add(req)
         self.requests[req.request_id] = req
+
+    def abort_request(self, request_id: str) -> Optional[Request]:
+        req = self.requests.get(request_id)
+        if req is None or not self.scheduler.abort(req):
+            return None
+        self.requests.pop(request_id, None)
+        return req
 
     def add_prefilled(self, req: Request, n_computed: int) -> None:
         """Benchmark/test utility: admit a request whose first n_computed tokens are taken as already
@@ -279,10 +323,16 @@ class LLMEngine:
     def has_work(self) -> bool:
         return self.scheduler.has_work()
 
+    def _take_failed(self) -> List[Request]:
+        failed, self.scheduler.failed = self.scheduler.failed, []
+        for r in failed:
+            self.requests.pop(r.request_id, None)
+        return failed
+
     def step(self) -> List[Request]:
         sched = self.scheduler.schedule()
         if not sched:
-            return []
+            return self._take_failed()
         batch = self.scheduler.build_batch(sched)
         if len(batch.logit_rows):
             sampled = self.runner.step(batch)
@@ -312,7 +362,7 @@ class LLMEngine:
         done = self.scheduler.commit(sched, sampled)
         for r in done:
             self.requests.pop(r.request_id, None)
-        return done
+        return done + self._take_failed()
 
     def generate(self, prompts: List[List[int]], max_tokens: int, ignore_eos: bool = True) -> List[List[int]]:
         reqs = [Request(f"gen-{i}", list(p), max_tokens=max_tokens, ignore_eos=ignore_eos) for i, p in enumerate(prompts)]

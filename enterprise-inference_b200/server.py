@@ -264,6 +264,11 @@ class EngineLoop:
         self.listeners[req.request_id] = (loop, q)
         self.inbox.put(req)
 
+    def abort(self, request_id: str):
+        """From any thread: the client disconnected, the SSE generator was cancelled, or a stop string was hit.
+        The engine thread drops the request, returns its KV blocks and sequence slot, and counts it as aborted."""
+        self.inbox.put(("abort", request_id))
+
     def _emit(self, rid: str, item):
         tgt = self.listeners.get(rid)
         if tgt:
@@ -277,9 +282,16 @@ class EngineLoop:
                 try:
                     while True:
                         req = self.inbox.get(block=not eng.has_work(), timeout=0.05)
+                        if isinstance(req, tuple):          # ("abort", request_id)
+                            gone = eng.abort_request(req[1])
+                            if gone is not None:
+                                self.metrics.finished(gone)
+                                self._emit(gone.request_id, ("done", "abort"))
+                            self.listeners.pop(req[1], None)
+                            continue
                         try:
                             eng.add_request(req)
-                        except ValueError as e:
+                        except (ValueError, OverflowError) as e:
                             self._emit(req.request_id, ("error", str(e)))
                             self.listeners.pop(req.request_id, None)
                 except queue.Empty:
@@ -298,7 +310,10 @@ class EngineLoop:
                         self._emit(r.request_id, ("tokens", r.output_ids[n0:]))
                 for r in done:
                     m.finished(r)
-                    self._emit(r.request_id, ("done", r.finish_reason))
+                    if r.error is not None:             # the scheduler gave up on this one request only
+                        self._emit(r.request_id, ("error", r.error))
+                    else:
+                        self._emit(r.request_id, ("done", r.finish_reason))
                     self.listeners.pop(r.request_id, None)
         except Exception as e:  # the engine died: /health goes non-200 and the pod is restarted
             self.error = f"{type(e).__name__}: {e}"
@@ -374,6 +389,40 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
     def check_model(name: str):
         if name != served_model_name:
             return error(404, f"The model `{name}` does not exist.", "NotFoundError")
+        return None
+
+    def unsupported(body: _Sampling) -> Optional[str]:
+        """Fields of docs/api-spec.yaml this backend parses but does not implement: a non-default value gets a 400,
+        never a 200 whose output silently ignores it."""
+        bad = []
+        if body.frequency_penalty:
+            bad.append("frequency_penalty")
+        if body.presence_penalty:
+            bad.append("presence_penalty")
+        if body.repetition_penalty not in (None, 1.0):
+            bad.append("repetition_penalty")
+        if body.length_penalty not in (None, 1.0):
+            bad.append("length_penalty")
+        if body.logit_bias:
+            bad.append("logit_bias")
+        if getattr(body, "allowed_token_ids", None):
+            bad.append("allowed_token_ids")
+        if getattr(body, "suffix", None):
+            bad.append("suffix")
+        for f in ("guided_json", "guided_regex", "guided_choice", "guided_grammar"):
+            if getattr(body, f) is not None:
+                bad.append(f)
+        if body.response_format is not None and body.response_format.get("type", "text") != "text":
+            bad.append("response_format")
+        if bad:
+            return ("not supported by this backend: " + ", ".join(bad) +
+                    " (penalties, logit_bias and guided decoding are not implemented; leave them at their defaults)")
+        if body.seed is not None and not -2 ** 63 <= body.seed < 2 ** 64:
+            return "seed must fit 64 bits"
+        if body.top_k is not None and not -1 <= body.top_k < 2 ** 31:
+            return "top_k must be -1 (off), 0 (off) or a positive 32-bit integer"
+        if body.max_tokens is not None and body.max_tokens < 1:
+            return "max_tokens must be at least 1"
         return None
 
     def make_request(body: _Sampling, prompt_ids: List[int]) -> Request:
@@ -460,6 +509,9 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
     async def run(body: _Sampling, prompt_ids: List[int], chat: bool, prompt_text: str = ""):
         if len(prompt_ids) == 0:
             return error(400, "the prompt is empty")
+        why = unsupported(body)
+        if why:
+            return error(400, why)
         n = body.n or 1
         if (body.best_of not in (None, n)) or body.use_beam_search:
             return error(400, "best_of != n and beam search are not supported by this backend")
@@ -473,7 +525,7 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
         for i in range(n):
             r_ = make_request(body, prompt_ids)
             if body.seed is not None:
-                r_.seed = body.seed + i
+                r_.seed = (body.seed + i) & (2 ** 64 - 1)
             reqs.append(r_)
         req0 = reqs[0]
         if len(prompt_ids) + req0.max_tokens > max_model_len:
@@ -509,8 +561,8 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                 kind, val = await q.get()
                 if kind == "tokens":
                     d = detok.push(val)
-                    if detok.stopped:           # stop string hit: finish the engine request early
-                        req.max_tokens = len(req.output_ids)
+                    if detok.stopped:           # stop string hit: the engine drops the request now
+                        loop_.abort(req.request_id)
                     yield "delta", d
                     if detok.stopped:
                         yield "done", "stop"
@@ -569,21 +621,32 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                 finally:
                     for t in tasks:
                         t.cancel()
+                    for r_ in reqs:            # client gone (generator closed / cancelled) or an error: free the engine side
+                        if not r_.finished:
+                            loop_.abort(r_.request_id)
                 if include_usage:
                     yield f"data: {json.dumps({'id': rid, 'object': 'chat.completion.chunk' if chat else 'text_completion', 'created': created, 'model': served_model_name, 'choices': [], 'usage': usage()})}\n\n"
                 yield "data: [DONE]\n\n"
             return StreamingResponse(sse(), media_type="text/event-stream")
 
         choices = []
-        for i in range(n):
-            text, finish = "", None
-            async for kind, val in events(i):
-                if kind == "delta":
-                    text += val
-                elif kind == "done":
-                    finish = val
-                else:
-                    return error(500, val, "InternalServerError")
+        try:
+            results = []
+            for i in range(n):
+                text, finish = "", None
+                async for kind, val in events(i):
+                    if kind == "delta":
+                        text += val
+                    elif kind == "done":
+                        finish = val
+                    else:
+                        return error(500, val, "InternalServerError")
+                results.append((text, finish))
+        finally:
+            for r_ in reqs:                    # cancelled (client disconnected) or failed: free the engine side
+                if not r_.finished:
+                    loop_.abort(r_.request_id)
+        for i, (text, finish) in enumerate(results):
             if chat:
                 content, tool_calls = text, []
                 if tool_parser is not None and getattr(body, "tools", None) and body.tool_choice != "none":

@@ -66,6 +66,10 @@ class ModelConfig:
     rope_llama3: bool = True          # llama3 scaling: factor 8, low 1, high 4, orig 8192
     rms_eps: float = 1e-5
     max_pos: int = 32768
+    rope_factor: float = 8.0          # llama3 scaling parameters ([V22] rotary_embedding/llama3_rope.py:19-31)
+    rope_low_freq: float = 1.0
+    rope_high_freq: float = 4.0
+    rope_orig_max_pos: int = 8192
 
     def to_dict(self):
         return asdict(self)
@@ -96,6 +100,9 @@ CONFIGS: Dict[str, ModelConfig] = {
     # G=8 (70B head ratio), 2 kv heads so TP=2 can shard it
     "tiny-g8": ModelConfig(name="tiny-g8", hidden=1024, n_layers=2, n_q_heads=16, n_kv_heads=2,
                            intermediate=2048, vocab=4096),
+    # G=8 over 8 kv heads: shards over 2, 4 and 8 tensor-parallel ranks
+    "tiny-g8x8": ModelConfig(name="tiny-g8x8", hidden=1024, n_layers=2, n_q_heads=64, n_kv_heads=8,
+                             intermediate=4096, vocab=4096),
     "llama-3.1-8b": ModelConfig(name="llama-3.1-8b", hidden=4096, n_layers=32, n_q_heads=32,
                                 n_kv_heads=8, intermediate=14336, vocab=128256, max_pos=131072),
     "qwen2-32b": ModelConfig(name="qwen2-32b", hidden=5120, n_layers=64, n_q_heads=40, n_kv_heads=8,
@@ -200,7 +207,7 @@ def rope_inv_freq(cfg: ModelConfig) -> torch.Tensor:
     inv = 1.0 / (cfg.rope_theta ** (torch.arange(0, d, 2, dtype=torch.float32) / d))
     if cfg.rope_llama3:
         # [V22] rotary_embedding/llama3_rope.py:33-54
-        factor, low, high, orig = 8.0, 1.0, 4.0, 8192
+        factor, low, high, orig = cfg.rope_factor, cfg.rope_low_freq, cfg.rope_high_freq, cfg.rope_orig_max_pos
         low_wl, high_wl = orig / low, orig / high
         wl = 2 * math.pi / inv
         smooth = (orig / wl - low) / (high - low)
@@ -387,13 +394,19 @@ class OracleModel:
         st.n += T
         return (logits, hidden) if return_hidden else logits
 
-    def step_batch(self, states: List[SeqState], token_ids: List[int], fast_linear: bool = False):
+    def step_batch(self, states: List[SeqState], token_ids: List[int], fast_linear: bool = False, kv_batch=None):
         """One decode step for B sequences (one new token each), linears batched over the rows —
         the shape of work the image's CPU model runner does per scheduler iteration.  With
         fast_linear the projections run as bf16 torch F.linear (oneDNN: fp32 accumulate, one
-        rounding — still R2) instead of an explicit fp32 matmul; used by the timed CPU baseline."""
+        rounding — still R2) instead of an explicit fp32 matmul; used by the timed CPU baseline.
+        kv_batch = (K, V), each [B, capacity, Hkv, d] with states[b].K[l] / .V[l] = row b of it for every layer and all
+        sequences at the same length (the timed baseline's synthetic cache): the attention of a layer is then ONE
+        batched bf16 scaled_dot_product_attention call (what the image's CPU attention backend does per step)
+        instead of a Python loop over sequences — timing path only, not a parity path (P stays in the SDPA
+        kernel's own precision instead of R4's fp32)."""
         c = self.cfg
         B = len(states)
+        batched = kv_batch is not None and len({st.n for st in states}) == 1
         lin = (lambda x, w, b=None: torch.nn.functional.linear(x, w, b)) if fast_linear else linear
         pos = torch.tensor([st.n for st in states])
         cos, sin = self.cs[pos, : c.head_dim // 2], self.cs[pos, c.head_dim // 2:]
@@ -409,12 +422,21 @@ class OracleModel:
             q = rope_apply(qkv[:, : c.q_size].view(B, c.n_q_heads, c.head_dim), cos, sin)
             k = rope_apply(qkv[:, c.q_size: c.q_size + c.kv_size].view(B, c.n_kv_heads, c.head_dim), cos, sin)
             v = qkv[:, c.q_size + c.kv_size:].view(B, c.n_kv_heads, c.head_dim)
-            outs = []
-            for b, st in enumerate(states):
-                st.K[l][st.n] = k[b]
-                st.V[l][st.n] = v[b]
-                outs.append(attend(q[b], st.K[l], st.V[l], st.n + 1, self.scale))
-            x = lin(torch.stack(outs).view(B, c.q_size), L["o_w"])
+            if batched:
+                n = states[0].n
+                kv_batch[0][:, n] = k
+                kv_batch[1][:, n] = v
+                att = torch.nn.functional.scaled_dot_product_attention(
+                    q.unsqueeze(2), kv_batch[0][:, : n + 1].permute(0, 2, 1, 3), kv_batch[1][:, : n + 1].permute(0, 2, 1, 3),
+                    scale=self.scale, enable_gqa=True)
+                x = lin(att.reshape(B, c.q_size), L["o_w"])
+            else:
+                outs = []
+                for b, st in enumerate(states):
+                    st.K[l][st.n] = k[b]
+                    st.V[l][st.n] = v[b]
+                    outs.append(attend(q[b], st.K[l], st.V[l], st.n + 1, self.scale))
+                x = lin(torch.stack(outs).view(B, c.q_size), L["o_w"])
             y, res = add_rms_norm(x, res, L["ln2"], c.rms_eps)
             x = lin(silu_mul(lin(y, L["gu_w"])), L["d_w"])
         y, _ = add_rms_norm(x, res, self.w["model.norm.weight"], c.rms_eps)

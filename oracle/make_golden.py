@@ -52,7 +52,10 @@ def hf_model(cfg, w):
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
-    for name, n_prompt, n_new in (("tiny", 24, 48), ("tiny-qwen", 17, 32), ("tiny-g8", 33, 32)):
+    only = sys.argv[1:]   # python oracle/make_golden.py [name ...]: regenerate just these fixtures
+    for name, n_prompt, n_new in (("tiny", 24, 48), ("tiny-qwen", 17, 32), ("tiny-g8", 33, 32), ("tiny-g8x8", 40, 24)):
+        if only and name not in only:
+            continue
         cfg = CONFIGS[name]
         w = make_weights(cfg, seed=1234, norm_jitter=0.1)
         om = OracleModel(cfg, w, capacity=256)

@@ -92,6 +92,59 @@ def test_stop_conditions_and_limits():
         eng.add_request(E.Request("d", [1] * 60, max_tokens=10))
 
 
+def test_abort_returns_blocks_and_row_wherever_the_request_is():
+    fr = FakeRunner(n_blocks=8, block_size=4, max_tokens=8, max_model_len=32)
+    eng = E.LLMEngine(fr, max_num_batched_tokens=8, max_num_seqs=2, max_model_len=32)
+    a, b, c = (E.Request(n, [1, 2, 3, 4, 5], max_tokens=12) for n in "abc")
+    for r in (a, b, c):
+        eng.add_request(r)
+    eng.step()                                  # a (and part of b) admitted; c waits (max_num_seqs = 2)
+    assert a in eng.scheduler.running and c in eng.scheduler.waiting
+    rows_before = len(eng.scheduler.free_rows)
+    assert eng.abort_request("a") is a and a.finished and a.finish_reason == "abort" and a.block_table == []
+    assert len(eng.scheduler.free_rows) == rows_before + 1
+    assert eng.abort_request("c") is c and c not in eng.scheduler.waiting
+    assert eng.abort_request("a") is None and eng.abort_request("nope") is None
+    while eng.has_work():
+        eng.step()
+    assert b.output_ids == expect([1, 2, 3, 4, 5], 12) and len(eng.blocks.free) == 8
+
+
+def test_a_request_that_can_never_be_admitted_fails_alone():
+    """with nothing running and the head of the queue too big for the free blocks the scheduler used to
+    return [] forever (has_work() stayed true: a busy spin).  Now add() rejects what can never fit, and a request that
+    stops fitting is failed by itself while the others go on."""
+    fr = FakeRunner(n_blocks=5, block_size=4, max_tokens=16, max_model_len=64)
+    eng = E.LLMEngine(fr, max_num_batched_tokens=16, max_num_seqs=4, max_model_len=64)
+    with pytest.raises(ValueError, match="KV cache"):
+        eng.add_request(E.Request("big", [1] * 20, max_tokens=8))          # 28 tokens > 20 slots
+    # a request that passed add() but whose chunk cannot be placed although nothing runs (blocks held elsewhere)
+    held = []
+    eng.blocks.grow(held, 12)                    # someone else holds 3 of the 5 blocks
+    stuck = E.Request("stuck", [1] * 9, max_tokens=2)                      # its first chunk needs 3 blocks, 2 are free
+    ok = E.Request("ok", [1, 2, 3], max_tokens=5)                          # 8 tokens = 2 blocks
+    eng.add_request(stuck)
+    eng.add_request(ok)
+    done = []
+    for _ in range(40):
+        if not eng.has_work():
+            break
+        done += eng.step()
+    assert not eng.has_work(), "the engine must not spin on a request that cannot be admitted"
+    assert stuck.finished and stuck.finish_reason == "error" and "KV cache" in stuck.error and stuck in done
+    assert ok.output_ids == expect([1, 2, 3], 5)
+
+
+def test_seed_and_top_k_are_brought_into_range():
+    fr = FakeRunner()
+    fr.cfg = type("C", (), {"vocab": 97})()
+    eng = E.LLMEngine(fr, max_num_batched_tokens=16, max_num_seqs=4, max_model_len=64)
+    r = E.Request("s", [1, 2], max_tokens=1, temperature=1.0, seed=-5, top_k=2 ** 40)
+    eng.add_request(r)
+    assert r.seed == 2 ** 64 - 5 and r.top_k == 97
+    np.asarray([r.seed], dtype=np.uint64), np.asarray([r.top_k], dtype=np.int32)   # what pack_sampling does
+
+
 from hypothesis import given, settings, strategies as st, HealthCheck
 
 

@@ -136,6 +136,75 @@ def test_validation_and_errors(client):
     assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "use_beam_search": True}).status_code == 400
 
 
+@pytest.mark.parametrize("field,value", [("frequency_penalty", 0.5), ("presence_penalty", -1.0), ("repetition_penalty", 1.2),
+                                         ("logit_bias", {"17": 5.0}), ("guided_json", {"type": "object"}),
+                                         ("guided_regex", "a+"), ("guided_choice", ["a", "b"]), ("guided_grammar", "root ::= 'a'"),
+                                         ("response_format", {"type": "json_object"}), ("length_penalty", 2.0)])
+def test_fields_the_backend_does_not_implement_get_a_400_not_a_silent_200(client, field, value):
+    """docs/api-spec.yaml:275-311,397,479-518 defines them; a 200 whose text ignores them would be a wrong answer."""
+    for path, extra in (("/v1/completions", {"prompt": "x"}), ("/v1/chat/completions", {"messages": [{"role": "user", "content": "x"}]})):
+        r = client.post(path, json={"model": MODEL, "temperature": 0, "max_tokens": 2, field: value, **extra})
+        assert r.status_code == 400 and r.json()["object"] == "error" and field in r.json()["message"], (path, r.text)
+    # the defaults of the same fields are fine
+    ok = {"frequency_penalty": 0.0, "presence_penalty": 0, "repetition_penalty": 1.0, "logit_bias": {}, "length_penalty": 1.0,
+          "response_format": {"type": "text"}}
+    r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "max_tokens": 2, "prompt": "x", **ok})
+    assert r.status_code == 200
+
+
+def test_seed_and_top_k_out_of_range_cannot_kill_the_engine(client):
+    """a negative or 65-bit seed / a 2^31 top_k used to raise inside the engine thread and take every
+    request down with it.  Negative int64 seeds are accepted (as vLLM does), absurd values get a 400, /health stays 200."""
+    base = {"model": MODEL, "prompt": "hello", "max_tokens": 3, "temperature": 1.0}
+    assert client.post("/v1/completions", json={**base, "seed": -7}).status_code == 200
+    assert client.post("/v1/completions", json={**base, "seed": 2 ** 64 - 1, "n": 2}).status_code == 200     # seed + i wraps
+    assert client.post("/v1/completions", json={**base, "seed": 2 ** 70}).status_code == 400
+    assert client.post("/v1/completions", json={**base, "top_k": 2 ** 31}).status_code == 400
+    assert client.post("/v1/completions", json={**base, "top_k": 2 ** 31 - 1}).status_code == 200              # clamped to the vocab
+    assert client.post("/v1/completions", json={**base, "max_tokens": 0}).status_code == 400
+    assert client.get("/health").status_code == 200
+
+
+def test_stop_string_aborts_the_engine_request(client):
+    """A stop string ends the request in the engine as well (no decoding on to max_tokens, blocks returned)."""
+    loop = client.app.state.engine_loop
+    ids = client.tok.encode("hello")
+    text = client.tok.decode(expect_ids(ids, 12))
+    stop = text[3:5]
+    r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "hello", "max_tokens": 200, "stop": stop})
+    assert r.status_code == 200 and r.json()["choices"][0]["finish_reason"] == "stop"
+    assert stop not in r.json()["choices"][0]["text"] and text.startswith(r.json()["choices"][0]["text"][:2])
+    import time
+    for _ in range(100):
+        if not loop.engine.has_work() and len(loop.engine.blocks.free) == loop.engine.blocks.n_blocks:
+            break
+        time.sleep(0.02)
+    assert not loop.engine.has_work() and len(loop.engine.blocks.free) == loop.engine.blocks.n_blocks
+    assert r.json()["usage"]["completion_tokens"] < 200
+    assert not loop.listeners
+
+
+def test_client_disconnect_aborts_a_stream(client):
+    """Closing an SSE stream early frees the request's KV blocks and sequence slot (vLLM aborts on disconnect)."""
+    import time
+    loop = client.app.state.engine_loop
+    with client.stream("POST", "/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "hello", "max_tokens": 240,
+                                                        "stream": True, "ignore_eos": True}) as s:
+        it = s.iter_lines()
+        got = 0
+        for line in it:
+            if line.startswith("data: "):
+                got += 1
+            if got >= 3:
+                break
+    for _ in range(200):
+        if not loop.engine.has_work():
+            break
+        time.sleep(0.02)
+    assert not loop.engine.has_work() and len(loop.engine.blocks.free) == loop.engine.blocks.n_blocks
+    assert client.get("/health").status_code == 200
+
+
 def test_stop_and_ignore_eos(client):
     ids = client.tok.encode("hello")
     first = expect_ids(ids, 1)[0]

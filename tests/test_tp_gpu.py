@@ -34,6 +34,31 @@ def _worker(rank, world, name, port, out_q, peer):
                              row_to_seq=torch.zeros(T, dtype=torch.int32).cuda(), out_logits=logits)
         torch.cuda.synchronize()
     full = logits.permute(1, 0, 2).reshape(T, ocfg.vocab).float().cpu()
+    # the collective of a half-layer on its own (b200_tp_allreduce): plain all-reduce and the fused
+    # all-reduce + add + RMSNorm, at the row counts that select the fused kernel (<= 16) and the one-shot kernel
+    abi, h = pkg("_abi"), ocfg.hidden
+    for i, Tr in enumerate((1, 16, 40, 64)):
+        g = torch.Generator().manual_seed(100 + Tr)
+        parts = [torch.randn(Tr, h, generator=g).to(torch.bfloat16) for _ in range(world)]
+        res0 = torch.randn(Tr, h, generator=g).to(torch.bfloat16)
+        nw = (1 + 0.1 * torch.randn(h, generator=g)).to(torch.bfloat16)
+        total = parts[0].float()
+        for p in parts[1:]:
+            total = total + p.float()                      # rank order, fp32, one rounding
+        want_x = total.to(torch.bfloat16)
+        mine, y = parts[rank].cuda(), torch.empty(Tr, h, dtype=torch.bfloat16, device="cuda")
+        abi.check(r.lib.b200_tp_allreduce(r.ctx, 0, mine.data_ptr(), Tr, None, None, y.data_ptr(), r.stream.cuda_stream))
+        r.stream.synchronize()
+        assert torch.equal(y.cpu(), want_x), f"all-reduce of {Tr} rows differs from the rank-ordered fp32 sum"
+        resd, nwd = res0.cuda(), nw.cuda()
+        abi.check(r.lib.b200_tp_allreduce(r.ctx, 1, mine.data_ptr(), Tr, resd.data_ptr(), nwd.data_ptr(), y.data_ptr(),
+                                          r.stream.cuda_stream))
+        r.stream.synchronize()
+        want_y, want_res = O.add_rms_norm(want_x, res0, nw, ocfg.rms_eps)
+        assert torch.equal(resd.cpu(), want_res), f"residual after the fused all-reduce + norm ({Tr} rows)"
+        d = (y.cpu().float() - want_y.float()).abs()
+        ulp = want_y.float().abs().clamp_min(2.0 ** -126).log2().floor().exp2() * 2.0 ** -7
+        assert (d <= torch.maximum(2 * ulp, torch.tensor(2.0 ** -9))).all() and (d > 0).float().mean() <= 0.01
     if rank == 0:
         out_q.put((full, toks.cpu()))
     dist.barrier()

@@ -1,10 +1,8 @@
 set -x
-nvidia-smi --query-gpu=name,memory.total --format=csv
-timeout 900 python -m pytest tests/test_kernels_gpu.py -x -q -k "folded or rmsnorm or linear" 2>&1 | tail -15
-timeout 900 python -m pytest tests/test_model_gpu.py -x -q 2>&1 | tail -15
-tools/gpu_ab.sh bs1_default llama8b-bs1 128
-tools/gpu_ab.sh bs1_nofold llama8b-bs1 128 B200_FUSE_NORM_MAX_T=0
-tools/gpu_ab.sh bs1_noahead llama8b-bs1 128 B200_O_L2_AHEAD=0
-tools/gpu_ab.sh bs1_neither llama8b-bs1 128 B200_O_L2_AHEAD=0 B200_FUSE_NORM_MAX_T=0
-tools/gpu_ab.sh bs64_default llama8b-bs64 64
-tools/gpu_ab.sh bs64_fold16 llama8b-bs64 64 B200_FUSE_NORM_MAX_T=16
+SECONDS=0; python bench.py --steps 20 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench took $SECONDS s"; tail -5 gpurun_out/bench_n1.err
+python - <<'PY'
+import json
+d=json.loads(open("gpurun_out/bench_n1.json").read().strip().splitlines()[-1])
+print({k:d[k] for k in ("value","ms_per_step","e2e","launches_per_step")}, d["roofline"]["frac"], d["roofline"]["whole_step"])
+print(json.dumps(d.get("also"),indent=1)); print(json.dumps(d.get("tp"),indent=1)); print(d.get("cpu_baseline",{}).get("value"))
+PY
