@@ -20,14 +20,7 @@
 
 namespace b200 {
 
-struct ArParams {
-  const __nv_bfloat16* bufs[8];   // every rank's partial for this buffer index (peer-mapped)
-  unsigned int* flags[8];         // every rank's flag block: [2 buffers][8 ranks] x 32 uints (128 B apart)
-  unsigned int* state;            // local: counter[2] | ticket[2]
-  __nv_bfloat16* out;
-  long long n_chunks;             // 16-byte chunks
-  int rank, world, buf_idx;
-};
+constexpr int kFlagKindStride = 2 * 8 * 32;   // uints between the "partial ready" and the "slice delivered" flags
 
 namespace {
 
@@ -194,7 +187,129 @@ allreduce_add_rmsnorm_kernel(ArParams p, __nv_bfloat16* res, const __nv_bfloat16
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Two-shot form for larger messages (T > 16): the rows are dealt to the ranks (row t belongs to rank t mod world).
+// After the same flag barrier the OWNER of a row pulls its partials from all ranks (1/world of the message instead of
+// all of it), sums them in rank order, adds the residual (kept only on the owner: nobody else needs it), normalises,
+// and writes the normed row into EVERY rank's gather buffer over NVLink; a second flag per rank ("my rows are
+// delivered") closes the kernel, which ends only when all ranks' rows have arrived.  NVLink traffic per rank:
+// 2 (world-1)/world of the message instead of (world-1) messages; collective + residual add + RMSNorm in one launch.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kArNormThreads)
+allreduce_twoshot_rmsnorm_kernel(ArParams p, int T, __nv_bfloat16* res, const __nv_bfloat16* __restrict__ w, int hidden,
+                                 float eps) {
+  __shared__ unsigned int seq_s;
+  __shared__ float red[kArNormThreads / 32];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int tid = threadIdx.x;
+  if (tid == 0) seq_s = *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) + 1u;
+  __syncthreads();
+  const unsigned int seq = seq_s;
+  const int slot = (p.buf_idx * 8 + p.rank) * 32;
+  if (blockIdx.x == 0 && tid < p.world) {
+    __threadfence_system();
+    st_release_sys(p.flags[tid] + slot, seq);                       // "my partial for this buffer is ready"
+  }
+  if (tid < p.world) {
+    const unsigned int* f = p.flags[p.rank] + (p.buf_idx * 8 + tid) * 32;
+    while ((int)(ld_acquire_sys(f) - seq) < 0) __nanosleep(20);
+  }
+  __syncthreads();
+  const int t = p.rank + (int)blockIdx.x * p.world;                 // my row of this CTA (grid = ceil(rows owned), >= 1)
+  const int nchunk = hidden >> 3;
+  if (t < T) {
+    const int c = tid;
+    float v[8];
+    float ss = 0.f;
+    const bool act = c < nchunk;
+    if (act) {
+      uint4 pv[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < p.world) pv[r] = ld_peer(reinterpret_cast<const uint4*>(p.bufs[r] + (int64_t)t * hidden) + c);
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        if (r < p.world) {
+          const uint4 q = pv[r];
+          acc[0] += bf16lo(q.x); acc[1] += bf16hi(q.x); acc[2] += bf16lo(q.y); acc[3] += bf16hi(q.y);
+          acc[4] += bf16lo(q.z); acc[5] += bf16hi(q.z); acc[6] += bf16lo(q.w); acc[7] += bf16hi(q.w);
+        }
+      }
+      uint4* rr = reinterpret_cast<uint4*>(res + (int64_t)t * hidden);
+      const uint4 b = rr[c];
+      const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[2 * j] = round_bf16(acc[2 * j]) + bf16lo(bw[j]);
+        v[2 * j + 1] = round_bf16(acc[2 * j + 1]) + bf16hi(bw[j]);
+        o[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+      }
+      rr[c] = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss = fmaf(v[j], v[j], ss);
+    }
+    ss = warp_sum(ss);
+    if ((tid & 31) == 0) red[tid >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int i = 0; i < kArNormThreads / 32; ++i) tot += red[i];
+    const float rinv = 1.0f / sqrtf(tot / (float)hidden + eps);
+    if (act) {
+      const uint4 wq = __ldg(reinterpret_cast<const uint4*>(w) + c);
+      const uint32_t ww[4] = {wq.x, wq.y, wq.z, wq.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float n0 = round_bf16(v[2 * j] * rinv), n1 = round_bf16(v[2 * j + 1] * rinv);
+        o[j] = pack_bf16(n0 * bf16lo(ww[j]), n1 * bf16hi(ww[j]));
+      }
+      const uint4 y = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < p.world) reinterpret_cast<uint4*>(p.gather[r] + (int64_t)t * hidden)[c] = y;   // all-gather by remote stores
+    }
+  }
+  // the last CTA of this rank tells every rank that its rows are delivered, waits for everybody else's, and advances
+  // the sequence number (graph-replay safe)
+  __threadfence_system();
+  __syncthreads();
+  __shared__ unsigned int last_s;
+  if (tid == 0) {
+    const unsigned int tk = atomicAdd(p.state + 2 + p.buf_idx, 1u);
+    last_s = (tk == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (last_s) {
+    if (tid < p.world) {
+      __threadfence_system();
+      st_release_sys(p.flags[tid] + kFlagKindStride + slot, seq);   // "my rows are in your gather buffer"
+      const unsigned int* f = p.flags[p.rank] + kFlagKindStride + (p.buf_idx * 8 + tid) * 32;
+      while ((int)(ld_acquire_sys(f) - seq) < 0) __nanosleep(20);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      p.state[2 + p.buf_idx] = 0u;
+      *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) = seq;
+    }
+  }
+}
+
 }  // namespace
+
+int allreduce_twoshot_rmsnorm(const ArParams& p, int T, __nv_bfloat16* res, const __nv_bfloat16* w, int hidden, float eps,
+                              cudaStream_t s) {
+  B200_REQUIRE(hidden % 8 == 0 && hidden <= 8 * kArNormThreads, B200_ERR_UNSUPPORTED,
+               "allreduce_twoshot_rmsnorm: hidden=%d unsupported", hidden);
+  if (T == 0) return B200_OK;
+  const int rows = T > p.rank ? (T - p.rank + p.world - 1) / p.world : 0;
+  B200_CUDA(launch(allreduce_twoshot_rmsnorm_kernel, dim3(rows > 0 ? rows : 1), dim3(kArNormThreads), 0, s, p, T, res, w,
+                   hidden, eps));
+  return B200_OK;
+}
 
 int allreduce_add_rmsnorm(const ArParams& p, int T, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int hidden,
                           float eps, cudaStream_t s) {

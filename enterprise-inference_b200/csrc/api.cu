@@ -107,20 +107,6 @@ __global__ void tp_pack_kernel(const float* __restrict__ mx, const int32_t* __re
 
 }  // namespace b200
 
-namespace b200 {
-struct ArParams {
-  const __nv_bfloat16* bufs[8];
-  unsigned int* flags[8];
-  unsigned int* state;
-  __nv_bfloat16* out;
-  long long n_chunks;
-  int rank, world, buf_idx;
-};
-int allreduce_oneshot(const ArParams& p, cudaStream_t s);
-int allreduce_add_rmsnorm(const ArParams& p, int T, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int hidden,
-                          float eps, cudaStream_t s);
-}  // namespace b200
-
 using namespace b200;
 
 // ------------------------------------------------------------------------------------------------
@@ -178,8 +164,8 @@ struct b200_ctx {
   void *tap_hidden = nullptr, *tap_res = nullptr;
   // TP
   ncclComm_t comm = nullptr;
-  // one-shot all-reduce over peer memory (allreduce.cu): one IPC-shareable allocation per rank
-  //   [ buffer 0 | buffer 1 | flag block (2 x 8 x 128 B) | state (counter[2], ticket[2]) ]
+  // all-reduce over peer memory (allreduce.cu): one IPC-shareable allocation per rank
+  //   [ partial 0 | partial 1 | gather 0 | gather 1 | flag block (2 x 2 x 8 x 128 B) | state (counter[2], ticket[2]) ]
   char* ar_mem = nullptr;
   int64_t ar_buf_bytes = 0, ar_total_bytes = 0;
   char* ar_peer[8] = {};
@@ -194,6 +180,7 @@ struct b200_ctx {
 };
 
 static int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+constexpr int64_t kArFlagBytes = 2 * 2 * 8 * 128;   // "partial ready" and "rows delivered" flags: [kind][buffer][rank] x 128 B
 
 extern "C" const char* b200_last_error(void) { return g_err; }
 extern "C" int b200_abi_version(void) { return 1; }
@@ -305,7 +292,7 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
   }
   if (W > 1) {
     c->ar_buf_bytes = align_up(T * h * 2, 1024);
-    c->ar_total_bytes = 2 * c->ar_buf_bytes + 2 * 8 * 128 + 256;
+    c->ar_total_bytes = 4 * c->ar_buf_bytes + kArFlagBytes + 256;
     e = cudaMalloc((void**)&c->ar_mem, c->ar_total_bytes);
     if (e == cudaSuccess) e = cudaMemset(c->ar_mem, 0, c->ar_total_bytes);
     if (e != cudaSuccess) {
@@ -665,9 +652,10 @@ static ArParams ar_params(b200_ctx* c, int buf_idx, int T) {
   ArParams p = {};
   for (int r = 0; r < c->cfg.tp_world; ++r) {
     p.bufs[r] = reinterpret_cast<const __nv_bfloat16*>(c->ar_peer[r] + (int64_t)buf_idx * c->ar_buf_bytes);
-    p.flags[r] = reinterpret_cast<unsigned int*>(c->ar_peer[r] + 2 * c->ar_buf_bytes);
+    p.flags[r] = reinterpret_cast<unsigned int*>(c->ar_peer[r] + 4 * c->ar_buf_bytes);
+    p.gather[r] = reinterpret_cast<__nv_bfloat16*>(c->ar_peer[r] + (int64_t)(2 + buf_idx) * c->ar_buf_bytes);
   }
-  p.state = reinterpret_cast<unsigned int*>(c->ar_mem + 2 * c->ar_buf_bytes + 2 * 8 * 128);
+  p.state = reinterpret_cast<unsigned int*>(c->ar_mem + 4 * c->ar_buf_bytes + kArFlagBytes);
   p.out = c->x;
   p.n_chunks = (int64_t)T * c->cfg.hidden / 8;
   p.rank = c->cfg.tp_rank;
@@ -680,12 +668,24 @@ static int tp_reduce(b200_ctx* c, int buf_idx, int T, cudaStream_t s) {
   if (!use_peer_ar(c, T)) return b200_allreduce_bf16(c, c->x, count, s);   // NCCL
   return allreduce_oneshot(ar_params(c, buf_idx, T), s);
 }
-// all-reduce of buffer buf_idx + residual add + RMSNorm: ONE fused peer-memory kernel for latency-bound
-// messages, else (NCCL or single rank) the all-reduce followed by the add+RMSNorm kernel
-static int tp_reduce_norm(b200_ctx* c, int buf_idx, int T, const __nv_bfloat16* w, cudaStream_t s) {
+// all-reduce of buffer buf_idx + residual add + RMSNorm; *normed receives where the normed rows are.  Peer memory:
+// ONE kernel does collective + add + norm — up to 16 rows every rank pulls everything (one flag round, latency bound),
+// above that the rows are dealt to the ranks (two-shot: 1/world of the NVLink traffic, the normed rows land in this
+// rank's gather buffer).  NCCL or a single rank: the all-reduce followed by the add+RMSNorm kernel.
+static int tp_reduce_norm(b200_ctx* c, int buf_idx, int T, const __nv_bfloat16* w, const __nv_bfloat16** normed, cudaStream_t s) {
   static const int fuse_env = getenv("B200_FUSE_AR_NORM") ? atoi(getenv("B200_FUSE_AR_NORM")) : 1;   // 70B TP8 batch 1: 6.41 ms/step fused vs 6.88 ms as two kernels
+  static const int twoshot_env = getenv("B200_AR_TWOSHOT") ? atoi(getenv("B200_AR_TWOSHOT")) : 1;
   const b200_model_cfg& m = c->cfg;
-  if (m.tp_world > 1 && fuse_env && T <= 16 && use_peer_ar(c, T))   // the latency-bound regime; larger T: one-shot + norm
+  *normed = c->normed;
+  const bool peer = m.tp_world > 1 && fuse_env && c->tap_layer < 0 && use_peer_ar(c, T) && m.hidden <= 8192;
+  // Measured (70B, [64 x 8192] rows): TP8 two-shot 21.8 us vs one-shot 24.4 us per call; TP2 two-shot 18.8 us, where the
+  // one-shot pull moves a single MiB: the second flag round only pays once the pull would move several MiB per rank.
+  if (peer && twoshot_env && T > 16 && (int64_t)(m.tp_world - 1) * T * m.hidden * 2 >= (4 << 20)) {
+    const ArParams p = ar_params(c, buf_idx, T);
+    *normed = p.gather[m.tp_rank];
+    return allreduce_twoshot_rmsnorm(p, T, c->res, w, m.hidden, m.rms_eps, s);
+  }
+  if (peer)   // one CTA per row pulls that row from every rank: one flag round
     return allreduce_add_rmsnorm(ar_params(c, buf_idx, T), T, c->res, w, c->normed, m.hidden, m.rms_eps, s);
   if (m.tp_world > 1) {
     int rc = tp_reduce(c, buf_idx, T, s);
@@ -700,20 +700,22 @@ static int tp_reduce_norm(b200_ctx* c, int buf_idx, int T, const __nv_bfloat16* 
 // place, y = normed rows), without it the plain all-reduce into y.
 extern "C" int b200_tp_allreduce(b200_ctx* c, int32_t buf_idx, const void* partial, int32_t T, void* res, const void* norm_w,
                                  void* y, void* stream) {
-  B200_REQUIRE(c && y && T > 0 && T <= c->cfg.max_tokens && (buf_idx == 0 || buf_idx == 1), B200_ERR_INVALID,
+  B200_REQUIRE(c && T > 0 && T <= c->cfg.max_tokens && (buf_idx == 0 || buf_idx == 1), B200_ERR_INVALID,
                "tp_allreduce: bad argument");
   B200_REQUIRE(c->cfg.tp_world > 1 && c->comm, B200_ERR_STATE, "tp_allreduce: needs tp_world > 1 and b200_nccl_init");
-  B200_REQUIRE(!norm_w || res, B200_ERR_INVALID, "tp_allreduce: the fused norm needs the residual");
+  B200_REQUIRE(norm_w || y, B200_ERR_INVALID, "tp_allreduce: the plain all-reduce needs an output");
   cudaStream_t s = (cudaStream_t)stream;
   const size_t bytes = (size_t)T * c->cfg.hidden * 2;
   if (partial) B200_CUDA(cudaMemcpyAsync(partial_dst(c, buf_idx, T), partial, bytes, cudaMemcpyDeviceToDevice, s));
   int rc;
   if (norm_w) {
-    B200_CUDA(cudaMemcpyAsync(c->res, res, bytes, cudaMemcpyDeviceToDevice, s));
-    rc = tp_reduce_norm(c, buf_idx, T, (const __nv_bfloat16*)norm_w, s);
+    // res == NULL / y == NULL: stay on the ctx's own residual and normed rows (timing: the collective kernel alone)
+    if (res) B200_CUDA(cudaMemcpyAsync(c->res, res, bytes, cudaMemcpyDeviceToDevice, s));
+    const __nv_bfloat16* normed = nullptr;
+    rc = tp_reduce_norm(c, buf_idx, T, (const __nv_bfloat16*)norm_w, &normed, s);
     if (rc) return rc;
-    B200_CUDA(cudaMemcpyAsync(res, c->res, bytes, cudaMemcpyDeviceToDevice, s));
-    B200_CUDA(cudaMemcpyAsync(y, c->normed, bytes, cudaMemcpyDeviceToDevice, s));
+    if (res) B200_CUDA(cudaMemcpyAsync(res, c->res, bytes, cudaMemcpyDeviceToDevice, s));   // two-shot: only this rank's rows (t % world == rank) are current
+    if (y) B200_CUDA(cudaMemcpyAsync(y, normed, bytes, cudaMemcpyDeviceToDevice, s));
   } else {
     rc = tp_reduce(c, buf_idx, T, s);
     if (rc) return rc;
@@ -776,6 +778,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     if (built < 0) return built;
     if (built == 1) attn_pack = 2;
   }
+  const __nv_bfloat16* normed = c->normed;   // where the current normed rows are (the two-shot all-reduce delivers them elsewhere)
   if (fnorm)
     STEP(embed_stream(a.ids, c->embed, c->sres, c->ssq, T, h, m.vocab, s));
   else
@@ -786,7 +789,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       if (l == 0)
         STEP(rmsnorm(c->res, nullptr, L.ln1, c->normed, T, h, m.rms_eps, s));
       else
-        STEP(defer_ar ? tp_reduce_norm(c, 1, T, L.ln1, s) : rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
+        STEP(defer_ar ? tp_reduce_norm(c, 1, T, L.ln1, &normed, s) : rmsnorm(c->x, c->res, L.ln1, c->normed, T, h, m.rms_eps, s));
     }
     __nv_bfloat16* kcl = c->kc + (int64_t)l * kv_layer_elems;
     __nv_bfloat16* vcl = c->vc + (int64_t)l * kv_layer_elems;
@@ -805,7 +808,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
         ex.block_size = m.block_size;
       }
       if (fnorm) norm_in(ex, L.ln1);
-      STEP(linear_any(c->normed, h, L.qkv, L.qkv_b, c->qkv_buf, qn, T, qn, h, 0, c->gemv_max_t, c->lin_ws,
+      STEP(linear_any(normed, h, L.qkv, L.qkv_b, c->qkv_buf, qn, T, qn, h, 0, c->gemv_max_t, c->lin_ws,
                       c->lin_ws_bytes, &ex, s));
       if (ex.mode != 2)
         STEP(rope_kv_append(c->qkv_buf, a.positions, a.slots, c->cos_sin, kcl, vcl, T, c->hq, c->hkv, m.block_size, s));
@@ -823,7 +826,7 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       STEP(linear_any(c->attn_out, ok, L.o, nullptr, tp ? partial_dst(c, 0, T) : c->x, h, T, on, ok, 0, c->gemv_max_t,
                       c->lin_ws, c->lin_ws_bytes, &ex, s));
     }
-    if (!fnorm) STEP(tp_reduce_norm(c, 0, T, L.ln2, s));   // (all-reduce +) residual add + RMSNorm
+    if (!fnorm) STEP(tp_reduce_norm(c, 0, T, L.ln2, &normed, s));   // (all-reduce +) residual add + RMSNorm
     {  // gate_up (+ SiLU*mul in the epilogue over interleaved slabs)
       LinearExtra ex;
       const bool tcp = tc_path(T, gn, h, c->gemv_max_t);
@@ -831,10 +834,10 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
       if (L.gu_interleaved) {
         B200_REQUIRE(tcp, B200_ERR_UNSUPPORTED, "interleaved gate_up weights need the tcgen05 path");
         ex.mode = 1;
-        STEP(linear_any(c->normed, h, L.gu, nullptr, c->act, c->inter, T, gn, h, 0, c->gemv_max_t, c->lin_ws,
+        STEP(linear_any(normed, h, L.gu, nullptr, c->act, c->inter, T, gn, h, 0, c->gemv_max_t, c->lin_ws,
                         c->lin_ws_bytes, &ex, s));
       } else {
-        STEP(linear_any(c->normed, h, L.gu, nullptr, c->gu_buf, gn, T, gn, h, 0, c->gemv_max_t, c->lin_ws,
+        STEP(linear_any(normed, h, L.gu, nullptr, c->gu_buf, gn, T, gn, h, 0, c->gemv_max_t, c->lin_ws,
                         c->lin_ws_bytes, &ex, s));
         STEP(silu_mul(c->gu_buf, c->act, T, c->inter, s));
       }
@@ -869,10 +872,10 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
     STEP(linear_any(lm_in, h, c->lm_head, nullptr, c->logits, c->vocab_local, a.R, c->vocab_local, h, 0, c->gemv_max_t,
                     c->lin_ws, c->lin_ws_bytes, &ex, s));
   } else {
-    STEP(defer_ar ? tp_reduce_norm(c, 1, T, c->final_norm, s) : rmsnorm(c->x, c->res, c->final_norm, c->normed, T, h, m.rms_eps, s));
-    const __nv_bfloat16* lm_in = c->normed;
+    STEP(defer_ar ? tp_reduce_norm(c, 1, T, c->final_norm, &normed, s) : rmsnorm(c->x, c->res, c->final_norm, c->normed, T, h, m.rms_eps, s));
+    const __nv_bfloat16* lm_in = normed;
     if (a.logit_rows) {
-      STEP(embed(a.logit_rows, c->normed, c->lm_in, a.R, h, T, s));  // row gather
+      STEP(embed(a.logit_rows, normed, c->lm_in, a.R, h, T, s));  // row gather
       lm_in = c->lm_in;
     }
     STEP(linear_any(lm_in, h, c->lm_head, nullptr, c->logits, c->vocab_local, a.R, c->vocab_local, h, 0, c->gemv_max_t,

@@ -202,6 +202,23 @@ int advance_rows(int32_t* ids, int32_t* positions, int32_t* slots, int32_t* ctx_
                  int bt_stride, const int32_t* row_to_seq, const int32_t* sampled, int n, int block_size,
                  cudaStream_t s);
 int silu_mul(const __nv_bfloat16* gu, __nv_bfloat16* out, int T, int inter, cudaStream_t s);
+
+// Peer-memory tensor-parallel all-reduce (allreduce.cu).  One IPC-shareable allocation per rank:
+//   [ partial 0 | partial 1 | gather 0 | gather 1 | flags: 2 kinds x 2 buffers x 8 ranks x 128 B | state ]
+struct ArParams {
+  const __nv_bfloat16* bufs[8];   // every rank's partial for this buffer index (peer-mapped)
+  unsigned int* flags[8];         // every rank's flag block
+  unsigned int* state;            // local: counter[2] | ticket[2]
+  __nv_bfloat16* out;
+  long long n_chunks;             // 16-byte chunks
+  int rank, world, buf_idx;
+  __nv_bfloat16* gather[8];       // two-shot: every rank's normed-row buffer for this buffer index (peer-mapped)
+};
+int allreduce_oneshot(const ArParams& p, cudaStream_t s);
+int allreduce_add_rmsnorm(const ArParams& p, int T, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int hidden,
+                          float eps, cudaStream_t s);
+int allreduce_twoshot_rmsnorm(const ArParams& p, int T, __nv_bfloat16* res, const __nv_bfloat16* w, int hidden, float eps,
+                              cudaStream_t s);
 int argmax_rows(const __nv_bfloat16* logits, int64_t ld, int rows, int vocab, int index_offset,
                 int32_t* out_ids, float* out_max, cudaStream_t s);
 

@@ -323,7 +323,9 @@ B200_API int b200_allreduce_bf16(b200_ctx* ctx, void* buf, int64_t count, void* 
  * timing): `partial` [T][hidden] bf16 is this rank's row-parallel partial sum (NULL: reuse what the exchange buffer
  * holds); buf_idx 0 = the O projection's buffer, 1 = the down projection's (they alternate inside a step, and so
  * must consecutive calls).  norm_w == NULL: y = all-reduce(partial).  norm_w != NULL: the fused form the step uses,
- * s = bf16(all-reduce(partial)) + res; res = bf16(s); y = rmsnorm(s) * norm_w.  Every rank must make the same call.
+ * s = bf16(all-reduce(partial)) + res; res = bf16(s); y = rmsnorm(s) * norm_w (above 16 rows the peer-memory path deals
+ * the rows to the ranks: res is then current only for the rows t with t mod tp_world == tp_rank; res == NULL and
+ * y == NULL: run on the ctx's own residual / normed rows without any copy, for timing).  Every rank must make the same call.
  * Replaces the shm all-reduce of the image's CPU communicator followed by its fused_add_rms_norm
  * ([V22] vllm/distributed/device_communicators/cpu_communicator.py:229-276; vllm/ir/ops/layernorm.py:40-58). */
 B200_API int b200_tp_allreduce(b200_ctx* ctx, int32_t buf_idx, const void* partial, int32_t n_tokens, void* res,

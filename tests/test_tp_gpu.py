@@ -55,7 +55,9 @@ def _worker(rank, world, name, port, out_q, peer):
                                           r.stream.cuda_stream))
         r.stream.synchronize()
         want_y, want_res = O.add_rms_norm(want_x, res0, nw, ocfg.rms_eps)
-        assert torch.equal(resd.cpu(), want_res), f"residual after the fused all-reduce + norm ({Tr} rows)"
+        # above 16 rows the peer-memory path deals the rows to the ranks: a rank keeps the residual of ITS rows only
+        mine_rows = slice(rank, None, world) if (peer and Tr > 16) else slice(None)
+        assert torch.equal(resd.cpu()[mine_rows], want_res[mine_rows]), f"residual after the fused all-reduce + norm ({Tr} rows)"
         d = (y.cpu().float() - want_y.float()).abs()
         ulp = want_y.float().abs().clamp_min(2.0 ** -126).log2().floor().exp2() * 2.0 ** -7
         assert (d <= torch.maximum(2 * ulp, torch.tensor(2.0 ** -9))).all() and (d > 0).float().mean() <= 0.01
