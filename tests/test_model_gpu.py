@@ -285,3 +285,35 @@ def test_openai_server_end_to_end_on_the_gpu():
         n_ok += 1
     assert n_ok >= 1
     r.close()
+
+
+def test_server_boots_from_a_checkpoint_directory_on_the_gpu(tmp_path, monkeypatch):
+    """(f4) `--model <hf id>` end to end on the device: snapshot resolved under HF_HOME, sharded safetensors loaded and
+    fused, config.json's llama3 rope_scaling (factor 32, as Llama-3.2 ships) honoured, HF tokenizer + chat template; the
+    greedy tokens of /v1/chat/completions equal the oracle's on the same checkpoint (margin-aware)."""
+    from fastapi.testclient import TestClient
+    from ckpt_util import MODEL_ID, write_checkpoint
+    S = pkg("server")
+    snap, ocfg, w = write_checkpoint(str(tmp_path))
+    monkeypatch.setenv("HF_HOME", str(tmp_path))
+    args = S.make_arg_parser().parse_args(["--model", MODEL_ID, "--max-model-len", "512", "--max-num-batched-tokens", "64",
+                                           "--max-num-seqs", "4", "--block-size", "128", "--kv-cache-gib", "0.05"])
+    engine, tok, workers = S.build_engine(args)
+    assert engine.runner.cfg.rope_factor == 32.0
+    app = S.create_app(engine, tok, MODEL_ID, args.max_model_len, default_sampling=S.load_default_sampling(snap))
+    msgs = [{"role": "user", "content": "what is deep learning ? tell me about tensor cores and memory bandwidth please"}]
+    prompt_ids = tok.encode(tok.apply_chat_template(msgs, add_generation_prompt=True, tokenize=False), add_special_tokens=False)
+    n_new = 24
+    want, logits = O.OracleModel(ocfg, w, capacity=128).generate(prompt_ids, n_new, keep_logits=True)
+    with TestClient(app) as c:
+        r = c.post("/v1/chat/completions", json={"model": MODEL_ID, "messages": msgs, "max_tokens": n_new, "temperature": 0,
+                                                 "ignore_eos": True, "logprobs": True, "top_logprobs": 1})
+        assert r.status_code == 200, r.text
+        out = r.json()
+    assert out["usage"]["prompt_tokens"] == len(prompt_ids) and out["usage"]["completion_tokens"] == n_new
+    got = [tok.convert_tokens_to_ids(e["token"]) for e in out["choices"][0]["logprobs"]["content"]]
+    for i, (a, b) in enumerate(zip(got, want)):
+        if a != b:
+            assert float(O.top2_margin(logits[i])) < MARGIN, f"token {i} differs from the oracle outside a near-tie"
+            break
+    engine.runner.close()
