@@ -355,10 +355,13 @@ class OracleModel:
             st.V.append(torch.zeros(self.capacity, c.n_kv_heads, c.head_dim, dtype=BF16))
         return st
 
-    def forward(self, st: SeqState, token_ids: List[int], return_hidden: bool = False):
+    def forward(self, st: SeqState, token_ids: List[int], return_hidden: bool = False, fast_linear: bool = False):
         """Append T tokens to the sequence (causal) and return bf16 logits [T, V].
-        T>1 is a (chunked) prefill, T==1 a decode step: the arithmetic per token is the same."""
+        T>1 is a (chunked) prefill, T==1 a decode step: the arithmetic per token is the same.
+        fast_linear: the projections as bf16 F.linear (oneDNN: fp32 accumulation in its own order, one rounding — R2
+        all the same); a second correct implementation, used as a noise yardstick by the full-depth test."""
         c = self.cfg
+        linear = (lambda x, w, b=None: torch.nn.functional.linear(x, w, b)) if fast_linear else globals()["linear"]
         T = len(token_ids)
         pos = torch.arange(st.n, st.n + T)
         assert st.n + T <= self.capacity

@@ -588,7 +588,7 @@ def test_paged_attention_vs_oracle(lib, abi, hq, hkv, ctx_lens, bs):
     got = run_attn(lib, abi, q, K, V, ctx_lens, hq, hkv, bs=bs)
     want = torch.stack([O.attend(q[t], K[t], V[t], ctx_lens[t], 128 ** -0.5) for t in range(T)])
     assert torch.isfinite(got.float()).all()
-    ulp_close(got, want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
+    ulp_close(got, want, max_ulp=2, max_frac=0.02, atol_small=2 ** -8)   # measured <= 0.004 (gpurun_out/ulp_fractions.txt)
 
 
 @pytest.mark.parametrize("hq,hkv", [(4, 1), (5, 1), (16, 2), (8, 8), (2, 1)])
@@ -632,8 +632,8 @@ def test_paged_attention_prefill_rows_packed(lib, abi, hq, hkv):
         outs.append(out.cpu().view(T, hq, 128))
     want = torch.stack([O.attend(q[t], K[sq], V[sq], n, 128 ** -0.5) for t, (sq, n) in enumerate(rows)])
     assert torch.isfinite(outs[0].float()).all()
-    ulp_close(outs[0], want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
-    ulp_close(outs[0], outs[1], max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
+    ulp_close(outs[0], want, max_ulp=2, max_frac=0.02, atol_small=2 ** -8)      # measured <= 0.005
+    ulp_close(outs[0], outs[1], max_ulp=2, max_frac=0.02, atol_small=2 ** -8)
 
 
 @pytest.mark.parametrize("hq,hkv", [(8, 2), (5, 1), (8, 1)])
@@ -679,7 +679,7 @@ def test_prefill_attention_chunk_with_max_jumps(lib, abi, hq, hkv):
     got = out.cpu().view(T, hq, 128)
     want = torch.stack([O.attend(q[t], K[sq], V[sq], n, 128 ** -0.5) for t, (sq, n) in enumerate(rows)])
     assert torch.isfinite(got.float()).all()
-    ulp_close(got, want, max_ulp=2, max_frac=0.15, atol_small=2 ** -8)
+    ulp_close(got, want, max_ulp=2, max_frac=0.02, atol_small=2 ** -8)   # measured <= 0.004 (gpurun_out/ulp_fractions.txt)
 
 
 def test_paged_attention_split_invariance_long_context(lib, abi):
@@ -693,7 +693,7 @@ def test_paged_attention_split_invariance_long_context(lib, abi):
     a = run_attn(lib, abi, q, K, V, [n], hq, hkv)
     b = run_attn(lib, abi, q, K, V, [n], hq, hkv, max_ctx_hint=65536, seed=1)
     want = O.attend(q[0], K[0], V[0], n, 128 ** -0.5)[None]
-    ulp_close(a, want, max_ulp=2, max_frac=0.2, atol_small=2 ** -9)
+    ulp_close(a, want, max_ulp=2, max_frac=0.02, atol_small=2 ** -9)
     ulp_close(b, a, max_ulp=1, max_frac=0.05, atol_small=2 ** -9)
 
 

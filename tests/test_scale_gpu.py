@@ -103,15 +103,32 @@ def test_full_depth_8b_256_greedy_tokens_vs_oracle():
     dis = (torch.tensor(toks) != want.argmax(-1)).nonzero().flatten().tolist()   # the ENGINE's tokens vs the oracle's pick
     margins = O.top2_margin(want)
     first = dis[0] if dis else None
+    ldiff = (got - want).abs().amax(-1)                      # per step: largest logit difference over the vocabulary
+    ulp_top = want.amax(-1).abs().log2().floor().exp2() * 2.0 ** -7
     report(f"full-depth 8B, {n_new} greedy tokens through the engine: {len(dis)} divergence(s) from the oracle (first at step "
-           f"{first}), largest oracle margin at a divergence {max((float(margins[i]) for i in dis), default=0.0):.4f}, "
-           f"softmax max-abs error of the replayed logits {float(err.max()):.2e} (mean {float(err.mean()):.2e}), "
-           f"replay argmax != engine token at {replay_dis} step(s)")
+           f"{first}), largest oracle margin at a divergence {max((float(margins[i]) for i in dis), default=0.0):.4f}; replayed "
+           f"logits vs oracle: softmax max-abs error {float(err.max()):.2e} (mean {float(err.mean()):.2e}), largest logit "
+           f"difference {float(ldiff.max()):.3f} = {float((ldiff / ulp_top).max()):.1f} bf16 ulp of the row's top logit (median "
+           f"{float((ldiff / ulp_top).median()):.1f}); replay argmax != engine token at {replay_dis} step(s)")
     assert float(err.max()) <= 2e-2, "north_star logit bar"
-    assert float(err.max()) <= 5e-3
+    assert float(err.max()) <= 2e-3
+    # Random-init logits over 128k tokens are nearly flat: after 32 layers of bf16 roundings two correct implementations
+    # differ by a few ulp of the top logit, which is also the typical top-1/top-2 margin.  So: the logit noise itself is
+    # bounded (8 ulp of the top logit), and a greedy token may differ from the oracle's only where the oracle's margin is
+    # within that measured noise (each of the two candidates can move by the row's largest difference).
+    # yardstick: ANOTHER correct implementation of the same rounding points — the oracle with its linears as bf16 oneDNN
+    # matmuls (fp32 accumulate in another order, one rounding: still R2) — against the oracle itself
+    other = om.forward(om.new_seq(), ids, fast_linear=True)[n_prompt - 1:].float()
+    odiff = (other - want).abs().amax(-1)
+    report(f"  yardstick (oracle with bf16 oneDNN linears vs oracle): largest logit difference {float(odiff.max()):.3f} = "
+           f"{float((odiff / ulp_top).max()):.1f} ulp (median {float((odiff / ulp_top).median()):.1f}), "
+           f"{int((other.argmax(-1) != want.argmax(-1)).sum())} argmax differences")
+    assert float((ldiff / ulp_top).max()) <= max(2.0 * float((odiff / ulp_top).max()), 8.0), \
+        "the device's logit noise is more than twice that of another correct implementation"
     for i in dis:
-        assert float(margins[i]) < MARGIN, f"step {i}: greedy token differs at an oracle margin of {float(margins[i]):.3f}"
-    assert len(dis) <= n_new // 8, f"{len(dis)} near-tie divergences over {n_new} tokens"
+        assert float(margins[i]) <= 2.0 * float(ldiff[i]) + 1e-6, \
+            f"step {i}: greedy token differs at an oracle margin of {float(margins[i]):.3f} with logit noise {float(ldiff[i]):.3f}"
+    assert len(dis) <= n_new // 4, f"{len(dis)} near-tie divergences over {n_new} tokens"
 
 
 def test_batch64_decode_step_at_bench_shape_vs_oracle():
@@ -135,7 +152,7 @@ def test_batch64_decode_step_at_bench_shape_vs_oracle():
         r.step_device(torch.tensor(prompts[i], dtype=torch.int32).cuda(), pos.cuda(), slots.cuda(), bt[i:i + 1].contiguous(),
                       (pos + 1).cuda(), n, row_to_seq=torch.zeros(n, dtype=torch.int32).cuda(),
                       logit_rows=torch.tensor([n - 1], dtype=torch.int32).cuda())
-    torch.cuda.synchronize()
+        torch.cuda.synchronize()      # the step runs on the runner's stream: its inputs above must outlive it
     # the cache as the oracle's contiguous per-sequence K/V (what the decode step will read)
     kc, vc = r.k_cache.cpu(), r.v_cache.cpu()                   # [L][blocks][hkv][bs][128]
     om = O.OracleModel(cfg, w_host, capacity=blocks_per_seq * bs)
@@ -177,7 +194,11 @@ def test_batch64_decode_step_at_bench_shape_vs_oracle():
         for l in range(cfg.n_layers):
             for mine, theirs in ((kc2[l][blk][:, off], states[i].K[l][p]), (vc2[l][blk][:, off], states[i].V[l][p])):
                 d = (mine.float() - theirs.float()).abs()
-                assert float(d.max()) <= 2.0 ** -5 and float((d > 0).float().mean()) <= 0.05
+                # layer 0 sees identical inputs (embedding -> norm -> projection -> RoPE): ulp-level and rare; layer 1's
+                # inputs already carry layer 0's last-bit differences, so most of its values move by an ulp
+                assert float(d.max()) <= 2.0 ** -4
+                if l == 0:
+                    assert float((d > 0).float().mean()) <= 0.02
     r.close()
 
 
