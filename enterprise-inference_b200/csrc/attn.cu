@@ -311,12 +311,9 @@ int launch_attn(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, co
                 const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                 __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tiles_per_split,
                 float scale, float* part_o, float* part_ml, cudaStream_t s) {
-  static bool attr_set = false;
+  static bool attr_set[64] = {};
   const size_t smem = sizeof(AttnSmem);
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(paged_attn_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  B200_CUDA(ensure_dynamic_smem(paged_attn_kernel<G>, (int)smem, attr_set));
   B200_CUDA(launch(paged_attn_kernel<G>, dim3(n_splits, hkv, T), dim3(kAttnThreads), smem, s, q, ldq, kc, vc,
                    block_table, bt_stride, row_to_seq, ctx_lens, out, ldo, hkv, block_size, tiles_per_split, n_splits,
                    scale, part_o, part_ml));

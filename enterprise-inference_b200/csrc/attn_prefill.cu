@@ -566,11 +566,8 @@ template <int G>
 int launch_fa(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfloat16* q, int64_t ldq, const int32_t* block_table,
               int bt_stride, const int32_t* ctx_lens, __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size,
               float scale, const PlanItem* plan, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(paged_prefill_fa_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFaSmem));
-    attr_set = true;
-  }
+  static bool attr_set[64] = {};
+  B200_CUDA(ensure_dynamic_smem(paged_prefill_fa_kernel<G>, kFaSmem, attr_set));
   const int64_t max_work = (int64_t)T * hkv;   // upper bound on items x kv heads; the kernel reads the real count
   const int grid = (int)(max_work < kNumSMs ? max_work : kNumSMs);
   B200_CUDA(launch(paged_prefill_fa_kernel<G>, dim3(grid), dim3(kFaThreads), (size_t)kFaSmem, s, mk, mv, q, ldq, block_table,

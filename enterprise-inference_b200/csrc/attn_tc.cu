@@ -635,12 +635,8 @@ int launch_attn_tc3(const CUtensorMap& mk, const CUtensorMap& mv, const __nv_bfl
                     const int32_t* block_table, int bt_stride, const int32_t* row_to_seq, const int32_t* ctx_lens,
                     __nv_bfloat16* out, int64_t ldo, int T, int hkv, int block_size, int n_splits, int tps, float scale,
                     float* part_o, float* part_ml, int early, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(paged_attn_tc_kernel<G, R, NSLOT, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   attn_tc_smem(NSLOT)));
-    attr_set = true;
-  }
+  static bool attr_set[64] = {};
+  B200_CUDA(ensure_dynamic_smem(paged_attn_tc_kernel<G, R, NSLOT, CG>, attn_tc_smem(NSLOT), attr_set));
   static const int trace_on = getenv("B200_ATTN_TRACE") ? atoi(getenv("B200_ATTN_TRACE")) : 0;
   if (trace_on) cudaMemcpyToSymbol(g_attn_trace_on, &trace_on, sizeof(int));
   const int64_t items = (int64_t)n_splits * hkv * ((T + R - 1) / R);

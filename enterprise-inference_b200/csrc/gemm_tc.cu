@@ -777,14 +777,9 @@ Plan make_plan(int T, int n_out, int k) {
 
 template <int N, int MODE, int S, bool NI>
 int launch_tc3(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
-  static bool attr_set[64] = {};   // per device: a process may drive several GPUs
+  static bool attr_set[64] = {};
   const int smem = S * stage_bytes(N) + 1024 + kTailBytes;
-  int dev = 0;
-  B200_CUDA(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    B200_CUDA(cudaFuncSetAttribute(linear_tc_kernel<N, MODE, S, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    if (dev >= 0 && dev < 64) attr_set[dev] = true;
-  }
+  B200_CUDA(ensure_dynamic_smem(linear_tc_kernel<N, MODE, S, NI>, smem, attr_set));
   B200_CUDA(launch_cluster(linear_tc_kernel<N, MODE, S, NI>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads),
                            (size_t)smem, s, p.cluster ? dim3(1, pl.splits, 1) : dim3(1, 1, 1), mw, mx, p));
   return B200_OK;

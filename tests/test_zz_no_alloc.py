@@ -47,10 +47,15 @@ def run_both(lib, abi, c):
     abi.check(lib.b200_paged_attn_decode(c["q"].data_ptr(), hq * 128, c["kc"].data_ptr(), c["vc"].data_ptr(),
                                          c["bt"].data_ptr(), c["stride"], None, c["cl"].data_ptr(), ref.data_ptr(),
                                          hq * 128, T, hq, hkv, bs, c["max_ctx"], 128 ** -0.5, ws.data_ptr(), ws_bytes, None))
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info()[0]
     abi.check(lib.b200_paged_attn_decode_static(c["q"].data_ptr(), hq * 128, c["kc"].data_ptr(), c["vc"].data_ptr(),
                                                 c["bt"].data_ptr(), c["stride"], None, c["cl"].data_ptr(), got.data_ptr(),
                                                 hq * 128, T, hq, hkv, bs, c["max_ctx"], 128 ** -0.5, None))
     torch.cuda.synchronize()
+    # the property in the entry point's name: the device's free memory is the same after the call as before it
+    # (the caller of this entry point has no way to give memory back, so the library must not take any)
+    assert torch.cuda.mem_get_info()[0] == free_before, "the static-scratch entry point changed the device's free memory"
     return got, ref
 
 
@@ -60,6 +65,11 @@ def test_static_scratch_attention_matches_workspace_attention_twice_in_a_row():
     assert lib.b200_paged_attn_static_scratch_bytes() == 2 << 20
     # first call: split-KV plan (few rows, long context) -> the built-in scratch is really used
     a = make_case(T=2, hq=8, hkv=2, ctx_lens=[4097, 900], seed=1)
+    # (the very first launch of a kernel loads its module and may grow the context once: warm up, then measure)
+    lib.b200_paged_attn_decode_static(a["q"].data_ptr(), 8 * 128, a["kc"].data_ptr(), a["vc"].data_ptr(), a["bt"].data_ptr(),
+                                      a["stride"], None, a["cl"].data_ptr(), torch.empty(2, 8 * 128, dtype=BF, device="cuda").data_ptr(),
+                                      8 * 128, 2, 8, 2, 128, a["max_ctx"], 128 ** -0.5, None)
+    torch.cuda.synchronize()
     got, ref = run_both(lib, abi, a)
     assert torch.isfinite(got.float()).all()
     # same kernels, same split plan, same summation order: the tolerance of the attention tests
