@@ -182,3 +182,26 @@ def test_sampling_probs_min_p_matches_vllm_masks():
         keep = torch.from_numpy(z[f"mp_keep_{sd}"])
         assert torch.equal(probs > 0, keep), f"min_p case {sd}: kept sets differ ({int((probs > 0).sum())} vs {int(keep.sum())})"
         assert abs(float(probs.sum()) - 1.0) < 1e-5
+
+
+@pytest.mark.parametrize("hq,hkv,n", [(4, 1, 1), (32, 8, 129), (40, 8, 700), (64, 8, 2049)])
+def test_oracle_attention_against_torch_sdpa(hq, hkv, n):
+    """R4 has no host-runnable vLLM implementation in this image (its CPU attention is compiled code the CUDA wheel
+    lacks), so it stays a restatement; this narrows it against the independent implementation vLLM-CPU's SDPA backend
+    itself calls for prefill rows: torch.nn.functional.scaled_dot_product_attention on the host, GQA, causal last row.
+    fp32 SDPA: the bf16 results agree to 1 ulp on almost every element (SDPA scales q and k by sqrt(scale) each, the
+    oracle scales the scores: different roundings, same arithmetic).  bf16 SDPA (P rounded to bf16 before P.V, which
+    R4 does NOT do): within 2 ulp."""
+    g = torch.Generator().manual_seed(hq * 1000 + n)
+    q = torch.randn(hq, 128, generator=g).to(torch.bfloat16)
+    K = torch.randn(n, hkv, 128, generator=g).to(torch.bfloat16)
+    V = torch.randn(n, hkv, 128, generator=g).to(torch.bfloat16)
+    want = O.attend(q, K, V, n, 128 ** -0.5).float()
+    F = torch.nn.functional
+    for dt, max_ulp, max_frac in ((torch.float32, 1, 0.02), (torch.bfloat16, 2, 0.6)):
+        o = F.scaled_dot_product_attention(q.to(dt)[None, :, None, :], K.to(dt).permute(1, 0, 2)[None], V.to(dt).permute(1, 0, 2)[None],
+                                           scale=128 ** -0.5, enable_gqa=True)[0, :, 0].to(torch.bfloat16).float()
+        d = (o - want).abs()
+        ulp = want.abs().clamp_min(2.0 ** -126).log2().floor().exp2() * 2.0 ** -7
+        assert (d <= torch.maximum(max_ulp * ulp, torch.tensor(2.0 ** -9))).all(), f"{dt}: max diff {float(d.max()):.3e}"
+        assert float((d > 0).float().mean()) <= max_frac, f"{dt}: {float((d > 0).float().mean()):.3f} of elements differ"
