@@ -54,7 +54,7 @@ constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 #endif
 __host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? B200_STAGES16 : (N <= 32 ? 4 : (N <= 64 ? B200_STAGES64 : (N <= 128 ? 3 : B200_STAGES256))); }
 __host__ __device__ constexpr int stage_bytes(int N) { return kBlockM * kBlockK * 2 + N * kBlockK * 2; }
-constexpr int kTailBytes = 1024;   // barriers, TMEM slot, ticket | per-token 1/rms [64] | source rows [64] (fused-norm consumer)
+constexpr int kTailBytes = 1024;   // barriers, TMEM slot, ticket | per-token 1/rms [64] (fused-norm consumer)
 __host__ __device__ constexpr int smem_bytes_for(int N) { return stages_for(N) * stage_bytes(N) + 1024 + kTailBytes; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -280,43 +280,49 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // t*128 + ((c ^ (t & 7)) << 4)); rows >= T keep whatever the ring held (their accumulator columns are never read).
 template <int N, int S>
 __device__ __forceinline__ void norm_b_tiles(const TcParams& p, unsigned char* smem, uint64_t* full, uint64_t* empty,
-                                             float* rinv_s, int* row_s, int tok0, int kb0, int nkb, int wq, int lane) {
+                                             float* rinv_s, int tok0, int kb0, int nkb, int wq, int lane) {
   constexpr int kStageBytes = stage_bytes(N);
   constexpr int kABytes = kBlockM * kBlockK * 2;
   constexpr int U = 4;
   const int te = wq * 32 + lane;
   const int tmax = min(N, p.T - tok0);
   const int hidden = p.nslab * kBlockM;
+  const int ntask = tmax * 8;   // (token row, 16-byte chunk of the 64-wide K block)
+  float4 a[U][2];
+  uint4 wv[U];
+  auto load = [&](int i, int task0) {
+    const int kcol = (kb0 + i) * kBlockK;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int task = task0 + 32 * u;
+      if (task < ntask) {
+        const int t = task >> 3, c = task & 7;
+        const int row = p.rows ? __ldg(p.rows + tok0 + t) : tok0 + t;
+        const float4* src = reinterpret_cast<const float4*>(p.sres + (int64_t)row * hidden + kcol + c * 8);
+        a[u][0] = __ldcg(src);
+        a[u][1] = __ldcg(src + 1);
+        wv[u] = __ldg(reinterpret_cast<const uint4*>(p.norm_w + kcol + c * 8));
+      }
+    }
+  };
+  // the first tasks' stream rows are requested BEFORE the variance is summed: the two L2 round trips (ssq, sres)
+  // that follow griddepcontrol.wait overlap instead of following each other
+  if (wq < nkb) load(wq, lane);
   if (te < tmax) {
-    const int row = p.rows ? p.rows[tok0 + te] : tok0 + te;
+    const int row = p.rows ? __ldg(p.rows + tok0 + te) : tok0 + te;
     const float* q = p.ssq + (int64_t)row * p.nslab;
     float tot = 0.f;
 #pragma unroll 8
     for (int i = 0; i < p.nslab; ++i) tot += __ldcg(q + i);
     rinv_s[te] = 1.0f / sqrtf(tot / (float)hidden + p.eps);
-    row_s[te] = row;
   }
   asm volatile("bar.sync 1, 128;" ::: "memory");
-  const int ntask = tmax * 8;   // (token row, 16-byte chunk of the 64-wide K block)
   for (int i = wq; i < nkb; i += 4) {
     const int st = i % S;
-    const int kcol = (kb0 + i) * kBlockK;
     const uint32_t bbase = smem_u32(smem + st * kStageBytes + kABytes);
     bool need_wait = i >= S;
     for (int task0 = lane; task0 < ntask; task0 += 32 * U) {
-      float4 a[U][2];
-      uint4 wv[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int task = task0 + 32 * u;
-        if (task < ntask) {
-          const int t = task >> 3, c = task & 7;
-          const float4* src = reinterpret_cast<const float4*>(p.sres + (int64_t)row_s[t] * hidden + kcol + c * 8);
-          a[u][0] = __ldcg(src);
-          a[u][1] = __ldcg(src + 1);
-          wv[u] = __ldg(reinterpret_cast<const uint4*>(p.norm_w + kcol + c * 8));
-        }
-      }
+      if (i != wq || task0 != lane) load(i, task0);
       if (need_wait) {   // the MMAs that read this stage's previous tile have completed
         mbar_wait(&empty[st], ((i / S) - 1) & 1);
         need_wait = false;
@@ -362,7 +368,6 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
   int* ticket_slot = reinterpret_cast<int*>(tmem_slot + 1);
   float* rinv_s = reinterpret_cast<float*>(smem + S * kStageBytes + 256);   // [64]
-  int* row_s = reinterpret_cast<int*>(rinv_s + 64);                         // [64]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // Several token tiles (prefill): the token tile is the FAST index, so that the CTAs that share a weight slab
@@ -455,7 +460,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     const int tok0 = tok_tile * N;
     const int wq = warp - 2;
     pdl_wait();
-    if constexpr (NI) norm_b_tiles<N, S>(p, smem, full, empty, rinv_s, row_s, tok0, kb0, nkb, wq, lane);
+    if constexpr (NI) norm_b_tiles<N, S>(p, smem, full, empty, rinv_s, tok0, kb0, nkb, wq, lane);
     if (nkb > 0) {
       mbar_wait(tmem_full, 0);
       tc_fence_after();
@@ -767,7 +772,7 @@ Plan make_plan(int T, int n_out, int k) {
   const int tiles = pl.m_tiles * pl.tok_tiles;
   int s = 1;
   if (tiles < slots) {
-    s = (slots + tiles / 2) / tiles;                  // nearest to one wave
+    s = (slots + tiles / 2) / tiles;                  // nearest to one wave (rounding down instead: 3 % slower at batch 1)
     s = min(s, max(pl.n_kblocks / min_kb, 1));        // at least min_kb K blocks (64 KiB of W each) per split
     s = max(1, min(s, 32));
   }

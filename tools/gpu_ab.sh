@@ -2,7 +2,7 @@
 # A/B runs of bench.py under environment switches; every line lands in gpurun_out/ab_<tag>.jsonl
 # usage: tools/gpu_ab.sh <tag> <workload> <steps> [ENV=VAL ...]   (one bench run)
 tag=$1; wl=$2; steps=$3; shift 3
-env "$@" python bench.py --workload "$wl" --steps "$steps" --warmup 8 --no-cpu-baseline 2>gpurun_out/ab_${tag}.err | tail -1 > gpurun_out/ab_${tag}.json
+env "$@" timeout 180 python bench.py --workload "$wl" --steps "$steps" --warmup 8 --no-cpu-baseline --headline-only 2>gpurun_out/ab_${tag}.err | tail -1 > gpurun_out/ab_${tag}.json
 python - "$tag" <<'PY'
 import json,sys
 t=sys.argv[1]

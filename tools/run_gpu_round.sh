@@ -1,6 +1,5 @@
 set -x
-rm -f gpurun_out/scale_report.txt
-SECONDS=0
-timeout 1500 python -m pytest tests/test_scale_gpu.py -q -s 2>&1 | grep -v "^    \|^$" | tail -25
-echo "scale tests took $SECONDS s"
-cat gpurun_out/scale_report.txt
+tools/gpu_ab.sh bs64_base llama8b-bs64 64 X=1
+tools/gpu_ab.sh bs64_g148 llama8b-bs64 64 B200_ATTN_GRID=148
+tools/gpu_ab.sh bs64_s2 llama8b-bs64 64 B200_ATTN_SPLITS=2
+tools/gpu_ab.sh bs64_s2g148 llama8b-bs64 64 B200_ATTN_SPLITS=2 B200_ATTN_GRID=148
