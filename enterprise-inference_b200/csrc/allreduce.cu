@@ -40,11 +40,13 @@ __device__ __forceinline__ uint4 ld_peer(const void* p) {
 
 __global__ void __launch_bounds__(256) allreduce_oneshot_kernel(ArParams p) {
   __shared__ unsigned int seq_s;
-  pdl_wait();  // the partial of this rank was written by the previous kernel of the stream
-  pdl_launch_dependents();
+  // the sequence number of this buffer was last advanced by the collective two half-layers ago (complete: only the
+  // directly preceding kernel can still be running under programmatic dependent launch): read it before the wait
   const int tid = threadIdx.x;
   if (tid == 0) seq_s = *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) + 1u;
   __syncthreads();
+  pdl_wait();  // the partial of this rank was written by the previous kernel of the stream
+  pdl_launch_dependents();
   const unsigned int seq = seq_s;
   const int slot = (p.buf_idx * 8 + p.rank) * 32;
   if (blockIdx.x == 0 && tid < p.world) {
@@ -101,11 +103,11 @@ allreduce_add_rmsnorm_kernel(ArParams p, __nv_bfloat16* res, const __nv_bfloat16
                              int hidden, float eps) {
   __shared__ unsigned int seq_s;
   __shared__ float red[kArNormThreads / 32];
+  const int tid = threadIdx.x;
+  if (tid == 0) seq_s = *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) + 1u;   // see allreduce_oneshot_kernel
+  __syncthreads();
   pdl_wait();
   pdl_launch_dependents();
-  const int tid = threadIdx.x;
-  if (tid == 0) seq_s = *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) + 1u;
-  __syncthreads();
   const unsigned int seq = seq_s;
   if (blockIdx.x == 0 && tid < p.world) {
     __threadfence_system();
@@ -200,11 +202,11 @@ allreduce_twoshot_rmsnorm_kernel(ArParams p, int T, __nv_bfloat16* res, const __
                                  float eps) {
   __shared__ unsigned int seq_s;
   __shared__ float red[kArNormThreads / 32];
+  const int tid = threadIdx.x;
+  if (tid == 0) seq_s = *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) + 1u;   // see allreduce_oneshot_kernel
+  __syncthreads();
   pdl_wait();
   pdl_launch_dependents();
-  const int tid = threadIdx.x;
-  if (tid == 0) seq_s = *reinterpret_cast<volatile unsigned int*>(p.state + p.buf_idx) + 1u;
-  __syncthreads();
   const unsigned int seq = seq_s;
   const int slot = (p.buf_idx * 8 + p.rank) * 32;
   if (blockIdx.x == 0 && tid < p.world) {
