@@ -72,6 +72,8 @@ SIGNATURES = {
     "b200_argmax": (C.c_int, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp]),
     "b200_sample": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200_ctx_sample_last": (C.c_int, [_vp, _i32, _vp, _vp, _vp]),
+    "b200_logit_adjust": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200_ctx_adjust_last": (C.c_int, [_vp, _i32, _vp, _i32, _vp]),
     "b200_logprobs": (C.c_int, [_vp, _i64, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "b200_ctx_logprobs_last": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp]),
     "b200_advance_decode_rows": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _vp]),

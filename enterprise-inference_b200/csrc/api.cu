@@ -154,6 +154,7 @@ struct b200_ctx {
   float* d_gathered;  // [world][rows][2]
   void* d_sample;     // sampling parameters of the rows, packed (b200_ctx_sample_last)
   void* d_logprob;    // [rows] chosen ids | [rows] logprob | [rows][32] top ids | [rows][32] top logprobs
+  void* d_adjust;     // packed penalties / logit_bias of the step's rows (b200_ctx_adjust_last)
   __nv_bfloat16* logits_full;  // TP only: [world][rows][vocab_local], gathered for the sampler
   // graphs
   bool graphs = true;
@@ -180,6 +181,7 @@ struct b200_ctx {
 };
 
 static int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+constexpr int64_t kAdjustMaxInts = 4ll << 20;   // 16 MiB: ~1 M (row, token) entries of penalties / logit_bias per step
 constexpr int64_t kArFlagBytes = 2 * 2 * 8 * 128;   // "partial ready" and "rows delivered" flags: [kind][buffer][rank] x 128 B
 
 extern "C" const char* b200_last_error(void) { return g_err; }
@@ -269,6 +271,7 @@ extern "C" int b200_ctx_create(const b200_model_cfg* cfg, b200_ctx** out) {
       {(void**)&c->d_gathered, R * 8 * W},
       {(void**)&c->d_sample, R * 40},
       {(void**)&c->d_logprob, R * (8 + 32 * 8)},
+      {(void**)&c->d_adjust, kAdjustMaxInts * 4},
       {(void**)&c->logits_full, W > 1 ? R * (int64_t)c->vocab_local * 2 * W : 16},
   };
   int64_t total = 0;
@@ -1017,6 +1020,35 @@ extern "C" int b200_ctx_sample_last(b200_ctx* c, int32_t n_rows, const void* hos
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(host_out_ids, c->d_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
   return B200_OK;
+}
+
+extern "C" int b200_logit_adjust(void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const float* row_params,
+                                 const int32_t* offsets, const int32_t* ids, const int32_t* counts, const int32_t* seen,
+                                 const float* bias, void* stream) {
+  B200_REQUIRE(n_rows >= 0 && vocab > 0 && ld >= vocab, B200_ERR_INVALID, "logit_adjust: bad sizes (rows=%d vocab=%d ld=%lld)", n_rows,
+               vocab, (long long)ld);
+  return logit_adjust_rows((__nv_bfloat16*)logits, ld, n_rows, vocab, 0, row_params, offsets, ids, counts, seen, bias,
+                           (cudaStream_t)stream);
+}
+
+// Penalties / logit_bias over the logit rows of the LAST step (still in the ctx's buffer), before b200_ctx_sample_last.
+// host_packed (int32 words): float row_params[3 n] | int32 offsets[n + 1] | int32 ids[E] | int32 counts[E] | int32 seen[E]
+// | float bias[E], E = offsets[n] = n_entries.  With tensor parallelism every rank adjusts its own vocabulary shard.
+extern "C" int b200_ctx_adjust_last(b200_ctx* c, int32_t n_rows, const void* host_packed, int32_t n_entries, void* stream) {
+  B200_REQUIRE(c && host_packed, B200_ERR_INVALID, "adjust_last: null argument");
+  B200_REQUIRE(n_rows > 0 && n_rows <= c->max_logit_rows && n_entries >= 0, B200_ERR_INVALID, "adjust_last: n_rows=%d outside (0,%d]",
+               n_rows, c->max_logit_rows);
+  const int64_t n = n_rows, E = n_entries, words = 3 * n + n + 1 + 4 * E;
+  B200_REQUIRE(words <= kAdjustMaxInts, B200_ERR_UNSUPPORTED, "adjust_last: %lld entries exceed the %lld-word buffer", (long long)E,
+               (long long)kAdjustMaxInts);
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_CUDA(cudaMemcpyAsync(c->d_adjust, host_packed, (size_t)words * 4, cudaMemcpyHostToDevice, s));
+  const int32_t* w = static_cast<const int32_t*>(c->d_adjust);
+  const float* row_params = reinterpret_cast<const float*>(w);
+  const int32_t* offsets = w + 3 * n;
+  const int32_t* ids = offsets + n + 1;
+  return logit_adjust_rows(c->logits, c->vocab_local, n_rows, c->vocab_local, c->cfg.tp_rank * c->vocab_local, row_params, offsets, ids,
+                           ids + E, ids + 2 * E, reinterpret_cast<const float*>(ids + 3 * E), s);
 }
 
 extern "C" int b200_logprobs(const void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const int32_t* token_ids,

@@ -206,6 +206,9 @@ int paged_attn_ex(const __nv_bfloat16* q, int64_t ldq, const __nv_bfloat16* kc, 
 int sample_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
                 const float* temperature, const int32_t* top_k, const float* top_p, const float* min_p,
                 const uint64_t* seeds, const uint64_t* draws, int32_t* out, cudaStream_t s);
+int logit_adjust_rows(__nv_bfloat16* logits, int64_t ld, int n_rows, int vocab_local, int index_offset, const float* row_params,
+                      const int32_t* offsets, const int32_t* ids, const int32_t* counts, const int32_t* seen, const float* bias,
+                      cudaStream_t s);
 int logprob_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
                  const int32_t* tok, int n_top, float* out_lp, int32_t* top_ids, float* top_lp, cudaStream_t s);
 // once per step when pack > 0: builds the prefill attention's row plan in ws; 1 = built (use pack = 2), 0 = not used

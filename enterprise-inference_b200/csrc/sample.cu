@@ -378,7 +378,51 @@ logprob_kernel(const __nv_bfloat16* __restrict__ logits, int64_t ld, int vocab, 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// (a10, widened) logit_bias and repetition / frequency / presence penalties on the logit rows of a step, in the order
+// of the image's sampler ([V22] vllm/v1/sample/sampler.py:366-416: logit_bias with the non-argmax-invariant
+// processors, then apply_penalties = vllm/model_executor/layers/utils.py:51-89 with
+// vllm/_custom_ops.py:360-373): for a token that occurs in the prompt or the output
+//     x += bias;  x *= (x > 0 ? 1/rep : rep);  x -= freq * count_in_output;  x -= pres * (count_in_output > 0)
+// in fp32.  Only tokens of the request's own history or bias table change, so the work is SPARSE: one entry per
+// distinct (row, token), rows in CSR form.  The adjusted value is rounded back to the bf16 logits buffer (the one
+// deviation from the image, which keeps the processed logits in fp32: R7) so that argmax, sampling and log-probabilities
+// run on it unchanged.  Entries of one row must name distinct tokens (read-modify-write).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+logit_adjust_kernel(__nv_bfloat16* __restrict__ logits, int64_t ld, int vocab_local, int index_offset,
+                    const float* __restrict__ row_params, const int32_t* __restrict__ offsets,
+                    const int32_t* __restrict__ ids, const int32_t* __restrict__ counts, const int32_t* __restrict__ seen,
+                    const float* __restrict__ bias) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int row = blockIdx.x;
+  const float rep = row_params[3 * row], freq = row_params[3 * row + 1], pres = row_params[3 * row + 2];
+  const float rep_inv = 1.0f / rep;
+  for (int e = offsets[row] + threadIdx.x; e < offsets[row + 1]; e += blockDim.x) {
+    const int id = ids[e] - index_offset;          // tensor parallel: this rank's vocabulary shard only
+    if (id < 0 || id >= vocab_local) continue;
+    __nv_bfloat16* px = logits + (int64_t)row * ld + id;
+    float x = __bfloat162float(*px) + bias[e];
+    if (seen[e]) x *= (x > 0.f ? rep_inv : rep);
+    const int c = counts[e];
+    x -= freq * (float)c;
+    x -= pres * (c > 0 ? 1.0f : 0.0f);
+    *px = __float2bfloat16_rn(x);
+  }
+}
+
 }  // namespace
+
+int logit_adjust_rows(__nv_bfloat16* logits, int64_t ld, int n_rows, int vocab_local, int index_offset, const float* row_params,
+                      const int32_t* offsets, const int32_t* ids, const int32_t* counts, const int32_t* seen, const float* bias,
+                      cudaStream_t s) {
+  B200_REQUIRE(logits && row_params && offsets && ids && counts && seen && bias, B200_ERR_INVALID, "logit_adjust: null argument");
+  if (n_rows == 0) return B200_OK;
+  B200_CUDA(launch(logit_adjust_kernel, dim3(n_rows), dim3(256), (size_t)0, s, logits, ld, vocab_local, index_offset, row_params,
+                   offsets, ids, counts, seen, bias));
+  return B200_OK;
+}
 
 int logprob_rows(const __nv_bfloat16* logits, int64_t ld, int n_rows, int vocab, int seg_len, int64_t seg_stride,
                  const int32_t* tok, int n_top, float* out_lp, int32_t* top_ids, float* top_lp, cudaStream_t s) {

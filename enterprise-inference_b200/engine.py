@@ -70,6 +70,11 @@ class Request:
     min_p: float = 0.0                  # 0: off
     seed: Optional[int] = None          # None: drawn once when the request is added
     logprobs: Optional[int] = None      # None: off; N >= 0: logprob of each emitted token + the N most likely
+    # logit_bias / penalties (docs/api-spec.yaml:275-311): applied to the step's logits before the token is chosen
+    repetition_penalty: float = 1.0
+    frequency_penalty: float = 0.0
+    presence_penalty: float = 0.0
+    logit_bias: Optional[Dict[int, float]] = None
     arrival: float = field(default_factory=time.monotonic)
     # state
     output_ids: List[int] = field(default_factory=list)
@@ -83,6 +88,10 @@ class Request:
     token_times: List[float] = field(default_factory=list)
     logprob_data: List[tuple] = field(default_factory=list)   # per emitted token: (logprob, [(id, logprob), ...])
     error: Optional[str] = None         # set when the engine failed this request (finish_reason "error")
+
+    @property
+    def adjusts(self) -> bool:
+        return bool(self.logit_bias) or self.repetition_penalty != 1.0 or self.frequency_penalty != 0.0 or self.presence_penalty != 0.0
 
     @property
     def all_ids(self) -> List[int]:
@@ -342,9 +351,17 @@ class LLMEngine:
             sampled = []
         self.steps += 1
         sampled = list(sampled)
-        if sampled and any(s.samples and s.req.temperature > 0.0 for s in sched):
-            # some rows do not want the argmax: one more kernel over the logits the step left on the device
-            # (greedy rows get their argmax back).  Draw number = tokens generated so far: a seed replays.
+        adjusted = bool(sampled) and any(s.samples and s.req.adjusts for s in sched)
+        if adjusted:
+            # logit_bias / penalties: a sparse kernel over the logits the step left on the device, before any token is
+            # chosen from them (the step's own argmax of these rows is discarded: the sampler below re-takes it)
+            rows = [s.req for s in sched if s.samples]
+            self.runner.adjust_last([dict(prompt=r.prompt_ids, output=r.output_ids, rep=r.repetition_penalty,
+                                          freq=r.frequency_penalty, pres=r.presence_penalty, bias=r.logit_bias)
+                                     if r.adjusts else None for r in rows])
+        if sampled and (adjusted or any(s.samples and s.req.temperature > 0.0 for s in sched)):
+            # some rows do not want the step's argmax: one more kernel over the logits the step left on the device
+            # (greedy rows get the argmax of those logits).  Draw number = tokens generated so far: a seed replays.
             rows = [s.req for s in sched if s.samples]
             sampled = list(self.runner.sample_last([r.temperature for r in rows], [r.top_k for r in rows],
                                                    [r.top_p for r in rows], [r.seed or 0 for r in rows],

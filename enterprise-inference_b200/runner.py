@@ -253,6 +253,64 @@ class ModelRunner:
         temperature 0 rows return the step's greedy token.  The greedy hot path never calls this."""
         return self.sample_packed(self.pack_sampling(temperature, top_k, top_p, seeds, draws, min_p), sync)
 
+    ADJUST_MAX_WORDS = 4 << 20    # b200_ctx_adjust_last's buffer (16 MiB)
+
+    def pack_adjust(self, rows) -> tuple:
+        """rows: one entry per logit row of the last step, None (untouched) or a dict(prompt, output, rep, freq, pres,
+        bias={token: value}).  Writes the packed buffer of b200_ctx_adjust_last into pinned memory (allocated on first
+        use); returns (n_rows, n_entries).  One entry per distinct token of a row's prompt, output and bias table."""
+        n = len(rows)
+        if not 0 < n <= self.max_logit_rows:
+            raise ValueError(f"adjust_last: {n} rows outside (0, {self.max_logit_rows}]")
+        if getattr(self, "_h_adjust", None) is None:
+            self._h_adjust = torch.zeros(self.ADJUST_MAX_WORDS, dtype=torch.int32)
+            if torch.cuda.is_available():
+                self._h_adjust = self._h_adjust.pin_memory()
+            self._h_adjust_np = self._h_adjust.numpy()
+        ids, counts, seen, bias, offsets = [], [], [], [], [0]
+        params = np.empty(3 * n, dtype=np.float32)
+        for i, r in enumerate(rows):
+            if r is None:
+                params[3 * i:3 * i + 3] = (1.0, 0.0, 0.0)
+                offsets.append(offsets[-1])
+                continue
+            params[3 * i:3 * i + 3] = (r["rep"], r["freq"], r["pres"])
+            out_t, out_c = np.unique(np.asarray(r["output"], dtype=np.int64), return_counts=True)
+            hist = np.union1d(np.asarray(r["prompt"], dtype=np.int64), out_t)
+            b = r.get("bias") or {}
+            toks = np.union1d(hist, np.fromiter(b.keys(), dtype=np.int64, count=len(b))) if b else hist
+            c = np.zeros(len(toks), dtype=np.int32)
+            c[np.searchsorted(toks, out_t)] = out_c
+            bb = np.zeros(len(toks), dtype=np.float32)
+            if b:
+                bb[np.searchsorted(toks, np.fromiter(b.keys(), dtype=np.int64, count=len(b)))] = np.fromiter(b.values(), dtype=np.float32, count=len(b))
+            ids.append(toks.astype(np.int32))
+            counts.append(c)
+            seen.append(np.isin(toks, hist).astype(np.int32))
+            bias.append(bb)
+            offsets.append(offsets[-1] + len(toks))
+        E = offsets[-1]
+        words = 3 * n + n + 1 + 4 * E
+        if words > self.ADJUST_MAX_WORDS:
+            raise ValueError(f"adjust_last: {E} (row, token) entries exceed the step's buffer")
+        a = self._h_adjust_np
+        a[:3 * n].view(np.float32)[:] = params
+        a[3 * n:4 * n + 1] = offsets
+        o = 4 * n + 1
+        if E:
+            a[o:o + E] = np.concatenate(ids)
+            a[o + E:o + 2 * E] = np.concatenate(counts)
+            a[o + 2 * E:o + 3 * E] = np.concatenate(seen)
+            a[o + 3 * E:o + 4 * E].view(np.float32)[:] = np.concatenate(bias)
+        return n, E
+
+    def adjust_packed(self, n: int, n_entries: int):
+        _abi.check(self.lib.b200_ctx_adjust_last(self.ctx, n, self._h_adjust.data_ptr(), n_entries, self.stream.cuda_stream))
+
+    def adjust_last(self, rows):
+        """logit_bias / penalties on the logit rows of the LAST step, in place, before sample_last (see pack_adjust)."""
+        self.adjust_packed(*self.pack_adjust(rows))
+
     def logprobs_last(self, token_ids, n_top: int = 0):
         """Log-probabilities (log softmax of the raw logits) of `token_ids` under the LAST step's logit rows, plus
         the n_top most likely tokens per row: (logprob[n], top_ids[n, n_top], top_logprobs[n, n_top])."""

@@ -395,16 +395,8 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
         """Fields of docs/api-spec.yaml this backend parses but does not implement: a non-default value gets a 400,
         never a 200 whose output silently ignores it."""
         bad = []
-        if body.frequency_penalty:
-            bad.append("frequency_penalty")
-        if body.presence_penalty:
-            bad.append("presence_penalty")
-        if body.repetition_penalty not in (None, 1.0):
-            bad.append("repetition_penalty")
         if body.length_penalty not in (None, 1.0):
             bad.append("length_penalty")
-        if body.logit_bias:
-            bad.append("logit_bias")
         if getattr(body, "allowed_token_ids", None):
             bad.append("allowed_token_ids")
         if getattr(body, "suffix", None):
@@ -416,7 +408,27 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
             bad.append("response_format")
         if bad:
             return ("not supported by this backend: " + ", ".join(bad) +
-                    " (penalties, logit_bias and guided decoding are not implemented; leave them at their defaults)")
+                    " (guided decoding, allowed_token_ids, suffix and length_penalty are not implemented; leave them unset)")
+        for name, lo, hi in (("frequency_penalty", -2.0, 2.0), ("presence_penalty", -2.0, 2.0)):
+            v = getattr(body, name)
+            if v is not None and not lo <= v <= hi:
+                return f"{name} must be in [{lo}, {hi}]"
+        if body.repetition_penalty is not None and not 0.0 < body.repetition_penalty <= 100.0:
+            return "repetition_penalty must be in (0, 100]"
+        if body.logit_bias:
+            if len(body.logit_bias) > 1024:
+                return "logit_bias accepts at most 1024 entries"
+            vocab = engine.runner.cfg.vocab
+            for k, v in body.logit_bias.items():
+                if not str(k).lstrip("-").isdigit() or not 0 <= int(k) < vocab:
+                    return f"logit_bias key {k!r} is not a token id of this model (0..{vocab - 1})"
+                if not -100.0 <= float(v) <= 100.0:
+                    return "logit_bias values must be in [-100, 100]"
+        adjusts = bool(body.logit_bias) or bool(body.frequency_penalty) or bool(body.presence_penalty) or \
+            body.repetition_penalty not in (None, 1.0)
+        if adjusts and body.logprobs not in (None, False):
+            return ("logprobs together with logit_bias or a penalty is not supported (the image reports log-probabilities of "
+                    "the raw logits; this backend adjusts the logits in place)")
         if body.seed is not None and not -2 ** 63 <= body.seed < 2 ** 64:
             return "seed must fit 64 bits"
         if body.top_k is not None and not -1 <= body.top_k < 2 ** 31:
@@ -438,7 +450,10 @@ def create_app(engine: LLMEngine, tokenizer, served_model_name: str, max_model_l
                        stop_token_ids=tuple(body.stop_token_ids or ()), min_tokens=body.min_tokens or 0,
                        temperature=max(float(temperature), 0.0), top_k=max(int(top_k), 0),
                        top_p=min(max(float(top_p), 0.0), 1.0), min_p=min(max(float(body.min_p or 0.0), 0.0), 1.0),
-                       seed=body.seed, logprobs=want_logprobs(body))
+                       seed=body.seed, logprobs=want_logprobs(body),
+                       repetition_penalty=float(body.repetition_penalty if body.repetition_penalty is not None else 1.0),
+                       frequency_penalty=float(body.frequency_penalty or 0.0), presence_penalty=float(body.presence_penalty or 0.0),
+                       logit_bias={int(k): float(v) for k, v in body.logit_bias.items()} if body.logit_bias else None)
 
     def want_logprobs(body: _Sampling) -> Optional[int]:
         """None: off.  Completions: `logprobs: N`; chat: `logprobs: true` + `top_logprobs: N`."""

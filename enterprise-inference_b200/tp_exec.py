@@ -16,7 +16,7 @@ import torch
 import torch.distributed as dist
 
 HEADER = 8   # T, R, S, bt_stride, max_ctx, n_ints, opcode, reserved
-OP_STEP, OP_STOP, OP_SAMPLE, OP_LOGPROBS = 1, 2, 3, 4
+OP_STEP, OP_STOP, OP_SAMPLE, OP_LOGPROBS, OP_ADJUST = 1, 2, 3, 4, 5
 
 
 class TPLeader:
@@ -44,6 +44,16 @@ class TPLeader:
         dist.broadcast(self._hdr, src=0, group=self.group)
         dist.broadcast(r._h_sample[:32 * n], src=0, group=self.group)
         return r.sample_packed(n)
+
+    def adjust_last(self, rows):
+        """logit_bias / penalties on the last step's logits: every rank adjusts its own vocabulary shard."""
+        r = self.runner
+        n, E = r.pack_adjust(rows)
+        words = 4 * n + 1 + 4 * E
+        self._hdr[:7] = torch.tensor([n, E, 0, 0, 0, words, OP_ADJUST], dtype=torch.int32)
+        dist.broadcast(self._hdr, src=0, group=self.group)
+        dist.broadcast(r._h_adjust[:words], src=0, group=self.group)
+        r.adjust_packed(n, E)
 
     def logprobs_last(self, token_ids, n_top: int = 0):
         """Log-probabilities over the last step's logits: a collective like sample_last (rank 0 returns the result)."""
@@ -80,6 +90,13 @@ def worker_loop(runner, group=None) -> None:
         if op == OP_SAMPLE:
             dist.broadcast(runner._h_sample[:32 * T], src=0, group=group)
             runner.sample_packed(T)
+            continue
+        if op == OP_ADJUST:
+            if getattr(runner, "_h_adjust", None) is None:
+                runner._h_adjust = torch.zeros(runner.ADJUST_MAX_WORDS, dtype=torch.int32).pin_memory()
+                runner._h_adjust_np = runner._h_adjust.numpy()
+            dist.broadcast(runner._h_adjust[:n_ints], src=0, group=group)
+            runner.adjust_packed(T, R)
             continue
         dist.broadcast(runner._h_meta[:n_ints], src=0, group=group)
         runner.step_packed(T, R, S, bt_stride, max_ctx, n_ints)

@@ -293,6 +293,21 @@ B200_API int b200_sample(const void* logits, int64_t ld, int32_t n_rows, int32_t
 B200_API int b200_ctx_sample_last(b200_ctx* ctx, int32_t n_rows, const void* host_params, int32_t* host_out_ids,
                          void* stream);
 
+/* (a10, widened) OpenAI `logit_bias`, `frequency_penalty`, `presence_penalty` and vLLM's `repetition_penalty` on logit
+ * rows [n_rows][ld] (bf16, modified in place), in the image's order and arithmetic ([V22] vllm/v1/sample/sampler.py:366-416,
+ * vllm/model_executor/layers/utils.py:51-89, vllm/_custom_ops.py:360-373), fp32 per touched token:
+ *   x += bias;  if the token is in the prompt or the output: x *= (x > 0 ? 1/rep : rep);
+ *   x -= freq * (occurrences in the output);  x -= pres * (occurs in the output ? 1 : 0)
+ * then ONE rounding back to bf16 (the image keeps the processed logits in fp32: the only deviation).  Sparse: row r owns
+ * the entries offsets[r] .. offsets[r+1]-1 of (ids, counts, seen, bias), distinct tokens per row; row_params = (rep, freq,
+ * pres) per row.  Device pointers.  b200_ctx_adjust_last applies the same to the logit rows of the LAST step of a ctx from
+ * ONE packed host buffer (float row_params[3n] | int32 offsets[n+1] | int32 ids[E] | int32 counts[E] | int32 seen[E] |
+ * float bias[E]); call it before b200_ctx_sample_last, on every tensor-parallel rank (each adjusts its vocabulary shard). */
+B200_API int b200_logit_adjust(void* logits, int64_t ld, int32_t n_rows, int32_t vocab, const float* row_params,
+                      const int32_t* offsets, const int32_t* ids, const int32_t* counts, const int32_t* seen,
+                      const float* bias, void* stream);
+B200_API int b200_ctx_adjust_last(b200_ctx* ctx, int32_t n_rows, const void* host_packed, int32_t n_entries, void* stream);
+
 /* (a10, widened) OpenAI `logprobs` / `top_logprobs`: log softmax over the raw logits (vLLM's default logprobs mode,
  * [V22] vllm/v1/sample/sampler.py:90-118).  out_logprob[r] = l[token_ids[r]] - logsumexp(l); out_top_ids /
  * out_top_logprobs [r][n_top] = the n_top (<= 32) most likely tokens, value descending, ties by lowest index

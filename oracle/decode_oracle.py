@@ -312,6 +312,34 @@ def sampling_probs(logits_bf16: torch.Tensor, temperature: float, top_k: int = 0
     return out.softmax(dim=-1)
 
 
+def adjust_logits(logits_bf16: torch.Tensor, prompt_ids, output_ids, repetition_penalty: float = 1.0,
+                  frequency_penalty: float = 0.0, presence_penalty: float = 0.0, logit_bias=None) -> torch.Tensor:
+    """One logits row [V] through logit_bias and the penalties, fp32, in the image's order and arithmetic:
+    [V22] vllm/v1/sample/sampler.py:366-416 (logit_bias is a non-argmax-invariant processor and runs BEFORE the
+    penalties), vllm/v1/sample/logits_processor/builtin.py:161-164 (logits += bias),
+    vllm/model_executor/layers/utils.py:51-89 (apply_penalties) and vllm/_custom_ops.py:360-373 (repetition: tokens
+    of the prompt OR the output are scaled by 1/rep where the logit is positive, by rep otherwise — a multiplication by
+    the fp32 reciprocal, not a division; then - freq * count in the OUTPUT, - pres * (count > 0)).
+    Pinned against those functions themselves by tests/golden/penalties.npz (tools/make_penalty_golden.py)."""
+    x = logits_bf16.float().clone()
+    V = x.numel()
+    if logit_bias:
+        for tok, b in logit_bias.items():
+            x[int(tok)] += torch.tensor(float(b), dtype=torch.float32)
+    counts = torch.zeros(V, dtype=torch.float32)
+    for t in output_ids:
+        counts[int(t)] += 1
+    seen = counts > 0
+    for t in prompt_ids:
+        seen[int(t)] = True
+    rep = torch.tensor(float(repetition_penalty), dtype=torch.float32)
+    pen = torch.where(seen, rep, torch.tensor(1.0))
+    x = x * torch.where(x > 0, 1.0 / pen, pen)
+    x = x - torch.tensor(float(frequency_penalty), dtype=torch.float32) * counts
+    x = x - torch.tensor(float(presence_penalty), dtype=torch.float32) * (counts > 0).float()
+    return x
+
+
 # --------------------------------------------------------------------------------------
 # the model
 # --------------------------------------------------------------------------------------

@@ -183,3 +183,25 @@ def test_scheduler_property_any_arrival_pattern_matches_sequential(prompts, max_
     for r, p, n in zip(reqs, prompts, max_new):
         assert r.finished and r.output_ids == expect(p, n)
     assert len(eng.blocks.free) == n_blocks
+
+
+def test_pack_adjust_builds_one_entry_per_distinct_token():
+    """runner.pack_adjust (host side of b200_ctx_adjust_last): CSR rows over the distinct tokens of prompt, output and bias
+    table, output counts, the seen flag (prompt or output), untouched rows as empty rows with neutral parameters."""
+    R = pkg("runner")
+    stub = type("Stub", (), {"max_logit_rows": 8, "ADJUST_MAX_WORDS": R.ModelRunner.ADJUST_MAX_WORDS, "_h_adjust": None})()
+    rows = [dict(prompt=[5, 9, 5], output=[9, 9, 2], rep=1.3, freq=0.5, pres=-1.0, bias={7: 2.5, 9: -1.0}), None,
+            dict(prompt=[1], output=[], rep=1.0, freq=0.0, pres=0.0, bias={4: 1.0})]
+    n, E = R.ModelRunner.pack_adjust(stub, rows)
+    a = stub._h_adjust_np
+    assert (n, E) == (3, 6)
+    params = a[:9].view(np.float32).tolist()
+    assert params == pytest.approx([1.3, 0.5, -1.0, 1.0, 0.0, 0.0, 1.0, 0.0, 0.0])
+    assert a[9:13].tolist() == [0, 4, 4, 6]
+    o = 13
+    assert a[o:o + E].tolist() == [2, 5, 7, 9, 1, 4]                       # ids, sorted per row
+    assert a[o + E:o + 2 * E].tolist() == [1, 0, 0, 2, 0, 0]               # occurrences in the output
+    assert a[o + 2 * E:o + 3 * E].tolist() == [1, 1, 0, 1, 1, 0]           # in prompt or output (7 and 4 are bias-only)
+    assert a[o + 3 * E:o + 4 * E].view(np.float32).tolist() == pytest.approx([0.0, 0.0, 2.5, -1.0, 0.0, 1.0])
+    with pytest.raises(ValueError):
+        R.ModelRunner.pack_adjust(stub, [None] * 9)

@@ -494,6 +494,58 @@ def test_sample_min_p_against_vllm_masks(lib, abi, seed):
         assert set(got.tolist()) <= set(torch.nonzero(row.float() == row.float().max()).flatten().tolist())
 
 
+def pack_adjust(rows):
+    """rows: list of dicts(prompt, output, rep, freq, pres, bias) -> the CSR arrays of b200_logit_adjust (one entry per
+    distinct token of a row's prompt, output and bias table)."""
+    params, offsets, ids, counts, seen, bias = [], [0], [], [], [], []
+    for r in rows:
+        cnt, sn = {}, set(int(t) for t in r["prompt"])
+        for t in r["output"]:
+            cnt[int(t)] = cnt.get(int(t), 0) + 1
+            sn.add(int(t))
+        toks = sorted(sn | set(int(k) for k in r["bias"]))
+        for t in toks:
+            ids.append(t)
+            counts.append(cnt.get(t, 0))
+            seen.append(1 if t in sn else 0)
+            bias.append(float(r["bias"].get(t, 0.0)))
+        params += [r["rep"], r["freq"], r["pres"]]
+        offsets.append(len(ids))
+    i32 = lambda a: torch.tensor(a, dtype=torch.int32)
+    return (torch.tensor(params, dtype=torch.float32), i32(offsets), i32(ids), i32(counts), i32(seen),
+            torch.tensor(bias, dtype=torch.float32))
+
+
+def test_logit_adjust_against_vllm_penalties(lib, abi):
+    """b200_logit_adjust on the rows captured from vLLM's apply_penalties + logit_bias (tests/golden/penalties.npz): every
+    touched logit equals bf16(vLLM's fp32 value) — the one rounding the kernel adds — and no other logit changes; the
+    argmax of the adjusted row is vLLM's unless the rounding creates a tie.  All cases as rows of one launch (ragged)."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "penalties.npz"))
+    seeds = sorted(int(k.split("_")[1]) for k in z.files if k.startswith("logits_"))
+    V = max(len(z[f"logits_{sd}"]) for sd in seeds)
+    rows, logits = [], torch.full((len(seeds), V), -30.0, dtype=BF)
+    for i, sd in enumerate(seeds):
+        l = torch.from_numpy(z[f"logits_{sd}"].copy()).view(BF)
+        logits[i, : len(l)] = l
+        rep, freq, pres = (float(v) for v in z[f"params_{sd}"])
+        rows.append(dict(prompt=z[f"prompt_{sd}"].tolist(), output=z[f"output_{sd}"].tolist(), rep=rep, freq=freq, pres=pres,
+                         bias={int(a): float(b) for a, b in zip(z[f"bias_ids_{sd}"], z[f"bias_{sd}"])}))
+    arrs = [dev(a) for a in pack_adjust(rows)]
+    ld = dev(logits.clone())
+    sync_check(abi, lib.b200_logit_adjust(ld.data_ptr(), V, len(seeds), V, *[a.data_ptr() for a in arrs], None))
+    got = ld.cpu()
+    for i, sd in enumerate(seeds):
+        want = torch.from_numpy(z[f"want_{sd}"])
+        n = len(want)
+        assert torch.equal(got[i, :n], want.to(BF)), f"case {sd}"
+        assert torch.equal(got[i, n:], logits[i, n:])
+        top = got[i, :n].float().max()
+        assert got[i, :n].float()[int(want.argmax())] == top
+    # a second application is NOT idempotent (penalties compound): the engine applies them once per step
+    sync_check(abi, lib.b200_logit_adjust(ld.data_ptr(), V, len(seeds), V, *[a.data_ptr() for a in arrs], None))
+    assert not torch.equal(ld.cpu(), got)
+
+
 @pytest.mark.parametrize("V,n_top", [(5003, 5), (32000, 20), (300, 0), (64, 32)])
 def test_logprobs_match_log_softmax(lib, abi, V, n_top):
     """b200_logprobs: log softmax of the raw logits for the chosen token and the n_top most likely tokens (value

@@ -317,3 +317,44 @@ def test_server_boots_from_a_checkpoint_directory_on_the_gpu(tmp_path, monkeypat
             assert float(O.top2_margin(logits[i])) < MARGIN, f"token {i} differs from the oracle outside a near-tie"
             break
     engine.runner.close()
+
+
+def test_engine_penalties_and_logit_bias_vs_oracle(golden_dir):
+    """Greedy requests with logit_bias / repetition / frequency / presence penalties through the engine: every emitted token
+    is the argmax of the oracle's logits (teacher-forced on the engine's own tokens) after oracle.adjust_logits — vLLM's
+    own arithmetic, tests/golden/penalties.npz — rounded to bf16 as the device does, wherever that argmax is not a
+    near-tie; a +100 bias forces its token; an untouched request in the same batch keeps the plain greedy tokens."""
+    g = np.load(f"{golden_dir}/tiny.npz")
+    cfg = O.CONFIGS["tiny"]
+    w = O.make_weights(cfg, seed=int(g["seed"]), norm_jitter=float(g["norm_jitter"]))
+    r = make_runner(cfg, w)
+    E = pkg("engine")
+    prompt = g["prompt"].tolist()
+    n_new = 24
+    specs = [dict(repetition_penalty=1.3, frequency_penalty=0.4, presence_penalty=0.2, logit_bias={11: 4.0, 500: -3.0}),
+             dict(), dict(logit_bias={77: 100.0}), dict(frequency_penalty=1.5)]
+    eng = E.LLMEngine(r, max_num_batched_tokens=64, max_num_seqs=8, max_model_len=1024)
+    reqs = [E.Request(f"p{i}", list(prompt), max_tokens=n_new, ignore_eos=True, **kw) for i, kw in enumerate(specs)]
+    for q in reqs:
+        eng.add_request(q)
+    while eng.has_work():
+        eng.step()
+    assert reqs[1].output_ids[:8] == g["tokens"].tolist()[:8]
+    assert reqs[2].output_ids == [77] * n_new
+    om = O.OracleModel(cfg, w, capacity=256)
+    checked = 0
+    for q, kw in zip(reqs, specs):
+        if not kw:
+            continue
+        logits = om.forward(om.new_seq(), prompt + q.output_ids[:-1])[len(prompt) - 1:]
+        for i, tok in enumerate(q.output_ids):
+            x = O.adjust_logits(logits[i], prompt, q.output_ids[:i], kw.get("repetition_penalty", 1.0), kw.get("frequency_penalty", 0.0),
+                                kw.get("presence_penalty", 0.0), kw.get("logit_bias")).to(torch.bfloat16).float()
+            if int(x.argmax()) != tok:
+                assert float(O.top2_margin(x)) < MARGIN, f"request {q.request_id} token {i}: not the argmax of the adjusted logits"
+            checked += 1
+    assert checked == 3 * n_new
+    # the frequency penalty changes what plain greedy would have produced (it repeats tokens on this fixture)
+    assert reqs[3].output_ids != reqs[1].output_ids
+    assert len(eng.blocks.free) == r.n_blocks
+    r.close()

@@ -205,3 +205,20 @@ def test_oracle_attention_against_torch_sdpa(hq, hkv, n):
         ulp = want.abs().clamp_min(2.0 ** -126).log2().floor().exp2() * 2.0 ** -7
         assert (d <= torch.maximum(max_ulp * ulp, torch.tensor(2.0 ** -9))).all(), f"{dt}: max diff {float(d.max()):.3e}"
         assert float((d > 0).float().mean()) <= max_frac, f"{dt}: {float((d > 0).float().mean()):.3f} of elements differ"
+
+
+def test_adjust_logits_equals_vllm_penalties_and_logit_bias():
+    """oracle.adjust_logits against rows processed by vLLM's own apply_penalties (+ the logit_bias add of its
+    LogitBiasLogitsProcessor), captured by tools/make_penalty_golden.py: bit for bit in fp32."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "penalties.npz"))
+    seeds = sorted(int(k.split("_")[1]) for k in z.files if k.startswith("logits_"))
+    assert len(seeds) >= 8
+    for sd in seeds:
+        logits = torch.from_numpy(z[f"logits_{sd}"].copy()).view(torch.bfloat16)
+        rep, freq, pres = (float(v) for v in z[f"params_{sd}"])
+        bias = {int(i): float(b) for i, b in zip(z[f"bias_ids_{sd}"], z[f"bias_{sd}"])}
+        got = O.adjust_logits(logits, z[f"prompt_{sd}"].tolist(), z[f"output_{sd}"].tolist(), rep, freq, pres, bias)
+        want = torch.from_numpy(z[f"want_{sd}"])
+        assert torch.equal(got, want), f"case {sd}: {(got != want).sum()} logits differ, max {(got - want).abs().max():.3e}"
+        changed = (want != logits.float())
+        assert changed.any() and changed.sum() <= len(z[f"prompt_{sd}"]) + len(z[f"output_{sd}"]) + len(bias)

@@ -39,6 +39,11 @@ class FakeRunner:
         return np.array([t + 1 if temperature[i] > 0 else t for i, t in enumerate(self.last)], dtype=np.int32)
 
 
+    def adjust_last(self, rows):
+        """Records the rows the engine wants adjusted (None = untouched)."""
+        snap = [None if r is None else dict(r, prompt=list(r["prompt"]), output=list(r["output"])) for r in rows]
+        self.adjust_calls = getattr(self, "adjust_calls", []) + [snap]
+
     def logprobs_last(self, token_ids, n_top=0):
         """logprob of the chosen token = -0.25; alternatives = the next token ids with -1, -2, ..."""
         n = len(token_ids)
@@ -136,8 +141,7 @@ def test_validation_and_errors(client):
     assert client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "use_beam_search": True}).status_code == 400
 
 
-@pytest.mark.parametrize("field,value", [("frequency_penalty", 0.5), ("presence_penalty", -1.0), ("repetition_penalty", 1.2),
-                                         ("logit_bias", {"17": 5.0}), ("guided_json", {"type": "object"}),
+@pytest.mark.parametrize("field,value", [("guided_json", {"type": "object"}),
                                          ("guided_regex", "a+"), ("guided_choice", ["a", "b"]), ("guided_grammar", "root ::= 'a'"),
                                          ("response_format", {"type": "json_object"}), ("length_penalty", 2.0)])
 def test_fields_the_backend_does_not_implement_get_a_400_not_a_silent_200(client, field, value):
@@ -147,8 +151,36 @@ def test_fields_the_backend_does_not_implement_get_a_400_not_a_silent_200(client
         assert r.status_code == 400 and r.json()["object"] == "error" and field in r.json()["message"], (path, r.text)
     # the defaults of the same fields are fine
     ok = {"frequency_penalty": 0.0, "presence_penalty": 0, "repetition_penalty": 1.0, "logit_bias": {}, "length_penalty": 1.0,
-          "response_format": {"type": "text"}}
+          "response_format": {"type": "text"}, "guided_json": None}
     r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "max_tokens": 2, "prompt": "x", **ok})
+    assert r.status_code == 200
+
+
+def test_penalties_and_logit_bias_reach_the_device_and_are_validated(client):
+    """docs/api-spec.yaml:275-311,397: frequency_penalty, presence_penalty, logit_bias (and vLLM's repetition_penalty) are
+    applied on the device to the step's logits before the token is chosen: the engine hands the runner each request's
+    own history and table once per step, then takes every row's token from the sampler (also greedy rows: the step's
+    own argmax predates the adjustment).  Out-of-range values and the combination with logprobs are 400s."""
+    fr = client.app.state.engine_loop.engine.runner
+    base = {"model": MODEL, "prompt": "hello", "max_tokens": 3, "temperature": 0}
+    r = client.post("/v1/completions", json={**base, "frequency_penalty": 0.5, "presence_penalty": -1.0, "repetition_penalty": 1.2,
+                                             "logit_bias": {"17": 5.0, "300": -100}})
+    assert r.status_code == 200, r.text
+    assert len(fr.adjust_calls) == 3 and len(fr.sample_calls) == 3          # once per generated token
+    row = fr.adjust_calls[-1][0]
+    ids = client.tok.encode("hello")
+    assert row["prompt"] == ids and len(row["output"]) == 2 and row["bias"] == {17: 5.0, 300: -100.0}
+    assert (row["rep"], row["freq"], row["pres"]) == (1.2, 0.5, -1.0)
+    assert fr.sample_calls[-1]["temperature"] == [0.0]
+    n = len(fr.adjust_calls)
+    assert client.post("/v1/completions", json=base).status_code == 200
+    assert len(fr.adjust_calls) == n, "a request without penalties must not pay for the adjustment"
+    for bad in ({"frequency_penalty": 2.5}, {"presence_penalty": -3}, {"repetition_penalty": 0}, {"logit_bias": {"abc": 1}},
+                {"logit_bias": {"99999": 1}}, {"logit_bias": {"5": 101}}, {"logit_bias": {"5": 1}, "logprobs": 2}):
+        r = client.post("/v1/completions", json={**base, **bad})
+        assert r.status_code == 400 and r.json()["object"] == "error", (bad, r.text)
+    r = client.post("/v1/chat/completions", json={"model": MODEL, "messages": [{"role": "user", "content": "x"}], "max_tokens": 2,
+                                                  "temperature": 0, "presence_penalty": 0.5})
     assert r.status_code == 200
 
 

@@ -141,6 +141,11 @@ def test_tp2_serving_executor_generates_oracle_tokens():
                 assert top[0][1] == top[1][1], f"top_k=1 left the argmax at step {i} without a tie"
                 break
         assert all(0 <= t < cfg.vocab for t in a[0].output_ids)
+        # logit_bias / penalties are applied shard by shard on every rank: a +100 bias forces its token on whichever rank
+        # owns it (one id per vocabulary shard), and a penalised request still runs next to an untouched one
+        c = run([dict(logit_bias={5: 100.0}), dict(logit_bias={cfg.vocab - 3: 100.0}, repetition_penalty=1.4), dict()])
+        assert c[0].output_ids == [5] * 8 and c[1].output_ids == [cfg.vocab - 3] * 8
+        assert c[2].output_ids == b[2].output_ids
         for tok, (lp, top) in zip(a[2].output_ids, a[2].logprob_data):
             assert top[0][0] == tok and abs(top[0][1] - lp) < 1e-6 and lp <= 0
     finally:
