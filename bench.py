@@ -38,7 +38,7 @@ sys.path.insert(0, ROOT)
 PKG = "enterprise-inference_b200"
 
 OUT_LEN = {"llama8b-bs64": 256, "llama8b-bs1": 128, "llama8b-ctx32k": 64, "llama70b-tp": 256, "llama70b-tp-bs1": 128,
-           "qwen32b-tp": 256, "tiny": 16}   # generated tokens per request: a finished request is replaced by a new one
+           "qwen32b-tp": 256, "llama70b-shard8": 256, "llama70b-shard8-bs1": 128, "tiny": 16}   # generated tokens per request: a finished request is replaced by a new one
 
 WORKLOADS = {
     # name: (model, batch, ctx_start, description)
@@ -49,6 +49,8 @@ WORKLOADS = {
     "llama70b-tp": ("llama-3.1-70b", 64, 512, "Llama-3.1-70B-Instruct bf16 decode, TP=N, batch 64 (configs[4])"),
     "llama70b-tp-bs1": ("llama-3.1-70b", 1, 128, "Llama-3.1-70B-Instruct bf16 decode, TP=N, batch 1, 128-in/128-out (configs[4])"),
     "qwen32b-tp": ("qwen2-32b", 32, 512, "DeepSeek-R1-Distill-Qwen-32B bf16 decode, TP=N, batch 32 (configs[3])"),
+    "llama70b-shard8": ("llama-3.1-70b-tp8-shard", 64, 512, "one rank's share of Llama-3.1-70B at TP8 on one GPU, no collectives, batch 64 (profiling)"),
+    "llama70b-shard8-bs1": ("llama-3.1-70b-tp8-shard", 1, 128, "one rank's share of Llama-3.1-70B at TP8 on one GPU, no collectives, batch 1 (profiling)"),
     "tiny": ("tiny", 4, 16, "tiny config (self-test)"),
 }
 KV_BLOCK = 128

@@ -59,6 +59,11 @@ class ModelConfig:
 
 MODELS: Dict[str, ModelConfig] = {
     "tiny": ModelConfig(),
+    # ONE rank's share of Llama-3.1-70B at tensor-parallel 8 as a model of its own (8 of 64 q heads, 1 of 8 kv heads, 1/8 of
+    # the MLP and of the vocabulary, full hidden size): the kernels of a TP8 step minus its collectives, for single-GPU
+    # profiling (ncu must not wrap a multi-rank command)
+    "llama-3.1-70b-tp8-shard": ModelConfig(name="llama-3.1-70b-tp8-shard", hidden=8192, n_layers=80, n_q_heads=8, n_kv_heads=1,
+                                           intermediate=3584, vocab=16032, max_pos=131072),
     # the 70B head ratio (G = 8) over 8 kv heads on a small body: shards over 2, 4 and 8 tensor-parallel ranks
     "tiny-g8x8": ModelConfig(name="tiny-g8x8", hidden=1024, n_layers=2, n_q_heads=64, n_kv_heads=8, intermediate=4096,
                              vocab=4096),

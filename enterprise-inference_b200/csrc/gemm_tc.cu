@@ -775,6 +775,8 @@ Plan make_plan(int T, int n_out, int k) {
     s = (slots + tiles / 2) / tiles;                  // nearest to one wave (rounding down instead: 3 % slower at batch 1)
     s = min(s, max(pl.n_kblocks / min_kb, 1));        // at least min_kb K blocks (64 KiB of W each) per split
     s = max(1, min(s, 32));
+    static const int cap_env = getenv("B200_TC_MAX_SPLIT") ? atoi(getenv("B200_TC_MAX_SPLIT")) : 0;   // experiment
+    if (cap_env > 0) s = min(s, cap_env);
   }
   pl.splits = s;
   return pl;
