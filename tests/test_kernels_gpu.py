@@ -118,6 +118,18 @@ def test_linear_tcgen05(lib, abi, T, n_out, k, bias):
     assert not ws[:65536].any(), "split-K tickets must be zero again after the launch"
 
 
+def test_linear_global_split_k_path_in_a_fresh_process():
+    """B200_TC_CLUSTER=0 (read once per process) keeps the split-K partials in the global workspace with a last-CTA
+    ticket instead of reducing through DSMEM inside a cluster: the A/B path of DESIGN.md §4, kept correct by this run of
+    the linear test's split shapes in a child process."""
+    import subprocess, sys
+    env = dict(os.environ, B200_TC_CLUSTER="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", os.path.abspath(__file__), "-k",
+                        "test_linear_tcgen05 and (64-6144-4096 or 256-512-4096 or 64-4096-14336 or 1-1024-4096)"],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and " passed" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def test_linear_tcgen05_matches_gemv_bitwise_up_to_order(lib, abi):
     """Both linear paths implement R2 (fp32 accumulate, one rounding): they may differ only by
     summation order."""
