@@ -222,3 +222,25 @@ def test_adjust_logits_equals_vllm_penalties_and_logit_bias():
         assert torch.equal(got, want), f"case {sd}: {(got != want).sum()} logits differ, max {(got - want).abs().max():.3e}"
         changed = (want != logits.float())
         assert changed.any() and changed.sum() <= len(z[f"prompt_{sd}"]) + len(z[f"output_{sd}"]) + len(bias)
+
+
+def test_oracle_mlp_and_norm_against_vllm_modules():
+    """One level above the operator pins: vLLM's own LlamaMLP and RMSNorm MODULES run on the host
+    (tools/make_vllm_module_golden.py) against the oracle's layer pieces on the same weights.  The norm is bit-exact; the
+    MLP may differ by the summation order of the host's bf16 GEMM from the oracle's fp32 GEMM (R2 leaves it free):
+    <= 1 bf16 ulp on <= 1 % of the outputs (bit-equal on the box that made the fixture)."""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "vllm_modules.npz"))
+    for tag, h, inter, T in (("a", 512, 1024, 5), ("b", 1024, 2048, 17), ("c", 640, 1536, 3)):
+        g = torch.Generator().manual_seed(h + T)      # the generator's stream: gate_up, down, x, norm weight, residual
+        gu = (0.02 * torch.randn(2 * inter, h, generator=g)).to(torch.bfloat16)
+        down = (0.02 * torch.randn(h, inter, generator=g)).to(torch.bfloat16)
+        x = torch.randn(T, h, generator=g).to(torch.bfloat16)
+        nw = (1 + 0.1 * torch.randn(h, generator=g)).to(torch.bfloat16)
+        res = torch.randn(T, h, generator=g).to(torch.bfloat16)
+        assert int(gu.view(torch.int16).long().sum() + x.view(torch.int16).long().sum()) == int(z[f"mlp_{tag}_digest"]), "RNG stream drifted"
+        got, want = O.linear(O.silu_mul(O.linear(x, gu)), down).float(), _bf(z[f"mlp_{tag}_y"]).float()
+        d = (got - want).abs()
+        ulp = want.abs().clamp_min(2.0 ** -126).log2().floor().exp2() * 2.0 ** -7
+        assert (d <= torch.maximum(ulp, torch.tensor(2.0 ** -12))).all() and float((d > 0).float().mean()) <= 0.01, tag
+        y, r = O.add_rms_norm(x, res, nw, 1e-5)
+        assert torch.equal(y, _bf(z[f"norm_{tag}_y"])) and torch.equal(r, _bf(z[f"norm_{tag}_r"])), tag
