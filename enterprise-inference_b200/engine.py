@@ -188,26 +188,29 @@ class Scheduler:
         running and newly admitted sequences until the token budget is spent."""
         budget = self.max_tokens
         out: List[Scheduled] = []
+        bs = self.blocks.block_size
         # running: decode or continue prefill
         for req in list(self.running):
             if budget == 0:
                 break
             if req.row < 0:               # preempted earlier in this pass
                 continue
-            remaining = req.n_total - req.n_computed
-            n_new = min(remaining, budget)
-            if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
-                # preempt the youngest running request (recompute later), vLLM's default policy
-                victim = self.running[-1]
-                if victim is req and len(self.running) == 1:
-                    self._fail(req, "the sequence no longer fits the KV cache")   # add() bounds this; belt and braces
-                    continue
-                self._preempt(victim)
-                if victim is req:
-                    continue
+            remaining = len(req.prompt_ids) + len(req.output_ids) - req.n_computed
+            n_new = remaining if remaining < budget else budget
+            # the common decode row stays inside its last block: no allocator call at all
+            if req.n_computed + n_new > len(req.block_table) * bs:
                 if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
-                    continue
-            self._grow(req, req.n_computed + n_new)
+                    # preempt the youngest running request (recompute later), vLLM's default policy
+                    victim = self.running[-1]
+                    if victim is req and len(self.running) == 1:
+                        self._fail(req, "the sequence no longer fits the KV cache")   # add() bounds this; belt and braces
+                        continue
+                    self._preempt(victim)
+                    if victim is req:
+                        continue
+                    if not self.blocks.can_grow(req.block_table, req.n_computed + n_new):
+                        continue
+                self._grow(req, req.n_computed + n_new)
             out.append(Scheduled(req, n_new, n_new == remaining))
             budget -= n_new
         # admit
