@@ -775,8 +775,12 @@ Plan make_plan(int T, int n_out, int k) {
     s = (slots + tiles / 2) / tiles;                  // nearest to one wave (rounding down instead: 3 % slower at batch 1)
     s = min(s, max(pl.n_kblocks / min_kb, 1));        // at least min_kb K blocks (64 KiB of W each) per split
     s = max(1, min(s, 32));
-    static const int cap_env = getenv("B200_TC_MAX_SPLIT") ? atoi(getenv("B200_TC_MAX_SPLIT")) : 0;   // experiment
-    if (cap_env > 0) s = min(s, cap_env);
+    // Never more splits than a cluster can reduce through DSMEM (8): the global-memory split-K (partials + tickets)
+    // that larger counts fall back to is far slower — one TP8 rank's share of 70B, whose 10 QKV slabs were cut 15 ways:
+    // 8.41 ms/step at batch 64 against 7.05 with 8 splits, 5.11 against 4.94 at batch 1.  (Clusters of 16 through the
+    // non-portable size: 4.92 / 7.25 ms, no better.)  B200_TC_CLUSTER=0 still reaches the global path for A/B runs.
+    static const int cluster_env = getenv("B200_TC_CLUSTER") ? atoi(getenv("B200_TC_CLUSTER")) : 1;
+    if (cluster_env) s = min(s, 8);
   }
   pl.splits = s;
   return pl;
