@@ -347,7 +347,9 @@ void attn_split_plan_tc(int T, int hkv, int max_ctx, int* n_splits, int* tiles_p
   const int64_t base = max((int64_t)T * hkv, (int64_t)1);
   int s = 1;
   if (base < 2 * kNumSMs) {   // enough rows x kv heads already: splitting only adds partials and a merge launch
-    const int64_t chunk = max((int64_t)4, (int64_t)tiles * base / (8 * kNumSMs));   // >= 512 tokens per item
+    // >= 1024 tokens per item: with 512, 64 rows x 1 kv head at a context of 530 (one TP8 rank of 70B; the plan sees the
+    // power-of-two bucket 1024) were cut into a 4-tile and a 1-tile item plus a merge launch
+    const int64_t chunk = max((int64_t)8, (int64_t)tiles * base / (8 * kNumSMs));
     s = (int)min((int64_t)64, (tiles + chunk - 1) / chunk);
   }
   s = max(1, min(s, tiles));
