@@ -14,6 +14,8 @@ lib = abi.lib()
 BF = torch.bfloat16
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 shapes = [("qkv", 6144, 4096), ("o", 4096, 4096), ("down", 4096, 14336)]
+if len(sys.argv) > 2:      # python tools/linear_ncu.py 64 o   -> that shape only (ncu -k regex:linear_tc_kernel -s 4 -c 1)
+    shapes = [sh for sh in shapes if sh[0] == sys.argv[2]]
 copies = 6
 W = {n: [torch.randn(no, k, device="cuda", dtype=BF) * 0.02 for _ in range(copies)] for n, no, k in shapes}
 X = {n: torch.randn(T, k, device="cuda", dtype=BF) for n, no, k in shapes}
