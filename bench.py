@@ -13,7 +13,8 @@ replicas (weak scaling, no data-path collective).
 Printed line (rank 0): metric/value/unit per the driver contract plus
   roofline      dominant kernel's achieved HBM GB/s (CUDA events, live) vs MEASURED_PEAKS.json
   cpu_baseline  the oracle (CPU port of the reference image's algorithm) timed on this host
-  e2e           same metric through the engine API with pinned HOST buffers (H2D + step + D2H)
+  e2e           same metric through the engine API with pinned HOST buffers (every step: H2D of its metadata, the
+                step, D2H of its tokens; the engine enqueues step n+1 before it reads step n, engine.py)
   also          (default workload, N = 1) the other single-GPU configs of BASELINE.json, a few dozen steps each:
                 8B batch 1 (configs[0], the north_star target) and 8B batch 8 at 32 k context (configs[2])
   tp            (default workload) the tensor-parallel path at TP = N: a parity check of the sharded step against

@@ -734,6 +734,9 @@ struct StepArgs {
   int32_t* out_tokens;
   void* out_logits;
   int n_seqs = 0;   // sequences in the step when the caller knows it (host-buffer entry), else 0
+  // host-buffer entry: the tokens the previous step left in the ctx; an id -(j+1) means "row j of those"
+  const int32_t* prev_tokens = nullptr;
+  int n_prev = 0;
 };
 
 static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
@@ -783,9 +786,9 @@ static int enqueue_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
   }
   const __nv_bfloat16* normed = c->normed;   // where the current normed rows are (the two-shot all-reduce delivers them elsewhere)
   if (fnorm)
-    STEP(embed_stream(a.ids, c->embed, c->sres, c->ssq, T, h, m.vocab, s));
+    STEP(embed_stream(a.ids, c->embed, c->sres, c->ssq, T, h, m.vocab, s, a.prev_tokens, a.n_prev));
   else
-    STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s));
+    STEP(embed(a.ids, c->embed, c->res, T, h, m.vocab, s, a.prev_tokens, a.n_prev));
   for (int l = 0; l < m.n_layers; ++l) {
     const LayerW& L = c->layers[l];
     if (!fnorm) {
@@ -944,7 +947,7 @@ static int run_step(b200_ctx* c, const StepArgs& a, cudaStream_t s) {
                       (uint64_t)a.block_table, (uint64_t)a.row_to_seq, (uint64_t)a.ctx_lens,
                       (uint64_t)a.logit_rows,  (uint64_t)a.out_tokens, (uint64_t)a.out_logits,
                       (uint64_t)a.bt_stride,   (uint64_t)a.T,          (uint64_t)pow2_bucket(a.max_ctx),
-                      (uint64_t)a.R,           (uint64_t)launch_opts().pdl, (uint64_t)a.n_seqs, 0ull}};
+                      (uint64_t)a.R,           (uint64_t)launch_opts().pdl, (uint64_t)a.n_seqs, (uint64_t)a.prev_tokens}};
   auto it = c->graph_cache.find(key);
   if (it == c->graph_cache.end()) {
     StepArgs b = a;
@@ -1119,6 +1122,8 @@ extern "C" int b200_decode_step_host(b200_ctx* c, const int32_t* host_packed, in
   StepArgs a{d, d + T, d + 2 * T, d + 5 * T + n_logit_rows, d + 4 * T, d + 3 * T, d + 5 * T, bt_stride, n_tokens,
              max_ctx_len, n_logit_rows, c->d_tokens, nullptr};
   a.n_seqs = n_seqs;
+  a.prev_tokens = c->d_tokens;
+  a.n_prev = c->max_logit_rows;
   int rc = run_step(c, a, s);
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(host_out_token_ids, c->d_tokens, (size_t)n_logit_rows * 4, cudaMemcpyDeviceToHost, s));

@@ -185,12 +185,13 @@ int linear_tc(const __nv_bfloat16* x, int64_t ldx, const __nv_bfloat16* w, const
 int rmsnorm(const __nv_bfloat16* x, __nv_bfloat16* res, const __nv_bfloat16* w, __nv_bfloat16* y, int T,
             int hidden, float eps, cudaStream_t s);
 // fp32 residual stream (RMSNorm folded into the linears): embedding rows -> sres/ssq; stream rows -> normed bf16
+// (prev, n_prev: tokens a negative id -(j+1) refers to, see elementwise.cu; nullptr = no such ids)
 int embed_stream(const int32_t* ids, const __nv_bfloat16* table, float* sres, float* ssq, int T, int hidden, int vocab,
-                 cudaStream_t s);
+                 cudaStream_t s, const int32_t* prev = nullptr, int n_prev = 0);
 int rmsnorm_stream(const float* sres, const float* ssq, const int32_t* rows, const __nv_bfloat16* w, __nv_bfloat16* y,
                    int R, int hidden, float eps, cudaStream_t s);
 int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, int T, int hidden, int vocab,
-          cudaStream_t s);
+          cudaStream_t s, const int32_t* prev = nullptr, int n_prev = 0);
 int rope_kv_append(__nv_bfloat16* qkv, const int32_t* positions, const int32_t* slots,
                    const __nv_bfloat16* cos_sin, __nv_bfloat16* kc, __nv_bfloat16* vc, int T, int hq,
                    int hkv, int block_size, cudaStream_t s);

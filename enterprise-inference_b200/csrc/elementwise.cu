@@ -11,14 +11,20 @@ namespace {
 // ---------------------------------------------------------------------------------------
 // (a1) embedding
 // ---------------------------------------------------------------------------------------
+// A negative id -(j+1) stands for "the token the previous step chose for its logit row j", still on the device
+// (prev): a host that schedules step n+1 while step n runs does not know that token yet.
+__device__ __forceinline__ int resolve_id(int id, int vocab, const int32_t* prev, int n_prev) {
+  if (id < 0 && prev != nullptr && -id - 1 < n_prev) id = prev[-id - 1];
+  return id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);  // ids are validated on the host; clamp, never fault
+}
+
 __global__ void __launch_bounds__(128)
 embed_kernel(const int32_t* __restrict__ ids, const __nv_bfloat16* __restrict__ table,
-             __nv_bfloat16* __restrict__ out, int hidden, int vocab) {
+             __nv_bfloat16* __restrict__ out, int hidden, int vocab, const int32_t* prev, int n_prev) {
   pdl_wait();
   pdl_launch_dependents();
   const int t = blockIdx.x;
-  int id = ids[t];
-  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);  // ids are validated on the host; clamp, never fault
+  const int id = resolve_id(ids[t], vocab, prev, n_prev);
   const uint4* src = reinterpret_cast<const uint4*>(table + (int64_t)id * hidden);
   uint4* dst = reinterpret_cast<uint4*>(out + (int64_t)t * hidden);
   for (int c = threadIdx.x; c < hidden / 8; c += blockDim.x) dst[c] = __ldg(src + c);
@@ -97,13 +103,12 @@ rmsnorm_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* res, const __
 // Embedding rows into the fp32 residual stream: sres[t] = float(table[ids[t]]), ssq[t][slab] in the order above.
 __global__ void __launch_bounds__(kNormThreads)
 embed_stream_kernel(const int32_t* __restrict__ ids, const __nv_bfloat16* __restrict__ table, float* __restrict__ sres,
-                    float* __restrict__ ssq, int hidden, int vocab) {
+                    float* __restrict__ ssq, int hidden, int vocab, const int32_t* prev, int n_prev) {
   pdl_wait();
   pdl_launch_dependents();
   const int t = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nslab = hidden >> 7;
-  int id = ids[t];
-  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const int id = resolve_id(ids[t], vocab, prev, n_prev);
   const uint2* src = reinterpret_cast<const uint2*>(table + (int64_t)id * hidden);
   float4* dst = reinterpret_cast<float4*>(sres + (int64_t)t * hidden);
   for (int slab = warp; slab < nslab; slab += kNormWarps) {
@@ -302,10 +307,10 @@ int advance_rows(int32_t* ids, int32_t* positions, int32_t* slots, int32_t* ctx_
 }
 
 int embed(const int32_t* ids, const __nv_bfloat16* table, __nv_bfloat16* out, int T, int hidden, int vocab,
-          cudaStream_t s) {
+          cudaStream_t s, const int32_t* prev, int n_prev) {
   B200_REQUIRE(hidden % 8 == 0, B200_ERR_UNSUPPORTED, "embed: hidden %% 8 != 0");
   if (T == 0) return B200_OK;
-  B200_CUDA(launch(embed_kernel, dim3(T), dim3(128), 0, s, ids, table, out, hidden, vocab));
+  B200_CUDA(launch(embed_kernel, dim3(T), dim3(128), 0, s, ids, table, out, hidden, vocab, prev, n_prev));
   return B200_OK;
 }
 
@@ -322,10 +327,10 @@ int rmsnorm(const __nv_bfloat16* x, __nv_bfloat16* res, const __nv_bfloat16* w, 
 }
 
 int embed_stream(const int32_t* ids, const __nv_bfloat16* table, float* sres, float* ssq, int T, int hidden, int vocab,
-                 cudaStream_t s) {
+                 cudaStream_t s, const int32_t* prev, int n_prev) {
   B200_REQUIRE(hidden % 128 == 0, B200_ERR_UNSUPPORTED, "embed_stream: hidden %% 128 != 0");
   if (T == 0) return B200_OK;
-  B200_CUDA(launch(embed_stream_kernel, dim3(T), dim3(kNormThreads), 0, s, ids, table, sres, ssq, hidden, vocab));
+  B200_CUDA(launch(embed_stream_kernel, dim3(T), dim3(kNormThreads), 0, s, ids, table, sres, ssq, hidden, vocab, prev, n_prev));
   return B200_OK;
 }
 

@@ -88,22 +88,32 @@ class Request:
     token_times: List[float] = field(default_factory=list)
     logprob_data: List[tuple] = field(default_factory=list)   # per emitted token: (logprob, [(id, logprob), ...])
     error: Optional[str] = None         # set when the engine failed this request (finish_reason "error")
+    # a step that will produce this request's next token has been enqueued but not read back: the token counts as
+    # present for scheduling, and its id is the (negative) code the device resolves (-(j+1): logit row j of that step)
+    pending: int = 0
 
     @property
     def adjusts(self) -> bool:
         return bool(self.logit_bias) or self.repetition_penalty != 1.0 or self.frequency_penalty != 0.0 or self.presence_penalty != 0.0
 
     @property
+    def plain(self) -> bool:
+        """The step's own argmax is the token: nothing has to run on the host between the step and the next one."""
+        return self.temperature <= 0.0 and self.logprobs is None and not self.adjusts
+
+    @property
     def all_ids(self) -> List[int]:
-        return self.prompt_ids + self.output_ids
+        return self.prompt_ids + self.output_ids + ([self.pending] if self.pending else [])
 
     @property
     def n_total(self) -> int:
-        return len(self.prompt_ids) + len(self.output_ids)
+        return len(self.prompt_ids) + len(self.output_ids) + (1 if self.pending else 0)
 
     def token_at(self, p: int) -> int:
         n = len(self.prompt_ids)
-        return self.prompt_ids[p] if p < n else self.output_ids[p - n]
+        if p < n:
+            return self.prompt_ids[p]
+        return self.output_ids[p - n] if p - n < len(self.output_ids) else self.pending
 
 
 @dataclass
@@ -163,6 +173,7 @@ class Scheduler:
         if req in self.waiting:
             self.waiting.remove(req)
         self._release(req)
+        req.pending = 0
         req.finished, req.finish_reason, req.error, req.finish_time = True, "error", why, time.monotonic()
         self.failed.append(req)
 
@@ -177,6 +188,7 @@ class Scheduler:
         else:
             return False
         self._release(req)
+        req.pending = 0
         req.finished, req.finish_reason, req.finish_time = True, "abort", time.monotonic()
         return True
 
@@ -195,7 +207,9 @@ class Scheduler:
                 break
             if req.row < 0:               # preempted earlier in this pass
                 continue
-            remaining = len(req.prompt_ids) + len(req.output_ids) - req.n_computed
+            if req.pending and len(req.output_ids) + 1 >= req.max_tokens:
+                continue                  # its last token is in flight: nothing more to compute
+            remaining = req.n_total - req.n_computed
             n_new = remaining if remaining < budget else budget
             # the common decode row stays inside its last block: no allocator call at all
             if req.n_computed + n_new > len(req.block_table) * bs:
@@ -263,17 +277,33 @@ class Scheduler:
             b.block_tables.append(r.block_table)
         return b
 
-    def commit(self, sched: List[Scheduled], sampled: List[int], now: Optional[float] = None) -> List[Request]:
-        """Apply a step's results; returns the requests that finished."""
+    def mark_launched(self, sched: List[Scheduled]) -> None:
+        """The step has been enqueued: its rows count as computed, and every sampling row owes one token (code -(k+1):
+        logit row k of that step) that resolve() fills in."""
+        k = 0
+        for s in sched:
+            r = s.req
+            if s.samples:
+                k += 1
+            if r.finished:      # finished (stop token, abort) while an earlier step was in flight: a wasted row
+                continue
+            r.n_computed += s.n_new
+            if s.samples:
+                r.pending = -k
+
+    def resolve(self, sched: List[Scheduled], sampled: List[int], now: Optional[float] = None) -> List[Request]:
+        """Apply a launched step's tokens; returns the requests that finished."""
         now = time.monotonic() if now is None else now
         done, k = [], 0
         for s in sched:
-            r = s.req
-            r.n_computed += s.n_new
             if not s.samples:
                 continue
             tok = int(sampled[k])
             k += 1
+            r = s.req
+            if r.finished:
+                continue
+            r.pending = 0
             r.output_ids.append(tok)
             r.token_times.append(now)
             if r.first_token_time is None:
@@ -289,10 +319,18 @@ class Scheduler:
                 reason = "length"
             if reason:
                 r.finished, r.finish_reason, r.finish_time = True, reason, now
-                self.running.remove(r)
+                if r in self.running:
+                    self.running.remove(r)
+                elif r in self.waiting:      # preempted while its token was in flight
+                    self.waiting.remove(r)
                 self._release(r)
                 done.append(r)
         return done
+
+    def commit(self, sched: List[Scheduled], sampled: List[int], now: Optional[float] = None) -> List[Request]:
+        """mark_launched + resolve in one go (the synchronous step)."""
+        self.mark_launched(sched)
+        return self.resolve(sched, sampled, now)
 
 
 class LLMEngine:
@@ -306,6 +344,14 @@ class LLMEngine:
                                    max_num_seqs=max_num_seqs, max_model_len=min(max_model_len, runner.max_model_len))
         self.requests: Dict[str, Request] = {}
         self.steps = 0
+        # Overlap: while every live request is `plain` (greedy, no logprobs, no logit adjustment) the engine enqueues
+        # step n+1 before it reads step n's tokens -- the rows' ids are codes the device resolves from the tokens step n
+        # left there -- so scheduling, packing and the token read-back of one step hide behind the next one
+        # (vLLM's async scheduling).  A runner without step_async (the TP leader, test doubles) keeps the
+        # synchronous step; B200_ENGINE_ASYNC=0 forces it.
+        self.overlap = hasattr(runner, "step_async") and os.environ.get("B200_ENGINE_ASYNC", "1") != "0"
+        self._special: set = set()       # ids of the live requests that are not plain
+        self._inflight = None            # (scheduled rows, runner handle) of the enqueued, unread step
 
     def add_request(self, req: Request) -> None:
         if req.temperature > 0.0 and req.seed is None:
@@ -314,13 +360,22 @@ class LLMEngine:
             req.seed = int(req.seed) & (2 ** 64 - 1)      # any Python int (vLLM takes int64 seeds, negatives too): 64 bits of key
         req.top_k = min(max(int(req.top_k), 0), self.runner.cfg.vocab) if hasattr(self.runner, "cfg") else max(int(req.top_k), 0)
         self.scheduler.add(req)
+        self._remember(req)
+
+    def _remember(self, req: Request) -> None:
         self.requests[req.request_id] = req
+        if not req.plain:
+            self._special.add(req.request_id)
+
+    def _forget(self, request_id: str) -> None:
+        self.requests.pop(request_id, None)
+        self._special.discard(request_id)
 
     def abort_request(self, request_id: str) -> Optional[Request]:
         req = self.requests.get(request_id)
         if req is None or not self.scheduler.abort(req):
             return None
-        self.requests.pop(request_id, None)
+        self._forget(request_id)
         return req
 
     def add_prefilled(self, req: Request, n_computed: int) -> None:
@@ -330,18 +385,47 @@ class LLMEngine:
         self.scheduler._grow(req, max(n_computed, 1))
         req.n_computed = n_computed
         self.scheduler.running.append(req)
-        self.requests[req.request_id] = req
+        self._remember(req)
 
     def has_work(self) -> bool:
-        return self.scheduler.has_work()
+        return self.scheduler.has_work() or self._inflight is not None
 
     def _take_failed(self) -> List[Request]:
         failed, self.scheduler.failed = self.scheduler.failed, []
         for r in failed:
-            self.requests.pop(r.request_id, None)
+            self._forget(r.request_id)
         return failed
 
+    def _resolve_inflight(self) -> List[Request]:
+        sched, handle = self._inflight
+        self._inflight = None
+        toks = self.runner.step_result(handle)          # waits for that step only; a later one keeps running
+        done = self.scheduler.resolve(sched, toks)
+        for r in done:
+            self._forget(r.request_id)
+        return done
+
     def step(self) -> List[Request]:
+        """One engine iteration; returns the requests that finished in it.  In overlap mode an iteration enqueues the
+        next step and then reads the previous one, so a token is reported one call after its step was enqueued (at the
+        same wall-clock time: the read waits for exactly that step)."""
+        if self.overlap and not self._special:
+            sched = self.scheduler.schedule()
+            handle = None
+            if sched:
+                batch = self.scheduler.build_batch(sched)
+                if not len(batch.logit_rows):
+                    batch.logit_rows.append(batch.n_tokens - 1)
+                handle = self.runner.step_async(batch)
+                self.steps += 1
+            done = self._resolve_inflight() if self._inflight is not None else []
+            if sched:
+                self.scheduler.mark_launched(sched)
+                self._inflight = (sched, handle)
+            return done + self._take_failed()
+        if self._inflight is not None:
+            # a request that needs the host between step and token has arrived: finish the step in flight first
+            return self._resolve_inflight() + self._take_failed()
         sched = self.scheduler.schedule()
         if not sched:
             return self._take_failed()
@@ -381,7 +465,7 @@ class LLMEngine:
                     r.logprob_data.append((float(lp[i]), [(int(ids[i, j]), float(tlp[i, j])) for j in range(k)]))
         done = self.scheduler.commit(sched, sampled)
         for r in done:
-            self.requests.pop(r.request_id, None)
+            self._forget(r.request_id)
         return done + self._take_failed()
 
     def generate(self, prompts: List[List[int]], max_tokens: int, ignore_eos: bool = True) -> List[List[int]]:

@@ -90,9 +90,14 @@ class ModelRunner:
 
         self._weights: List[torch.Tensor] = []   # keeps the borrowed device tensors alive
         meta_ints = 6 * max_tokens + max_tokens * self.max_blocks_per_seq
-        self._h_meta = torch.empty(meta_ints, dtype=torch.int32).pin_memory()
+        # two pinned (metadata, tokens) pairs: step_async alternates them, so the host can pack step n+1 while the
+        # copies of step n are still in flight; the synchronous calls use pair 0
+        self._h_meta2 = [torch.empty(meta_ints, dtype=torch.int32).pin_memory() for _ in range(2)]
+        self._h_out2 = [torch.empty(max(max_tokens, 1), dtype=torch.int32).pin_memory() for _ in range(2)]
+        self._done2 = [torch.cuda.Event() for _ in range(2)]
+        self._flip = 0
+        self._h_meta, self._h_out = self._h_meta2[0], self._h_out2[0]
         self._h_meta_np = self._h_meta.numpy()
-        self._h_out = torch.empty(max(max_tokens, 1), dtype=torch.int32).pin_memory()
         self._h_out_np = self._h_out.numpy()
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
@@ -175,12 +180,12 @@ class ModelRunner:
             dist.barrier(group=group)
 
     # ---- one step ---------------------------------------------------------------------------
-    def pack(self, b: StepBatch):
+    def pack(self, b: StepBatch, into: Optional[np.ndarray] = None):
         """Write the dense packed int32 buffer b200_decode_step_host expects into pinned memory."""
         T, R, S = b.n_tokens, len(b.logit_rows), len(b.block_tables)
         tables = b.block_tables
         bt_stride = tables.shape[1] if isinstance(tables, np.ndarray) else max(max(len(r) for r in tables), 1)
-        a = self._h_meta_np
+        a = self._h_meta_np if into is None else into
         a[0:T] = b.ids
         a[T:2 * T] = b.positions
         a[2 * T:3 * T] = b.slots
@@ -211,6 +216,23 @@ class ModelRunner:
         if sync:
             self.stream.synchronize()
         return self._h_out_np[:R]
+
+    def step_async(self, b: StepBatch) -> int:
+        """Enqueue a host-buffer step and return at once; step_result(handle) waits for its tokens.  At most two steps
+        may be outstanding.  Ids of -(j+1) in `b` mean "the token of logit row j of the step enqueued just before"."""
+        k = self._flip
+        self._flip ^= 1
+        T, R, S, bt_stride, n_ints = self.pack(b, self._h_meta2[k].numpy())
+        _abi.check(self.lib.b200_decode_step_host(self.ctx, self._h_meta2[k].data_ptr(), T, S, bt_stride, b.max_ctx, R,
+                                                  self._h_out2[k].data_ptr(), self.stream.cuda_stream))
+        self._done2[k].record(self.stream)
+        self.h2d_bytes_last, self.d2h_bytes_last = n_ints * 4, R * 4
+        return k | (R << 1)
+
+    def step_result(self, handle: int) -> np.ndarray:
+        k, R = handle & 1, handle >> 1
+        self._done2[k].synchronize()
+        return self._h_out2[k].numpy()[:R]
 
     def step_device(self, ids, positions, slots, block_table, ctx_lens, max_ctx, *, row_to_seq=None,
                     logit_rows=None, out_tokens=None, out_logits=None, stream=None):

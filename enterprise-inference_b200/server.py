@@ -250,6 +250,7 @@ class EngineLoop:
         self.engine, self.metrics = engine, metrics
         self.inbox: "queue.Queue" = queue.Queue()
         self.listeners: Dict[str, Any] = {}      # request_id -> (loop, asyncio.Queue)
+        self._sent: Dict[str, int] = {}          # request_id -> output tokens already emitted
         self.alive = True
         self.error: Optional[str] = None
         self.draining = False
@@ -284,6 +285,7 @@ class EngineLoop:
                         req = self.inbox.get(block=not eng.has_work(), timeout=0.05)
                         if isinstance(req, tuple):          # ("abort", request_id)
                             gone = eng.abort_request(req[1])
+                            self._sent.pop(req[1], None)
                             if gone is not None:
                                 self.metrics.finished(gone)
                                 self._emit(gone.request_id, ("done", "abort"))
@@ -298,17 +300,21 @@ class EngineLoop:
                     pass
                 if not eng.has_work():
                     continue
-                before = {r.request_id: len(r.output_ids) for r in eng.scheduler.running}
                 done = eng.step()
                 m = self.metrics
                 m.running.labels(m.m).set(len(eng.scheduler.running))
                 m.waiting.labels(m.m).set(len(eng.scheduler.waiting))
                 m.gpu_cache.labels(m.m).set(eng.blocks.usage)
-                for r in list(eng.scheduler.running) + done:
-                    n0 = before.get(r.request_id, 0)
+                # tokens not yet handed to the listener (a preempted request can receive the token of the step that was
+                # in flight while it sits in `waiting`, so the count is kept per request, not per step)
+                preempted = [r for r in eng.scheduler.waiting if r.output_ids]
+                for r in list(eng.scheduler.running) + preempted + done:
+                    n0 = self._sent.get(r.request_id, 0)
                     if len(r.output_ids) > n0:
                         self._emit(r.request_id, ("tokens", r.output_ids[n0:]))
+                        self._sent[r.request_id] = len(r.output_ids)
                 for r in done:
+                    self._sent.pop(r.request_id, None)
                     m.finished(r)
                     if r.error is not None:             # the scheduler gave up on this one request only
                         self._emit(r.request_id, ("error", r.error))

@@ -138,7 +138,11 @@ B200_API int b200_decode_step(b200_ctx* ctx, const int32_t* ids, const int32_t* 
  *   last n_logit_rows) followed by block_table [n_seqs][bt_stride],
  * copied H2D, the step, and the sampled ids copied D2H into host_out_token_ids.  The copies
  * are enqueued on `stream`; the caller synchronises.  This is the call the serving engine
- * makes every iteration (the `e2e` figure of bench.py). */
+ * makes every iteration (the `e2e` figure of bench.py).
+ * An id of -(j+1) stands for the token the PREVIOUS b200_decode_step_host call on this ctx chose for
+ * its logit row j (it is still on the device): an engine can enqueue step n+1 while step n runs and
+ * read step n's tokens afterwards (vLLM's async scheduling).  host_packed and host_out_token_ids must
+ * stay untouched until their copies have completed, so such an engine alternates two buffers of each. */
 B200_API int b200_decode_step_host(b200_ctx* ctx, const int32_t* host_packed, int32_t n_tokens,
                           int32_t n_seqs, int32_t bt_stride, int32_t max_ctx_len,
                           int32_t n_logit_rows, int32_t* host_out_token_ids, void* stream);

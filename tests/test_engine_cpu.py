@@ -31,6 +31,47 @@ class FakeRunner:
         return np.array(out, dtype=np.int32)
 
 
+class AsyncFakeRunner(FakeRunner):
+    """The same 'model' behind the runner's overlap interface: step_async enqueues (ids of -(j+1) are resolved from the
+    tokens of the step enqueued just before, as the device does), step_result hands the tokens over.  It checks the
+    engine's side of the contract: at most two steps outstanding, results read oldest first."""
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.last = np.zeros(0, dtype=np.int32)
+        self.outstanding = []
+        self.results = {}
+        self.n_async = 0
+        self.n_coded = 0
+
+    def step_async(self, b):
+        ids = np.array(b.ids, dtype=np.int64).copy()
+        for i, t in enumerate(ids):
+            if t < 0:
+                assert -t - 1 < len(self.last), "code refers to a logit row the previous step did not have"
+                ids[i] = self.last[-t - 1]
+                self.n_coded += 1
+        b.ids = ids
+        out = FakeRunner.step(self, b)
+        self.last = out
+        self.n_async += 1
+        h = self.n_async
+        self.outstanding.append(h)
+        assert len(self.outstanding) <= 2, "more than two steps in flight"
+        self.results[h] = out
+        return h
+
+    def step_result(self, h):
+        assert self.outstanding and self.outstanding[0] == h, "results must be read oldest first"
+        self.outstanding.pop(0)
+        return self.results.pop(h)
+
+    def step(self, b):
+        assert not self.outstanding, "a synchronous step while another one is in flight"
+        out = super().step(b)
+        self.last = out
+        return out
+
+
 def expect(prompt, n):
     ids = list(prompt)
     for _ in range(n):
@@ -183,6 +224,112 @@ def test_scheduler_property_any_arrival_pattern_matches_sequential(prompts, max_
     for r, p, n in zip(reqs, prompts, max_new):
         assert r.finished and r.output_ids == expect(p, n)
     assert len(eng.blocks.free) == n_blocks
+
+
+def test_overlap_mode_matches_sequential_and_really_overlaps():
+    """With a runner that has step_async the engine enqueues step n+1 before reading step n: same tokens as the
+    sequential run, decode rows carry device-side token codes, every block comes back."""
+    fr = AsyncFakeRunner(n_blocks=64, block_size=4, max_tokens=16)
+    eng = E.LLMEngine(fr, max_num_batched_tokens=16, max_num_seqs=8, max_model_len=64)
+    assert eng.overlap
+    prompts = [[1, 2, 3], list(range(5, 40)), [7] * 9, [11, 13]]
+    outs = eng.generate(prompts, max_tokens=6)
+    for p, o in zip(prompts, outs):
+        assert o == expect(p, 6)
+    assert len(eng.blocks.free) == 64 and not eng.requests and eng._inflight is None
+    assert fr.n_async == len(fr.batches) and fr.n_coded >= 4 * 4     # every decode row after the first came as a code
+
+
+def test_overlap_mode_preemption_and_unpredicted_stop():
+    fr = AsyncFakeRunner(n_blocks=6, block_size=4, max_tokens=32, max_model_len=32)
+    eng = E.LLMEngine(fr, max_num_batched_tokens=32, max_num_seqs=4, max_model_len=32)
+    prompts = [[3, 1, 4, 1, 5, 9, 2], [2, 7, 1, 8, 2, 8], [1, 6, 1, 8]]
+    outs = eng.generate(prompts, max_tokens=8)
+    for p, o in zip(prompts, outs):
+        assert o == expect(p, 8)
+    assert len(eng.blocks.free) == 6
+    # a stop token the host cannot foresee: the request is already part of the next enqueued step when its stop token is
+    # read; that row is wasted, its token discarded, and the neighbour is unaffected
+    fr = AsyncFakeRunner()
+    eng = E.LLMEngine(fr, max_num_batched_tokens=16, max_num_seqs=4, max_model_len=64)
+    want = expect([1, 2, 3], 10)
+    a = E.Request("a", [1, 2, 3], max_tokens=10, stop_token_ids=(want[3],))
+    b = E.Request("b", [5, 6], max_tokens=10, ignore_eos=True)
+    eng.add_request(a)
+    eng.add_request(b)
+    while eng.has_work():
+        eng.step()
+    assert a.output_ids == want[:4] and a.finish_reason == "stop" and a.pending == 0
+    assert b.output_ids == expect([5, 6], 10) and b.finish_reason == "length"
+    assert len(eng.blocks.free) == fr.n_blocks and not eng.requests
+
+
+def test_overlap_mode_abort_in_flight_and_special_request_drains():
+    fr = AsyncFakeRunner(n_blocks=32)
+    fr.cfg = type("C", (), {"vocab": 97})()
+    fr.sample_last = lambda t, k, p, s, d, min_p=None: fr.last      # 'sampling' = the step's own tokens
+    eng = E.LLMEngine(fr, max_num_batched_tokens=16, max_num_seqs=4, max_model_len=64)
+    a = E.Request("a", [1, 2, 3], max_tokens=12, ignore_eos=True)
+    b = E.Request("b", [4, 5], max_tokens=12, ignore_eos=True)
+    eng.add_request(a)
+    eng.add_request(b)
+    for _ in range(3):
+        eng.step()
+    assert eng._inflight is not None and a.pending < 0
+    gone = eng.abort_request("a")                       # its row of the step in flight is discarded
+    assert gone is a and a.pending == 0 and all(t >= 0 for t in a.output_ids)
+    n_a = len(a.output_ids)
+    eng.step()
+    assert len(a.output_ids) == n_a
+    # a sampling request arrives: the step in flight is read first, then the engine steps synchronously
+    c = E.Request("c", [9, 9], max_tokens=3, temperature=0.5, seed=1, ignore_eos=True)
+    eng.add_request(c)
+    n_async = fr.n_async
+    while not c.finished:
+        eng.step()
+    assert fr.n_async == n_async and eng._inflight is None     # no overlapped step while c was alive
+    while eng.has_work():
+        eng.step()
+    assert fr.n_async > n_async                                 # and overlap again afterwards
+    assert b.output_ids == expect([4, 5], 12) and c.output_ids == expect([9, 9], 3)
+    assert len(eng.blocks.free) == 32 and not eng.requests and not eng._special
+
+
+@settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(
+    prompts=st.lists(st.lists(st.integers(0, 96), min_size=1, max_size=20), min_size=1, max_size=7),
+    max_new=st.lists(st.integers(1, 9), min_size=7, max_size=7),
+    arrivals=st.lists(st.integers(0, 6), min_size=7, max_size=7),
+    stops=st.lists(st.integers(0, 96), min_size=0, max_size=12),
+    n_blocks=st.integers(8, 24), budget=st.sampled_from([4, 8, 16]), max_seqs=st.integers(1, 5),
+)
+def test_overlap_property_any_arrival_pattern_matches_sequential(prompts, max_new, arrivals, stops, n_blocks, budget, max_seqs):
+    """The property above for the overlapped engine, with stop tokens the host cannot foresee thrown in."""
+    bs = 4
+    need = max((len(p) + max_new[i] + bs - 1) // bs for i, p in enumerate(prompts))
+    n_blocks = max(n_blocks, need)
+    fr = AsyncFakeRunner(n_blocks=n_blocks, block_size=bs, max_tokens=budget, max_model_len=64)
+    eng = E.LLMEngine(fr, max_num_batched_tokens=budget, max_num_seqs=max_seqs, max_model_len=64)
+    reqs = [E.Request(f"r{i}", list(p), max_tokens=max_new[i], stop_token_ids=tuple(stops)) for i, p in enumerate(prompts)]
+    pending = sorted(range(len(reqs)), key=lambda i: arrivals[i])
+    step = 0
+    while pending or eng.has_work():
+        while pending and arrivals[pending[0]] <= step:
+            eng.add_request(reqs[pending.pop(0)])
+        if eng.has_work():
+            n_before = len(fr.batches)
+            eng.step()
+            for b in fr.batches[n_before:]:
+                assert b.n_tokens <= budget and len(b.block_tables) <= max_seqs
+            used = [blk for r in eng.scheduler.running for blk in r.block_table]
+            assert len(used) == len(set(used)), "a cache block is owned by two running requests"
+        step += 1
+        assert step < 2000
+    for r, p, n in zip(reqs, prompts, max_new):
+        want = expect(p, n)
+        cut = next((i + 1 for i, t in enumerate(want) if t in stops), n)
+        assert r.finished and r.pending == 0 and r.output_ids == want[:cut]
+    assert len(eng.blocks.free) == n_blocks and eng._inflight is None
 
 
 def test_pack_adjust_builds_one_entry_per_distinct_token():

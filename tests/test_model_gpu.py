@@ -107,6 +107,57 @@ def test_folded_norm_step_is_bit_identical_to_the_unfused_step(name, golden_dir,
 
 
 @pytest.mark.parametrize("name", ["tiny", "tiny-g8"])
+def test_overlapped_engine_steps_give_the_synchronous_tokens(name, golden_dir, monkeypatch):
+    """LLMEngine enqueues step n+1 before it reads step n (ids of the decode rows are codes -(j+1) that the embedding
+    kernel resolves from the tokens step n left on the device; two pinned buffer pairs): the tokens equal those of the
+    synchronous engine (B200_ENGINE_ASYNC=0) exactly, through chunked prefill, staggered arrivals and a stop token the
+    host cannot foresee.  Also the raw contract: a coded step equals the step with the ids spelled out."""
+    g = np.load(f"{golden_dir}/{name}.npz")
+    cfg = O.CONFIGS[name]
+    w = O.make_weights(cfg, seed=int(g["seed"]), norm_jitter=float(g["norm_jitter"]))
+    E, R = pkg("engine"), pkg("runner")
+    prompts = [g["prompt"].tolist()] + [O.make_prompt(cfg, i, n) for i, n in ((1, 5), (2, 130), (3, 64), (4, 17))]
+    outs = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("B200_ENGINE_ASYNC", mode)
+        r = make_runner(cfg, w)
+        eng = E.LLMEngine(r, max_num_batched_tokens=64, max_num_seqs=8, max_model_len=1024)
+        assert eng.overlap == (mode == "1")
+        reqs = [E.Request(f"q{i}", list(p), max_tokens=24 + 3 * i, ignore_eos=True) for i, p in enumerate(prompts)]
+        if "0" in outs:     # second pass: stop request 1 at a token it is known to produce
+            reqs[1].stop_token_ids = (outs["0"][1][7],)
+        for i, q in enumerate(reqs):
+            if i < 3:
+                eng.add_request(q)
+        n = 0
+        while eng.has_work() or n < 4:
+            if n == 3:
+                eng.add_request(reqs[3])
+                eng.add_request(reqs[4])
+            eng.step()
+            n += 1
+        outs[mode] = [q.output_ids for q in reqs]
+        assert len(eng.blocks.free) == r.n_blocks
+        if mode == "1":
+            # raw contract on the same runner: step A (ids known), then step B with codes == step B with ids
+            bs = r.block_size
+            def batch(ids, pos):
+                return R.StepBatch(ids=list(ids), positions=[pos, pos], slots=[0 * bs + pos, 1 * bs + pos], ctx_lens=[pos + 1] * 2,
+                                   row_to_seq=[0, 1], logit_rows=[0, 1], block_tables=[[0], [1]])
+            t0 = r.step_result(r.step_async(batch([5, 9], 0))).tolist()
+            hb = r.step_async(batch([-2, -1], 1))            # row 0 <- token of logit row 1, row 1 <- token of row 0
+            tb = r.step_result(hb).tolist()
+            assert r.step(batch([5, 9], 0)).tolist() == t0
+            assert r.step(batch([t0[1], t0[0]], 1)).tolist() == tb
+        r.close()
+    want = outs["0"]
+    cut = want[1].index(want[1][7]) + 1
+    assert outs["1"][1] == want[1][:cut]
+    for i in (0, 2, 3, 4):
+        assert outs["1"][i] == want[i]
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny-g8"])
 def test_engine_greedy_generation_vs_oracle(name, golden_dir):
     """Free-running greedy through the serving engine (scheduler, block manager, host-buffer step):
     tokens equal the oracle's until the first near-tie; report-and-allow only below MARGIN."""
