@@ -76,6 +76,17 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
@@ -374,61 +385,75 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread), software pipelined: S(n+1) is issued before waiting for P(n).
-    // The tiles of an item (all its runs) form one flat sequence: Q is the same for all of them. =====
-    if (lane == 0) {
+    // ===== MMA issuer, software pipelined: S(n+1) is issued before waiting for P(n).
+    // The tiles of an item (all its runs) form one flat sequence: Q is the same for all of them.
+    // The WHOLE warp walks the loop and waits on the barriers; only the tcgen05.mma / commit instructions are
+    // predicated to one lane.  Everything they consume (descriptors, TMEM addresses) is then warp-uniform by
+    // construction and lives in uniform registers: ~4 instructions per MMA instead of the ~20 (register -> uniform
+    // register broadcast loops) that a single-lane branch costs, on the one thread every tile waits for. =====
+    {
       constexpr uint32_t idesc_qk = make_idesc(0);
       constexpr uint32_t idesc_pv = make_idesc(1);
-      uint32_t q_addr = smem_u32(qs);
+      const bool issuer = elect_one();
+      // descriptor = base | (address >> 4): the base bits are constants, the address part is added per operand
+      const uint64_t desc_k0 = make_desc(smem_u32(kv), 16, 1024);
+      const uint64_t desc_v0 = make_desc(smem_u32(kv), kHalfBytes, 1024);
+      const uint64_t desc_q0 = make_desc(smem_u32(qs), 16, 1024);
+      const uint64_t desc_ph0 = make_desc(smem_u32(p_hi), 16, 1024);
+      const uint64_t desc_pl0 = make_desc(smem_u32(p_lo), 16, 1024);
+      uint64_t desc_q = desc_q0;
       auto issue_s = [&](int n) {
         const int qk = 2 * n, sk = qk % NSLOT;
         mbar_wait(&kv_full[sk], (qk / NSLOT) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(kv + sk * kSlotBytes);
+        const uint64_t dk = desc_k0 + (uint64_t)((sk * kSlotBytes) >> 4);
+        if (issuer) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
-          const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
-          tc_mma(tmem_base + (n & 1) * 16, make_desc(k_addr + ao, 16, 1024), make_desc(q_addr + bo, 16, 1024), idesc_qk,
-                 j ? 1u : 0u);
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
+            const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
+            tc_mma(tmem_base + (n & 1) * 16, dk + (ao >> 4), desc_q + (bo >> 4), idesc_qk, j ? 1u : 0u);
+          }
+          tc_commit(&kv_free[sk]);   // the K slot is free as soon as these MMAs have read it
+          tc_commit(&s_full[n & 1]);
         }
-        tc_commit(&kv_free[sk]);   // the K slot is free as soon as these MMAs have read it
-        tc_commit(&s_full[n & 1]);
+        __syncwarp();
       };
       int n = 0, active = 0;
       Item nxt = first_item();
       if (R > 1 && (int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-        const Item w = nxt;
+        const int nt = __shfl_sync(0xffffffffu, nxt.total_tiles, 0);   // warp-uniform, and known to be
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
-        const int nt = w.total_tiles;
         if (nt == 0) continue;
         mbar_wait(&q_ready[active & 1], (active >> 1) & 1);   // this item's Q is in shared memory
         tc_fence_after();
-        q_addr = smem_u32(qs + (active & 1) * 2 * kSmallTile);
+        desc_q = desc_q0 + (uint64_t)(((active & 1) * 2 * kSmallTile) >> 4);
         issue_s(n);
-        if (nt == 1) tc_commit(&q_free[active & 1]);
+        if (nt == 1 && issuer) tc_commit(&q_free[active & 1]);
         for (int i = 0; i < nt; ++i, ++n) {
           if (i + 1 < nt) {
             issue_s(n + 1);
-            if (i + 2 == nt) tc_commit(&q_free[active & 1]);   // last S of this item issued
+            if (i + 2 == nt && issuer) tc_commit(&q_free[active & 1]);   // last S of this item issued
           }
           const int qv = 2 * n + 1, sv = qv % NSLOT;
           mbar_wait(&kv_full[sv], (qv / NSLOT) & 1);
           mbar_wait(&p_ready[n & 1], (n >> 1) & 1);
           tc_fence_after();
-          const uint32_t v_addr = smem_u32(kv + sv * kSlotBytes);
-          const uint32_t ph = smem_u32(p_hi + (n & 1) * 2 * kSmallTile);
-          const uint32_t pl = smem_u32(p_lo + (n & 1) * 2 * kSmallTile);
+          const uint64_t dv = desc_v0 + (uint64_t)((sv * kSlotBytes) >> 4);
+          const uint64_t dph = desc_ph0 + (uint64_t)(((n & 1) * 2 * kSmallTile) >> 4);
+          const uint64_t dpl = desc_pl0 + (uint64_t)(((n & 1) * 2 * kSmallTile) >> 4);
+          if (issuer) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {  // 16 tokens per step: two 8-token K groups of the MN-major V tile
-            const uint64_t da = make_desc(v_addr + j * 2048, kHalfBytes, 1024);
-            const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
-            tc_mma(tmem_base + 32 + (n & 1) * 16, da, make_desc(ph + bo, 16, 1024), idesc_pv, j ? 1u : 0u);
-            tc_mma(tmem_base + 32 + (n & 1) * 16, da, make_desc(pl + bo, 16, 1024), idesc_pv, 1u);
+            for (int j = 0; j < 8; ++j) {  // 16 tokens per step: two 8-token K groups of the MN-major V tile
+              const uint32_t bo = (j >> 2) * kSmallTile + (j & 3) * 32;
+              tc_mma(tmem_base + 32 + (n & 1) * 16, dv + (uint64_t)((j * 2048) >> 4), dph + (bo >> 4), idesc_pv, j ? 1u : 0u);
+              tc_mma(tmem_base + 32 + (n & 1) * 16, dv + (uint64_t)((j * 2048) >> 4), dpl + (bo >> 4), idesc_pv, 1u);
+            }
+            tc_commit(&kv_free[sv]);  // the V slot is no longer read
+            tc_commit(&o_full[n & 1]);
           }
-          tc_commit(&kv_free[sv]);  // the V slot is no longer read
-          tc_commit(&o_full[n & 1]);
+          __syncwarp();
         }
         ++active;
       }
