@@ -76,17 +76,6 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "elect.sync _|p, 0xffffffff;\n"
-      "selp.u32 %0, 1, 0, p;\n"
-      "}\n"
-      : "=r"(pred));
-  return pred != 0;
-}
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
@@ -352,34 +341,46 @@ paged_attn_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_con
   // stalls the TMA stream.
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    // ===== TMA producer (whole warp in the loop, the TMA instructions predicated to one lane; loop bounds and block
+    // ids are broadcast from lane 0 so that the compiler knows them warp-uniform) =====
+    {
+      const bool issuer = elect_one();
+      pre_tiles = __shfl_sync(0xffffffffu, pre_tiles, 0);
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+      }
       int n = 0;
       Item nxt = first_item();
       if (R > 1 && (int)blockIdx.x < n_items) nxt = get_item(blockIdx.x);
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const Item w = nxt;
         if (it + (int)gridDim.x < n_items) nxt = get_item(it + gridDim.x);
+        const int nrun = __shfl_sync(0xffffffffu, w.nrun, 0);
 #pragma unroll
         for (int u = 0; u < R; ++u) {
-          if (u >= w.nrun) break;
-          for (int i = 0; i < w.run_tiles[u]; ++i, ++n) {
+          if (u >= nrun) break;
+          const int nt = __shfl_sync(0xffffffffu, w.run_tiles[u], 0);
+          for (int i = 0; i < nt; ++i, ++n) {
             const int qk = 2 * n, qv = 2 * n + 1;          // ring sequence numbers of this tile's K and V
             const int sk = qk % NSLOT, sv = qv % NSLOT;
             const int tok0 = (w.tile_begin + i) * kTileTok;
             if (n < pre_tiles) continue;   // requested before the set-up (decode-only steps)
-            const int blk = (u == 0 && i == 0) ? w.blk0 : w.run_bt[u][tok0 / block_size];
+            const int blk = __shfl_sync(0xffffffffu, (u == 0 && i == 0) ? w.blk0 : w.run_bt[u][tok0 / block_size], 0);
             const int row0 = (blk * hkv + w.kvh) * block_size + (tok0 % block_size);
             if (qk >= NSLOT) mbar_wait(&kv_free[sk], ((qk / NSLOT) - 1) & 1);
-            mbar_expect_tx(&kv_full[sk], kSlotBytes);
-            tma_load_2d(kv + sk * kSlotBytes, &map_k, 0, row0, &kv_full[sk]);
-            tma_load_2d(kv + sk * kSlotBytes + kHalfBytes, &map_k, 64, row0, &kv_full[sk]);
+            if (issuer) {
+              mbar_expect_tx(&kv_full[sk], kSlotBytes);
+              tma_load_2d(kv + sk * kSlotBytes, &map_k, 0, row0, &kv_full[sk]);
+              tma_load_2d(kv + sk * kSlotBytes + kHalfBytes, &map_k, 64, row0, &kv_full[sk]);
+            }
             if (qv >= NSLOT) mbar_wait(&kv_free[sv], ((qv / NSLOT) - 1) & 1);
-            mbar_expect_tx(&kv_full[sv], kSlotBytes);
-            tma_load_2d(kv + sv * kSlotBytes, &map_v, 0, row0, &kv_full[sv]);
-            tma_load_2d(kv + sv * kSlotBytes + kHalfBytes, &map_v, 64, row0, &kv_full[sv]);
+            if (issuer) {
+              mbar_expect_tx(&kv_full[sv], kSlotBytes);
+              tma_load_2d(kv + sv * kSlotBytes, &map_v, 0, row0, &kv_full[sv]);
+              tma_load_2d(kv + sv * kSlotBytes + kHalfBytes, &map_v, 64, row0, &kv_full[sv]);
+            }
+            __syncwarp();
           }
         }
       }

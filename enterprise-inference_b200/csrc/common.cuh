@@ -82,6 +82,19 @@ __device__ __forceinline__ float warp_max(float v) {
 // ---- Programmatic dependent launch -------------------------------------------------------
 // Every kernel of the step waits for its predecessor's memory here and lets its successor
 // start its prologue early; with no PDL attribute on the launch both are no-ops.
+// One lane of a converged warp (elect.sync): the predicate for single-thread instructions (tcgen05.mma, TMA) inside
+// warp-uniform code, which keeps their operands in uniform registers.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 

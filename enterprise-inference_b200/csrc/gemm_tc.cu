@@ -401,57 +401,72 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
+    // ===== TMA producer (whole warp in the loop, the TMA instructions predicated to one lane: see the MMA issuer) =====
+    const bool issuer = elect_one();
+    const int pre = min(S, nkb);
+    if (issuer) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
-      const int pre = min(S, nkb);
       // weights first: they do not depend on the producer of x
       for (int i = 0; i < pre; ++i) {
         mbar_expect_tx(&full[i], kTmaBytes);
         tma_load_2d(smem + i * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[i], w_policy);
       }
       tc_trace(p, 1);   // W of the first stages requested
-      pdl_wait();
+    }
+    __syncwarp();
+    pdl_wait();
+    if (issuer) {
       tc_trace(p, 2);   // previous kernel complete
       pdl_launch_dependents();
       if constexpr (!NI) {
         for (int i = 0; i < pre; ++i)
           tma_load_2d(smem + i * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[i], kEvictLast);
       }
-      for (int i = pre; i < nkb; ++i) {
-        const int st = i % S;
-        mbar_wait(&empty[st], ((i / S) - 1) & 1);
+    }
+    __syncwarp();
+    for (int i = pre; i < nkb; ++i) {
+      const int st = i % S;
+      mbar_wait(&empty[st], ((i / S) - 1) & 1);
+      if (issuer) {
         mbar_expect_tx(&full[st], kTmaBytes);
         tma_load_2d(smem + st * kStageBytes, &map_w, (kb0 + i) * kBlockK, m_tile * kBlockM, &full[st], w_policy);
         if constexpr (!NI)
           tma_load_2d(smem + st * kStageBytes + kABytes, &map_x, (kb0 + i) * kBlockK, tok_tile * N, &full[st], kEvictLast);
       }
-    } else {
-      pdl_wait();
+      __syncwarp();
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
+    // ===== MMA issuer: the whole warp walks the loop and waits; only the tcgen05 instructions are predicated to
+    // one lane, so that their operands (descriptors, TMEM address) are warp-uniform by construction and stay in
+    // uniform registers (a single-lane branch pays a register -> uniform-register broadcast loop per MMA) =====
     pdl_wait();
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = make_idesc(N);
+      const bool issuer = elect_one();
+      const uint64_t desc0 = make_desc(smem_u32(smem));
       for (int i = 0; i < nkb; ++i) {
         const int st = i % S;
         mbar_wait(&full[st], (i / S) & 1);
-        if (i == 0) tc_trace(p, 3);   // first stage landed
+        if (i == 0 && issuer) tc_trace(p, 3);   // first stage landed
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + st * kStageBytes);
-        const uint32_t b_addr = a_addr + kABytes;
+        const uint64_t da = desc0 + (uint64_t)((st * kStageBytes) >> 4);
+        const uint64_t db = da + (uint64_t)(kABytes >> 4);
+        if (issuer) {
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          // advancing K inside the 128-byte swizzle span = +32 bytes on the start address
-          tc_mma(tmem_base, make_desc(a_addr + k * kUmmaK * 2), make_desc(b_addr + k * kUmmaK * 2), idesc,
-                 (i | k) ? 1u : 0u);
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // advancing K inside the 128-byte swizzle span = +32 bytes on the start address
+            tc_mma(tmem_base, da + (uint64_t)((k * kUmmaK * 2) >> 4), db + (uint64_t)((k * kUmmaK * 2) >> 4), idesc,
+                   (i | k) ? 1u : 0u);
+          }
+          tc_commit(&empty[st]);  // arrives when the MMAs above have finished reading this stage
         }
-        tc_commit(&empty[st]);  // arrives when the MMAs above have finished reading this stage
+        __syncwarp();
       }
-      tc_trace(p, 4);           // last MMA issued
-      tc_commit(tmem_full);     // accumulator complete
+      if (issuer) {
+        tc_trace(p, 4);           // last MMA issued
+        tc_commit(tmem_full);     // accumulator complete
+      }
     }
   } else {
     // ===== epilogue: 4 warps, TMEM lane quadrant = warp % 4 =====
