@@ -259,86 +259,106 @@ paged_prefill_fa_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_
   };
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    // ===== TMA producer: the whole warp walks the loop, the TMA instructions are predicated to one elected lane and
+    // loop bounds / block ids are broadcast from lane 0, so that the operands stay in uniform registers =====
+    {
+      const bool issuer = elect_one();
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+      }
       int n = 0;
       for (int it = blockIdx.x; it < n_work; it += gridDim.x) {
         PlanItem w;
         int kvh;
         get_work(it, w, kvh);
-        const int nt = (w.ctx_max + kTileTok - 1) / kTileTok;
+        const int nt = __shfl_sync(0xffffffffu, (w.ctx_max + kTileTok - 1) / kTileTok, 0);
         const int32_t* bt = block_table + (int64_t)w.seq * bt_stride;
         for (int i = 0; i < nt; ++i, ++n) {
           const int qk = 2 * n, qv = 2 * n + 1;
           const int sk = qk % kSlots, sv = qv % kSlots;
           const int tok0 = i * kTileTok;
-          const int blk = bt[tok0 / block_size];
+          const int blk = __shfl_sync(0xffffffffu, bt[tok0 / block_size], 0);
           const int row0 = (blk * hkv + kvh) * block_size + (tok0 % block_size);
           if (qk >= kSlots) mbar_wait(&kv_free[sk], ((qk / kSlots) - 1) & 1);
-          mbar_expect_tx(&kv_full[sk], kTileBytes);
-          tma_load_2d(kv + sk * kTileBytes, &map_k, 0, row0, &kv_full[sk]);
-          tma_load_2d(kv + sk * kTileBytes + kHalfBytes, &map_k, 64, row0, &kv_full[sk]);
+          if (issuer) {
+            mbar_expect_tx(&kv_full[sk], kTileBytes);
+            tma_load_2d(kv + sk * kTileBytes, &map_k, 0, row0, &kv_full[sk]);
+            tma_load_2d(kv + sk * kTileBytes + kHalfBytes, &map_k, 64, row0, &kv_full[sk]);
+          }
           if (qv >= kSlots) mbar_wait(&kv_free[sv], ((qv / kSlots) - 1) & 1);
-          mbar_expect_tx(&kv_full[sv], kTileBytes);
-          tma_load_2d(kv + sv * kTileBytes, &map_v, 0, row0, &kv_full[sv]);
-          tma_load_2d(kv + sv * kTileBytes + kHalfBytes, &map_v, 64, row0, &kv_full[sv]);
+          if (issuer) {
+            mbar_expect_tx(&kv_full[sv], kTileBytes);
+            tma_load_2d(kv + sv * kTileBytes, &map_v, 0, row0, &kv_full[sv]);
+            tma_load_2d(kv + sv * kTileBytes + kHalfBytes, &map_v, 64, row0, &kv_full[sv]);
+          }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread): S(n+1) is issued before waiting for P(n) =====
-    if (lane == 0) {
+    // ===== MMA issuer: S(n+1) is issued before waiting for P(n).  Whole warp in the loop, tcgen05 instructions
+    // predicated to one elected lane, descriptors = uniform base + offset =====
+    {
       constexpr uint32_t idesc_qk = fa_idesc(0);
       constexpr uint32_t idesc_pv = fa_idesc(1);
-      const uint32_t q_addr = smem_u32(qs);
-      const uint32_t ph_addr = smem_u32(p_hi), pl_addr = smem_u32(p_lo);
+      const bool issuer = elect_one();
+      const uint64_t desc_q = make_desc(smem_u32(qs), 16, 1024);
+      const uint64_t desc_ph = make_desc(smem_u32(p_hi), 16, 1024);
+      const uint64_t desc_pl = make_desc(smem_u32(p_lo), 16, 1024);
+      const uint64_t desc_k0 = make_desc(smem_u32(kv), 16, 1024);
+      const uint64_t desc_v0 = make_desc(smem_u32(kv), kHalfBytes, 1024);
       auto issue_s = [&](int n) {
         const int qk = 2 * n, sk = qk % kSlots;
         mbar_wait(&kv_full[sk], (qk / kSlots) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(kv + sk * kTileBytes);
+        const uint64_t dk = desc_k0 + (uint64_t)((sk * kTileBytes) >> 4);
+        if (issuer) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {   // 16 head dims per step; +32 bytes inside the swizzle span, next half after 4
-          const uint32_t o = (j >> 2) * kHalfBytes + (j & 3) * 32;
-          tc_mma(tmem_base + (n & 1) * 128, make_desc(q_addr + o, 16, 1024), make_desc(k_addr + o, 16, 1024), idesc_qk,
-                 j ? 1u : 0u);
+          for (int j = 0; j < 8; ++j) {   // 16 head dims per step; +32 bytes inside the swizzle span, next half after 4
+            const uint32_t o = (j >> 2) * kHalfBytes + (j & 3) * 32;
+            tc_mma(tmem_base + (n & 1) * 128, desc_q + (o >> 4), dk + (o >> 4), idesc_qk, j ? 1u : 0u);
+          }
+          tc_commit(&kv_free[sk]);
+          tc_commit(&s_full[n & 1]);
         }
-        tc_commit(&kv_free[sk]);
-        tc_commit(&s_full[n & 1]);
+        __syncwarp();
       };
       int n = 0, active = 0;
       for (int it = blockIdx.x; it < n_work; it += gridDim.x) {
         PlanItem w;
         int kvh;
         get_work(it, w, kvh);
-        const int nt = (w.ctx_max + kTileTok - 1) / kTileTok;
+        const int nt = __shfl_sync(0xffffffffu, (w.ctx_max + kTileTok - 1) / kTileTok, 0);
         if (nt == 0) continue;
         mbar_wait(q_ready, active & 1);
         tc_fence_after();
         issue_s(n);
-        if (nt == 1) tc_commit(q_free);
+        if (nt == 1 && issuer) tc_commit(q_free);
         for (int i = 0; i < nt; ++i, ++n) {
           if (i + 1 < nt) {
             issue_s(n + 1);
-            if (i + 2 == nt) tc_commit(q_free);   // last S of this item issued
+            if (i + 2 == nt && issuer) tc_commit(q_free);   // last S of this item issued
           }
           const int qv = 2 * n + 1, sv = qv % kSlots;
           mbar_wait(&kv_full[sv], (qv / kSlots) & 1);
           mbar_wait(p_ready, n & 1);
           tc_fence_after();
-          const bool fresh = *reinterpret_cast<volatile int*>(pv_fresh) != 0;   // written before the P hand-over
-          const uint32_t v_addr = smem_u32(kv + sv * kTileBytes);
+          // written before the P hand-over; every lane reads the same word
+          const bool fresh = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile int*>(pv_fresh), 0) != 0;
+          const uint64_t dv = desc_v0 + (uint64_t)((sv * kTileBytes) >> 4);
+          if (issuer) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {   // 16 tokens per step
-            const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
-            const uint64_t db = make_desc(v_addr + j * 2048, kHalfBytes, 1024);   // MN-major: two 8-token groups
-            tc_mma(tmem_base + 256, make_desc(ph_addr + ao, 16, 1024), db, idesc_pv, (j || !fresh) ? 1u : 0u);
-            tc_mma(tmem_base + 256, make_desc(pl_addr + ao, 16, 1024), db, idesc_pv, 1u);
+            for (int j = 0; j < 8; ++j) {   // 16 tokens per step
+              const uint32_t ao = (j >> 2) * kHalfBytes + (j & 3) * 32;
+              const uint64_t db = dv + (uint64_t)((j * 2048) >> 4);   // MN-major: two 8-token groups
+              tc_mma(tmem_base + 256, desc_ph + (ao >> 4), db, idesc_pv, (j || !fresh) ? 1u : 0u);
+              tc_mma(tmem_base + 256, desc_pl + (ao >> 4), db, idesc_pv, 1u);
+            }
+            tc_commit(&kv_free[sv]);
+            tc_commit(&o_full[n & 1]);
           }
-          tc_commit(&kv_free[sv]);
-          tc_commit(&o_full[n & 1]);
+          __syncwarp();
         }
         ++active;
       }
