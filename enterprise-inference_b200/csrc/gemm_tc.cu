@@ -55,7 +55,10 @@ constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 __host__ __device__ constexpr int stages_for(int N) { return N <= 16 ? B200_STAGES16 : (N <= 32 ? 4 : (N <= 64 ? B200_STAGES64 : (N <= 128 ? 3 : B200_STAGES256))); }
 __host__ __device__ constexpr int stage_bytes(int N) { return kBlockM * kBlockK * 2 + N * kBlockK * 2; }
 constexpr int kTailBytes = 1024;   // barriers, TMEM slot, ticket | per-token 1/rms [64] (fused-norm consumer)
-__host__ __device__ constexpr int smem_bytes_for(int N) { return stages_for(N) * stage_bytes(N) + 1024 + kTailBytes; }
+// Decode-sized tiles (N <= 32) exchange their cluster split-K partials by PUSH: every CTA stores the tokens owner r
+// finalises straight into r's receive buffer [token][source rank][128 rows] (fp32) with st.async, whose transaction
+// bytes complete r's mbarrier: no cluster barrier and no remote-load round trip between the last MMA and the output.
+__host__ __device__ constexpr int recv_bytes(int N) { return N <= 32 ? (N + 8) * kBlockM * 4 : 0; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -76,6 +79,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "}\n" ::"r"(smem_u32(bar)),
       "r"(parity)
       : "memory");
+}
+// mbarrier wait that also acquires what peers of the cluster released before arriving (remote arrivals)
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAITC_LOOP:\n"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra.uni WAITC_DONE;\n"
+      "bra.uni WAITC_LOOP;\n"
+      "WAITC_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t local_smem_addr, int rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_smem_addr), "r"(rank));
+  return remote;
 }
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
                                             uint64_t policy) {
@@ -368,6 +390,9 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
   int* ticket_slot = reinterpret_cast<int*>(tmem_slot + 1);
   float* rinv_s = reinterpret_cast<float*>(smem + S * kStageBytes + 256);   // [64]
+  constexpr bool kPush = recv_bytes(N) > 0;
+  uint64_t* recv_bar = reinterpret_cast<uint64_t*>(smem + S * kStageBytes + 512);
+  float* recv = reinterpret_cast<float*>(smem + S * kStageBytes + kTailBytes);   // [token][source rank][128]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // Several token tiles (prefill): the token tile is the FAST index, so that the CTAs that share a weight slab
@@ -388,6 +413,14 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       mbar_init(&empty[s], 1);
     }
     mbar_init(tmem_full, 1);
+    if (kPush && p.cluster) {
+      // the peers' st.async stores complete transaction bytes on this barrier: S2 partials of every token this CTA
+      // finalises (tokens split, split + S2, ... of the tile), 128 fp32 rows each
+      const int tmax = min(N, p.T - tok_tile * N);
+      const int owned = split < tmax ? (tmax - split + p.splits - 1) / p.splits : 0;
+      mbar_init(recv_bar, 1);
+      if (owned) mbar_expect_tx(recv_bar, (uint32_t)(owned * p.splits * kBlockM * 4));
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -399,6 +432,10 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const bool push = kPush && p.cluster;
+  // push exchange: a peer may store into this CTA's receive buffer and arrive on its barrier only once the barrier
+  // exists -- every thread arrives here and waits (long since satisfied) before its first remote access / at the end
+  if (push && warp != 0) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");   // warp 0: after its first loads
 
   if (warp == 0) {
     // ===== TMA producer (whole warp in the loop, the TMA instructions predicated to one lane: see the MMA issuer) =====
@@ -415,6 +452,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tc_trace(p, 1);   // W of the first stages requested
     }
     __syncwarp();
+    if (push) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     pdl_wait();
     if (issuer) {
       tc_trace(p, 2);   // previous kernel complete
@@ -540,7 +578,26 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll
         for (int j = 0; j < 16; ++j) r[j] = 0u;
       }
-      if (direct) {
+      if (push) {
+        if constexpr (kPush) {
+          // token t of the tile goes to CTA t % splits, which finalises it: slot [t / splits][this rank][row]
+          if (c == 0) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // the peers' barriers exist
+          const int tmax = min(N, p.T - tok0);
+          const uint32_t recv_addr = smem_u32(recv), recv_bar_addr = smem_u32(recv_bar);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int t = c + j;
+            if (t < tmax) {
+              const int owner = t % p.splits, tl = t / p.splits;
+              const uint32_t dst = map_to_rank(recv_addr + (uint32_t)(((tl * p.splits + split) * kBlockM + srow) * 4), owner);
+              const uint32_t bar = map_to_rank(recv_bar_addr, owner);
+              asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];" ::"r"(dst),
+                           "r"(r[j]), "r"(bar)
+                           : "memory");
+            }
+          }
+        }
+      } else if (direct) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) stg[(c + j) * kBlockM + srow] = __uint_as_float(r[j]);
       } else {
@@ -552,7 +609,37 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     if (warp == 2 && lane == 0) tc_trace(p, 6);   // tile staged
     bool finalize = true;
     const int tile_id = m_tile * gridDim.z + tok_tile;
-    if (p.cluster) {
+    if (push) {
+      if constexpr (kPush) {
+        finalize = false;
+        const int tmax = min(N, p.T - tok0), S2 = p.splits, r4 = lane * 4;
+        if (threadIdx.x == 64) tc_trace(p, 7);    // partials pushed (each store signals the owner's barrier itself)
+        if (split < tmax) {
+          // this CTA finalises tokens split, split + S2, ...: all S2 partials of them are in its own shared memory once
+          // their transaction bytes have arrived; summed in rank order (deterministic, same order as the pull path)
+          mbar_wait_cluster(recv_bar, 0);
+          if (threadIdx.x == 64) tc_trace(p, 10);   // every partial of this CTA's tokens has landed
+          float bb[4] = {0.f, 0.f, 0.f, 0.f};
+          if (p.bias) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (m_tile * kBlockM + r4 + e < p.n_out) bb[e] = __bfloat162float(p.bias[m_tile * kBlockM + r4 + e]);
+          }
+          for (int tl = wq; split + S2 * tl < tmax; tl += 4) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int src = 0; src < S2; ++src) {
+              const float4 v = *reinterpret_cast<const float4*>(recv + (tl * S2 + src) * kBlockM + r4);
+              acc.x += v.x;
+              acc.y += v.y;
+              acc.z += v.z;
+              acc.w += v.w;
+            }
+            finalize4<MODE>(p, m_tile, lane, tok0 + split + S2 * tl, acc, bb);   // warp-uniform loop
+          }
+        }
+        if (threadIdx.x == 64) tc_trace(p, 11);   // this CTA's share finalized
+      }
+    } else if (p.cluster) {
       finalize = false;   // done after the cluster barrier below, by every CTA of the cluster for its share
     } else if (direct) {
       asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -622,8 +709,13 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     }   // !kChunked
     tc_fence_before();
   }
-  if (threadIdx.x == 64) tc_trace(p, 7);   // before the cluster phase
-  if (p.cluster) {
+  if (push) {
+    // the other warps still owe the wait of the start-up cluster barrier (the epilogue warps waited before pushing)
+    if (warp < 2) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  } else if (threadIdx.x == 64) {
+    tc_trace(p, 7);   // before the cluster phase
+  }
+  if (p.cluster && !push) {
     // ---- split-K over a thread-block cluster: every CTA staged its fp32 partial tile [token][128] in
     // its own shared memory; after a cluster barrier CTA `rank` finalises the tokens t = rank (mod S),
     // summing the S partials in rank order (deterministic) straight out of its peers' smem (DSMEM).
@@ -808,7 +900,7 @@ Plan make_plan(int T, int n_out, int k) {
 template <int N, int MODE, int S, bool NI>
 int launch_tc3(const CUtensorMap& mw, const CUtensorMap& mx, const TcParams& p, const Plan& pl, cudaStream_t s) {
   static bool attr_set[64] = {};
-  const int smem = S * stage_bytes(N) + 1024 + kTailBytes;
+  const int smem = S * stage_bytes(N) + 1024 + kTailBytes + recv_bytes(N);
   B200_CUDA(ensure_dynamic_smem(linear_tc_kernel<N, MODE, S, NI>, smem, attr_set));
   B200_CUDA(launch_cluster(linear_tc_kernel<N, MODE, S, NI>, dim3(pl.m_tiles, pl.splits, pl.tok_tiles), dim3(kTcThreads),
                            (size_t)smem, s, p.cluster ? dim3(1, pl.splits, 1) : dim3(1, 1, 1), mw, mx, p));

@@ -11,7 +11,8 @@ BF = torch.bfloat16
 names = ["cta_start", "W_requested", "pdl_wait_done", "first_stage_landed", "last_mma_issued", "accum_complete",
          "tile_staged", "before_cluster", "finalize_done", "cta_end", "cluster_ready", "own_share_done"]
 for (nm, T, n, k) in [("o T=64", 64, 4096, 4096), ("o T=1", 1, 4096, 4096), ("qkv T=64", 64, 6144, 4096), ("down T=64", 64, 4096, 14336),
-                      ("gate_up T=64", 64, 28672, 4096)]:
+                      ("gate_up T=64", 64, 28672, 4096), ("qkv T=1", 1, 6144, 4096), ("down T=1", 1, 4096, 14336),
+                      ("gate_up T=1", 1, 28672, 4096)]:
     x = torch.randn(T, k, device="cuda").to(BF)
     ws_ = [torch.randn(n, k, device="cuda").to(BF) * 0.02 for _ in range(3)]
     y = torch.empty(T, n, device="cuda", dtype=BF)
