@@ -53,6 +53,19 @@ class FakeRunner:
         return lp, ids, tlp
 
 
+class OverlapRunner(FakeRunner):
+    """The same model behind the runner's overlap interface (step_async / step_result): ids of -(j+1) are resolved from the
+    tokens of the step enqueued just before, as the device does.  LLMEngine then runs in overlap mode."""
+    def step_async(self, b):
+        prev = getattr(self, "last", np.zeros(0, dtype=np.int32))
+        b.ids = [int(prev[-int(t) - 1]) if int(t) < 0 else int(t) for t in b.ids]
+        self.n_async = getattr(self, "n_async", 0) + 1
+        return FakeRunner.step(self, b).copy()
+
+    def step_result(self, handle):
+        return handle
+
+
 def expect_ids(prompt_ids, n):
     ids = list(prompt_ids)
     for _ in range(n):
@@ -60,9 +73,12 @@ def expect_ids(prompt_ids, n):
     return ids[len(prompt_ids):]
 
 
-@pytest.fixture()
-def client():
-    eng = E.LLMEngine(FakeRunner(), max_num_batched_tokens=64, max_num_seqs=8, max_model_len=256)
+@pytest.fixture(params=["synchronous", "overlap"])
+def client(request):
+    """Every test of the OpenAI surface runs against the synchronous engine and against the overlapped one."""
+    eng = E.LLMEngine(FakeRunner() if request.param == "synchronous" else OverlapRunner(), max_num_batched_tokens=64,
+                      max_num_seqs=8, max_model_len=256)
+    assert eng.overlap == (request.param == "overlap")
     tok = S.ByteTokenizer(512)
     app = S.create_app(eng, tok, "meta-llama/Llama-3.1-8B-Instruct", 256)
     with TestClient(app) as c:
@@ -267,6 +283,8 @@ def test_health_goes_red_when_the_engine_dies(client):
     def boom(_):
         raise RuntimeError("device lost")
     loop.engine.runner.step = boom
+    if loop.engine.overlap:
+        loop.engine.runner.step_async = boom
     r = client.post("/v1/completions", json={"model": MODEL, "temperature": 0, "prompt": "x", "max_tokens": 2})
     assert r.status_code == 500
     assert client.get("/health").status_code == 503
